@@ -1,0 +1,729 @@
+"""Executor: graph compile (hook passes, device resolution, comm bring-up) and
+the per-step run loop.
+
+reference: python/hetu/gpu_ops/executor.py:134-1063 (HetuConfig, Executor,
+SubExecutor).  What is different by design:
+
+ * The reference walks every node in Python on every step, blocks the host on a
+   CUDA event before each node and issues one launch per node
+   (executor.py:1000-1056).  Here a step whose nodes are all ``graph_safe`` is
+   captured ONCE into a CUDA graph - pinned-host -> device input copies, every
+   kernel, the optimizer / fused all-reduce step - and replayed with a single
+   ``cudaGraphLaunch``.  Per-step varying scalars (lr, Adam step, dropout seed)
+   live in device memory so the replay stays valid.
+ * Cross-stream ordering is stream-ordered (wait_stream / wait_event).
+ * Memory: values are refcounted and dropped after their last consumer (eager
+   mode); in graph mode the capture's private pool does the reuse plan.
+"""
+from __future__ import annotations
+
+import os
+import pickle
+import time
+from typing import Dict, List, Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from .. import _lib as L
+from ..context import DeviceGroup, get_current_context, get_launch_config_by_traverse_nodes
+from ..dataloader import DataloaderOp, GNNDataLoaderOp
+from ..ndarray import (DLContext, IndexedSlices, NDArray, ND_Sparse_Array, cpu, gpu, is_gpu_ctx,
+                       to_tensor)
+from ..ops.variable import PlaceholderOp
+from ..optimizer import OptimizerOp
+from ..stream import Event, Stream
+from .autodiff import find_topo_sort, find_topo_sort_inference, gradients, sum_node_list
+from .node import Op
+
+
+def path_to_lib(name: str) -> str:
+    return os.path.join(L.LIB_DIR, name)
+
+
+# --------------------------------------------------------------------------- PS glue
+_ps_comm = None
+
+
+def get_worker_communicate():
+    return _ps_comm
+
+
+def worker_init():
+    global _ps_comm
+    from ..parallel.ps import PSWorker
+    if _ps_comm is None:
+        _ps_comm = PSWorker.from_env()
+    return _ps_comm
+
+
+def worker_finish():
+    global _ps_comm
+    if _ps_comm is not None:
+        _ps_comm.finalize()
+        _ps_comm = None
+
+
+def server_init():
+    from ..parallel.ps import start_server_from_env
+    return start_server_from_env()
+
+
+def server_finish():
+    from ..parallel.ps import stop_local_servers
+    stop_local_servers()
+
+
+def scheduler_init():
+    from ..parallel.ps import start_scheduler_from_env
+    return start_scheduler_from_env()
+
+
+def scheduler_finish():
+    from ..parallel.ps import stop_scheduler
+    stop_scheduler()
+
+
+from ..parallel.comm import (wrapped_mpi_nccl_init, new_group_comm, get_mpi_communicate,  # noqa: E402
+                             get_nccl_communicate)
+
+
+class HetuConfig(object):
+    __slots__ = [
+        'eval_node_list', 'train_name', 'val_name', 'context', 'seed', 'np_rand', 'comm_mode',
+        'node_strategy', 'context_launch', 'ps_comm', 'nccl_comm', 'local_rank', 'rank', 'nrank',
+        'comp_stream', 'h2d_stream', 'd2h_stream', 'nccl_stream', 'p2p_stream', 'h2d_ops', 'd2h_ops',
+        'ps_map', 'infer_ps_map', 'dataloader_ops', 'use_sparse_pull', 'cstable_policy', 'inference',
+        'enable_lazy', 'bsp', 'prefetch', 'cache_bound', 'log_path', 'my_eval_nodes',
+        'param_allreduce_group', 'placeholder_to_arr_map', 'gpipe', 'pipedream', 'dynamic_memory',
+        'dist_strategy', 'pipeline', 'use_preduce', 'overlap', 'use_nccl_collectives', 'symm',
+        'fuse_dp_update', 'use_cuda_graph', 'dp_rank', 'dp_nrank', 'mp_index', 'shard_dataloaders',
+        'all_forward_nodes', 'lcm_dp_nrank', 'pp_rank', 'pp_nrank', 'stage_ranks', 'memory_pool',
+        'timing',
+    ]
+
+    def __init__(self, eval_node_list, train_name, val_name, ctx=None, seed=None, comm_mode=None,
+                 use_sparse_pull=True, cstable_policy=None, bsp=-1, prefetch=True, enable_lazy=False,
+                 cache_bound=100, log_path=None, pipeline=None, dist_strategy=None,
+                 use_preduce=False, overlap=True, use_nccl_collectives=None, dynamic_memory=False,
+                 use_cuda_graph=None, fuse_dp_update=True, shard_dataloaders=True, timing=None):
+        assert pipeline in (None, "gpipe", "pipedream", "hetpipe")
+        assert comm_mode in (None, 'AllReduce', 'PS', 'Hybrid')
+        self.pipeline, self.use_preduce, self.overlap = pipeline, use_preduce, overlap
+        self.eval_node_list = eval_node_list
+        self.train_name, self.val_name = train_name, val_name
+        self.dist_strategy = dist_strategy
+        self.dynamic_memory = dynamic_memory
+        self.timing = timing
+        self.memory_pool = None
+        self.shard_dataloaders = shard_dataloaders
+        self.fuse_dp_update = fuse_dp_update
+
+        if dist_strategy is None:
+            if ctx is None:
+                ctx = get_current_context()
+        else:
+            ctx = dist_strategy.set_raw_ctxs_n_states(eval_node_list, None)
+        if ctx is None:
+            ctx = gpu(0) if torch.cuda.is_available() else cpu(0)
+        context_launch = isinstance(ctx, DeviceGroup)
+        self.context_launch = context_launch
+        self.comm_mode = comm_mode
+        self.node_strategy = {}
+
+        if context_launch:
+            launchMPI, launchPS, self.node_strategy, devices, _ = \
+                get_launch_config_by_traverse_nodes(eval_node_list, ctx)
+            if not launchMPI and not launchPS:
+                self.comm_mode = None
+            elif launchMPI and (not launchPS or use_preduce):
+                self.comm_mode = 'AllReduce'
+            elif not launchMPI and launchPS:
+                self.comm_mode = 'PS'
+            else:
+                self.comm_mode = 'Hybrid'
+
+        self.seed = int(seed) if seed is not None else int(time.time())
+        self.np_rand = np.random.RandomState(self.seed % (2 ** 32))
+
+        # ---- communication planes ---------------------------------------------------
+        self.ps_comm = None
+        self.nccl_comm = None
+        self.symm = None
+        self.local_rank = 0
+        self.rank, self.nrank = 0, 1
+        from ..parallel.comm import dist_env, world
+        env_rank, env_world, env_local = dist_env()
+        if self.comm_mode in ('PS', 'Hybrid') and os.environ.get('DMLC_PS_ROOT_URI'):
+            self.ps_comm = worker_init()
+            self.rank, self.nrank = self.ps_comm.rank(), self.ps_comm.nrank()
+        if self.comm_mode in ('AllReduce', 'Hybrid') or context_launch or env_world > 1:
+            self.nccl_comm = wrapped_mpi_nccl_init()
+            self.local_rank = self.nccl_comm.local_rank
+            self.rank, self.nrank = self.nccl_comm.rank, self.nccl_comm.nrank
+        self.dp_rank, self.dp_nrank = self.rank, self.nrank
+        self.mp_index = 0
+        self.pp_rank, self.pp_nrank, self.stage_ranks = 0, 1, None
+        self.all_forward_nodes, self.lcm_dp_nrank = None, 1
+
+        # ---- this process's device ----------------------------------------------------
+        if context_launch:
+            workers = ctx.workers
+            if workers:
+                unit = workers[self.rank % len(workers)] if self.nccl_comm is not None else workers[0]
+                if isinstance(unit, tuple):
+                    unit = unit[0]
+                self.context = unit
+            else:
+                self.context = ctx.servers[0]
+            if self.nccl_comm is not None and self.nccl_comm.multi:
+                # ranks map onto the flattened device list (DP x MP x PP placement)
+                flat = []
+                for node in find_topo_sort(eval_node_list):
+                    if node.raw_ctx is not None:
+                        for d in node.raw_ctx.flat_devices():
+                            if is_gpu_ctx(d) and d not in flat:
+                                flat.append(d)
+                flat.sort(key=lambda d: (d.hostname, d.device_id))
+                if flat and self.rank < len(flat):
+                    self.context = flat[self.rank]
+        else:
+            self.context = ctx
+        if is_gpu_ctx(self.context) and self.nccl_comm is not None and self.nccl_comm.multi \
+                and torch.cuda.is_available():
+            # one process per GPU: the process's device is its local rank
+            self.context = gpu(self.local_rank % torch.cuda.device_count())
+        if is_gpu_ctx(self.context) and torch.cuda.is_available():
+            torch.cuda.set_device(self.context.torch_device)
+
+        on_cuda = is_gpu_ctx(self.context) and torch.cuda.is_available()
+        if use_nccl_collectives is None:
+            use_nccl_collectives = os.environ.get('HETU_COLLECTIVES', 'symm') == 'nccl'
+        self.use_nccl_collectives = use_nccl_collectives
+        if (on_cuda and not use_nccl_collectives and self.nccl_comm is not None
+                and self.nccl_comm.multi and L.cuda_lib() is not None):
+            from ..parallel.symm import SymmEngine
+            self.symm = SymmEngine.get(self.nccl_comm)
+        if use_cuda_graph is None:
+            use_cuda_graph = os.environ.get('HETU_CUDA_GRAPH', '1') == '1'
+        self.use_cuda_graph = bool(use_cuda_graph) and on_cuda and timing is None
+
+        # ---- streams ------------------------------------------------------------------------
+        self.comp_stream = Stream(self.context) if on_cuda else None
+        self.h2d_stream = Stream(self.context) if on_cuda else None
+        self.d2h_stream = Stream(self.context) if on_cuda else None
+        self.nccl_stream = Stream(self.context) if on_cuda and self.nccl_comm is not None else None
+        self.p2p_stream = Stream(self.context) if on_cuda and (pipeline or context_launch) else None
+
+        self.use_sparse_pull = use_sparse_pull if self.comm_mode in ('PS', 'Hybrid') else False
+        self.cstable_policy = cstable_policy if self.comm_mode in ('PS', 'Hybrid') else None
+        self.prefetch = prefetch if self.comm_mode in ('PS', 'Hybrid') else False
+        self.bsp = bsp if self.comm_mode in ('PS', 'Hybrid') else -1
+        self.cache_bound = int(cache_bound)
+        self.log_path = log_path
+        if log_path is not None and self.ps_comm is not None:
+            self.ps_comm.startRecord(log_path)
+        self.enable_lazy = enable_lazy
+        self.h2d_ops, self.d2h_ops = {}, {}
+        self.ps_map, self.infer_ps_map = {}, {}
+        self.dataloader_ops = []
+        self.inference = False
+        self.my_eval_nodes = eval_node_list
+        self.param_allreduce_group = {}
+        self.placeholder_to_arr_map = {}
+        self.gpipe = pipeline == 'gpipe'
+        self.pipedream = pipeline in ('pipedream', 'hetpipe')
+
+        if context_launch and self.nccl_comm is not None and self.nccl_comm.multi:
+            from ..parallel.placement import assign_placement
+            assign_placement(self, eval_node_list)
+        topo_sort_with_hook(self.my_eval_nodes, self)
+
+
+def topo_sort_with_hook(node_list: List[Op], config: HetuConfig) -> None:
+    """DFS; per node: backward_hook on the way down (pre-order), forward_hook on
+    the way up (post-order).  reference executor.py:1285-1302."""
+    visited = set()
+    for root in node_list:
+        if root in visited:
+            continue
+        visited.add(root)
+        root.backward_hook(config)
+        stack = [(root, 0)]
+        while stack:
+            node, i = stack.pop()
+            if i < len(node.inputs):
+                stack.append((node, i + 1))
+                child = node.inputs[i]
+                if child is not None and child not in visited:
+                    visited.add(child)
+                    child.backward_hook(config)
+                    stack.append((child, 0))
+            else:
+                _post_hook(node, config)
+
+
+def _post_hook(node: Op, config: HetuConfig) -> None:
+    if isinstance(node, PlaceholderOp):
+        if node.tensor_value is not None and not node.ps_resident:
+            tv = node.tensor_value
+            config.placeholder_to_arr_map[node] = tv.tensor if isinstance(tv, NDArray) else tv
+        elif node.ps_resident:
+            config.placeholder_to_arr_map[node] = None
+    node.forward_hook(config)
+
+
+topo_sort_dfs_with_hook = topo_sort_with_hook
+
+
+def topo_sort_register_ps(node_list, ps_comm, comm_mode, seed, cstable_policy):
+    """Register every PS-resident parameter with the servers (InitTensor RPC)."""
+    for node in find_topo_sort(node_list):
+        if isinstance(node, PlaceholderOp) and node.trainable and (
+                comm_mode == 'PS' or node.is_embed):
+            ptype = 0 if not node.is_embed else (2 if cstable_policy is not None else 1)
+            if node.initializer is not None:
+                node.initializer.init_on_ps(ps_comm, node.id, ptype, seed + node.id, None)
+
+
+def get_pipeline_stage_info(node_list, ctx):
+    """(pp_rank, pp_nrank) of ``ctx`` among the distinct device groups of the graph."""
+    stages = []
+    for node in find_topo_sort(node_list):
+        rc = node.raw_ctx
+        if rc is None or isinstance(node, (OptimizerOp, DataloaderOp)) or rc.worker_num == 0:
+            continue
+        if rc not in stages:
+            stages.append(rc)
+    my = 0
+    for i, s in enumerate(stages):
+        if ctx in s:
+            my = i
+    return my, max(len(stages), 1)
+
+
+def fetch_sparse_parameter_value(node_list, config):
+    for node in node_list:
+        if isinstance(node, PlaceholderOp) and node.ps_resident and config.ps_comm is not None:
+            config.ps_comm.pull_full(node)
+
+
+fetch_dense_parameter_value = fetch_sparse_parameter_value
+
+
+class Executor(object):
+    """``Executor({'train': [loss, train_op], 'validate': [loss]}, ctx=..., comm_mode=...)``."""
+
+    def __init__(self, eval_node_dict, config: HetuConfig = None, timing: Optional[str] = None,
+                 **kargs):
+        if not isinstance(eval_node_dict, dict):
+            eval_node_dict = {'default': eval_node_dict}
+        train_name, val_name = None, None
+        for k, v in eval_node_dict.items():
+            if any(isinstance(n, OptimizerOp) for n in v):
+                assert train_name is None, 'Only one training sub-executor is supported.'
+                train_name = k
+            else:
+                val_name = k
+        all_eval_nodes = []
+        for v in eval_node_dict.values():
+            for n in v:
+                if n not in all_eval_nodes:
+                    all_eval_nodes.append(n)
+        if config is None:
+            config = HetuConfig(eval_node_list=all_eval_nodes, train_name=train_name,
+                                val_name=val_name, timing=timing, **kargs)
+        assert isinstance(config, HetuConfig)
+        self.eval_node_dict = eval_node_dict
+        self.config = config
+        self.comm_mode = config.comm_mode
+        self.ps_comm = config.ps_comm
+        self.rank, self.nrank = config.rank, config.nrank
+        self.local_rank = config.local_rank
+
+        def make(name, nodes):
+            if timing is not None:
+                from .timer import TimerSubExecutor
+                return TimerSubExecutor(name, nodes, config, timing)
+            if config.pipeline == 'gpipe' and name == train_name:
+                from ..parallel.pipeline import SubExecutor4Gpipe
+                return SubExecutor4Gpipe(name, nodes, config)
+            if config.pipeline in ('pipedream', 'hetpipe') and name == train_name:
+                from ..parallel.pipeline import SubExecutor4Pipedream
+                return SubExecutor4Pipedream(name, nodes, config)
+            return SubExecutor(name, nodes, config)
+
+        self.subexecutor: Dict[str, SubExecutor] = {k: make(k, v) for k, v in eval_node_dict.items()}
+        self.topo_order = find_topo_sort(all_eval_nodes)
+        self.param_nodes = [n for n in self.topo_order if isinstance(n, PlaceholderOp) and n.trainable]
+
+    # ------------------------------------------------------------------------------------
+    def profile(self, feed_shapes, log_file, profiler='cpu', name='default'):
+        self.subexecutor[name].profile(feed_shapes, log_file, profiler)
+
+    def run(self, name='default', eval_node_list=[], feed_dict={}, convert_to_numpy_ret_vals=False,
+            **kwargs):
+        if name not in self.subexecutor and len(self.subexecutor) == 1:
+            name = next(iter(self.subexecutor))
+        return self.subexecutor[name].run(eval_node_list, feed_dict, convert_to_numpy_ret_vals,
+                                          **kwargs)
+
+    @property
+    def batch_num(self):
+        assert len(self.subexecutor) == 1, 'Batch num should be used with only 1 subexecutor.'
+        return next(iter(self.subexecutor.values())).batch_num
+
+    def get_batch_num(self, name='default'):
+        return self.subexecutor[name].batch_num
+
+    # --------------------------------------------------------------------- checkpointing
+    def _named_params(self):
+        out = {}
+        for node in self.topo_order:
+            if isinstance(node, PlaceholderOp) and node.trainable:
+                out[node.name] = node
+        return out
+
+    def save(self, file_path: str, file_name: str, save_optimizer: bool = False):
+        """Pickle of ``{param.name: np.ndarray(float32)}`` - the reference's format
+        (executor.py:457-481).  PS-resident parameters are saved by the servers as
+        raw fp32 ``<dir>/<node_id>_<shard>.dat``.  ``save_optimizer`` additionally
+        writes ``<file_name>.opt`` with the slots/step the reference drops."""
+        os.makedirs(file_path, exist_ok=True)
+        cfg = self.config
+        if cfg.ps_comm is not None:
+            cfg.ps_comm.BarrierWorker()
+        state = {}
+        for name, node in self._named_params().items():
+            val = cfg.placeholder_to_arr_map.get(node)
+            if val is None:
+                if cfg.ps_comm is not None and self.rank == 0:
+                    cfg.ps_comm.SaveParam(node.id, file_path)
+                continue
+            if hasattr(val, 'export_dense'):
+                val = val.export_dense()
+            state[name] = val.detach().cpu().numpy()
+        # BatchNorm running statistics (not checkpointed upstream - SURVEY 5.4)
+        for node in self.topo_order:
+            if hasattr(node, 'state_tensors'):
+                for k, t in node.state_tensors().items():
+                    if t is not None:
+                        state['%s/%s' % (node.name, k)] = t.detach().cpu().numpy()
+        if self.rank in (0, None) or cfg.comm_mode is None or getattr(cfg, 'pp_nrank', 1) > 1:
+            with open(os.path.join(file_path, file_name), 'wb') as fw:
+                pickle.dump(state, fw)
+            if save_optimizer:
+                opt_state = {}
+                for sub in self.subexecutor.values():
+                    for n in sub.topo_order:
+                        if isinstance(n, OptimizerOp):
+                            opt_state.update(n.optimizer.state_dict())
+                with open(os.path.join(file_path, file_name + '.opt'), 'wb') as fw:
+                    pickle.dump(opt_state, fw)
+        if cfg.ps_comm is not None:
+            cfg.ps_comm.BarrierWorker()
+
+    def load(self, file_path: str, file_name: str, consider_splits: bool = False):
+        with open(os.path.join(file_path, file_name), 'rb') as fr:
+            state_dict = pickle.load(fr)
+        self.load_dict(state_dict, file_path, consider_splits)
+        opt_file = os.path.join(file_path, file_name + '.opt')
+        if os.path.exists(opt_file):
+            with open(opt_file, 'rb') as fr:
+                opt_state = pickle.load(fr)
+            for sub in self.subexecutor.values():
+                for n in sub.topo_order:
+                    if isinstance(n, OptimizerOp):
+                        n.optimizer.load_state_dict(opt_state)
+
+    def load_dict(self, state_dict, file_path: str = None, consider_splits: bool = False):
+        cfg = self.config
+        for name, node in self._named_params().items():
+            cur = cfg.placeholder_to_arr_map.get(node)
+            if cur is None:
+                if cfg.ps_comm is not None and file_path is not None:
+                    if self.rank == 0:
+                        cfg.ps_comm.LoadParam(node.id, file_path)
+                continue
+            if name not in state_dict:
+                continue
+            value = state_dict[name]
+            if consider_splits and node.reshaped:
+                value = node.reshape_tensor(np.asarray(value))
+            if hasattr(cur, 'import_dense'):
+                cur.import_dense(value)
+                continue
+            value = to_tensor(value)
+            assert tuple(value.shape) == tuple(cur.shape), \
+                'Shape mismatch for %s: %s vs %s' % (name, tuple(value.shape), tuple(cur.shape))
+            cur.copy_(value.to(cur.device))
+        for node in self.topo_order:
+            if hasattr(node, 'state_tensors'):
+                for k, t in node.state_tensors().items():
+                    key = '%s/%s' % (node.name, k)
+                    if key in state_dict:
+                        v = to_tensor(state_dict[key])
+                        if t is None:
+                            setattr(node, k, v.to(node.ctx.torch_device if node.ctx else 'cpu'))
+                        else:
+                            t.copy_(v.to(t.device))
+        if cfg.ps_comm is not None:
+            cfg.ps_comm.BarrierWorker()
+
+    def recordLoads(self):
+        if self.config.ps_comm is not None:
+            self.config.ps_comm.getLoads()
+
+    def logOut(self, *args, name='default', **kargs):
+        self.subexecutor[name].logOut(*args, **kargs)
+
+    def clearTimer(self, name='default'):
+        self.subexecutor[name].clearTimer()
+
+    def __del__(self):
+        pass
+
+
+class SubExecutor(object):
+    def __init__(self, name: str, eval_node_list: List[Op], config: HetuConfig):
+        self.name = name
+        self.eval_node_list = list(eval_node_list)
+        self.config = config
+        self.inference = not any(isinstance(n, OptimizerOp) for n in eval_node_list)
+        self.topo_order = (find_topo_sort_inference(self.eval_node_list) if self.inference
+                           else find_topo_sort(self.eval_node_list))
+        self.dataloader_nodes = [n for n in self.topo_order
+                                 if isinstance(n, (DataloaderOp, GNNDataLoaderOp))]
+        self.param_nodes = [n for n in self.topo_order
+                            if isinstance(n, PlaceholderOp) and not n.is_feed]
+        self.need_feed_nodes = [n for n in self.topo_order
+                                if isinstance(n, PlaceholderOp) and n.is_feed]
+        self.computing_nodes = [n for n in self.topo_order
+                                if not isinstance(n, (PlaceholderOp, DataloaderOp, GNNDataLoaderOp))]
+        self.batch_num = None
+        bn = set(n.get_batch_num(self.name) for n in self.dataloader_nodes
+                 if isinstance(n, DataloaderOp) and self.name in n.dataloaders)
+        if len(bn) == 1:
+            self.batch_num = bn.pop()
+        self.device = config.context.torch_device
+        # last consumer index per node -> eager-mode buffer release plan
+        self._last_use = {}
+        for i, node in enumerate(self.topo_order):
+            for inp in node.inputs:
+                self._last_use[inp] = i
+        self._eval_set = set(self.eval_node_list)
+        self._side_refs = set()
+        for node in self.topo_order:
+            fwd = getattr(node, 'forward_node', None)
+            if fwd is not None:
+                self._side_refs.add(fwd)
+        # CUDA graph state
+        self.graph_ok = (config.use_cuda_graph and self.device.type == 'cuda'
+                         and all(getattr(n, 'graph_safe', True) for n in self.topo_order))
+        self._graph = None
+        self._graph_key = None
+        self._static_in: Dict[Op, torch.Tensor] = {}
+        self._stage: Dict[Op, torch.Tensor] = {}
+        self._static_out: Dict[Op, object] = {}
+        self._eager_steps = 0
+        self.step_count = 0
+        self.node_to_shape_map: Dict[Op, tuple] = {}
+
+    # ------------------------------------------------------------------ shape inference
+    def infer_shape(self, feed_shapes: Dict[Op, tuple]) -> Dict[Op, tuple]:
+        shapes: Dict[Op, tuple] = {}
+        for node in self.topo_order:
+            if node in feed_shapes:
+                shapes[node] = tuple(feed_shapes[node])
+            elif isinstance(node, DataloaderOp):
+                shapes[node] = tuple(node.get_cur_shape(self.name))
+            elif isinstance(node, OptimizerOp):
+                shapes[node] = None
+            else:
+                in_shapes = [shapes.get(i) for i in node.inputs]
+                try:
+                    shapes[node] = node.infer_shape(in_shapes)
+                except Exception:
+                    shapes[node] = None
+        self.node_to_shape_map = shapes
+        return shapes
+
+    # ----------------------------------------------------------------------- feeding
+    def _feed_tensor(self, node, value) -> torch.Tensor:
+        if isinstance(value, NDArray):
+            t = value.tensor
+        elif isinstance(value, torch.Tensor):
+            t = value
+        elif isinstance(value, (ND_Sparse_Array, IndexedSlices)):
+            return value
+        else:
+            arr = np.asarray(value)
+            if arr.dtype == np.float64:
+                arr = arr.astype(np.float32)
+            elif arr.dtype not in (np.float32, np.int32, np.int64, np.float16, np.bool_):
+                arr = arr.astype(np.float32)
+            t = torch.from_numpy(np.ascontiguousarray(arr))
+        return t
+
+    def _to_device(self, t):
+        if isinstance(t, torch.Tensor) and t.device != self.device:
+            if t.device.type == 'cpu' and self.device.type == 'cuda' and not t.is_pinned() \
+                    and t.numel() * t.element_size() >= (1 << 16):
+                t = t.pin_memory()
+            return t.to(self.device, non_blocking=True)
+        return t
+
+    # ----------------------------------------------------------------------- compute
+    def _node_device(self, node) -> torch.device:
+        ctx = node.ctx
+        if isinstance(ctx, DLContext):
+            return ctx.torch_device
+        return self.device
+
+    def _compute_all(self, vals: Dict[Op, object], release: bool) -> None:
+        cfg = self.config
+        inference = self.inference
+        if self.device.type == 'cuda' and L.cuda_lib() is not None:
+            from ..ops.nn import step_counter
+            L.call('increment_i64', L.p(step_counter(self.device)), L.stream_ptr(self.device))
+        for idx, node in enumerate(self.topo_order):
+            if node in vals:
+                continue
+            if isinstance(node, PlaceholderOp):
+                v = cfg.placeholder_to_arr_map.get(node)
+                if v is None and node.tensor_value is not None:
+                    tv = node.tensor_value
+                    v = tv.tensor if isinstance(tv, NDArray) else tv
+                if v is None and not node.ps_resident:
+                    raise AssertionError('placeholder %s values provided by feed_dict' % node.name)
+                vals[node] = v
+                continue
+            ins = [vals[i] for i in node.inputs]
+            dev = self._node_device(node)
+            for j, v in enumerate(ins):
+                if isinstance(v, torch.Tensor) and v.device != dev and not isinstance(
+                        node, OptimizerOp) and v.device.type != 'meta':
+                    ins[j] = v.to(dev, non_blocking=True)
+            if getattr(node, 'takes_inference', False):
+                out = node.compute(ins, None, cfg.comp_stream, inference=inference)
+            else:
+                out = node.compute(ins, None, cfg.comp_stream)
+            vals[node] = out
+            if release:
+                for inp in node.inputs:
+                    if (self._last_use.get(inp) == idx and inp not in self._eval_set
+                            and not isinstance(inp, PlaceholderOp) and inp not in self._side_refs):
+                        vals[inp] = None
+
+    def _pre_step(self):
+        for node in self.topo_order:
+            if isinstance(node, OptimizerOp):
+                node.optimizer.sync_lr()
+
+    # --------------------------------------------------------------------------- run
+    def run(self, eval_node_list=[], feed_dict={}, convert_to_numpy_ret_vals=False, **kwargs):
+        eval_nodes = list(eval_node_list) if eval_node_list else self.eval_node_list
+        feeds: Dict[Op, object] = {}
+        for node, value in feed_dict.items():
+            feeds[node] = self._feed_tensor(node, value)
+        for node in self.dataloader_nodes:
+            if node not in feeds:
+                feeds[node] = node.get_arr(self.name)
+        for node in self.need_feed_nodes:
+            assert node in feeds, 'placeholder %s must be fed' % node.name
+        self._pre_step()
+        if self.graph_ok and all(isinstance(v, torch.Tensor) for v in feeds.values()):
+            vals = self._run_graph(feeds)
+        else:
+            vals = self._run_eager(feeds)
+        self.step_count += 1
+        results = []
+        for n in eval_nodes:
+            v = vals.get(n)
+            if v is None or isinstance(n, OptimizerOp):
+                results.append(None)
+            elif isinstance(v, IndexedSlices):
+                results.append(v)
+            elif convert_to_numpy_ret_vals:
+                results.append(v.detach().cpu().numpy())
+            else:
+                results.append(NDArray(v, n.ctx if isinstance(n.ctx, DLContext) else None))
+        return results
+
+    def _run_eager(self, feeds):
+        vals: Dict[Op, object] = {}
+        use_stream = self.config.comp_stream is not None and self.device.type == 'cuda'
+        if use_stream:
+            cur = torch.cuda.current_stream(self.device)
+        for node, t in feeds.items():
+            vals[node] = self._to_device(t)
+        self._compute_all(vals, release=True)
+        return vals
+
+    def _graph_signature(self, feeds):
+        return tuple((id(n), tuple(t.shape), str(t.dtype), t.device.type) for n, t in feeds.items())
+
+    def _run_graph(self, feeds):
+        key = self._graph_signature(feeds)
+        if self._graph is not None and key != self._graph_key:
+            # shapes changed (e.g. last partial batch): drop the graph, run eagerly
+            self._graph = None
+            self._eager_steps = 0
+        if self._graph is None:
+            if self._eager_steps < 2:
+                self._eager_steps += 1
+                self._graph_key = key
+                return self._run_eager(feeds)
+            self._capture(feeds, key)
+        # stage inputs
+        for node, t in feeds.items():
+            if t.device.type == 'cpu':
+                self._stage[node].copy_(t)
+            else:
+                st = self._static_in[node]
+                if st.data_ptr() != t.data_ptr():
+                    st.copy_(t, non_blocking=True)
+        self._graph.replay()
+        return self._static_out
+
+    def _capture(self, feeds, key):
+        dev = self.device
+        torch.cuda.synchronize(dev)
+        self._static_in, self._stage = {}, {}
+        for node, t in feeds.items():
+            if t.device.type == 'cpu':
+                self._stage[node] = torch.empty(tuple(t.shape), dtype=t.dtype, pin_memory=True)
+                self._stage[node].copy_(t)
+                self._static_in[node] = torch.empty(tuple(t.shape), dtype=t.dtype, device=dev)
+            else:
+                self._static_in[node] = t
+        graph = torch.cuda.CUDAGraph()
+        vals: Dict[Op, object] = {}
+        with torch.cuda.graph(graph):
+            for node, st in self._static_in.items():
+                if node in self._stage:
+                    st.copy_(self._stage[node], non_blocking=True)
+                vals[node] = st
+            self._compute_all(vals, release=False)
+        self._graph = graph
+        self._graph_key = key
+        self._static_out = vals
+        torch.cuda.synchronize(dev)
+
+    # ----------------------------------------------------------------------------- misc
+    def profile(self, feed_shapes, log_file, profiler='cpu'):
+        from ..utils.profiler import HetuProfiler
+        prof = HetuProfiler(self.computing_nodes, feed_shapes, self.node_to_shape_map,
+                            ctx=self.config.context)
+        prof.profile_n_log(log_file, profiler=profiler)
+
+    def logOut(self, *args, **kargs):
+        raise RuntimeError("logOut requires Executor(..., timing='gpu'|'cpu')")
+
+    def clearTimer(self):
+        pass
+
+    def logNodes(self, node_list, path):
+        with open(path, 'w') as fw:
+            for node in node_list:
+                print(node, node.inputs, node.ctx, file=fw)
