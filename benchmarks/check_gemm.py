@@ -1,0 +1,23 @@
+"""Per-shape / per-layout error table for hetu_gemm (diagnostic, run on the GPU box)."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from hetu_61a7_b200.ops.linalg import gemm
+
+dev = torch.device('cuda')
+shapes = [(128, 128, 128), (128, 128, 32), (128, 32, 32), (128, 32, 144), (256, 256, 64), (128, 256, 256),
+          (8192, 32, 144), (8192, 144, 32), (512, 384, 256), (2048, 2048, 2048), (1000, 520, 264), (96, 40, 72)]
+torch.manual_seed(0)
+for (m, n, k) in shapes:
+    for tA in (False, True):
+        for tB in (False, True):
+            a = torch.randn((k, m) if tA else (m, k), device=dev)
+            b = torch.randn((n, k) if tB else (k, n), device=dev)
+            ref = (a.t() if tA else a).double() @ (b.t() if tB else b).double()
+            out = gemm(a, b, tA, tB)
+            torch.cuda.synchronize()
+            err = (out.double() - ref).abs().max().item() / (ref.abs().max().item() + 1e-9)
+            nz = (out != 0).float().mean().item()
+            # per-quadrant error map to spot layout problems
+            print('M%5d N%5d K%5d tA=%d tB=%d  relerr %.3e  nonzero %.2f  %s' % (
+                m, n, k, tA, tB, err, nz, 'OK' if err < 2e-3 else 'FAIL'))

@@ -1,0 +1,496 @@
+// GEMM for sm_100a: C = act(alpha * op(A) op(B) + beta * C + bias), fp32 storage.
+//
+// reference: src/ops/MatrixMult.cu:22-26, Linear.cu:35-54, BatchMatrixMult.cu:31-36,
+// Addmm.cu, Baddbmm.cu - all cublasSgemm(StridedBatched) in fp32 on CUDA cores.
+//
+// Path 1 (tensor cores): warp-specialised tcgen05 kernel.
+//   warp 0      : TMA producer  (cp.async.bulk.tensor.3d -> 128B-swizzled smem ring, mbarrier tx)
+//   warp 1      : TMEM allocator + MMA issuer (one elected thread, tcgen05.mma kind::tf32,
+//                 fp32 accumulator in TMEM, tcgen05.commit releases smem stages)
+//   warps 2..5  : epilogue (tcgen05.ld 32x32b -> registers -> warp-private smem transpose ->
+//                 coalesced global stores with alpha/beta/bias/activation fused)
+//   Operands are consumed in place for all four transpose combinations: a row-major [rows, K]
+//   operand is "K-major", a row-major [K, cols] operand is "MN-major"; both are expressible
+//   in the shared-memory matrix descriptor, so nothing is transposed in memory.
+// Path 2 (CUDA cores): register-tiled FFMA kernel for shapes TMA cannot describe (row pitch
+//   not a multiple of 16 bytes), tiny problems, and the exact-fp32 precision mode.
+#include "common.cuh"
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include <mutex>
+#include <unordered_map>
+#include <string>
+#include <cstring>
+
+enum { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2, ACT_SIGMOID = 3 };
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+    if (act == ACT_RELU) return fmaxf(v, 0.f);
+    if (act == ACT_GELU) return v * 0.5f * (1.0f + erff(v * 0.70710678118654752f));
+    if (act == ACT_SIGMOID) return 1.f / (1.f + __expf(-v));
+    return v;
+}
+
+// ======================================================================= PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done, addr = smem_u32(bar);
+    do {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}" : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// shared-memory matrix descriptor (sm_100 UMMA): 14-bit fields in 16-byte units
+// layout_type: 2 = SWIZZLE_128B (K-major operands), 1 = SWIZZLE_128B_BASE32B (the only layout the
+// tensor core accepts for MN-major 32-bit operands: 32-byte chunks swizzled over 4 K-rows)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout_type = 2) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);            // start address
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;        // leading byte offset
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;        // stride byte offset
+    d |= (uint64_t)1 << 46;                                  // descriptor version (sm_100)
+    d |= (uint64_t)layout_type << 61;
+    return d;
+}
+
+// ================================================================== tcgen05 GEMM kernel
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 32;        // 32 fp32 = 128 bytes = one swizzle-128B row
+constexpr int UMMA_K = 8;          // kind::tf32
+constexpr int kGemmThreads = 192;  // 6 warps
+
+template <int BLOCK_N>
+struct GemmCfg {
+    static constexpr int kStages = BLOCK_N == 128 ? 3 : 4;   // N=128: 3 stages so two CTAs share an SM
+    static constexpr int kABytes = BLOCK_M * BLOCK_K * 4;     // 16 KB
+    static constexpr int kBBytes = BLOCK_N * BLOCK_K * 4;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kEpiBytes = 4 * 32 * 33 * 4;         // per-warp 32x33 transpose tiles (aliases stage 0)
+    static_assert(kEpiBytes <= kStageBytes, "epilogue staging must fit in one stage");
+    static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+    static constexpr int kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+};
+
+struct GemmParams {
+    float* C;
+    const float* bias;
+    int M, N, K;
+    long long sC;
+    int a_mn_major, b_mn_major;    // 1 = MN-major (A given as [K,M] / B given as [K,N])
+    int a_batched, b_batched;
+    float alpha, beta;
+    int act;
+};
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tf32_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
+    using Cfg = GemmCfg<BLOCK_N>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;                                               // [stages][16 KB]
+    uint8_t* smem_b = smem + Cfg::kStages * Cfg::kABytes;                 // [stages][kBBytes]
+    float* smem_epi = reinterpret_cast<float*>(smem);   // reused after the last MMA has retired
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+    uint64_t* empty_bar = full_bar + Cfg::kStages;
+    uint64_t* tmem_full_bar = empty_bar + Cfg::kStages;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * BLOCK_M, n0 = blockIdx.x * BLOCK_N, bz = blockIdx.z;
+    const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+        for (int i = 0; i < Cfg::kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr_smem, Cfg::kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            const int ba = p.a_batched ? bz : 0, bb = p.b_batched ? bz : 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int st = kb % Cfg::kStages;
+                if (kb >= Cfg::kStages) mbar_wait(&empty_bar[st], ((kb / Cfg::kStages) - 1) & 1);
+                mbar_expect_tx(&full_bar[st], Cfg::kStageBytes);
+                uint8_t* a_dst = smem_a + st * Cfg::kABytes;
+                uint8_t* b_dst = smem_b + st * Cfg::kBBytes;
+                const int k0 = kb * BLOCK_K;
+                if (!p.a_mn_major) {
+                    tma_load_3d(a_dst, &tmA, k0, m0, ba, &full_bar[st]);               // box {32k, 128m}
+                } else {
+#pragma unroll
+                    for (int j = 0; j < BLOCK_M / 32; ++j)                              // box {32m, 32k} x4
+                        tma_load_3d(a_dst + j * (BLOCK_K * 128), &tmA, m0 + j * 32, k0, ba, &full_bar[st]);
+                }
+                if (!p.b_mn_major) {
+                    tma_load_3d(b_dst, &tmB, k0, n0, bb, &full_bar[st]);               // box {32k, BLOCK_N n}
+                } else {
+#pragma unroll
+                    for (int j = 0; j < BLOCK_N / 32; ++j)
+                        tma_load_3d(b_dst + j * (BLOCK_K * 128), &tmB, n0 + j * 32, k0, bb, &full_bar[st]);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            // instruction descriptor: D=f32, A=B=tf32, majors, N>>3 @17, M>>4 @24
+            uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)p.a_mn_major << 15) |
+                             ((uint32_t)p.b_mn_major << 16) | ((uint32_t)(BLOCK_N >> 3) << 17) |
+                             ((uint32_t)(BLOCK_M >> 4) << 24);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int st = kb % Cfg::kStages;
+                mbar_wait(&full_bar[st], (kb / Cfg::kStages) & 1);
+                tc_fence_after();
+                const uint32_t a_base = smem_u32(smem_a + st * Cfg::kABytes);
+                const uint32_t b_base = smem_u32(smem_b + st * Cfg::kBBytes);
+#pragma unroll
+                for (int ki = 0; ki < BLOCK_K / UMMA_K; ++ki) {
+                    // K-major : rows of 128 B, 8-row groups 1024 B apart (SBO); K step = 32 B inside the row.
+                    // MN-major: [k][128 B of MN] atoms, 4-k-row groups 512 B apart (SBO), next 32 MN
+                    //           elements BLOCK_K*128 B further (LBO); K step = 8 rows = 1024 B.
+                    uint64_t a_desc = p.a_mn_major ? make_smem_desc(a_base + ki * (UMMA_K * 128), BLOCK_K * 128, 512, 1)
+                                                   : make_smem_desc(a_base + ki * (UMMA_K * 4), 16, 1024, 2);
+                    uint64_t b_desc = p.b_mn_major ? make_smem_desc(b_base + ki * (UMMA_K * 128), BLOCK_K * 128, 512, 1)
+                                                   : make_smem_desc(b_base + ki * (UMMA_K * 4), 16, 1024, 2);
+                    umma_tf32(tmem_base, a_desc, b_desc, idesc, (kb > 0 || ki > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[st]);       // smem stage reusable once these MMAs retire
+            }
+            umma_commit(tmem_full_bar);            // accumulator complete
+        }
+    } else {
+        // ------------------------------------------------------------ epilogue (warps 2..5)
+        const int q = warp & 3;                    // TMEM lane quadrant this warp may access
+        float* tile = smem_epi + (warp - 2) * (32 * 33);
+        mbar_wait(tmem_full_bar, 0);
+        tc_fence_after();
+        float* Cb = p.C + (size_t)bz * p.sC;
+        const int row_base = m0 + q * 32;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+            if (n0 + c0 >= p.N) break;
+            float v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = v[j];
+            __syncwarp();
+            const int col = n0 + c0 + lane;
+            const float bv = (p.bias != nullptr && col < p.N) ? __ldg(p.bias + col) : 0.f;
+#pragma unroll 4
+            for (int r = 0; r < 32; ++r) {
+                const int row = row_base + r;
+                if (row < p.M && col < p.N) {
+                    float o = p.alpha * tile[r * 33 + lane] + bv;
+                    float* dst = Cb + (size_t)row * p.N + col;
+                    if (p.beta != 0.f) o += p.beta * (*dst);
+                    *dst = apply_act(o, p.act);
+                }
+            }
+            __syncwarp();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+// ---------------------------------------------------------------- host: tensor maps
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(ptr);
+    });
+    return fn;
+}
+
+// 3-D fp32 tensor map {inner, rows, batch}, 128B swizzle, box {32, box_rows, 1}
+static int make_tmap(CUtensorMap* map, const float* base, long long inner, long long rows, long long batch,
+                     long long batch_stride_elems, int box_rows, bool mn_major) {
+    auto fn = get_encode_fn();
+    if (!fn) { hetu_set_error("cuTensorMapEncodeTiled entry point not found"); return -1; }
+    cuuint64_t dims[3] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)(batch > 0 ? batch : 1)};
+    cuuint64_t strides[2] = {(cuuint64_t)inner * 4, (cuuint64_t)(batch > 1 ? batch_stride_elems : inner * rows) * 4};
+    cuuint32_t box[3] = {32, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { hetu_set_error("cuTensorMapEncodeTiled failed with %d (inner=%lld rows=%lld)", (int)r, inner, rows); return -1; }
+    return 0;
+}
+
+template <int BLOCK_N>
+static int launch_tc(const float* A, const float* B, GemmParams& p, int batch, long long sA, long long sB, cudaStream_t s) {
+    using Cfg = GemmCfg<BLOCK_N>;
+    CUtensorMap tmA, tmB;
+    // A: K-major -> memory [M][K]: inner=K rows=M, box rows 128.  MN-major -> memory [K][M]: inner=M rows=K, box rows 32.
+    if (!p.a_mn_major) { if (make_tmap(&tmA, A, p.K, p.M, p.a_batched ? batch : 1, sA, BLOCK_M, false)) return -1; }
+    else { if (make_tmap(&tmA, A, p.M, p.K, p.a_batched ? batch : 1, sA, BLOCK_K, true)) return -1; }
+    if (!p.b_mn_major) { if (make_tmap(&tmB, B, p.K, p.N, p.b_batched ? batch : 1, sB, BLOCK_N, false)) return -1; }
+    else { if (make_tmap(&tmB, B, p.N, p.K, p.b_batched ? batch : 1, sB, BLOCK_K, true)) return -1; }
+    static bool attr_set = false;
+    if (!attr_set) {
+        HETU_CUDA(cudaFuncSetAttribute(gemm_tf32_tcgen05_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmem));
+        attr_set = true;
+    }
+    dim3 grid((p.N + BLOCK_N - 1) / BLOCK_N, (p.M + BLOCK_M - 1) / BLOCK_M, batch);
+    gemm_tf32_tcgen05_kernel<BLOCK_N><<<grid, kGemmThreads, Cfg::kSmem, s>>>(tmA, tmB, p);
+    return 0;
+}
+
+// ==================================================================== SIMT fp32 kernel
+// 64x64 tile, BK = 16, 256 threads, 4x4 micro-tile per thread; all transposes by indexing.
+__global__ void __launch_bounds__(256) gemm_fp32_simt_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                             float* __restrict__ C, const float* __restrict__ bias, int M,
+                                                             int N, int K, int tA, int tB, long long sA, long long sB,
+                                                             long long sC, float alpha, float beta, int act) {
+    __shared__ float As[16][64 + 4];
+    __shared__ float Bs[16][64 + 4];
+    const int bz = blockIdx.z;
+    A += (size_t)bz * sA; B += (size_t)bz * sB; C += (size_t)bz * sC;
+    const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    float acc[4][4] = {};
+    for (int k0 = 0; k0 < K; k0 += 16) {
+        for (int i = threadIdx.x; i < 16 * 64; i += 256) {
+            int kk, mm;
+            if (!tA) { kk = i & 15; mm = i >> 4; } else { mm = i & 63; kk = i >> 6; }   // keep global reads contiguous
+            int gm = m0 + mm, gk = k0 + kk;
+            float v = 0.f;
+            if (gm < M && gk < K) v = tA ? A[(size_t)gk * M + gm] : A[(size_t)gm * K + gk];
+            As[kk][mm] = v;
+        }
+        for (int i = threadIdx.x; i < 16 * 64; i += 256) {
+            int kk, nn;
+            if (!tB) { nn = i & 63; kk = i >> 6; } else { kk = i & 15; nn = i >> 4; }
+            int gn = n0 + nn, gk = k0 + kk;
+            float v = 0.f;
+            if (gn < N && gk < K) v = tB ? B[(size_t)gn * K + gk] : B[(size_t)gk * N + gn];
+            Bs[kk][nn] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) {
+            float a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = As[kk][ty * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = Bs[kk][tx * 4 + j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        int gm = m0 + ty * 4 + i;
+        if (gm >= M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int gn = n0 + tx * 4 + j;
+            if (gn >= N) continue;
+            float o = alpha * acc[i][j] + (bias ? bias[gn] : 0.f);
+            float* dst = C + (size_t)gm * N + gn;
+            if (beta != 0.f) o += beta * (*dst);
+            *dst = apply_act(o, act);
+        }
+    }
+}
+
+// Skinny GEMV-like case N == 1 (WDL's final [B, 3584] x [3584, 1]) and its transposes are
+// handled well enough by the SIMT kernel; a split-K variant keeps dW-style products
+// (tiny M x N, huge K) from running on a single CTA.
+__global__ void __launch_bounds__(256) gemm_fp32_splitk_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                               float* __restrict__ C, int M, int N, int K, int tA, int tB,
+                                                               float alpha, int kchunk) {
+    // each CTA: 16x16 output tile, K range [blockIdx.z*kchunk, +kchunk); atomicAdd into zeroed C
+    __shared__ float As[16][17], Bs[16][17];
+    int m0 = blockIdx.y * 16, n0 = blockIdx.x * 16;
+    int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    int kbeg = blockIdx.z * kchunk, kend = min(K, kbeg + kchunk);
+    float acc = 0.f;
+    for (int k0 = kbeg; k0 < kend; k0 += 16) {
+        int gm = m0 + ty, gk = k0 + tx;
+        As[ty][tx] = (gm < M && gk < kend) ? (tA ? A[(size_t)gk * M + gm] : A[(size_t)gm * K + gk]) : 0.f;
+        int gn = n0 + tx; gk = k0 + ty;
+        Bs[ty][tx] = (gn < N && gk < kend) ? (tB ? B[(size_t)gn * K + gk] : B[(size_t)gk * N + gn]) : 0.f;
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) acc = fmaf(As[ty][kk], Bs[kk][tx], acc);
+        __syncthreads();
+    }
+    int gm = m0 + ty, gn = n0 + tx;
+    if (gm < M && gn < N) atomicAdd(C + (size_t)gm * N + gn, alpha * acc);
+}
+
+__global__ void __launch_bounds__(256) gemm_finish_kernel(float* __restrict__ C, const float* __restrict__ bias, size_t n,
+                                                          int N, int act) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        C[i] = apply_act(C[i] + (bias ? bias[i % N] : 0.f), act);
+}
+
+// ============================================================================ dispatch
+static bool aligned16p(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, int transA,
+                       int transB, int batch, long long sA, long long sB, long long sC, float alpha, float beta, int act,
+                       int mode, cudaStream_t s) {
+    if (M <= 0 || N <= 0 || batch <= 0) return 0;
+    if (K <= 0) {
+        hetu_set_error("hetu_gemm: K must be positive");
+        return -1;
+    }
+    // TMA needs 16-byte aligned bases and row pitches: the contiguous dim of each operand % 4 == 0
+    long long a_inner = transA ? M : K, b_inner = transB ? K : N;
+    bool tma_ok = aligned16p(A) && aligned16p(B) && (a_inner % 4 == 0) && (b_inner % 4 == 0) &&
+                  (sA % 4 == 0) && (sB % 4 == 0);
+    bool big = (double)M * N * K >= (double)(1 << 20) && M >= 32 && N >= 8 && K >= 32;
+    static int force_simt = -1;
+    if (force_simt < 0) { const char* e = getenv("HETU_GEMM_FORCE_SIMT"); force_simt = (e && e[0] == '1') ? 1 : 0; }
+    if (mode != 1 && tma_ok && big && !force_simt) {
+        GemmParams p;
+        p.C = C; p.bias = bias; p.M = M; p.N = N; p.K = K; p.sC = sC;
+        p.a_mn_major = transA ? 1 : 0;
+        p.b_mn_major = transB ? 0 : 1;
+        p.a_batched = (batch > 1 && sA != 0) ? 1 : 0;
+        p.b_batched = (batch > 1 && sB != 0) ? 1 : 0;
+        p.alpha = alpha; p.beta = beta; p.act = act;
+        int rc;
+        if (N > 128) rc = launch_tc<256>(A, B, p, batch, sA, sB, s);
+        else if (N > 64) rc = launch_tc<128>(A, B, p, batch, sA, sB, s);
+        else if (N > 32) rc = launch_tc<64>(A, B, p, batch, sA, sB, s);
+        else rc = launch_tc<32>(A, B, p, batch, sA, sB, s);
+        if (rc) return rc;
+        HETU_CHECK_LAUNCH("hetu_gemm(tcgen05)");
+        return 0;
+    }
+    // split-K for tiny outputs with a long reduction (weight gradients of small layers)
+    if (batch == 1 && beta == 0.f && (long long)M * N <= 64 * 64 && K >= 2048) {
+        int tiles = ((M + 15) / 16) * ((N + 15) / 16);
+        int splits = (kNumSMs * 2 + tiles - 1) / tiles;
+        int kchunk = ((K + splits - 1) / splits + 15) / 16 * 16;
+        splits = (K + kchunk - 1) / kchunk;
+        cudaMemsetAsync(C, 0, (size_t)M * N * sizeof(float), s);
+        gemm_fp32_splitk_kernel<<<dim3((N + 15) / 16, (M + 15) / 16, splits), 256, 0, s>>>(A, B, C, M, N, K, transA, transB, alpha, kchunk);
+        if (bias || act != ACT_NONE)
+            gemm_finish_kernel<<<ew_grid((size_t)M * N, 256), 256, 0, s>>>(C, bias, (size_t)M * N, N, act);
+        HETU_CHECK_LAUNCH("hetu_gemm(splitk)");
+        return 0;
+    }
+    dim3 grid((N + 63) / 64, (M + 63) / 64, batch);
+    gemm_fp32_simt_kernel<<<grid, 256, 0, s>>>(A, B, C, bias, M, N, K, transA, transB, sA, sB, sC, alpha, beta, act);
+    HETU_CHECK_LAUNCH("hetu_gemm(simt)");
+    return 0;
+}
+
+// ==================================================================== CSR SpMM (GNN)
+// reference: src/ops/CuSparseCsrmm.cu (hand spmm_kernel / spmm_T_kernel).  One warp per CSR
+// row; lanes stride over the dense columns.  trans: scatter with atomics into out[col].
+__global__ void __launch_bounds__(256) csr_spmm_kernel(const float* __restrict__ val, const int* __restrict__ rowptr,
+                                                       const int* __restrict__ colidx, const float* __restrict__ dense,
+                                                       float* __restrict__ out, int nrow, int n, int trans) {
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    int nwarp = (gridDim.x * blockDim.x) >> 5;
+    for (int r = warp; r < nrow; r += nwarp) {
+        int beg = rowptr[r], end = rowptr[r + 1];
+        if (!trans) {
+            for (int c = lane; c < n; c += 32) {
+                float acc = 0.f;
+                for (int e = beg; e < end; ++e) acc += val[e] * dense[(size_t)colidx[e] * n + c];
+                out[(size_t)r * n + c] = acc;
+            }
+        } else {
+            for (int e = beg; e < end; ++e) {
+                float v = val[e];
+                int col = colidx[e];
+                for (int c = lane; c < n; c += 32) atomicAdd(out + (size_t)col * n + c, v * dense[(size_t)r * n + c]);
+            }
+        }
+    }
+}
+HETU_API int hetu_csr_spmm(const float* val, const int* rowptr, const int* colidx, const float* dense, float* out,
+                           int nrow, int n, int trans, cudaStream_t s) {
+    if (nrow == 0 || n == 0) return 0;
+    csr_spmm_kernel<<<ew_grid((size_t)nrow * 32, 256, 16), 256, 0, s>>>(val, rowptr, colidx, dense, out, nrow, n, trans);
+    HETU_CHECK_LAUNCH("hetu_csr_spmm");
+    return 0;
+}

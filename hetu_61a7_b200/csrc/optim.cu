@@ -1,0 +1,152 @@
+// Multi-tensor dense optimizer step: every parameter tensor of the model in ONE launch.
+// reference: src/ops/Optimizers.cu:39-402 - one launch per tensor per step
+// (sgd_update / momentum_update / adagrad_update / adam_update / adamw_update /
+// calc_lamb_update + lamb_update_step with cudnnReduceTensor norms).
+//
+// grid = (x-chunks, tensor index).  Pointers travel by value in the launch parameters;
+// lr and the step count are read from device memory so a captured CUDA graph stays valid
+// while the schedule / bias correction advance.
+#include "common.cuh"
+
+enum { OPT_SGD = 0, OPT_MOMENTUM, OPT_NESTEROV, OPT_ADAGRAD, OPT_ADAM, OPT_ADAMW, OPT_LAMB };
+constexpr int kMaxTensors = 48;
+
+struct TensorList {
+    float* p[kMaxTensors];
+    const float* g[kMaxTensors];
+    float* s1[kMaxTensors];
+    float* s2[kMaxTensors];
+    long long n[kMaxTensors];
+};
+
+template <int KIND>
+__global__ void __launch_bounds__(256) multi_tensor_opt_kernel(TensorList tl, const float* __restrict__ lr_p,
+                                                               const long long* __restrict__ step_p, float h0, float h1,
+                                                               float h2, float h3, float l2reg, float grad_scale) {
+    int t = blockIdx.y;
+    long long n = tl.n[t];
+    float* __restrict__ p = tl.p[t];
+    const float* __restrict__ g = tl.g[t];
+    float* __restrict__ s1 = tl.s1[t];
+    float* __restrict__ s2 = tl.s2[t];
+    float lr = *lr_p;
+    float b1t = 1.f, b2t = 1.f;
+    if (KIND >= OPT_ADAM) {
+        float st = (float)(*step_p);
+        b1t = 1.f - powf(h0, st);
+        b2t = 1.f - powf(h1, st);
+    }
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float pv = p[i];
+        float gv = g[i] * grad_scale + l2reg * pv;
+        if (KIND == OPT_SGD) {
+            p[i] = pv - lr * gv;
+        } else if (KIND == OPT_MOMENTUM) {
+            float v = h0 * s1[i] - lr * gv;
+            s1[i] = v;
+            p[i] = pv + v;
+        } else if (KIND == OPT_NESTEROV) {
+            float tmp = lr * gv;
+            float v = h0 * (s1[i] - tmp);
+            s1[i] = v;
+            p[i] = pv + v - tmp;
+        } else if (KIND == OPT_ADAGRAD) {
+            float a = s1[i] + gv * gv;
+            s1[i] = a;
+            p[i] = pv - lr * gv / (sqrtf(a) + h0);
+        } else {
+            float m = h0 * s1[i] + (1.f - h0) * gv;
+            float v = h1 * s2[i] + (1.f - h1) * gv * gv;
+            s1[i] = m;
+            s2[i] = v;
+            float upd = (m / b1t) / (sqrtf(v / b2t) + h2);
+            if (KIND == OPT_ADAM) p[i] = pv - lr * upd;
+            else p[i] = pv - lr * (upd + h3 * pv);
+        }
+    }
+}
+
+// Lamb, phase 1: moments + per-tensor ||p||^2 and ||update||^2 into scratch[2t], scratch[2t+1]
+__global__ void __launch_bounds__(256) lamb_phase1_kernel(TensorList tl, const long long* __restrict__ step_p, float h0,
+                                                          float h1, float h2, float l2reg, float grad_scale,
+                                                          float* __restrict__ scratch) {
+    __shared__ float sm[32];
+    int t = blockIdx.y;
+    long long n = tl.n[t];
+    float st = (float)(*step_p);
+    float b1t = 1.f - powf(h0, st), b2t = 1.f - powf(h1, st);
+    float np = 0.f, nu = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float pv = tl.p[t][i];
+        float gv = tl.g[t][i] * grad_scale + l2reg * pv;
+        float m = h0 * tl.s1[t][i] + (1.f - h0) * gv;
+        float v = h1 * tl.s2[t][i] + (1.f - h1) * gv * gv;
+        tl.s1[t][i] = m;
+        tl.s2[t][i] = v;
+        float upd = (m / b1t) / (sqrtf(v / b2t) + h2);
+        np += pv * pv;
+        nu += upd * upd;
+    }
+    np = block_sum(np, sm);
+    nu = block_sum(nu, sm);
+    if (threadIdx.x == 0) {
+        atomicAdd(scratch + 2 * t, np);
+        atomicAdd(scratch + 2 * t + 1, nu);
+    }
+}
+__global__ void __launch_bounds__(256) lamb_phase2_kernel(TensorList tl, const float* __restrict__ lr_p,
+                                                          const long long* __restrict__ step_p, float h0, float h1, float h2,
+                                                          float h3, const float* __restrict__ scratch) {
+    int t = blockIdx.y;
+    long long n = tl.n[t];
+    float st = (float)(*step_p);
+    float b1t = 1.f - powf(h0, st), b2t = 1.f - powf(h1, st);
+    float ratio = sqrtf(scratch[2 * t]) / sqrtf(scratch[2 * t + 1]);
+    float lr = *lr_p;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float pv = tl.p[t][i];
+        float upd = (tl.s1[t][i] / b1t) / (sqrtf(tl.s2[t][i] / b2t) + h2);
+        tl.p[t][i] = pv - lr * ratio * (upd + h3 * pv);
+    }
+}
+
+HETU_API int hetu_multi_tensor_opt(int kind, int ntensors, void* const* params, void* const* grads, void* const* s1,
+                                   void* const* s2, const long long* sizes, const float* lr_p, const void* step_p,
+                                   float h0, float h1, float h2, float h3, float l2reg, float* scratch,
+                                   cudaStream_t s) {
+    if (ntensors <= 0) return 0;
+    if (ntensors > kMaxTensors) { hetu_set_error("multi_tensor_opt: %d tensors > %d per launch", ntensors, kMaxTensors); return -1; }
+    TensorList tl;
+    long long maxn = 0;
+    for (int i = 0; i < kMaxTensors; ++i) {
+        bool on = i < ntensors;
+        tl.p[i] = on ? (float*)params[i] : nullptr;
+        tl.g[i] = on ? (const float*)grads[i] : nullptr;
+        tl.s1[i] = on ? (float*)s1[i] : nullptr;
+        tl.s2[i] = on ? (float*)s2[i] : nullptr;
+        tl.n[i] = on ? sizes[i] : 0;
+        if (on && sizes[i] > maxn) maxn = sizes[i];
+    }
+    int gx = (int)((maxn + 256 * 4 - 1) / (256 * 4));
+    int cap = (kNumSMs * 8 + ntensors - 1) / ntensors;
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    dim3 grid(gx, ntensors);
+    const long long* st = (const long long*)step_p;
+    switch (kind) {
+        case OPT_SGD: multi_tensor_opt_kernel<OPT_SGD><<<grid, 256, 0, s>>>(tl, lr_p, st, h0, h1, h2, h3, l2reg, 1.f); break;
+        case OPT_MOMENTUM: multi_tensor_opt_kernel<OPT_MOMENTUM><<<grid, 256, 0, s>>>(tl, lr_p, st, h0, h1, h2, h3, l2reg, 1.f); break;
+        case OPT_NESTEROV: multi_tensor_opt_kernel<OPT_NESTEROV><<<grid, 256, 0, s>>>(tl, lr_p, st, h0, h1, h2, h3, l2reg, 1.f); break;
+        case OPT_ADAGRAD: multi_tensor_opt_kernel<OPT_ADAGRAD><<<grid, 256, 0, s>>>(tl, lr_p, st, h0, h1, h2, h3, l2reg, 1.f); break;
+        case OPT_ADAM: multi_tensor_opt_kernel<OPT_ADAM><<<grid, 256, 0, s>>>(tl, lr_p, st, h0, h1, h2, h3, l2reg, 1.f); break;
+        case OPT_ADAMW: multi_tensor_opt_kernel<OPT_ADAMW><<<grid, 256, 0, s>>>(tl, lr_p, st, h0, h1, h2, h3, l2reg, 1.f); break;
+        case OPT_LAMB:
+            if (!scratch) { hetu_set_error("multi_tensor_opt: Lamb needs a zeroed scratch of 2 floats per tensor"); return -1; }
+            lamb_phase1_kernel<<<grid, 256, 0, s>>>(tl, st, h0, h1, h2, l2reg, 1.f, scratch);
+            lamb_phase2_kernel<<<grid, 256, 0, s>>>(tl, lr_p, st, h0, h1, h2, h3, scratch);
+            break;
+        default: hetu_set_error("multi_tensor_opt: bad kind %d", kind); return -1;
+    }
+    HETU_CHECK_LAUNCH("hetu_multi_tensor_opt");
+    return 0;
+}

@@ -598,7 +598,7 @@ class SubExecutor(object):
                     raise AssertionError('placeholder %s values provided by feed_dict' % node.name)
                 vals[node] = v
                 continue
-            ins = [vals[i] for i in node.inputs]
+            ins = [vals[i] if i is not None else None for i in node.inputs]
             dev = self._node_device(node)
             for j, v in enumerate(ins):
                 if isinstance(v, torch.Tensor) and v.device != dev and not isinstance(
@@ -611,7 +611,7 @@ class SubExecutor(object):
             vals[node] = out
             if release:
                 for inp in node.inputs:
-                    if (self._last_use.get(inp) == idx and inp not in self._eval_set
+                    if (inp is not None and self._last_use.get(inp) == idx and inp not in self._eval_set
                             and not isinstance(inp, PlaceholderOp) and inp not in self._side_refs):
                         vals[inp] = None
 
@@ -699,6 +699,7 @@ class SubExecutor(object):
                 self._static_in[node] = t
         graph = torch.cuda.CUDAGraph()
         vals: Dict[Op, object] = {}
+        launches_before = L.launch_count
         with torch.cuda.graph(graph):
             for node, st in self._static_in.items():
                 if node in self._stage:
@@ -708,6 +709,7 @@ class SubExecutor(object):
         self._graph = graph
         self._graph_key = key
         self._static_out = vals
+        self.graph_launches = L.launch_count - launches_before   # native kernels per replay
         torch.cuda.synchronize(dev)
 
     # ----------------------------------------------------------------------------- misc

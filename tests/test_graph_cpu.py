@@ -1,0 +1,341 @@
+"""Graph core on CPU: ops + symbolic autodiff against torch autograd, optimizers against
+closed forms, schedulers, dataloader, executor save/load (pattern: reference
+tests/test_transformer_ops.py - second framework as oracle; test_optimizer.py)."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+
+import hetu as ht
+
+
+def run_graph(build, feeds, wrt_names, seed=0):
+    """build(vars) -> scalar loss node; returns (loss, grads) evaluated on CPU."""
+    vars_ = {k: ht.Variable(name=k, value=v.copy()) for k, v in feeds.items()}
+    loss = build(vars_)
+    grads = ht.gradients(loss, [vars_[k] for k in wrt_names])
+    # a zero-lr optimizer makes this a *training* sub-executor (BN / dropout in train mode)
+    train = ht.optim.SGDOptimizer(0.0).minimize(loss)
+    ex = ht.Executor([loss] + grads + [train], ctx=ht.cpu(0), seed=seed)
+    out = ex.run(convert_to_numpy_ret_vals=True)
+    return out[0], out[1:-1]
+
+
+def check(build_ht, build_torch, feeds, wrt=None, rtol=1e-4, atol=1e-5):
+    wrt = wrt or list(feeds.keys())
+    loss, grads = run_graph(build_ht, feeds, wrt)
+    tvars = {k: torch.tensor(v, requires_grad=(k in wrt)) for k, v in feeds.items()}
+    tl = build_torch(tvars)
+    tl.backward()
+    np.testing.assert_allclose(np.asarray(loss).reshape(-1), tl.detach().numpy().reshape(-1), rtol=rtol, atol=atol)
+    for k, g in zip(wrt, grads):
+        np.testing.assert_allclose(g, tvars[k].grad.numpy(), rtol=rtol, atol=atol, err_msg=k)
+
+
+R = np.random.RandomState(0)
+
+
+def f32(*s):
+    return R.randn(*s).astype(np.float32)
+
+
+def test_mlp_softmax_ce_grads():
+    feeds = {'x': f32(8, 12), 'w1': f32(12, 16), 'b1': f32(16), 'w2': f32(16, 5)}
+    y = np.eye(5, dtype=np.float32)[R.randint(0, 5, 8)]
+
+    def b_ht(v):
+        h = ht.relu_op(ht.linear_op(v['x'], v['w1'], v['b1']))
+        logits = ht.matmul_op(h, v['w2'])
+        return ht.reduce_mean_op(ht.softmaxcrossentropy_op(logits, ht.Variable('y', value=y)), [0])
+
+    def b_t(v):
+        h = torch.relu(v['x'] @ v['w1'] + v['b1'])
+        return torch.nn.functional.cross_entropy(h @ v['w2'], torch.tensor(y).argmax(1))
+
+    check(b_ht, b_t, feeds)
+
+
+def test_elementwise_grads():
+    feeds = {'a': f32(4, 6), 'b': np.abs(f32(4, 6)) + 0.5}
+
+    def b_ht(v):
+        a, b = v['a'], v['b']
+        t = ht.tanh_op(a) * ht.sigmoid_op(b) + ht.exp_op(a * 0.1) + ht.log_op(b) + ht.sqrt_op(b)
+        t = t + ht.gelu_op(a) + ht.leaky_relu_op(a, 0.1) + ht.div_op(a, b) + ht.pow_op(b, 1.5)
+        t = t + ht.sin_op(a) + ht.cos_op(a) + ht.abs_op(a) + ht.rsqrt_op(b) + ht.div_const_op(2.0, b)
+        t = t + ht.minus_op(a, b) + ht.minus_byconst_op(a, 3.0) + ht.opposite_op(a) + ht.const_pow_op(a, 2.0)
+        return ht.reduce_sum_op(ht.reduce_sum_op(t, [1]), [0])
+
+    def b_t(v):
+        a, b = v['a'], v['b']
+        t = torch.tanh(a) * torch.sigmoid(b) + torch.exp(a * 0.1) + torch.log(b) + torch.sqrt(b)
+        t = t + torch.nn.functional.gelu(a) + torch.nn.functional.leaky_relu(a, 0.1) + a / b + b ** 1.5
+        t = t + torch.sin(a) + torch.cos(a) + a.abs() + torch.rsqrt(b) + 2.0 / b
+        t = t + (a - b) + (3.0 - a) + (-a) + torch.pow(torch.tensor(2.0), a)
+        return t.sum()
+
+    check(b_ht, b_t, feeds, rtol=1e-3, atol=1e-4)
+
+
+def test_broadcast_reduce_shape_grads():
+    feeds = {'a': f32(3, 4, 5), 'b': f32(5), 'c': f32(3, 1, 5)}
+
+    def b_ht(v):
+        a, b, c = v['a'], v['b'], v['c']
+        t = a + ht.broadcastto_op(b, a)
+        t = ht.mul_op(t, ht.broadcastto_op(c, a))
+        t = ht.transpose_op(t, [2, 0, 1])
+        t = ht.array_reshape_op(t, [5, 12])
+        s = ht.slice_op(t, [1, 2], [3, 6])
+        s2 = ht.split_op(t, [1], [1], [3])
+        cat = ht.concat_op(s2, ht.pad_op(s, [[0, 2], [0, 0]]), axis=1)
+        cat = ht.concatenate_op([cat, cat * 2.0], axis=0)
+        r = ht.reduce_mean_op(cat, [0]) * ht.reduce_sum_op(ht.repeat_op(ht.reduce_sum_op(a, [0, 1]), [2]), [0])
+        return ht.reduce_sum_op(r, [0])
+
+    def b_t(v):
+        a, b, c = v['a'], v['b'], v['c']
+        t = ((a + b) * c).permute(2, 0, 1).reshape(5, 12)
+        s = t[1:4, 2:8]
+        s2 = t[:, 4:8]
+        cat = torch.cat([s2, torch.nn.functional.pad(s, (0, 0, 0, 2))], dim=1)
+        cat = torch.cat([cat, cat * 2.0], dim=0)
+        r = cat.mean(0) * a.sum((0, 1)).repeat(2).sum()
+        return r.sum()
+
+    check(b_ht, b_t, feeds)
+
+
+def test_norm_layers_and_losses():
+    feeds = {'x': f32(6, 10), 'g': f32(10), 'b': f32(10), 'w': f32(10, 3)}
+    lab = R.randint(0, 3, 6).astype(np.float32)
+
+    def b_ht(v):
+        h = ht.layer_normalization_op(v['x'], v['g'], v['b'], eps=1e-5)
+        logits = ht.matmul_op(h, v['w'])
+        l1 = ht.reduce_mean_op(ht.softmaxcrossentropy_sparse_op(logits, ht.Variable('lab', value=lab)), [0])
+        p = ht.softmax_op(logits)
+        l2 = ht.reduce_mean_op(ht.crossentropy_sparse_op(p, ht.Variable('lab2', value=lab)), [0])
+        return l1 + l2
+
+    def b_t(v):
+        h = torch.nn.functional.layer_norm(v['x'], (10,), v['g'], v['b'], 1e-5)
+        logits = h @ v['w']
+        l = torch.nn.functional.cross_entropy(logits, torch.tensor(lab).long())
+        return l + l
+
+    check(b_ht, b_t, feeds, rtol=1e-3, atol=1e-5)
+
+
+def test_conv_bn_pool_grads():
+    feeds = {'x': f32(2, 3, 8, 8), 'w': f32(4, 3, 3, 3) * 0.3, 'bias': f32(4), 'g': np.abs(f32(4)) + 0.5, 'b': f32(4)}
+
+    def b_ht(v):
+        y = ht.conv2d_add_bias_op(v['x'], v['w'], v['bias'], padding=1, stride=1)
+        y = ht.batch_normalization_op(y, v['g'], v['b'], eps=1e-5)
+        y = ht.relu_op(y)
+        y = ht.max_pool2d_op(y, 2, 2, 0, 2) + ht.avg_pool2d_op(y, 2, 2, 0, 2)
+        y = ht.conv2d_op(y, ht.Variable('w2', value=np.ones((2, 4, 1, 1), np.float32)), padding=0, stride=2)
+        return ht.reduce_sum_op(ht.array_reshape_op(y, [-1]), [0])
+
+    def b_t(v):
+        F = torch.nn.functional
+        y = F.conv2d(v['x'], v['w'], v['bias'], padding=1)
+        y = F.batch_norm(y, None, None, v['g'], v['b'], True, 0.1, 1e-5)
+        y = torch.relu(y)
+        y = F.max_pool2d(y, 2, 2) + F.avg_pool2d(y, 2, 2)
+        y = F.conv2d(y, torch.ones(2, 4, 1, 1), stride=2)
+        return y.sum()
+
+    check(b_ht, b_t, feeds, rtol=2e-3, atol=1e-4)
+
+
+def test_embedding_sparse_grad_and_optimizers():
+    table = f32(20, 4)
+    ids = R.randint(0, 20, (6, 3)).astype(np.float32)
+    for make, torch_make in [
+        (lambda: ht.optim.SGDOptimizer(0.1), lambda p: torch.optim.SGD(p, 0.1)),
+        (lambda: ht.optim.AdaGradOptimizer(0.1, eps=1e-10), lambda p: torch.optim.Adagrad(p, 0.1, eps=1e-10)),
+        (lambda: ht.optim.AdamOptimizer(0.01, epsilon=1e-8), lambda p: torch.optim.Adam(p, 0.01, eps=1e-8)),
+    ]:
+        emb = ht.Variable('emb', value=table.copy())
+        w = ht.Variable('w', value=np.ones((12, 1), np.float32))
+        idn = ht.Variable('ids', value=ids, trainable=False)
+        e = ht.array_reshape_op(ht.embedding_lookup_op(emb, idn), (-1, 12))
+        loss = ht.reduce_mean_op(ht.reduce_sum_op(ht.mul_op(ht.matmul_op(e, w), ht.matmul_op(e, w)), [1]), [0])
+        train = make().minimize(loss)
+        ex = ht.Executor([loss, train], ctx=ht.cpu(0))
+        for _ in range(3):
+            ex.run()
+        got = ex.config.placeholder_to_arr_map[emb].numpy()
+        te = torch.tensor(table.copy(), requires_grad=True)
+        tw = torch.ones(12, 1, requires_grad=True)
+        opt = torch_make([te, tw])
+        for _ in range(3):
+            opt.zero_grad()
+            ee = te[torch.tensor(ids).long()].reshape(-1, 12)
+            l = ((ee @ tw) ** 2).sum(1).mean()
+            l.backward()
+            opt.step()
+        # AdaGrad/Adam sparse semantics: only touched rows move (matches dense for SGD; for the
+        # adaptive ones untouched rows have zero grad so the dense torch step leaves them too,
+        # except Adam's moment decay which has no effect on zero-initialised moments)
+        np.testing.assert_allclose(got, te.detach().numpy(), rtol=2e-3, atol=2e-4)
+
+
+def test_dense_optimizers_closed_form():
+    p0, g = f32(5, 3), f32(5, 3)
+    cases = {
+        'momentum': (ht.optim.MomentumOptimizer(0.1, 0.9), lambda p, v: (p + (0.9 * v - 0.1 * g), 0.9 * v - 0.1 * g)),
+        'nesterov': (ht.optim.MomentumOptimizer(0.1, 0.9, nesterov=True),
+                     lambda p, v: (p + 0.9 * (v - 0.1 * g) - 0.1 * g, 0.9 * (v - 0.1 * g))),
+    }
+    for name, (opt, step) in cases.items():
+        w = ht.Variable('w_' + name, value=p0.copy())
+        loss = ht.reduce_sum_op(ht.reduce_sum_op(ht.mul_op(w, ht.Variable('g', value=g, trainable=False)), [1]), [0])
+        ex = ht.Executor([loss, opt.minimize(loss)], ctx=ht.cpu(0))
+        p, v = p0.copy(), np.zeros_like(p0)
+        for _ in range(3):
+            ex.run()
+            p, v = step(p, v)
+        np.testing.assert_allclose(ex.config.placeholder_to_arr_map[w].numpy(), p, rtol=1e-5, atol=1e-6)
+    # AdamW / Lamb one step vs formula (reference tests/test_optimizer.py)
+    for cls, lamb in ((ht.optim.AdamWOptimizer, False), (ht.optim.LambOptimizer, True)):
+        w = ht.Variable('w', value=p0.copy())
+        loss = ht.reduce_sum_op(ht.reduce_sum_op(ht.mul_op(w, ht.Variable('g', value=g, trainable=False)), [1]), [0])
+        ex = ht.Executor([loss, cls(0.01, 0.9, 0.999, 1e-7, 0.1).minimize(loss)], ctx=ht.cpu(0))
+        ex.run()
+        m, v = 0.1 * g, 0.001 * g * g
+        upd = (m / 0.1) / (np.sqrt(v / 0.001) + 1e-7)
+        if lamb:
+            ratio = np.linalg.norm(p0) / np.linalg.norm(upd)
+            exp = p0 - 0.01 * ratio * (upd + 0.1 * p0)
+        else:
+            exp = p0 - 0.01 * (upd + 0.1 * p0)
+        np.testing.assert_allclose(ex.config.placeholder_to_arr_map[w].numpy(), exp, rtol=1e-4, atol=1e-6)
+
+
+def test_lr_schedulers():
+    s = ht.lr.StepScheduler(1.0, 2, 0.5)
+    assert [s.step() for _ in range(5)] == [1.0, 0.5, 0.5, 0.25, 0.25]
+    m = ht.lr.MultiStepScheduler(1.0, [2, 4], 0.1)
+    vals = [m.step() for _ in range(5)]
+    assert vals[0] == 1.0 and abs(vals[1] - 0.1) < 1e-12 and abs(vals[3] - 0.01) < 1e-12
+    e = ht.lr.ExponentialScheduler(1.0, 0.5, ending=0.2)
+    assert [e.step() for _ in range(4)] == [0.5, 0.25, 0.2, 0.2]
+    r = ht.lr.ReduceOnPlateauScheduler(1.0, patience=1, factor=0.1)
+    out = [r.step(v) for v in [1.0, 1.0, 1.0, 1.0]]
+    assert out[-1] < 1.0
+    # scheduler drives the optimizer's device-side lr
+    w = ht.Variable('w', value=np.ones((2, 2), np.float32))
+    loss = ht.reduce_sum_op(ht.reduce_sum_op(w, [1]), [0])
+    sched = ht.lr.StepScheduler(1.0, 1, 0.5)
+    opt = ht.optim.SGDOptimizer(sched)
+    ex = ht.Executor([loss, opt.minimize(loss)], ctx=ht.cpu(0))
+    ex.run()
+    sched.step()
+    ex.run()
+    np.testing.assert_allclose(ex.config.placeholder_to_arr_map[w].numpy(), np.ones((2, 2)) - 1.0 - 0.5)
+
+
+def test_dataloader_and_subexecutors():
+    x = np.arange(40, dtype=np.float32).reshape(20, 2)
+    dl = ht.dataloader_op([ht.Dataloader(x, 4, 'train'), ht.Dataloader(x[:8], 4, 'validate')])
+    w = ht.Variable('w', value=np.ones((2, 1), np.float32))
+    y = ht.matmul_op(dl, w)
+    loss = ht.reduce_mean_op(ht.reduce_sum_op(y, [1]), [0])
+    train = ht.optim.SGDOptimizer(0.0).minimize(loss)
+    ex = ht.Executor({'train': [loss, train], 'validate': [loss]}, ctx=ht.cpu(0))
+    assert ex.get_batch_num('train') == 5 and ex.get_batch_num('validate') == 2
+    seen = [float(ex.run('train')[0].asnumpy()) for _ in range(7)]
+    expect = [x[i * 4:(i + 1) * 4].sum(1).mean() for i in range(5)]
+    np.testing.assert_allclose(seen, expect + expect[:2], rtol=1e-6)
+    v = [float(ex.run('validate')[0].asnumpy()) for _ in range(3)]
+    np.testing.assert_allclose(v, [expect[0], expect[1], expect[0]], rtol=1e-6)
+
+
+def test_save_load_roundtrip():
+    w = ht.init.random_normal((4, 3), name='W_save')
+    b = ht.init.zeros((3,), name='b_save')
+    x = ht.Variable('x')
+    loss = ht.reduce_sum_op(ht.reduce_sum_op(ht.linear_op(x, w, b), [1]), [0])
+    ex = ht.Executor([loss, ht.optim.AdamOptimizer(0.1).minimize(loss)], ctx=ht.cpu(0), seed=3)
+    xv = f32(5, 4)
+    ex.run(feed_dict={x: xv})
+    with tempfile.TemporaryDirectory() as d:
+        ex.save(d, 'ckpt.bin', save_optimizer=True)
+        import pickle
+        state = pickle.load(open(os.path.join(d, 'ckpt.bin'), 'rb'))
+        assert set(state.keys()) == {'W_save', 'b_save'} and state['W_save'].dtype == np.float32
+        saved = {k: v.copy() for k, v in state.items()}
+        ex.run(feed_dict={x: xv})
+        after1 = ex.config.placeholder_to_arr_map[w].numpy().copy()
+        ex.load(d, 'ckpt.bin')
+        np.testing.assert_allclose(ex.config.placeholder_to_arr_map[w].numpy(), saved['W_save'])
+        ex.run(feed_dict={x: xv})      # optimizer slots were restored too -> same step as before
+        np.testing.assert_allclose(ex.config.placeholder_to_arr_map[w].numpy(), after1, rtol=1e-6)
+
+
+def test_moe_layer_cpu_forward_backward():
+    from hetu_61a7_b200.models.moe import moe_model
+    x, t = ht.Variable('x'), ht.Variable('t')
+    for gate in ('top', 'ktop1', 'sam'):
+        loss, y = moe_model(x, t, batch_size=2, num_tokens=32, model_dim=16, hidden_size=24,
+                            num_local_experts=4, world=1, top=2, gate=gate, num_local_gpus=2)
+        train = ht.optim.SGDOptimizer(0.01).minimize(loss)
+        ex = ht.Executor([loss, y, train], ctx=ht.cpu(0), seed=0)
+        out = ex.run(feed_dict={x: f32(2, 32, 16), t: np.zeros(2, np.float32)})
+        assert np.isfinite(out[0].asnumpy()).all() and out[1].shape == (2, 32)
+
+
+def test_moe_dispatch_combine_identity():
+    """combine(dispatch(x)) with gate 1 and enough capacity returns x for kept tokens."""
+    T, d, E = 64, 8, 4
+    xv = f32(T, d)
+    idx = R.randint(0, E, T).astype(np.float32)
+    onehot = np.eye(E, dtype=np.float32)[idx.astype(int)]
+    loc = ((np.cumsum(onehot, 0) - 1) * onehot).sum(1).astype(np.float32)
+    x = ht.Variable('x', value=xv)
+    i, l = ht.Variable('i', value=idx, trainable=False), ht.Variable('l', value=loc, trainable=False)
+    g = ht.Variable('g', value=np.ones(T, np.float32), trainable=False)
+    disp = ht.layout_transform_op(x, [i], [l], T, E)
+    back = ht.reverse_layout_transform_op(disp, [i], [l], [g], T, E)
+    ex = ht.Executor([back], ctx=ht.cpu(0))
+    np.testing.assert_allclose(ex.run()[0].asnumpy(), xv)
+
+
+def test_wdl_trains_on_cpu():
+    from hetu_61a7_b200.models.ctr import wdl_criteo
+    dense, sparse, y_ = ht.Variable('dense'), ht.Variable('sparse'), ht.Variable('y_')
+    loss, pred, _, train = wdl_criteo(dense, sparse, y_, feature_dimension=1000, learning_rate=0.5)
+    ex = ht.Executor({'train': [loss, pred, train]}, ctx=ht.cpu(0), seed=1)
+    d, s, l = ht.data.criteo_synthetic(64, vocab=1000, seed=1)
+    losses = [float(ex.run('train', feed_dict={dense: d, sparse: s.astype(np.float32), y_: l})[0].asnumpy())
+              for _ in range(30)]
+    assert losses[-1] < losses[0]
+
+
+def test_context_and_device_group():
+    g = ht.DeviceGroup(['cpu:0', 'gpu:0', 'gpu:1'])
+    assert g.worker_num == 2 and g.server_num == 1 and not g.is_mp
+    g2 = ht.DeviceGroup([(ht.gpu(0), ht.gpu(1)), (ht.gpu(2), ht.gpu(3))])
+    assert g2.worker_num == 2 and g2.is_mp and g2.mp_dev_num == 2
+    with ht.context([ht.gpu(0), ht.gpu(1)]):
+        n = ht.Variable('ctxvar', value=np.zeros(1, np.float32))
+    assert n.raw_ctx.worker_num == 2
+    r = ht.DeviceGroup('node1:gpu:3')
+    assert not r.workers[0].local and r.workers[0].device_id == 3
+
+
+def test_metrics_tokenizer():
+    y = (R.rand(500) > 0.5).astype(np.float32)
+    p = np.clip(y * 0.6 + R.rand(500) * 0.5, 0, 1)
+    a1, a2 = ht.metrics.auc(p, y), ht.metrics.roc_auc_exact(p, y)
+    assert abs(a1 - a2) < 0.02 and a2 > 0.8
+    vocab = ['[PAD]', '[UNK]', '[CLS]', '[SEP]', 'hello', 'world', '##s', ',']
+    tok = ht.BertTokenizer(vocab=vocab)
+    assert tok.tokenize('Hello, worlds foo') == ['hello', ',', 'world', '##s', '[UNK]']
+    ids, types, mask = tok.encode('hello world', 'hello', max_seq_length=8)
+    assert ids[:6] == [2, 4, 5, 3, 4, 3] and sum(mask) == 6 and types[4] == 1
