@@ -1,0 +1,137 @@
+/* hetu_b200.h - C ABI of libhetu_b200.so (hand-written sm_100a kernels).
+ *
+ * Every function returns 0 on success; on failure a message is available from
+ * hetu_last_error().  All pointers are device pointers unless noted; `s` is the
+ * CUDA stream to launch on.  Tensors are dense row-major fp32 unless noted; row ids
+ * are passed with an `idx_code` (0 = float32-encoded like the reference, 1 = int32,
+ * 2 = int64).  The comment above each group names the reference code it replaces
+ * (paths under the Hetu tree, /root/reference).
+ */
+#ifndef HETU_B200_H_
+#define HETU_B200_H_
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- runtime ------------------------------------------------------------------ */
+const char* hetu_last_error(void);
+int hetu_version(void);
+/* *p += 1 on the device (step counters read by dropout / Adam; graph-capturable). */
+int hetu_increment_i64(void* p, cudaStream_t s);
+
+/* ---- element-wise: reference src/ops/{Abs,AddConst,...,Where}.cu ---------------- */
+int hetu_unary(int op, const float* x, float* y, size_t n, float a, float b, cudaStream_t s);
+int hetu_binary(int op, const float* x, const float* y, float* o, size_t n, float a, cudaStream_t s);
+/* mode 0: y[inner] broadcast over rows (bias); mode 1: y[outer] broadcast along each row. */
+int hetu_binary_bcast(int op, const float* x, const float* y, float* o, size_t n, size_t inner, int mode, cudaStream_t s);
+int hetu_where(const float* c, const float* a, const float* b, float* o, size_t n, cudaStream_t s);
+/* generic strided copy (transpose/slice/concat/pad/broadcast): reference
+ * src/ops/{Transpose,Slice,Concat,Concatenate,Pad,Broadcast,BroadcastShape}.cu */
+int hetu_strided_copy(const float* src, float* dst, int nd, const long long* shape, const long long* ss,
+                      const long long* ds, size_t n, cudaStream_t s);
+int hetu_one_hot(const float* idx, float* out, size_t n, int classes, cudaStream_t s); /* OneHot.cu */
+
+/* ---- reductions: ReduceSum.cu ReduceMean.cu ReduceSumAxisZero.cu Max.cu Min.cu
+ *      Argmax.cu TopKIdx.cu TopKVal.cu CumSum.cu -------------------------------------- */
+int hetu_reduce_mid(const float* x, float* out, size_t A, size_t R, size_t B, int mode, cudaStream_t s);
+int hetu_argmax_rows(const float* x, float* out, size_t rows, size_t cols, cudaStream_t s);
+int hetu_topk_rows(const float* x, float* idx, float* val, size_t rows, size_t cols, int k, cudaStream_t s);
+int hetu_cumsum_cols(const float* x, float* out, size_t T, size_t E, float bias, cudaStream_t s);
+
+/* ---- GEMM (tcgen05 + TMA; FFMA fallback): MatrixMult.cu Linear.cu Addmm.cu
+ *      BatchMatrixMult.cu Baddbmm.cu (cublasSgemm*) ; CSR SpMM: CuSparseCsrmm.cu --------
+ * C = act(alpha * op(A) op(B) + beta * C + bias); mode 0 = tf32 tensor cores when
+ * eligible, 1 = exact fp32 FFMA; act 0 none, 1 relu, 2 gelu, 3 sigmoid. */
+int hetu_gemm(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, int transA,
+              int transB, int batch, long long sA, long long sB, long long sC, float alpha, float beta, int act,
+              int mode, cudaStream_t s);
+int hetu_csr_spmm(const float* val, const int* rowptr, const int* colidx, const float* dense, float* out,
+                  int nrow, int n, int trans, cudaStream_t s);
+
+/* ---- NN: CudnnSoftmax.cu Softmax.cu LayerNorm.cu InstanceNorm2d.cu CudnnBn.cu Dropout.cu
+ *      Conv2d.cu (im2col) CudnnConv2d.cu MaxPool.cu AvgPool.cu Cudnn{Max,Avg}Pool.cu ------ */
+int hetu_softmax_rows(const float* x, float* y, int rows, int cols, cudaStream_t s);
+int hetu_softmax_grad_rows(const float* y, const float* dy, float* dx, int rows, int cols, cudaStream_t s);
+int hetu_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean, float* rstd,
+                       int rows, int cols, float eps, cudaStream_t s);
+int hetu_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                       float* dx, float* dgamma, float* dbeta, int rows, int cols, cudaStream_t s);
+int hetu_batchnorm_fwd(const float* x, const float* gamma, const float* beta, float* y, float* run_mean,
+                       float* run_var, float* save_mean, float* save_rstd, int N, int C, int HW, float momentum,
+                       float eps, int inference, cudaStream_t s);
+int hetu_batchnorm_bwd(const float* dy, const float* x, const float* gamma, const float* save_mean,
+                       const float* save_rstd, float* dx, float* dgamma, float* dbeta, int N, int C, int HW,
+                       cudaStream_t s);
+int hetu_dropout(const float* x, float* y, size_t n, float p, unsigned long long seed, const void* step, cudaStream_t s);
+int hetu_im2col(const float* x, float* col, int N, int C, int H, int W, int kh, int kw, int ph, int pw, int sh,
+                int sw, int OH, int OW, cudaStream_t s);
+int hetu_col2im(const float* col, float* x, int N, int C, int H, int W, int kh, int kw, int ph, int pw, int sh,
+                int sw, int OH, int OW, cudaStream_t s);
+int hetu_pool2d_fwd(const float* x, float* y, int NC, int H, int W, int kh, int kw, int pad, int stride, int OH,
+                    int OW, int is_max, cudaStream_t s);
+int hetu_pool2d_bwd(const float* x, const float* y, const float* dy, float* dx, int NC, int H, int W, int kh, int kw,
+                    int pad, int stride, int OH, int OW, int is_max, cudaStream_t s);
+
+/* ---- losses: SoftmaxCrossEntropy.cu CudnnSoftmaxEntropy.cu SoftmaxCrossEntropySparse.cu
+ *      BinaryCrossEntropy.cu ------------------------------------------------------------ */
+int hetu_softmax_xent(const float* x, const float* y, float* loss, int rows, int cols, cudaStream_t s);
+int hetu_softmax_xent_grad(const float* x, const float* y, const float* g, float* dx, int rows, int cols, cudaStream_t s);
+int hetu_softmax_xent_sparse(const float* x, const float* lab, float* loss, int rows, int cols, int ignored, cudaStream_t s);
+int hetu_softmax_xent_sparse_grad(const float* x, const float* lab, const float* g, float* dx, int rows, int cols,
+                                  int ignored, cudaStream_t s);
+int hetu_bce(const float* p, const float* y, float* o, size_t n, cudaStream_t s);
+int hetu_bce_grad(const float* p, const float* y, const float* g, float* o, size_t n, cudaStream_t s);
+
+/* ---- embedding + sparse optimizers: EmbeddingLookup.cu OptimizersSparse.cu IndexedSlices.cu;
+ *      the *_sharded variants replace the PS SparsePull / SparsePush RPCs
+ *      (ps-lite/include/ps/server/PSFHandle.h:101-164) with NVLink peer loads / red.adds ---- */
+int hetu_gather_rows(const float* table, const void* idx, int idx_code, float* out, size_t n, int width,
+                     size_t vocab, cudaStream_t s);
+int hetu_gather_rows_sharded(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code,
+                             float* out, size_t n, int width, size_t vocab, cudaStream_t s);
+int hetu_dedup_sorted_rows(const void* sidx, const void* perm, const float* vals, void* didx, float* dval, size_t n,
+                           int width, cudaStream_t s);
+int hetu_sparse_opt(int kind, float* param, const void* idx, const float* grad, float* s1, float* s2, size_t n,
+                    int width, const float* lr_p, const void* step_p, float h0, float h1, float h2, float h3,
+                    float l2reg, int use_atomic, cudaStream_t s);
+int hetu_sparse_sgd_sharded(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code,
+                            const float* grad, size_t n, int width, size_t vocab, const float* lr_p, float scale,
+                            cudaStream_t s);
+int hetu_scatter_add_rows(float* dense, const void* idx, int idx_code, const float* vals, size_t n, int width,
+                          size_t vocab, cudaStream_t s);
+
+/* ---- dense optimizers, all tensors in one launch: Optimizers.cu ------------------------
+ * kind: 0 SGD 1 Momentum 2 Nesterov 3 AdaGrad 4 Adam 5 AdamW 6 Lamb.  The pointer arrays are
+ * HOST arrays of device pointers (<= 48 entries).  Lamb needs `scratch`: 2 floats per tensor of
+ * device memory, zeroed by the caller, for the parameter / update norms. */
+int hetu_multi_tensor_opt(int kind, int ntensors, void* const* params, void* const* grads, void* const* s1,
+                          void* const* s2, const long long* sizes, const float* lr_p, const void* step_p, float h0,
+                          float h1, float h2, float h3, float l2reg, float* scratch, cudaStream_t s);
+
+/* ---- MoE layout transforms: LayoutTransform.cu; *_peer: AllToAll fused with the transform
+ *      (python/hetu/gpu_ops/AllToAll.py:13-29 + mpi_nccl_communication.cu:245-277) --------- */
+int hetu_moe_dispatch(const float* x, void* const* idx, void* const* loc, void* const* gate, int k, int has_gate,
+                      float* out, int T, int d, int capacity, int total_experts, cudaStream_t s);
+int hetu_moe_combine(const float* y, void* const* idx, void* const* loc, void* const* gate, int k, int has_gate,
+                     float* out, int T, int d, int capacity, int rows, cudaStream_t s);
+int hetu_moe_gate_grad(const float* dout, const float* y, const float* idx, const float* loc, float* out, int T,
+                       int d, int capacity, int rows, cudaStream_t s);
+int hetu_moe_dispatch_peer(const float* x, void* const* idx, void* const* loc, void* const* gate, int k,
+                           int has_gate, void* const* peer_bases, int world, int rank, int T, int d, int capacity,
+                           int e_local, cudaStream_t s);
+int hetu_moe_combine_peer(void* const* idx, void* const* loc, void* const* gate, int k, int has_gate,
+                          void* const* peer_bases, int world, int rank, float* out, int T, int d, int capacity,
+                          int e_local, cudaStream_t s);
+
+/* ---- parameter initialisation: Initializers.cu ------------------------------------------
+ * kind 0 constant(a) 1 uniform[a,b) 2 normal(mean a, std b) 3 truncated normal (|z| <= 2). */
+int hetu_init_random(float* out, size_t n, int kind, float a, float b, unsigned long long seed, cudaStream_t s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HETU_B200_H_ */

@@ -125,7 +125,7 @@ def test_gemm_fp32_mode_and_epilogue(L):
     a, b, bias = rnd(512, 256), rnd(256, 384, seed=1), rnd(384, seed=2)
     out = gemm(a, b, bias=bias, act=ACT_RELU)
     ref = torch.relu(a @ b + bias)
-    assert (out - ref).abs().max().item() < 0.05
+    assert (out - ref).abs().max().item() / ref.abs().max().item() < 2e-3      # tf32 operands
 
 
 def test_gemm_batched(L):
