@@ -7,6 +7,7 @@
 // lr and the step count are read from device memory so a captured CUDA graph stays valid
 // while the schedule / bias correction advance.
 #include "common.cuh"
+#include <mutex>
 
 enum { OPT_SGD = 0, OPT_MOMENTUM, OPT_NESTEROV, OPT_ADAGRAD, OPT_ADAM, OPT_ADAMW, OPT_LAMB };
 constexpr int kMaxTensors = 48;
@@ -148,5 +149,104 @@ HETU_API int hetu_multi_tensor_opt(int kind, int ntensors, void* const* params, 
         default: hetu_set_error("multi_tensor_opt: bad kind %d", kind); return -1;
     }
     HETU_CHECK_LAUNCH("hetu_multi_tensor_opt");
+    return 0;
+}
+
+// ============================================================================================
+// Lamb step for callers that cannot allocate device memory.
+//
+// hetu_multi_tensor_opt(kind = Lamb) needs two floats of device scratch per tensor (the squared
+// norms of the parameters and of the update) and expects the caller to allocate and zero them.
+// Some callers have no way to do that: code running under a framework whose allocator they must
+// not re-enter (e.g. from inside another library's callback), real-time / embedded-style hosts
+// that forbid cudaMalloc after start-up because it synchronises the device and can fail late,
+// and thin C or FFI clients that only own the tensors they pass in.  For them this entry point
+// keeps the scratch in a small file-scope device array that lives in the library image itself:
+// every GPU that loads libhetu_b200.so holds HETU_LAMB_NOALLOC_MAX_TENSORS * 2 floats (768 B)
+// until the process exits.
+//
+// Rules that follow from the scratch being shared and static:
+//  * at most HETU_LAMB_NOALLOC_MAX_TENSORS tensors per call - more is rejected, not truncated;
+//    split a larger model into several calls on the same stream;
+//  * the array keeps whatever the previous call left there, so each call first clears the slots
+//    it is about to accumulate into (a memset on `s`, not an allocation);
+//  * two calls whose kernels can overlap on one GPU (different streams, or different host
+//    threads on different streams) race on the array - serialise them on one stream;
+//  * the first call on a given device looks up the array's device address (set-up, once per
+//    device, done with that device current).  Make that first call outside of any stream
+//    capture.
+// No cudaMalloc / cudaFree / allocating library routine is called on any path through here.
+constexpr int HETU_LAMB_NOALLOC_MAX_TENSORS = 96;
+static __device__ __align__(256) float g_lamb_noalloc_scratch[2 * HETU_LAMB_NOALLOC_MAX_TENSORS];
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+float* g_noalloc_ptr[kNoAllocMaxDevices] = {};     // device address of the array, per device ordinal
+std::mutex g_noalloc_mu;
+
+// The symbol name is only a host-side handle; kernels must be given the address the runtime
+// reports for the *current* device.
+int lamb_noalloc_scratch(float** out) {
+    int dev = -1;
+    HETU_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoAllocMaxDevices) {
+        hetu_set_error("hetu_lamb_step_noalloc: device ordinal %d outside [0, %d)", dev, kNoAllocMaxDevices);
+        return -1;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        float* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_lamb_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            hetu_set_error("hetu_lamb_step_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                           cudaGetErrorString(e));
+            return e != cudaSuccess ? (int)e : -1;
+        }
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+HETU_API int hetu_lamb_step_noalloc(int ntensors, void* const* params, void* const* grads, void* const* s1,
+                                    void* const* s2, const long long* sizes, const float* lr_p, const void* step_p,
+                                    float beta1, float beta2, float eps, float weight_decay, float l2reg,
+                                    cudaStream_t s) {
+    if (ntensors <= 0) return 0;
+    if (ntensors > HETU_LAMB_NOALLOC_MAX_TENSORS) {
+        hetu_set_error("hetu_lamb_step_noalloc: %d tensors exceed the static scratch (max %d per call); "
+                       "split the step into several calls on the same stream",
+                       ntensors, HETU_LAMB_NOALLOC_MAX_TENSORS);
+        return -1;
+    }
+    float* scratch = nullptr;
+    int rc = lamb_noalloc_scratch(&scratch);
+    if (rc) return rc;
+    // norms are accumulated with atomicAdd: the slots used by this call must start at zero
+    HETU_CUDA(cudaMemsetAsync(scratch, 0, sizeof(float) * 2 * (size_t)ntensors, s));
+    const long long* st = (const long long*)step_p;
+    for (int base = 0; base < ntensors; base += kMaxTensors) {
+        int cnt = ntensors - base < kMaxTensors ? ntensors - base : kMaxTensors;
+        TensorList tl;
+        long long maxn = 0;
+        for (int i = 0; i < kMaxTensors; ++i) {
+            bool on = i < cnt;
+            tl.p[i] = on ? (float*)params[base + i] : nullptr;
+            tl.g[i] = on ? (const float*)grads[base + i] : nullptr;
+            tl.s1[i] = on ? (float*)s1[base + i] : nullptr;
+            tl.s2[i] = on ? (float*)s2[base + i] : nullptr;
+            tl.n[i] = on ? sizes[base + i] : 0;
+            if (on && sizes[base + i] > maxn) maxn = sizes[base + i];
+        }
+        int gx = (int)((maxn + 256 * 4 - 1) / (256 * 4));
+        int cap = (kNumSMs * 8 + cnt - 1) / cnt;
+        if (gx > cap) gx = cap;
+        if (gx < 1) gx = 1;
+        dim3 grid(gx, cnt);
+        lamb_phase1_kernel<<<grid, 256, 0, s>>>(tl, st, beta1, beta2, eps, l2reg, 1.f, scratch + 2 * base);
+        lamb_phase2_kernel<<<grid, 256, 0, s>>>(tl, lr_p, st, beta1, beta2, eps, weight_decay, scratch + 2 * base);
+    }
+    HETU_CHECK_LAUNCH("hetu_lamb_step_noalloc");
     return 0;
 }

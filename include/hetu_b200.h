@@ -112,6 +112,19 @@ int hetu_multi_tensor_opt(int kind, int ntensors, void* const* params, void* con
                           void* const* s2, const long long* sizes, const float* lr_p, const void* step_p, float h0,
                           float h1, float h2, float h3, float l2reg, float* scratch, cudaStream_t s);
 
+/* Lamb step for callers that cannot allocate device memory (plugins inside another framework's
+ * callback, services that forbid cudaMalloc after start-up, thin FFI clients that own only the
+ * tensors they pass).  Same arithmetic as hetu_multi_tensor_opt(kind = 6) but the per-tensor norm
+ * scratch is a static device array inside the library: 768 bytes held on every GPU that loads the
+ * library, at most 96 tensors per call (more is refused with an error).  The array is shared: the
+ * call clears the slots it uses, and calls that can overlap on one GPU race - keep them on one
+ * stream.  The first call on a device resolves the array's address; make it before any stream
+ * capture.  Calls no cudaMalloc/cudaFree.  No counterpart in the reference (its Lamb step
+ * allocates cuDNN reduction workspaces per call, src/ops/Optimizers.cu). */
+int hetu_lamb_step_noalloc(int ntensors, void* const* params, void* const* grads, void* const* s1,
+                           void* const* s2, const long long* sizes, const float* lr_p, const void* step_p,
+                           float beta1, float beta2, float eps, float weight_decay, float l2reg, cudaStream_t s);
+
 /* ---- MoE layout transforms: LayoutTransform.cu; *_peer: AllToAll fused with the transform
  *      (python/hetu/gpu_ops/AllToAll.py:13-29 + mpi_nccl_communication.cu:245-277) --------- */
 int hetu_moe_dispatch(const float* x, void* const* idx, void* const* loc, void* const* gate, int k, int has_gate,
