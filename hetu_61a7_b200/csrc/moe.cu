@@ -215,3 +215,36 @@ HETU_API int hetu_moe_combine_peer(void* const* idx, void* const* loc, void* con
     HETU_CHECK_LAUNCH("hetu_moe_combine_peer");
     return 0;
 }
+
+// d gate_j[t] = < dout[t, :], y[route_j(t)] > with the expert output row read from its owner GPU
+__global__ void __launch_bounds__(256) moe_gate_grad_peer_kernel(const float* __restrict__ dout, const float* __restrict__ idx,
+                                                                 const float* __restrict__ loc, PeerBufs pb,
+                                                                 float* __restrict__ out, int T, int d, int capacity,
+                                                                 int e_local) {
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    int nwarp = (gridDim.x * blockDim.x) >> 5;
+    int total = e_local * pb.world;
+    for (int t = warp; t < T; t += nwarp) {
+        float fi = idx[t], fl = loc[t];
+        int e = (int)fi, slot = (int)fl;
+        float acc = 0.f;
+        if (fi >= 0.f && fl >= 0.f && slot < capacity && e < total) {
+            const float* row = pb.base[e / e_local] + ((((size_t)(e % e_local)) * pb.world + pb.rank) * capacity + slot) * d;
+            for (int c = lane; c < d; c += 32) acc += dout[(size_t)t * d + c] * row[c];
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) out[t] = acc;
+    }
+}
+HETU_API int hetu_moe_gate_grad_peer(const float* dout, const float* idx, const float* loc, void* const* peer_bases,
+                                     int world, int rank, float* out, int T, int d, int capacity, int e_local,
+                                     cudaStream_t s) {
+    if (T == 0) return 0;
+    if (world > kMaxPeers) { hetu_set_error("moe_gate_grad_peer: world %d > %d", world, kMaxPeers); return -1; }
+    PeerBufs pb;
+    pb.world = world; pb.rank = rank;
+    for (int i = 0; i < kMaxPeers; ++i) pb.base[i] = i < world ? (float*)peer_bases[i] : nullptr;
+    moe_gate_grad_peer_kernel<<<ew_grid((size_t)T * 32, 256, 16), 256, 0, s>>>(dout, idx, loc, pb, out, T, d, capacity, e_local);
+    HETU_CHECK_LAUNCH("hetu_moe_gate_grad_peer");
+    return 0;
+}

@@ -215,6 +215,7 @@ class HetuConfig(object):
         self.nccl_stream = Stream(self.context) if on_cuda and self.nccl_comm is not None else None
         self.p2p_stream = Stream(self.context) if on_cuda and (pipeline or context_launch) else None
 
+        self.bsp = bsp
         self.use_sparse_pull = use_sparse_pull if self.comm_mode in ('PS', 'Hybrid') else False
         self.cstable_policy = cstable_policy if self.comm_mode in ('PS', 'Hybrid') else None
         self.prefetch = prefetch if self.comm_mode in ('PS', 'Hybrid') else False

@@ -256,7 +256,7 @@ class MoELayer(BaseLayer):
 
     def __init__(self, gate=None, experts=None, num_tokens=None, embed_dim=None, all2all_size=None,
                  name='MoELayer', device_id=None, top=None, k=None, num_local_gpus=8,
-                 hierarchical=None):
+                 hierarchical=None, fused=None):
         self.name, self.gate, self.experts = name, gate, experts
         self.num_local_experts = len(experts)
         self.num_tokens, self.embed_dim = num_tokens, embed_dim
@@ -265,6 +265,11 @@ class MoELayer(BaseLayer):
         self.top = top if top is not None else k
         self.num_local_gpus = num_local_gpus
         self.hierarchical = hierarchical
+        # fused peer-store dispatch/combine (ops/moe_fused.py) unless the NCCL baseline is requested
+        if fused is None:
+            import os
+            fused = os.environ.get('HETU_MOE_FUSED', '1') == '1' and hierarchical is None
+        self.fused = fused and name != 'BalanceAssignmentLayer'
         if name == 'BalanceAssignmentLayer':
             self.arange_array = Variable(value=np.arange(num_tokens).astype(np.float32),
                                          name='arange_array', trainable=False)
@@ -298,6 +303,21 @@ class MoELayer(BaseLayer):
             l_aux, extra, indices_s, location_s, gates_s, capacity = self.gate(reshaped)
         else:
             l_aux, indices_s, location_s, gates_s, capacity = self.gate(reshaped)
+        if self.fused:
+            from ..ops.moe_fused import fused_moe_dispatch_op, fused_moe_combine_op
+            E, W = self.num_local_experts, self.all2all_size
+            recv = fused_moe_dispatch_op(reshaped, indices_s, location_s, capacity, E, W)
+            outs = []
+            for i in range(E):
+                tok = ht.split_op(recv, axes=[0], indices=[i], splits=[E])          # contiguous slab: a view
+                outs.append(ht.array_reshape_op(self.experts[i](tok), [1, W, -1, self.embed_dim]))
+            y = ht.concatenate_op(outs, axis=0) if E > 1 else outs[0]
+            out = fused_moe_combine_op(y, indices_s, location_s, capacity, E, W, gates=gates_s)
+            if gates_s is None:
+                return out
+            if extra is not None:
+                return out, l_aux, extra
+            return out, l_aux
         dispatched = ht.layout_transform_op(reshaped, indices_s, location_s, capacity, total)
         dispatched = self._a2a(dispatched)
         y = self._experts(dispatched)

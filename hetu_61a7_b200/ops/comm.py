@@ -67,7 +67,7 @@ class AllReduceCommunicateOp(_CommOp):
             return v
         eng = _symm_engine(self)
         if eng is not None and v.is_cuda and v.dtype == torch.float32:
-            return eng.allreduce(v)
+            return eng.allreduce(v, key=('op', self.id))
         out = v.clone()
         comm.allreduce(out)
         return out
@@ -102,7 +102,7 @@ class AllGatherCommunicateOp(_CommOp):
             return torch.empty((v.shape[0] * comm.nrank,) + tuple(v.shape[1:]), device='meta')
         eng = _symm_engine(self)
         if eng is not None and comm.multi and v.is_cuda and v.dtype == torch.float32:
-            return eng.allgather(v)
+            return eng.allgather(v, key=('op', self.id))
         return comm.allgather(v)
 
     def gradient(self, g):
@@ -126,7 +126,7 @@ class ReduceScatterCommunicateOp(_CommOp):
             return torch.empty((v.shape[0] // comm.nrank,) + tuple(v.shape[1:]), device='meta')
         eng = _symm_engine(self)
         if eng is not None and comm.multi and v.is_cuda and v.dtype == torch.float32:
-            return eng.reducescatter(v)
+            return eng.reducescatter(v, key=('op', self.id))
         return comm.reducescatter(v)
 
     def gradient(self, g):
@@ -188,7 +188,7 @@ class AllToAllOp(_CommOp):
             return v
         eng = _symm_engine(self)
         if eng is not None and v.is_cuda and v.dtype == torch.float32:
-            return eng.alltoall(v)
+            return eng.alltoall(v, key=('op', self.id))
         return comm.alltoall(v.contiguous())
 
     def gradient(self, g):
@@ -217,7 +217,7 @@ class HAllToAllOp(_CommOp):
             'halltoall: num_nodes*num_local_gpus must equal the group size'
         eng = _symm_engine(self)
         if eng is not None and v.is_cuda and v.dtype == torch.float32:
-            return eng.alltoall(v)
+            return eng.alltoall(v, key=('op', self.id))
         return comm.alltoall(v.contiguous())
 
     def gradient(self, g):

@@ -36,6 +36,7 @@ class PlaceholderOp(Op):
         self.parts = {}
         self.cur_part = {}
         self.ps_resident = False
+        self.sharded = False
 
     @property
     def is_feed(self) -> bool:
@@ -68,6 +69,17 @@ class PlaceholderOp(Op):
             self.event = (_stream.CSEvent(config.ps_comm, self.id)
                           if config.cstable_policy is not None and self.is_embed
                           else _stream.PSEvent(config.ps_comm, self.id))
+            return
+        from ..parallel.sharded_embedding import should_shard, ShardedTable
+        if should_shard(self, config) and self.shape is not None and len(self.shape) == 2:
+            table = ShardedTable(config.symm, self.shape, self.initializer, config.seed + self.id,
+                                 name='%s_%d' % (self.name, self.id), bsp=config.bsp)
+            if self.initializer is None and self.tensor_value is not None:
+                tv = self.tensor_value
+                table.import_dense(tv.asnumpy() if isinstance(tv, NDArray) else tv)
+            self.initializer = None
+            self.tensor_value = table
+            self.sharded = True
             return
         if self.initializer is not None:
             self.initializer(self, config.seed, config.np_rand, config.comp_stream)

@@ -429,9 +429,11 @@ class OptimizerOp(Op):
                 if config.ps_comm is not None:
                     from .ops.ps_ops import parameterServerCommunicate_op
                     cur_node = parameterServerCommunicate_op(node, cur_param, self.optimizer.get_config())
-                elif config.nccl_comm is not None and config.nccl_comm.multi and not getattr(
-                        cur_param, 'sharded', False):
-                    cur_node = allreduceCommunicate_op(node, config.nccl_comm)
+                else:
+                    from .parallel.sharded_embedding import should_shard
+                    if config.nccl_comm is not None and config.nccl_comm.multi and not (
+                            getattr(cur_param, 'sharded', False) or should_shard(cur_param, config)):
+                        cur_node = allreduceCommunicate_op(node, config.nccl_comm)
             new_inputs.append(cur_node)
         self.inputs = new_inputs
         if fused_ids:

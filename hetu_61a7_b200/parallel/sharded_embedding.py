@@ -1,0 +1,104 @@
+"""GPU-sharded embedding table over the NVSwitch domain.
+
+reference: embeddings live in host DRAM behind ps-lite; every step the worker pulls rows
+(SparsePull / HET cache ``embedding_lookup``), copies them H2D, and pushes ``-lr * grad``
+back (``SparsePush``; server does ``+=``) - python/hetu/gpu_ops/ParameterServerCommunicate.py:
+38-57, ps-lite/include/ps/server/PSFHandle.h:101-164.
+
+Here row ``r`` lives in the HBM of GPU ``r % world`` at local row ``r // world`` inside a
+CUDA-IPC symmetric buffer.  The lookup kernel reads rows straight from the owner over
+NVLink (``hetu_gather_rows_sharded``); the update kernel adds ``-lr * grad`` into the owner's
+rows with remote atomics (``hetu_sparse_sgd_sharded``) - the PS pull, push and server-side
+``+=`` are one kernel each, with ASP semantics by default and BSP when ``bsp == 0``
+(a cross-GPU barrier after the update).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .. import _lib as L
+from ..ops.embedding import _IDX_CODE
+
+
+def should_shard(node, config) -> bool:
+    if not (getattr(node, 'is_embed', False) and node.trainable and config.symm is not None):
+        return False
+    if config.ps_comm is not None:
+        return False
+    strategy = config.node_strategy.get(node, config.comm_mode)
+    return strategy in ('Hybrid', 'PS') or config.comm_mode in ('Hybrid', 'PS')
+
+
+class ShardedTable(object):
+    sharded = True
+
+    def __init__(self, engine, shape, initializer, seed, name='embedding', bsp=-1):
+        self.engine = engine
+        self.shape = tuple(shape)
+        self.vocab, self.width = int(shape[0]), int(shape[1])
+        self.world, self.rank = engine.world, engine.rank
+        self.local_rows = (self.vocab + self.world - 1) // self.world
+        self.bsp = bsp
+        self.name = name
+        nbytes = self.local_rows * self.width * 4
+        self.buf = engine.buffer(('embed', name), nbytes)
+        self.local = self.buf.tensor(numel=self.local_rows * self.width).view(self.local_rows, self.width)
+        self.device = engine.device
+        self.dtype = torch.float32
+        if initializer is not None:
+            a, b = initializer.args()
+            L.call('init_random', L.p(self.local), L.c_sz(self.local.numel()), L.c_int(initializer.kind),
+                   L.c_f32(a), L.c_f32(b), L.c_u64((seed * 1000003 + self.rank) & 0xFFFFFFFFFFFFFFFF),
+                   L.stream_ptr(self.device))
+        torch.cuda.synchronize(self.device)
+        engine.comm.barrier()
+
+    def numel(self):
+        return self.vocab * self.width
+
+    def lookup(self, idx: torch.Tensor) -> torch.Tensor:
+        if idx.device.type == 'meta':
+            return torch.empty(tuple(idx.shape) + (self.width,), device='meta')
+        idx = idx.contiguous()
+        if idx.dtype not in _IDX_CODE:
+            idx = idx.long()
+        out = torch.empty(tuple(idx.shape) + (self.width,), dtype=torch.float32, device=self.device)
+        L.call('gather_rows_sharded', self.buf.ptrs, L.c_int(self.world), L.p(idx), L.c_int(_IDX_CODE[idx.dtype]),
+               L.p(out), L.c_sz(idx.numel()), L.c_int(self.width), L.c_sz(self.vocab), L.stream_ptr(self.device))
+        return out
+
+    def apply_sparse_grad(self, ind: torch.Tensor, val: torch.Tensor, optimizer) -> None:
+        from ..optimizer import OPT_SGD
+        if optimizer.kind != OPT_SGD:
+            raise NotImplementedError('sharded embedding tables are updated with SGD (the reference PS '
+                                      'applies "+=" of -lr*grad as well); got %s' % optimizer.name)
+        ind = ind.contiguous()
+        L.call('sparse_sgd_sharded', self.buf.ptrs, L.c_int(self.world), L.p(ind), L.c_int(_IDX_CODE[ind.dtype]),
+               L.p(val.contiguous()), L.c_sz(ind.numel()), L.c_int(self.width), L.c_sz(self.vocab),
+               L.p(optimizer.lr_t), L.c_f32(1.0), L.stream_ptr(self.device))
+        if self.bsp == 0:
+            self.engine.barrier()
+
+    # -- checkpointing ---------------------------------------------------------------------------
+    def export_dense(self) -> torch.Tensor:
+        """Full table on the host (rows fetched through the same peer-gather kernel, in chunks)."""
+        out = torch.empty((self.vocab, self.width), dtype=torch.float32)
+        step = 1 << 20
+        for s in range(0, self.vocab, step):
+            ids = torch.arange(s, min(self.vocab, s + step), device=self.device)
+            out[s:s + ids.numel()] = self.lookup(ids).cpu()
+        return out
+
+    def import_dense(self, value) -> None:
+        v = torch.as_tensor(np.asarray(value), dtype=torch.float32)
+        mine = v[self.rank::self.world]
+        self.local[:mine.shape[0]].copy_(mine.to(self.device))
+        torch.cuda.synchronize(self.device)
+        self.engine.comm.barrier()
+
+    def detach(self):
+        return self
+
+    def cpu(self):
+        return self.export_dense()

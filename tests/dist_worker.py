@@ -1,0 +1,145 @@
+"""Multi-process worker used by test_distributed.py (launched with torch.distributed.run).
+mode 'cpu'  : gloo, host-side logic (comm ops, DP all-reduce equivalence, PS-free paths)
+mode 'gpu'  : nccl + symmetric heap: in-kernel collectives vs NCCL, fused DP update, sharded
+              embedding, fused MoE dispatch/combine."""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import hetu as ht                                                     # noqa: E402
+from hetu_61a7_b200.parallel.comm import world                       # noqa: E402
+
+mode = sys.argv[1]
+if mode == 'cpu':
+    os.environ['HETU_COMM_BACKEND'] = 'gloo'
+comm = ht.wrapped_mpi_nccl_init()
+rank, nrank = comm.rank, comm.nrank
+gpu = mode == 'gpu'
+dev = torch.device('cuda', torch.cuda.current_device()) if gpu else torch.device('cpu')
+ctx = ht.gpu(dev.index) if gpu else ht.cpu(0)
+
+
+def log(*a):
+    if rank == 0:
+        print(*a, flush=True)
+
+
+def check(name, a, b, rtol=1e-5, atol=1e-6):
+    torch.testing.assert_close(a, b, rtol=rtol, atol=atol, msg=lambda m: '%s: %s' % (name, m))
+    log('ok', name)
+
+
+# ---------------------------------------------------------------- raw collectives
+g = torch.Generator().manual_seed(rank)
+x = torch.randn(nrank * 64, 32, generator=g).to(dev)
+ref = x.clone(); comm.allreduce(ref)
+if gpu:
+    from hetu_61a7_b200.parallel.symm import SymmEngine
+    eng = SymmEngine.get(comm)
+    assert eng is not None, 'symmetric heap must come up on a multi-GPU box'
+    for it in range(3):
+        check('symm allreduce %d' % it, eng.allreduce(x, key='t_ar'), ref, rtol=1e-5, atol=1e-5)
+    check('symm allgather', eng.allgather(x, key='t_ag').clone(), comm.allgather(x))
+    check('symm reducescatter', eng.reducescatter(x, key='t_rs'), comm.reducescatter(x), rtol=1e-5, atol=1e-5)
+    check('symm alltoall', eng.alltoall(x, key='t_a2a').clone(), comm.alltoall(x))
+    big = torch.randn(nrank * 4096, 512, generator=g).to(dev)
+    check('symm alltoall big', eng.alltoall(big, key='t_a2ab').clone(), comm.alltoall(big))
+    refb = big.clone(); comm.allreduce(refb)
+    check('symm allreduce big', eng.allreduce(big, key='t_arb'), refb, rtol=1e-4, atol=1e-4)
+
+
+# ---------------------------------------------- data-parallel equivalence (graph level)
+def build_mlp(seed_data):
+    rng = np.random.RandomState(0)
+    W1 = ht.Variable('W1', value=(rng.randn(20, 32) * 0.1).astype(np.float32))
+    b1 = ht.Variable('b1', value=np.zeros(32, np.float32))
+    W2 = ht.Variable('W2', value=(rng.randn(32, 4) * 0.1).astype(np.float32))
+    x, y_ = ht.Variable('x'), ht.Variable('y_')
+    h = ht.relu_op(ht.linear_op(x, W1, b1))
+    loss = ht.reduce_mean_op(ht.softmaxcrossentropy_op(ht.matmul_op(h, W2), y_), [0])
+    return x, y_, loss, [W1, b1, W2]
+
+
+data_rng = np.random.RandomState(42)
+X = data_rng.randn(nrank * 16, 20).astype(np.float32)
+Y = np.eye(4, dtype=np.float32)[data_rng.randint(0, 4, nrank * 16)]
+for opt_name, mk in (('sgd', lambda: ht.optim.SGDOptimizer(0.1 / nrank)), ('adam', lambda: ht.optim.AdamOptimizer(0.01))):
+    for engine in (['nccl', 'symm'] if gpu else ['nccl']):
+        x, y_, loss, params = build_mlp(0)
+        # sum-all-reduce of per-shard mean losses == nrank * full-batch mean gradient
+        train = mk().minimize(loss)
+        ex = ht.Executor({'train': [loss, train]}, ctx=ctx, comm_mode='AllReduce', seed=1,
+                         use_nccl_collectives=(engine == 'nccl'))
+        sl = slice(rank * 16, (rank + 1) * 16)
+        for _ in range(5):
+            ex.run('train', feed_dict={x: X[sl], y_: Y[sl]})
+        got = [ex.config.placeholder_to_arr_map[p].detach().cpu() for p in params]
+        # oracle: single process, full batch, gradient scaled by nrank (sum of shard means)
+        tW1 = torch.tensor((np.random.RandomState(0).randn(20, 32) * 0.1).astype(np.float32), requires_grad=True)
+        rs = np.random.RandomState(0); w1 = (rs.randn(20, 32) * 0.1).astype(np.float32); w2 = (rs.randn(32, 4) * 0.1).astype(np.float32)
+        tW1 = torch.tensor(w1, requires_grad=True); tb1 = torch.zeros(32, requires_grad=True); tW2 = torch.tensor(w2, requires_grad=True)
+        topt = torch.optim.SGD([tW1, tb1, tW2], 0.1 / nrank) if opt_name == 'sgd' else torch.optim.Adam([tW1, tb1, tW2], 0.01, eps=1e-7)
+        for _ in range(5):
+            topt.zero_grad()
+            l = sum(torch.nn.functional.cross_entropy(torch.relu(torch.tensor(X[r * 16:(r + 1) * 16]) @ tW1 + tb1) @ tW2,
+                                                      torch.tensor(Y[r * 16:(r + 1) * 16]).argmax(1)) for r in range(nrank))
+            l.backward()
+            topt.step()
+        for a, b, n in zip(got, [tW1, tb1, tW2], ['W1', 'b1', 'W2']):
+            check('dp %s %s %s' % (opt_name, engine, n), a, b.detach(), rtol=2e-3, atol=2e-5)
+
+# -------------------------------------------------------- sharded embedding (hybrid)
+if gpu:
+    V, D = 1000, 16
+    table0 = np.random.RandomState(3).randn(V, D).astype(np.float32)
+    ids_all = np.random.RandomState(4).randint(0, V, (nrank, 8, 4))
+    emb = ht.Variable('emb', value=table0.copy())
+    idn = ht.Variable('ids')
+    w = ht.Variable('w_emb', value=np.ones((4 * D, 1), np.float32))
+    e = ht.array_reshape_op(ht.embedding_lookup_op(emb, idn), (-1, 4 * D))
+    loss = ht.reduce_mean_op(ht.reduce_sum_op(ht.mul_op(ht.matmul_op(e, w), ht.matmul_op(e, w)), [1]), [0])
+    train = ht.optim.SGDOptimizer(0.01).minimize(loss, var_list=[emb])
+    ex = ht.Executor({'train': [loss, train]}, ctx=ctx, comm_mode='Hybrid', seed=1, bsp=0)
+    tab = ex.config.placeholder_to_arr_map[emb]
+    assert getattr(tab, 'sharded', False), 'embedding must be sharded over the symmetric heap'
+    check('sharded lookup', tab.lookup(torch.arange(V, device=dev)).cpu(), torch.tensor(table0))
+    for step in range(3):
+        ex.run('train', feed_dict={idn: ids_all[rank].astype(np.float32)})
+    te = torch.tensor(table0.copy(), requires_grad=True)
+    for step in range(3):
+        te.grad = None
+        tot = 0
+        for r in range(nrank):
+            ee = te[torch.tensor(ids_all[r])].reshape(-1, 4 * D)
+            tot = tot + (ee.sum(1) ** 2).mean()
+        tot.backward()
+        with torch.no_grad():
+            te -= 0.01 * te.grad
+    check('sharded sgd (bsp)', tab.export_dense(), te.detach(), rtol=1e-3, atol=1e-4)
+
+# ------------------------------------------------------------------ MoE fused vs NCCL
+if gpu:
+    from hetu_61a7_b200.models.moe import moe_model
+    losses = {}
+    for fused in ('1', '0'):
+        os.environ['HETU_MOE_FUSED'] = fused
+        xx, tt = ht.Variable('x'), ht.Variable('t')
+        ht_loss, _ = moe_model(xx, tt, batch_size=2, num_tokens=64, model_dim=64, hidden_size=64,
+                               num_local_experts=2, world=nrank, rank=rank, top=2)
+        tr = ht.optim.SGDOptimizer(0.05).minimize(ht_loss)
+        ex = ht.Executor({'train': [ht_loss, tr]}, ctx=ctx, comm_mode='AllReduce', seed=5,
+                         use_nccl_collectives=(fused == '0'))
+        xv = np.random.RandomState(10 + rank).randn(2, 64, 64).astype(np.float32)
+        ls = []
+        for _ in range(4):
+            ls.append(float(ex.run('train', feed_dict={xx: xv, tt: np.zeros(2, np.float32)})[0].asnumpy().reshape(-1)[0]))
+        losses[fused] = ls
+    log('moe losses fused', losses['1'], 'nccl', losses['0'])
+    assert np.allclose(losses['1'], losses['0'], rtol=2e-3, atol=1e-4), losses
+
+comm.barrier()
+log('ALL DIST CHECKS PASSED (mode %s, %d ranks)' % (mode, nrank))

@@ -1,0 +1,40 @@
+"""Multi-process tests: gloo world of 2 on CPU (host-side logic) and, on a multi-GPU box, the
+in-kernel NVLink collectives / fused DP update / sharded embedding / fused MoE exchange against
+the NCCL baseline (pattern: reference examples/runner/parallel/validate_results.py)."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        return s.getsockname()[1]
+
+
+def _launch(mode, nproc, timeout=600):
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(nproc),
+           '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
+           os.path.join(ROOT, 'tests', 'dist_worker.py'), mode]
+    env = dict(os.environ, OMP_NUM_THREADS='2')
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
+    assert r.returncode == 0 and 'ALL DIST CHECKS PASSED' in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_gloo_world2_host_logic():
+    _launch('cpu', 2)
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(900)
+def test_multi_gpu_symm_paths():
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip('needs >= 2 GPUs (gpurun --gpus 2)')
+    _launch('gpu', min(n, 4), timeout=800)
