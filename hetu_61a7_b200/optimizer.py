@@ -98,7 +98,7 @@ class Optimizer(object):
             else:
                 self.states.append([])
         dev = next((t.device for t in self.tensors if isinstance(t, torch.Tensor)),
-                   torch.device('cpu'))
+                   config.context.torch_device)
         self.step_t = torch.zeros(1, dtype=torch.int64, device=dev)
         self.lr_t = torch.full((1,), float(self.learning_rate), dtype=torch.float32, device=dev)
         self._lr_host = float(self.learning_rate)

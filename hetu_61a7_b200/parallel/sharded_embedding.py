@@ -74,6 +74,8 @@ class ShardedTable(object):
             raise NotImplementedError('sharded embedding tables are updated with SGD (the reference PS '
                                       'applies "+=" of -lr*grad as well); got %s' % optimizer.name)
         ind = ind.contiguous()
+        if self.bsp == 0:
+            self.engine.barrier()      # BSP: every rank has finished reading this step's rows
         L.call('sparse_sgd_sharded', self.buf.ptrs, L.c_int(self.world), L.p(ind), L.c_int(_IDX_CODE[ind.dtype]),
                L.p(val.contiguous()), L.c_sz(ind.numel()), L.c_int(self.width), L.c_sz(self.vocab),
                L.p(optimizer.lr_t), L.c_f32(1.0), L.stream_ptr(self.device))

@@ -133,6 +133,13 @@ if gpu:
         tr = ht.optim.SGDOptimizer(0.05).minimize(ht_loss)
         ex = ht.Executor({'train': [ht_loss, tr]}, ctx=ctx, comm_mode='AllReduce', seed=5,
                          use_nccl_collectives=(fused == '0'))
+        # identical initial weights for both engines (node ids, hence init seeds, differ per build)
+        named = ex._named_params()
+        if fused == '1':
+            snapshot = {n: ex.config.placeholder_to_arr_map[p].detach().cpu().numpy().copy()
+                        for n, p in named.items()}
+        else:
+            ex.load_dict(snapshot)
         xv = np.random.RandomState(10 + rank).randn(2, 64, 64).astype(np.float32)
         ls = []
         for _ in range(4):
