@@ -126,7 +126,7 @@ struct GemmCfg {
     static constexpr int kABytes = BLOCK_M * BLOCK_K * 4;     // 16 KB
     static constexpr int kBBytes = BLOCK_N * BLOCK_K * 4;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kEpiBytes = 4 * 32 * 33 * 4;         // per-warp 32x33 transpose tiles (aliases stage 0)
+    static constexpr int kEpiBytes = 4 * 32 * 36 * 4;         // per-warp 32x36 transpose tiles (aliases stage 0)
     static_assert(kEpiBytes <= kStageBytes, "epilogue staging must fit in one stage");
     static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
     static constexpr int kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
@@ -231,30 +231,58 @@ gemm_tf32_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         }
     } else {
         // ------------------------------------------------------------ epilogue (warps 2..5)
+        // TMEM lane = output row, so a thread holds one row x 32 columns per tcgen05.ld.  Rows are
+        // transposed through a warp-private smem tile (row pitch 36 floats: 16 B aligned and
+        // conflict-free for 128-bit accesses), then each pass stores 4 rows x 128 B: lanes 0-7
+        // cover one row with float4s.
         const int q = warp & 3;                    // TMEM lane quadrant this warp may access
-        float* tile = smem_epi + (warp - 2) * (32 * 33);
+        float* tile = smem_epi + (warp - 2) * (32 * 36);
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
         float* Cb = p.C + (size_t)bz * p.sC;
         const int row_base = m0 + q * 32;
+        const bool vec_ok = (p.N & 3) == 0 && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
+        const int sub_row = lane >> 3, c4 = (lane & 7) * 4;
 #pragma unroll 1
         for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
             if (n0 + c0 >= p.N) break;
             float v[32];
             tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = v[j];
+            for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(&tile[lane * 36 + j * 4]) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
             __syncwarp();
-            const int col = n0 + c0 + lane;
-            const float bv = (p.bias != nullptr && col < p.N) ? __ldg(p.bias + col) : 0.f;
-#pragma unroll 4
-            for (int r = 0; r < 32; ++r) {
-                const int row = row_base + r;
-                if (row < p.M && col < p.N) {
-                    float o = p.alpha * tile[r * 33 + lane] + bv;
-                    float* dst = Cb + (size_t)row * p.N + col;
-                    if (p.beta != 0.f) o += p.beta * (*dst);
-                    *dst = apply_act(o, p.act);
+            const int col = n0 + c0 + c4;
+            if (vec_ok && col + 3 < p.N) {
+                float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (p.bias != nullptr) bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+#pragma unroll
+                for (int r = 0; r < 32; r += 4) {
+                    const int row = row_base + r + sub_row;
+                    if (row < p.M) {
+                        float4 a = *reinterpret_cast<const float4*>(&tile[(r + sub_row) * 36 + c4]);
+                        float4 o = make_float4(p.alpha * a.x + bv.x, p.alpha * a.y + bv.y, p.alpha * a.z + bv.z, p.alpha * a.w + bv.w);
+                        float4* dst = reinterpret_cast<float4*>(Cb + (size_t)row * p.N + col);
+                        if (p.beta != 0.f) {
+                            float4 c = *dst;
+                            o.x += p.beta * c.x; o.y += p.beta * c.y; o.z += p.beta * c.z; o.w += p.beta * c.w;
+                        }
+                        if (p.act != ACT_NONE) { o.x = apply_act(o.x, p.act); o.y = apply_act(o.y, p.act); o.z = apply_act(o.z, p.act); o.w = apply_act(o.w, p.act); }
+                        *dst = o;
+                    }
+                }
+            } else {
+                for (int r = 0; r < 32; r += 4) {
+                    const int row = row_base + r + sub_row;
+                    if (row >= p.M) continue;
+                    for (int u = 0; u < 4; ++u) {
+                        const int cc = col + u;
+                        if (cc >= p.N) break;
+                        float o = p.alpha * tile[(r + sub_row) * 36 + c4 + u] + (p.bias ? __ldg(p.bias + cc) : 0.f);
+                        float* dst = Cb + (size_t)row * p.N + cc;
+                        if (p.beta != 0.f) o += p.beta * (*dst);
+                        *dst = apply_act(o, p.act);
+                    }
                 }
             }
             __syncwarp();
@@ -408,6 +436,115 @@ __global__ void __launch_bounds__(256) gemm_finish_kernel(float* __restrict__ C,
         C[i] = apply_act(C[i] + (bias ? bias[i % N] : 0.f), act);
 }
 
+// ===================================================================== small-GEMM kernel
+// Latency-optimised path for the tiny products of recommendation models (batch 128 x 256 x 256,
+// 128 x 3584 x 1 ...): 16 x 64 output tile per CTA so even a 128 x 256 output spreads over 32
+// SMs, K consumed in chunks of 32 with register prefetch of the next chunk, optional split-K
+// (gridDim.z) with atomic accumulation for long reductions feeding a handful of tiles.
+constexpr int KC = 128;     // K elements per chunk: 40 loads in flight per thread hide the L2/HBM latency
+template <int TA, int TB>
+__global__ void __launch_bounds__(256) gemm_small_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                         float* __restrict__ C, const float* __restrict__ bias, int M, int N,
+                                                         int K, long long sA, long long sB, long long sC, float alpha,
+                                                         float beta, int act, int kchunk, int splits, int batch) {
+    __shared__ float As[KC][16 + 1];
+    __shared__ __align__(16) float Bs[KC][64];
+    const int bz = blockIdx.z / splits, split = blockIdx.z % splits;
+    A += (size_t)bz * sA; B += (size_t)bz * sB; C += (size_t)bz * sC;
+    const int m0 = blockIdx.y * 16, n0 = blockIdx.x * 64;
+    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+    const int kbeg = split * kchunk, kend = min(K, kbeg + kchunk);
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    constexpr int NA = 16 * KC / 256, NB = 64 * KC / 256;
+    float ra[NA], rb[NB];
+    auto load_chunk = [&](int k0) {
+#pragma unroll
+        for (int u = 0; u < NA; ++u) {
+            int e = tid + u * 256;
+            int kk, mm;
+            if (!TA) { kk = e % KC; mm = e / KC; } else { mm = e & 15; kk = e >> 4; }
+            int gm = m0 + mm, gk = k0 + kk;
+            ra[u] = (gm < M && gk < kend) ? (TA ? A[(size_t)gk * M + gm] : A[(size_t)gm * K + gk]) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < NB; ++u) {
+            int e = tid + u * 256;
+            int kk, nn;
+            if (!TB) { nn = e & 63; kk = e >> 6; } else { kk = e % KC; nn = e / KC; }
+            int gn = n0 + nn, gk = k0 + kk;
+            rb[u] = (gn < N && gk < kend) ? (TB ? B[(size_t)gn * K + gk] : B[(size_t)gk * N + gn]) : 0.f;
+        }
+    };
+    auto store_chunk = [&]() {
+#pragma unroll
+        for (int u = 0; u < NA; ++u) {
+            int e = tid + u * 256;
+            int kk, mm;
+            if (!TA) { kk = e % KC; mm = e / KC; } else { mm = e & 15; kk = e >> 4; }
+            As[kk][mm] = ra[u];
+        }
+#pragma unroll
+        for (int u = 0; u < NB; ++u) {
+            int e = tid + u * 256;
+            int kk, nn;
+            if (!TB) { nn = e & 63; kk = e >> 6; } else { kk = e % KC; nn = e / KC; }
+            Bs[kk][nn] = rb[u];
+        }
+    };
+    if (kbeg < kend) load_chunk(kbeg);
+    for (int k0 = kbeg; k0 < kend; k0 += KC) {
+        store_chunk();
+        __syncthreads();
+        if (k0 + KC < kend) load_chunk(k0 + KC);      // prefetch while computing
+        const int kmax = min(KC, kend - k0);
+#pragma unroll 8
+        for (int kk = 0; kk < kmax; ++kk) {
+            float a = As[kk][ty];
+            float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+            acc[0] = fmaf(a, b.x, acc[0]); acc[1] = fmaf(a, b.y, acc[1]);
+            acc[2] = fmaf(a, b.z, acc[2]); acc[3] = fmaf(a, b.w, acc[3]);
+        }
+        __syncthreads();
+    }
+    const int gm = m0 + ty;
+    if (gm >= M) return;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int gn = n0 + tx * 4 + j;
+        if (gn >= N) continue;
+        float* dst = C + (size_t)gm * N + gn;
+        if (splits > 1) {
+            atomicAdd(dst, alpha * acc[j]);           // C pre-zeroed; bias/act applied by the finish kernel
+        } else {
+            float o = alpha * acc[j] + (bias ? bias[gn] : 0.f);
+            if (beta != 0.f) o += beta * (*dst);
+            *dst = apply_act(o, act);
+        }
+    }
+}
+
+static void launch_small(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, int tA, int tB,
+                         int batch, long long sA, long long sB, long long sC, float alpha, float beta, int act,
+                         cudaStream_t s) {
+    int tiles = ((M + 15) / 16) * ((N + 63) / 64) * batch;
+    int splits = 1;
+    if (beta == 0.f && tiles < kNumSMs && K >= 2 * KC) {
+        splits = (kNumSMs + tiles - 1) / tiles;
+        int maxs = K / KC;
+        if (splits > maxs) splits = maxs;
+        if (splits < 1) splits = 1;
+    }
+    int kchunk = ((K + splits - 1) / splits + KC - 1) / KC * KC;
+    splits = (K + kchunk - 1) / kchunk;
+    dim3 grid((N + 63) / 64, (M + 15) / 16, batch * splits);
+    if (splits > 1) cudaMemsetAsync(C, 0, sizeof(float) * (size_t)M * N * batch, s);
+#define SMALL(TA_, TB_) gemm_small_kernel<TA_, TB_><<<grid, 256, 0, s>>>(A, B, C, bias, M, N, K, sA, sB, sC, alpha, beta, act, kchunk, splits, batch)
+    if (!tA && !tB) SMALL(0, 0); else if (!tA && tB) SMALL(0, 1); else if (tA && !tB) SMALL(1, 0); else SMALL(1, 1);
+#undef SMALL
+    if (splits > 1 && (bias || act != ACT_NONE))
+        gemm_finish_kernel<<<ew_grid((size_t)M * N * batch, 256), 256, 0, s>>>(C, bias, (size_t)M * N * batch, N, act);
+}
+
 // ============================================================================ dispatch
 static bool aligned16p(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
@@ -423,7 +560,8 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
     long long a_inner = transA ? M : K, b_inner = transB ? K : N;
     bool tma_ok = aligned16p(A) && aligned16p(B) && (a_inner % 4 == 0) && (b_inner % 4 == 0) &&
                   (sA % 4 == 0) && (sB % 4 == 0);
-    bool big = (double)M * N * K >= (double)(1 << 20) && M >= 32 && N >= 8 && K >= 32;
+    const double macs = (double)M * N * K * batch;
+    bool big = macs > (double)(1 << 25) && M >= 64 && N >= 8 && K >= 32;
     static int force_simt = -1;
     if (force_simt < 0) { const char* e = getenv("HETU_GEMM_FORCE_SIMT"); force_simt = (e && e[0] == '1') ? 1 : 0; }
     if (mode != 1 && tma_ok && big && !force_simt) {
@@ -443,17 +581,9 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
         HETU_CHECK_LAUNCH("hetu_gemm(tcgen05)");
         return 0;
     }
-    // split-K for tiny outputs with a long reduction (weight gradients of small layers)
-    if (batch == 1 && beta == 0.f && (long long)M * N <= 64 * 64 && K >= 2048) {
-        int tiles = ((M + 15) / 16) * ((N + 15) / 16);
-        int splits = (kNumSMs * 2 + tiles - 1) / tiles;
-        int kchunk = ((K + splits - 1) / splits + 15) / 16 * 16;
-        splits = (K + kchunk - 1) / kchunk;
-        cudaMemsetAsync(C, 0, (size_t)M * N * sizeof(float), s);
-        gemm_fp32_splitk_kernel<<<dim3((N + 15) / 16, (M + 15) / 16, splits), 256, 0, s>>>(A, B, C, M, N, K, transA, transB, alpha, kchunk);
-        if (bias || act != ACT_NONE)
-            gemm_finish_kernel<<<ew_grid((size_t)M * N, 256), 256, 0, s>>>(C, bias, (size_t)M * N, N, act);
-        HETU_CHECK_LAUNCH("hetu_gemm(splitk)");
+    if (macs <= (double)(1 << 27)) {
+        launch_small(A, B, C, bias, M, N, K, transA, transB, batch, sA, sB, sC, alpha, beta, act, s);
+        HETU_CHECK_LAUNCH("hetu_gemm(small)");
         return 0;
     }
     dim3 grid((N + 63) / 64, (M + 63) / 64, batch);
