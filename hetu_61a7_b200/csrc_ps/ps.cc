@@ -1,0 +1,658 @@
+// Parameter server: scheduler / server / worker roles in one library (libhetu_ps.so).
+//
+// reference: ps-lite/ (9.2 kLoC: ZeroMQ/IB vans, protobuf meta, Postoffice, KVWorker/KVServer,
+// PSAgent partitioning, PS function set in include/ps/psf/PSFunc.h:33-58, server handlers in
+// include/ps/server/PSFHandle.h and src/PSFhandle_embedding.cc, SSP in ssp_handler.h, partial
+// reduce matchmaking in src/preduce_handler.cc, C API src/python_binding.cc:8-149).
+//
+// Same roles, same PS-function set and semantics ("server does +=", versioned cache rows,
+// SSP, partial reduce, .dat save format <dir>/<node>_<server>.dat), new implementation: plain
+// TCP with length-prefixed frames (net.h), one handler thread per connection, contiguous
+// per-server shards (AveragePartitioner semantics), async requests on the worker through
+// std::async with per-tensor Wait().  This is the host-DRAM tier; the B200 fast path for
+// embeddings is the NVLink-sharded table (parallel/sharded_embedding.py).
+#include "net.h"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstdio>
+#include <cstdlib>
+#include <functional>
+#include <future>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <random>
+#include <shared_mutex>
+#include <thread>
+#include <unordered_map>
+
+#define HPS_API extern "C" __attribute__((visibility("default")))
+
+namespace hps {
+
+enum PsfType : uint32_t {
+    kDensePull = 0, kDensePush, kDDPushPull, kSparsePull, kSparsePush, kSDPushPull, kSSPushPull, kParamInit,
+    kParamClear, kParamSave, kParamLoad, kSyncEmbedding, kPushEmbedding, kPushSyncEmbedding, kSSPInit, kSSPSync,
+    kPReduceGetPartner,
+    kRegister = 100, kBarrier, kTerminate, kHeartbeat, kOk, kError
+};
+
+// ------------------------------------------------------------------------------- server state
+struct Param {
+    int type = 0;                 // 0 dense, 1 2-D sparse-addressable, 2 cache table (versioned rows)
+    size_t len = 0, width = 1;    // len = elements (dense) or rows (2-D)
+    std::vector<float> data;
+    std::vector<int64_t> ver;
+    std::shared_mutex mu;
+};
+
+class Server {
+  public:
+    Server(int id, int nservers) : id_(id), nservers_(nservers) {}
+    void set_id(int id) { id_ = id; }
+
+    void handle(const Message& req, Message* rsp) {
+        while (id_.load() < 0) usleep(1000);        // rank not yet assigned by the scheduler
+        rsp->type = kOk;
+        rsp->key = req.key;
+        switch (req.type) {
+            case kParamInit: param_init(req); break;
+            case kParamClear: { std::unique_lock<std::mutex> l(map_mu_); params_.erase(req.key); break; }
+            case kDensePull: dense_pull(req, rsp); break;
+            case kDensePush: dense_push(req); break;
+            case kDDPushPull: dense_push(req); dense_pull(req, rsp); break;
+            case kSparsePull: sparse_pull(req, 0, rsp); break;
+            case kSparsePush: sparse_push(req, 0, 1); break;
+            case kSDPushPull: sparse_push(req, 0, 1); dense_pull(req, rsp); break;
+            case kSSPushPull: sparse_push(req, 0, 1); sparse_pull(req, 2, rsp); break;
+            case kParamSave: save(req); break;
+            case kParamLoad: load(req); break;
+            case kSyncEmbedding: sync_embedding(req, 0, rsp); break;
+            case kPushEmbedding: push_embedding(req, 0); break;
+            case kPushSyncEmbedding: push_embedding(req, 2); sync_embedding(req, 0, rsp); break;
+            default: rsp->type = kError; rsp->add_str("unknown PS function");
+        }
+    }
+
+  private:
+    std::shared_ptr<Param> get(uint64_t key) {
+        std::unique_lock<std::mutex> l(map_mu_);
+        auto it = params_.find(key);
+        if (it == params_.end()) throw std::runtime_error("parameter " + std::to_string(key) + " not initialised on server");
+        return it->second;
+    }
+    // arrays: [0] = {type, len, width, init_type, opt_type} as int64, [1] = {a, b} double, [2] = seed u64
+    void param_init(const Message& req) {
+        const int64_t* h = req.data<int64_t>(0);
+        const double* ab = req.data<double>(1);
+        uint64_t seed = *req.data<uint64_t>(2);
+        auto p = std::make_shared<Param>();
+        p->type = (int)h[0]; p->len = (size_t)h[1]; p->width = (size_t)h[2];
+        size_t n = p->type == 0 ? p->len : p->len * p->width;
+        p->data.resize(n);
+        if (p->type == 2) p->ver.assign(p->len, 0);
+        int init_type = (int)h[3];
+        std::mt19937_64 rng(seed * 1000003ull + (uint64_t)id_.load());
+        if (init_type == 0) {
+            std::fill(p->data.begin(), p->data.end(), (float)ab[0]);
+        } else if (init_type == 1) {
+            std::uniform_real_distribution<float> d((float)ab[0], (float)ab[1]);
+            for (auto& v : p->data) v = d(rng);
+        } else {
+            std::normal_distribution<float> d(0.f, 1.f);
+            for (auto& v : p->data) {
+                float z = d(rng);
+                if (init_type == 3) while (z < -2.f || z > 2.f) z = d(rng);
+                v = (float)ab[0] + (float)ab[1] * z;
+            }
+        }
+        std::unique_lock<std::mutex> l(map_mu_);
+        if (!params_.count(req.key)) params_[req.key] = p;      // first initialiser wins (all workers call it)
+    }
+    void dense_pull(const Message& req, Message* rsp) {
+        auto p = get(req.key);
+        std::shared_lock<std::shared_mutex> l(p->mu);
+        rsp->add(p->data.data(), p->data.size());
+    }
+    void dense_push(const Message& req) {
+        auto p = get(req.key);
+        std::unique_lock<std::shared_mutex> l(p->mu);
+        const float* g = req.data<float>(0);
+        size_t n = std::min(p->data.size(), req.count<float>(0));
+        for (size_t i = 0; i < n; ++i) p->data[i] += g[i];
+    }
+    void sparse_pull(const Message& req, size_t off_idx, Message* rsp) {
+        auto p = get(req.key);
+        std::shared_lock<std::shared_mutex> l(p->mu);
+        const int64_t* rows = req.data<int64_t>(off_idx);
+        size_t n = req.count<int64_t>(off_idx), w = p->width;
+        std::vector<float> out(n * w);
+        for (size_t i = 0; i < n; ++i) {
+            int64_t r = rows[i];
+            if (r >= 0 && (size_t)r < p->len) memcpy(&out[i * w], &p->data[(size_t)r * w], w * sizeof(float));
+        }
+        rsp->add(out.data(), out.size());
+    }
+    void sparse_push(const Message& req, size_t off_idx, size_t data_idx) {
+        auto p = get(req.key);
+        std::unique_lock<std::shared_mutex> l(p->mu);
+        const int64_t* rows = req.data<int64_t>(off_idx);
+        const float* g = req.data<float>(data_idx);
+        size_t n = req.count<int64_t>(off_idx), w = p->width;
+        for (size_t i = 0; i < n; ++i) {
+            int64_t r = rows[i];
+            if (r < 0 || (size_t)r >= p->len) continue;
+            float* dst = &p->data[(size_t)r * w];
+            for (size_t j = 0; j < w; ++j) dst[j] += g[i * w + j];
+        }
+    }
+    // arrays: rows(i64), versions(i64); arg0 = bound.  response: idx(i64), versions(i64), data(f32)
+    void sync_embedding(const Message& req, size_t base, Message* rsp) {
+        auto p = get(req.key);
+        std::shared_lock<std::shared_mutex> l(p->mu);
+        const int64_t* rows = req.data<int64_t>(base);
+        const int64_t* cver = req.data<int64_t>(base + 1);
+        size_t n = req.count<int64_t>(base), w = p->width;
+        int64_t bound = req.arg0;
+        std::vector<int64_t> idx, ver;
+        std::vector<float> data;
+        for (size_t i = 0; i < n; ++i) {
+            int64_t r = rows[i];
+            if (r < 0 || (size_t)r >= p->len) continue;
+            int64_t sv = p->ver.empty() ? 0 : p->ver[(size_t)r];
+            if (cver[i] == -1 || sv - cver[i] > bound) {
+                idx.push_back((int64_t)i);
+                ver.push_back(sv);
+                data.insert(data.end(), &p->data[(size_t)r * w], &p->data[(size_t)r * w] + w);
+            }
+        }
+        rsp->add(idx.data(), idx.size());
+        rsp->add(ver.data(), ver.size());
+        rsp->add(data.data(), data.size());
+    }
+    // arrays at base: rows(i64), data(f32), updates(i64)
+    void push_embedding(const Message& req, size_t base) {
+        auto p = get(req.key);
+        std::unique_lock<std::shared_mutex> l(p->mu);
+        const int64_t* rows = req.data<int64_t>(base);
+        const float* g = req.data<float>(base + 1);
+        const int64_t* upd = req.data<int64_t>(base + 2);
+        size_t n = req.count<int64_t>(base), w = p->width;
+        for (size_t i = 0; i < n; ++i) {
+            int64_t r = rows[i];
+            if (r < 0 || (size_t)r >= p->len) continue;
+            if (!p->ver.empty()) p->ver[(size_t)r] += upd[i];
+            float* dst = &p->data[(size_t)r * w];
+            for (size_t j = 0; j < w; ++j) dst[j] += g[i * w + j];
+        }
+    }
+    std::string path_of(const Message& req) const {
+        return req.str(0) + "/" + std::to_string(req.key) + "_" + std::to_string(id_.load()) + ".dat";
+    }
+    void save(const Message& req) {
+        auto p = get(req.key);
+        std::shared_lock<std::shared_mutex> l(p->mu);
+        FILE* f = fopen(path_of(req).c_str(), "wb");
+        if (!f) throw std::runtime_error("cannot open " + path_of(req));
+        fwrite(p->data.data(), sizeof(float), p->data.size(), f);
+        fclose(f);
+    }
+    void load(const Message& req) {
+        auto p = get(req.key);
+        std::unique_lock<std::shared_mutex> l(p->mu);
+        FILE* f = fopen(path_of(req).c_str(), "rb");
+        if (!f) throw std::runtime_error("cannot open " + path_of(req));
+        size_t got = fread(p->data.data(), sizeof(float), p->data.size(), f);
+        fclose(f);
+        if (got != p->data.size()) throw std::runtime_error("short read from " + path_of(req));
+    }
+
+    std::atomic<int> id_;
+    int nservers_;
+    std::mutex map_mu_;
+    std::unordered_map<uint64_t, std::shared_ptr<Param>> params_;
+};
+
+// ---------------------------------------------------------------------------- scheduler state
+struct NodeInfo { int role; std::string host; int port; };
+
+class Scheduler {
+  public:
+    Scheduler(int nworkers, int nservers) : nworkers_(nworkers), nservers_(nservers) {}
+
+    // register: arg0 = role (0 worker, 1 server), arg1 = port, array0 = host.  Blocks until the
+    // whole cluster is present; response: arg0 = rank, arrays = server "host:port" strings.
+    void handle(const Message& req, Message* rsp) {
+        rsp->type = kOk;
+        switch (req.type) {
+            case kRegister: do_register(req, rsp); break;
+            case kBarrier: barrier((int)req.arg0); break;
+            case kSSPInit: ssp_init(req); break;
+            case kSSPSync: ssp_sync(req, rsp); break;
+            case kPReduceGetPartner: preduce(req, rsp); break;
+            case kHeartbeat: { std::unique_lock<std::mutex> l(mu_); heartbeat_[req.arg0] = std::chrono::steady_clock::now(); break; }
+            default: rsp->type = kError; rsp->add_str("unknown scheduler request");
+        }
+    }
+
+  private:
+    void do_register(const Message& req, Message* rsp) {
+        std::unique_lock<std::mutex> l(mu_);
+        int role = (int)req.arg0;
+        int rank;
+        if (role == 1) { rank = (int)servers_.size(); servers_.push_back({role, req.str(0), (int)req.arg1}); }
+        else { rank = nworkers_seen_++; }
+        cv_.notify_all();
+        cv_.wait(l, [&] { return (int)servers_.size() == nservers_ && nworkers_seen_ >= nworkers_; });
+        rsp->arg0 = rank;
+        rsp->arg1 = nworkers_;
+        for (auto& s : servers_) rsp->add_str(s.host + ":" + std::to_string(s.port));
+    }
+    void barrier(int group_size) {
+        std::unique_lock<std::mutex> l(mu_);
+        int gen = barrier_gen_;
+        if (++barrier_count_ >= (group_size > 0 ? group_size : nworkers_)) {
+            barrier_count_ = 0;
+            ++barrier_gen_;
+            cv_.notify_all();
+        } else {
+            cv_.wait(l, [&] { return barrier_gen_ != gen; });
+        }
+    }
+    struct Ssp { std::vector<int64_t> clock; int64_t tol = 0; };
+    void ssp_init(const Message& req) {
+        std::unique_lock<std::mutex> l(mu_);
+        auto& s = ssp_[req.key];
+        if (s.clock.empty()) { s.clock.assign((size_t)req.arg1, 0); s.tol = *req.data<int64_t>(0); }
+    }
+    // arg0 = rank, arg1 = version: blocks while this worker is more than `tol` clocks ahead of the slowest
+    void ssp_sync(const Message& req, Message* rsp) {
+        std::unique_lock<std::mutex> l(mu_);
+        auto& s = ssp_[req.key];
+        if (s.clock.empty()) return;
+        s.clock[(size_t)req.arg0] = req.arg1;
+        cv_.notify_all();
+        cv_.wait(l, [&] { return req.arg1 - *std::min_element(s.clock.begin(), s.clock.end()) <= s.tol; });
+        rsp->arg0 = 1;
+    }
+    struct PGroup { std::vector<int> ranks; bool closed = false; std::chrono::steady_clock::time_point deadline; };
+    // arg0 = rank, arg1 = wanted group size, array0 = {wait_ms} float.  Whoever is ready inside the
+    // window forms the group (heterogeneity-aware partial reduce).
+    void preduce(const Message& req, Message* rsp) {
+        std::unique_lock<std::mutex> l(mu_);
+        float wait_ms = *req.data<float>(0);
+        auto& cur = pgroups_[req.key];
+        if (!cur || cur->closed) {
+            cur = std::make_shared<PGroup>();
+            cur->deadline = std::chrono::steady_clock::now() + std::chrono::microseconds((long long)(wait_ms * 1000));
+        }
+        auto g = cur;
+        g->ranks.push_back((int)req.arg0);
+        if ((int)g->ranks.size() >= (int)req.arg1) { g->closed = true; cv_.notify_all(); }
+        while (!g->closed) {
+            if (cv_.wait_until(l, g->deadline) == std::cv_status::timeout) { g->closed = true; cv_.notify_all(); }
+        }
+        std::vector<int> out = g->ranks;
+        std::sort(out.begin(), out.end());
+        rsp->add(out.data(), out.size());
+    }
+
+    int nworkers_, nservers_, nworkers_seen_ = 0, barrier_count_ = 0, barrier_gen_ = 0;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::vector<NodeInfo> servers_;
+    std::unordered_map<uint64_t, Ssp> ssp_;
+    std::unordered_map<uint64_t, std::shared_ptr<PGroup>> pgroups_;
+    std::unordered_map<int64_t, std::chrono::steady_clock::time_point> heartbeat_;
+};
+
+// ------------------------------------------------------------------------------ accept loop
+template <class H>
+class Listener {
+  public:
+    Listener(std::shared_ptr<H> h, int port) : h_(h) { fd_ = listen_on(port, &port_); th_ = std::thread([this] { loop(); }); }
+    ~Listener() { stop(); }
+    int port() const { return port_; }
+    void stop() {
+        if (stopped_.exchange(true)) return;
+        ::shutdown(fd_, SHUT_RDWR);
+        ::close(fd_);
+        if (th_.joinable()) th_.join();
+    }
+    void wait() { if (th_.joinable()) th_.join(); }
+
+  private:
+    void loop() {
+        while (!stopped_) {
+            int c = ::accept(fd_, nullptr, nullptr);
+            if (c < 0) { if (stopped_) break; continue; }
+            int one = 1;
+            setsockopt(c, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+            std::thread([this, c] {
+                Message req, rsp;
+                while (recv_msg(c, &req)) {
+                    rsp = Message();
+                    if (req.type == kTerminate) { rsp.type = kOk; send_msg(c, rsp); stopped_ = true; ::shutdown(fd_, SHUT_RDWR); break; }
+                    try { h_->handle(req, &rsp); }
+                    catch (const std::exception& e) { rsp = Message(); rsp.type = kError; rsp.add_str(e.what()); }
+                    try { send_msg(c, rsp); } catch (...) { break; }
+                }
+                ::close(c);
+            }).detach();
+        }
+    }
+    std::shared_ptr<H> h_;
+    int fd_ = -1, port_ = 0;
+    std::thread th_;
+    std::atomic<bool> stopped_{false};
+};
+
+// ------------------------------------------------------------------------------------ worker
+struct Conn {
+    int fd = -1;
+    std::mutex mu;
+    Message call(const Message& req) {
+        std::unique_lock<std::mutex> l(mu);
+        send_msg(fd, req);
+        Message rsp;
+        if (!recv_msg(fd, &rsp)) throw std::runtime_error("connection to PS lost");
+        if (rsp.type == kError) throw std::runtime_error("PS error: " + (rsp.arrays.empty() ? std::string("?") : rsp.str(0)));
+        return rsp;
+    }
+};
+
+struct TensorMeta { int type; size_t len, width; };
+
+class Worker {
+  public:
+    Worker(const std::string& sched_host, int sched_port) {
+        sched_.fd = connect_to(sched_host, sched_port);
+        Message req;
+        req.type = kRegister; req.arg0 = 0; req.arg1 = 0; req.add_str("worker");
+        Message rsp = sched_.call(req);
+        rank_ = (int)rsp.arg0;
+        nrank_ = (int)rsp.arg1;
+        for (size_t i = 0; i < rsp.arrays.size(); ++i) {
+            std::string hp = rsp.str(i);
+            size_t c = hp.rfind(':');
+            auto conn = std::make_unique<Conn>();
+            conn->fd = connect_to(hp.substr(0, c), atoi(hp.substr(c + 1).c_str()));
+            servers_.push_back(std::move(conn));
+        }
+    }
+    ~Worker() { for (auto& s : servers_) ::close(s->fd); ::close(sched_.fd); }
+    int rank() const { return rank_; }
+    int nrank() const { return nrank_; }
+    int nservers() const { return (int)servers_.size(); }
+
+    // contiguous shard of `total` items owned by server s (ps-lite AveragePartitioner)
+    void shard(size_t total, int s, size_t* beg, size_t* end) const {
+        size_t S = servers_.size();
+        *beg = total * (size_t)s / S;
+        *end = total * (size_t)(s + 1) / S;
+    }
+    void init_tensor(uint64_t key, int type, size_t len, size_t width, int init_type, double a, double b, uint64_t seed) {
+        { std::unique_lock<std::mutex> l(mu_); meta_[key] = {type, len, width}; }
+        for (int s = 0; s < nservers(); ++s) {
+            size_t beg, end;
+            shard(len, s, &beg, &end);
+            Message req;
+            req.type = kParamInit; req.key = key;
+            int64_t h[5] = {type, (int64_t)(end - beg), (int64_t)width, init_type, 0};
+            double ab[2] = {a, b};
+            req.add(h, 5); req.add(ab, 2); req.add(&seed, 1);
+            count(req, servers_[s]->call(req));
+        }
+        barrier(0);
+    }
+    TensorMeta meta(uint64_t key) {
+        std::unique_lock<std::mutex> l(mu_);
+        auto it = meta_.find(key);
+        if (it == meta_.end()) throw std::runtime_error("tensor " + std::to_string(key) + " was not InitTensor'ed");
+        return it->second;
+    }
+    void dense(uint32_t type, uint64_t key, const float* push, float* pull) {
+        TensorMeta m = meta(key);
+        size_t total = m.type == 0 ? m.len : m.len;             // shards are by element (dense) / row (2-D)
+        size_t unit = m.type == 0 ? 1 : m.width;
+        std::vector<std::future<void>> fs;
+        for (int s = 0; s < nservers(); ++s)
+            fs.push_back(std::async(std::launch::async, [=] {
+                size_t beg, end;
+                shard(total, s, &beg, &end);
+                Message req;
+                req.type = type; req.key = key;
+                if (push) req.add(push + beg * unit, (end - beg) * unit);
+                Message rsp = servers_[s]->call(req);
+                count(req, rsp);
+                if (pull && !rsp.arrays.empty()) memcpy(pull + beg * unit, rsp.arrays[0].data(), rsp.arrays[0].size());
+            }));
+        for (auto& f : fs) f.get();
+    }
+    // rows are global ids; grads [n, width] (may be null); out [n_pull, width] (may be null)
+    void sparse(uint32_t type, uint64_t key, const int64_t* rows, size_t n, const float* grads, const int64_t* pull_rows,
+                size_t n_pull, float* out, float* dense_out) {
+        TensorMeta m = meta(key);
+        size_t w = m.width;
+        std::vector<std::future<void>> fs;
+        for (int s = 0; s < nservers(); ++s)
+            fs.push_back(std::async(std::launch::async, [=] {
+                size_t beg, end;
+                shard(m.len, s, &beg, &end);
+                std::vector<int64_t> local, pos, plocal, ppos;
+                std::vector<float> g;
+                for (size_t i = 0; i < n; ++i)
+                    if (rows[i] >= (int64_t)beg && rows[i] < (int64_t)end) {
+                        local.push_back(rows[i] - (int64_t)beg);
+                        pos.push_back((int64_t)i);
+                        if (grads) g.insert(g.end(), grads + i * w, grads + (i + 1) * w);
+                    }
+                const int64_t* pr = pull_rows ? pull_rows : rows;
+                size_t pn = pull_rows ? n_pull : n;
+                if (type == kSSPushPull)
+                    for (size_t i = 0; i < pn; ++i)
+                        if (pr[i] >= (int64_t)beg && pr[i] < (int64_t)end) { plocal.push_back(pr[i] - (int64_t)beg); ppos.push_back((int64_t)i); }
+                Message req;
+                req.type = type; req.key = key;
+                req.add(local.data(), local.size());
+                if (type == kSparsePush || type == kSDPushPull || type == kSSPushPull) req.add(g.data(), g.size());
+                if (type == kSSPushPull) req.add(plocal.data(), plocal.size());
+                if (local.empty() && plocal.empty() && type != kSDPushPull) return;
+                Message rsp = servers_[s]->call(req);
+                count(req, rsp);
+                if (type == kSparsePull && out) {
+                    const float* d = rsp.data<float>(0);
+                    for (size_t i = 0; i < pos.size(); ++i) memcpy(out + (size_t)pos[i] * w, d + i * w, w * sizeof(float));
+                } else if (type == kSSPushPull && out) {
+                    const float* d = rsp.data<float>(0);
+                    for (size_t i = 0; i < ppos.size(); ++i) memcpy(out + (size_t)ppos[i] * w, d + i * w, w * sizeof(float));
+                } else if (type == kSDPushPull && dense_out) {
+                    memcpy(dense_out + beg * w, rsp.arrays[0].data(), rsp.arrays[0].size());
+                }
+            }));
+        for (auto& f : fs) f.get();
+    }
+    // HET cache RPCs: returns (idx into request, versions, data) merged over servers
+    void sync_embedding(uint32_t type, uint64_t key, const int64_t* rows, const int64_t* vers, size_t n, int64_t bound,
+                        const int64_t* prow, const float* pdata, const int64_t* pupd, size_t pn,
+                        std::vector<int64_t>* idx, std::vector<int64_t>* over, std::vector<float>* odata) {
+        TensorMeta m = meta(key);
+        size_t w = m.width;
+        std::mutex out_mu;
+        std::vector<std::future<void>> fs;
+        for (int s = 0; s < nservers(); ++s)
+            fs.push_back(std::async(std::launch::async, [&, s] {
+                size_t beg, end;
+                shard(m.len, s, &beg, &end);
+                std::vector<int64_t> local, lver, pos, pl, pu;
+                std::vector<float> pd;
+                for (size_t i = 0; i < n; ++i)
+                    if (rows[i] >= (int64_t)beg && rows[i] < (int64_t)end) { local.push_back(rows[i] - (int64_t)beg); lver.push_back(vers[i]); pos.push_back((int64_t)i); }
+                for (size_t i = 0; i < pn; ++i)
+                    if (prow[i] >= (int64_t)beg && prow[i] < (int64_t)end) {
+                        pl.push_back(prow[i] - (int64_t)beg); pu.push_back(pupd[i]);
+                        pd.insert(pd.end(), pdata + i * w, pdata + (i + 1) * w);
+                    }
+                if (local.empty() && pl.empty()) return;
+                Message req;
+                req.type = type; req.key = key; req.arg0 = bound;
+                if (type == kPushEmbedding) { req.add(pl.data(), pl.size()); req.add(pd.data(), pd.size()); req.add(pu.data(), pu.size()); }
+                else { req.add(local.data(), local.size()); req.add(lver.data(), lver.size());
+                       if (type == kPushSyncEmbedding) { req.add(pl.data(), pl.size()); req.add(pd.data(), pd.size()); req.add(pu.data(), pu.size()); } }
+                Message rsp = servers_[s]->call(req);
+                count(req, rsp);
+                if (type == kPushEmbedding || !idx) return;
+                std::unique_lock<std::mutex> l(out_mu);
+                const int64_t* ri = rsp.data<int64_t>(0);
+                size_t k = rsp.count<int64_t>(0);
+                for (size_t i = 0; i < k; ++i) idx->push_back(pos[(size_t)ri[i]]);
+                over->insert(over->end(), rsp.data<int64_t>(1), rsp.data<int64_t>(1) + k);
+                odata->insert(odata->end(), rsp.data<float>(2), rsp.data<float>(2) + k * w);
+            }));
+        for (auto& f : fs) f.get();
+    }
+    void simple(uint32_t type, uint64_t key, const std::string& path) {
+        for (int s = 0; s < nservers(); ++s) {
+            Message req;
+            req.type = type; req.key = key;
+            if (!path.empty()) req.add_str(path);
+            servers_[s]->call(req);
+        }
+    }
+    void barrier(int group) { Message r; r.type = kBarrier; r.arg0 = group; sched_.call(r); }
+    void ssp_init(uint64_t key, int group_size, int64_t tol) { Message r; r.type = kSSPInit; r.key = key; r.arg0 = rank_; r.arg1 = group_size; r.add(&tol, 1); sched_.call(r); }
+    void ssp_sync(uint64_t key, int64_t version) { Message r; r.type = kSSPSync; r.key = key; r.arg0 = rank_; r.arg1 = version; sched_.call(r); }
+    std::vector<int> preduce(uint64_t key, int want, float wait_ms) {
+        Message r; r.type = kPReduceGetPartner; r.key = key; r.arg0 = rank_; r.arg1 = want; r.add(&wait_ms, 1);
+        Message rsp = sched_.call(r);
+        return std::vector<int>(rsp.data<int>(0), rsp.data<int>(0) + rsp.count<int>(0));
+    }
+    // async bookkeeping -----------------------------------------------------------------
+    void submit(uint64_t key, std::function<void()> fn) {
+        std::unique_lock<std::mutex> l(mu_);
+        pending_[key].push_back(std::async(std::launch::async, std::move(fn)));
+    }
+    void wait(uint64_t key) {
+        std::vector<std::future<void>> fs;
+        { std::unique_lock<std::mutex> l(mu_); fs.swap(pending_[key]); }
+        for (auto& f : fs) f.get();
+    }
+    void count(const Message& req, const Message& rsp) { if (record_) { sent_ += req.bytes(); recv_ += rsp.bytes(); } }
+    std::atomic<bool> record_{false};
+    std::atomic<uint64_t> sent_{0}, recv_{0};
+
+  private:
+    Conn sched_;
+    std::vector<std::unique_ptr<Conn>> servers_;
+    int rank_ = 0, nrank_ = 1;
+    std::mutex mu_;
+    std::unordered_map<uint64_t, TensorMeta> meta_;
+    std::unordered_map<uint64_t, std::vector<std::future<void>>> pending_;
+};
+
+static std::unique_ptr<Worker> g_worker;
+static std::unique_ptr<Listener<Scheduler>> g_sched;
+static std::vector<std::unique_ptr<Listener<Server>>> g_servers;
+static thread_local std::string g_err;
+
+static const char* env_or(const char* k, const char* d) { const char* v = getenv(k); return v ? v : d; }
+
+}  // namespace hps
+
+using namespace hps;
+
+#define HPS_TRY(body)                                  \
+    try { body; return 0; }                            \
+    catch (const std::exception& e) { g_err = e.what(); return -1; }
+
+HPS_API const char* hps_last_error() { return g_err.c_str(); }
+
+// ---- roles (env: DMLC_PS_ROOT_URI, DMLC_PS_ROOT_PORT, DMLC_NUM_WORKER, DMLC_NUM_SERVER) ----------
+HPS_API int hps_start_scheduler(int port, int nworkers, int nservers) {
+    HPS_TRY(g_sched = std::make_unique<Listener<Scheduler>>(std::make_shared<Scheduler>(nworkers, nservers), port));
+}
+HPS_API int hps_scheduler_port() { return g_sched ? g_sched->port() : -1; }
+HPS_API int hps_stop_scheduler() { if (g_sched) g_sched->stop(); g_sched.reset(); return 0; }
+HPS_API int hps_wait_scheduler() { if (g_sched) g_sched->wait(); return 0; }
+
+// start a server in this process (listens on an ephemeral port, registers with the scheduler)
+HPS_API int hps_start_server(const char* sched_host, int sched_port, const char* my_host, int nservers) {
+    HPS_TRY({
+        int fd = connect_to(sched_host, sched_port);
+        // the listener must exist before registering so that workers can connect once released
+        auto srv = std::make_shared<Server>(-1, nservers);
+        auto lst = std::make_unique<Listener<Server>>(srv, 0);
+        Message req;
+        req.type = kRegister; req.arg0 = 1; req.arg1 = lst->port(); req.add_str(my_host);
+        g_servers.push_back(std::move(lst));
+        std::thread([fd, req, srv] {
+            try { Message rsp; send_msg(fd, req); if (recv_msg(fd, &rsp)) srv->set_id((int)rsp.arg0); } catch (...) {}
+            ::close(fd);
+        }).detach();
+    });
+}
+HPS_API int hps_wait_servers() { for (auto& s : g_servers) s->wait(); return 0; }
+HPS_API int hps_stop_servers() { for (auto& s : g_servers) s->stop(); g_servers.clear(); return 0; }
+
+HPS_API int hps_worker_init(const char* sched_host, int sched_port) { HPS_TRY(g_worker = std::make_unique<Worker>(sched_host, sched_port)); }
+HPS_API int hps_worker_finalize() { g_worker.reset(); return 0; }
+HPS_API int hps_rank() { return g_worker ? g_worker->rank() : -1; }
+HPS_API int hps_nrank() { return g_worker ? g_worker->nrank() : 0; }
+HPS_API int hps_nservers() { return g_worker ? g_worker->nservers() : 0; }
+
+// ---- PS functions (synchronous; *_async variants enqueue and are joined by hps_wait(key)) -------
+HPS_API int hps_init_tensor(uint64_t key, int type, uint64_t len, uint64_t width, int init_type, double a, double b, uint64_t seed) {
+    HPS_TRY(g_worker->init_tensor(key, type, len, width, init_type, a, b, seed));
+}
+HPS_API int hps_pull(uint64_t key, float* out) { HPS_TRY(g_worker->dense(kDensePull, key, nullptr, out)); }
+HPS_API int hps_push(uint64_t key, const float* grad) { HPS_TRY(g_worker->dense(kDensePush, key, grad, nullptr)); }
+HPS_API int hps_dd_pushpull(uint64_t key, const float* grad, float* out) { HPS_TRY(g_worker->dense(kDDPushPull, key, grad, out)); }
+HPS_API int hps_sparse_pull(uint64_t key, const int64_t* rows, uint64_t n, float* out) {
+    HPS_TRY(g_worker->sparse(kSparsePull, key, rows, n, nullptr, nullptr, 0, out, nullptr));
+}
+HPS_API int hps_sparse_push(uint64_t key, const int64_t* rows, uint64_t n, const float* grads) {
+    HPS_TRY(g_worker->sparse(kSparsePush, key, rows, n, grads, nullptr, 0, nullptr, nullptr));
+}
+HPS_API int hps_sd_pushpull(uint64_t key, const int64_t* rows, uint64_t n, const float* grads, float* dense_out) {
+    HPS_TRY(g_worker->sparse(kSDPushPull, key, rows, n, grads, nullptr, 0, nullptr, dense_out));
+}
+HPS_API int hps_ss_pushpull(uint64_t key, const int64_t* rows, uint64_t n, const float* grads, const int64_t* pull_rows,
+                            uint64_t n_pull, float* out) {
+    HPS_TRY(g_worker->sparse(kSSPushPull, key, rows, n, grads, pull_rows, n_pull, out, nullptr));
+}
+HPS_API int hps_push_async(uint64_t key, const float* grad) { HPS_TRY(g_worker->submit(key, [=] { g_worker->dense(kDensePush, key, grad, nullptr); })); }
+HPS_API int hps_pull_async(uint64_t key, float* out) { HPS_TRY(g_worker->submit(key, [=] { g_worker->dense(kDensePull, key, nullptr, out); })); }
+HPS_API int hps_dd_pushpull_async(uint64_t key, const float* grad, float* out) {
+    HPS_TRY(g_worker->submit(key, [=] { g_worker->dense(kDDPushPull, key, grad, out); }));
+}
+HPS_API int hps_sparse_push_async(uint64_t key, const int64_t* rows, uint64_t n, const float* grads) {
+    HPS_TRY(g_worker->submit(key, [=] { g_worker->sparse(kSparsePush, key, rows, n, grads, nullptr, 0, nullptr, nullptr); }));
+}
+HPS_API int hps_sparse_pull_async(uint64_t key, const int64_t* rows, uint64_t n, float* out) {
+    HPS_TRY(g_worker->submit(key, [=] { g_worker->sparse(kSparsePull, key, rows, n, nullptr, nullptr, 0, out, nullptr); }));
+}
+HPS_API int hps_wait(uint64_t key) { HPS_TRY(g_worker->wait(key)); }
+HPS_API int hps_clear(uint64_t key) { HPS_TRY(g_worker->simple(kParamClear, key, "")); }
+HPS_API int hps_save(uint64_t key, const char* dir) { HPS_TRY(g_worker->simple(kParamSave, key, dir)); }
+HPS_API int hps_load(uint64_t key, const char* dir) { HPS_TRY(g_worker->simple(kParamLoad, key, dir)); }
+HPS_API int hps_barrier(int group) { HPS_TRY(g_worker->barrier(group)); }
+HPS_API int hps_ssp_init(uint64_t key, int group_size, int64_t tolerance) { HPS_TRY(g_worker->ssp_init(key, group_size, tolerance)); }
+HPS_API int hps_ssp_sync(uint64_t key, int64_t version) { HPS_TRY(g_worker->ssp_sync(key, version)); }
+HPS_API int hps_preduce_get_partner(uint64_t key, int want, float wait_ms, int* out, int* n_out) {
+    HPS_TRY({ auto v = g_worker->preduce(key, want, wait_ms); *n_out = (int)v.size(); for (size_t i = 0; i < v.size(); ++i) out[i] = v[i]; });
+}
+HPS_API int hps_start_record() { if (g_worker) g_worker->record_ = true; return 0; }
+HPS_API int hps_get_loads(uint64_t* sent, uint64_t* recv) { if (!g_worker) return -1; *sent = g_worker->sent_; *recv = g_worker->recv_; return 0; }
+
+// HET-cache RPCs used by cache.cc ---------------------------------------------------------------
+namespace hps {
+void worker_sync_embedding(uint32_t type, uint64_t key, const int64_t* rows, const int64_t* vers, size_t n, int64_t bound,
+                           const int64_t* prow, const float* pdata, const int64_t* pupd, size_t pn,
+                           std::vector<int64_t>* idx, std::vector<int64_t>* over, std::vector<float>* odata) {
+    if (!g_worker) throw std::runtime_error("PS worker not initialised");
+    g_worker->sync_embedding(type, key, rows, vers, n, bound, prow, pdata, pupd, pn, idx, over, odata);
+}
+}  // namespace hps
