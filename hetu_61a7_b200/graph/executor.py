@@ -266,7 +266,7 @@ def topo_sort_with_hook(node_list: List[Op], config: HetuConfig) -> None:
 
 def _post_hook(node: Op, config: HetuConfig) -> None:
     if isinstance(node, PlaceholderOp):
-        if node.tensor_value is not None and not node.ps_resident:
+        if node.tensor_value is not None:
             tv = node.tensor_value
             config.placeholder_to_arr_map[node] = tv.tensor if isinstance(tv, NDArray) else tv
         elif node.ps_resident:

@@ -40,8 +40,33 @@ class EmbeddingLookUp(Op):
         if hasattr(embedding, 'is_embed'):
             embedding.is_embed = True
 
+    def forward_hook(self, config):
+        super().forward_hook(config)
+        emb = self.inputs[0]
+        if getattr(emb, 'ps_resident', False) and getattr(emb, 'is_embed', False):
+            # PS / Hybrid: rows come from the parameter server (through the HET cache when one
+            # is configured) every step -> host round trip, so this graph runs eagerly
+            self._ps_comm = config.ps_comm
+            self.graph_safe = False
+
+    def _ps_lookup(self, idx):
+        import numpy as np
+        emb = self.inputs[0]
+        ids = idx.detach().cpu().numpy().astype(np.int64).reshape(-1)
+        cache = getattr(emb, 'cache', None)
+        width = int(emb.shape[-1])
+        if cache is not None:
+            rows = cache.embedding_lookup(ids, sync=True)
+        else:
+            rows = self._ps_comm.SparsePull(emb.id, ids, width)
+        t = torch.from_numpy(np.asarray(rows).reshape(tuple(idx.shape) + (width,)))
+        dev = self.ctx.torch_device if self.ctx is not None else idx.device
+        return t.to(dev, non_blocking=True)
+
     def compute(self, input_vals, output_val=None, stream_handle=None):
         table, idx = input_vals
+        if table is None and getattr(self, '_ps_comm', None) is not None:
+            return self._ps_lookup(idx)
         if hasattr(table, 'lookup'):                       # ShardedTable / cache handle
             return table.lookup(idx)
         if table.device.type == 'meta':

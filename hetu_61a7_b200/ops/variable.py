@@ -40,7 +40,7 @@ class PlaceholderOp(Op):
 
     @property
     def is_feed(self) -> bool:
-        return self.tensor_value is None and self.initializer is None
+        return self.tensor_value is None and self.initializer is None and not self.ps_resident
 
     def compute(self, input_vals, output_val=None, stream_handle=None):
         assert self.shape, "placeholder %s values provided by feed_dict" % self.name
@@ -64,11 +64,7 @@ class PlaceholderOp(Op):
         strategy = config.node_strategy.get(self, config.comm_mode)
         on_ps = self.trainable and (strategy == 'PS' or (strategy == 'Hybrid' and self.is_embed))
         if on_ps and config.ps_comm is not None:
-            self.ps_resident = True
-            self.ctx = cpu(0)
-            self.event = (_stream.CSEvent(config.ps_comm, self.id)
-                          if config.cstable_policy is not None and self.is_embed
-                          else _stream.PSEvent(config.ps_comm, self.id))
+            self._init_on_ps(config)
             return
         from ..parallel.sharded_embedding import should_shard, ShardedTable
         if should_shard(self, config) and self.shape is not None and len(self.shape) == 2:
@@ -97,6 +93,39 @@ class PlaceholderOp(Op):
                 t = t.to(dev)
             elif not isinstance(value, NDArray):
                 t = t.clone()
+            self.tensor_value = NDArray(t, self.ctx)
+
+    def _init_on_ps(self, config):
+        """Hand the parameter to the servers: ParamInit on every shard (server-side RNG), or
+        zero-init + a push of the user's value from rank 0.  Dense parameters keep a device
+        replica refreshed by DDPushPull; embedding tables stay remote and are read row-wise
+        (SparsePull / HET cache).  reference: executor.py:1191-1217, initializers.py:28-38."""
+        comm = config.ps_comm
+        self.ps_resident = True
+        ptype = 0 if not self.is_embed else (2 if config.cstable_policy is not None else 1)
+        if ptype == 0:
+            length, width = int(np.prod(self.shape)), 1
+        else:
+            length, width = int(self.shape[0]), int(np.prod(self.shape[1:]))
+        if self.initializer is not None:
+            self.initializer.init_on_ps(comm, self.id, ptype, seed=config.seed + self.id)
+            self.initializer = None
+        else:
+            comm.InitTensor(self.id, ptype, length, width, 0, 0.0, 1.0, 0)
+            if comm.rank() == 0:
+                v = self.tensor_value
+                v = v.asnumpy() if isinstance(v, NDArray) else (v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else np.asarray(v))
+                if ptype == 0:
+                    comm.Push(self.id, v.astype(np.float32).reshape(-1))
+                else:
+                    comm.SparsePush(self.id, np.arange(length), v.astype(np.float32).reshape(length, width))
+            comm.BarrierWorker()
+        self.event = (_stream.CSEvent(comm, self.id) if ptype == 2 else _stream.PSEvent(comm, self.id))
+        if self.is_embed:
+            self.tensor_value = None
+        else:
+            flat = comm.Pull(self.id)
+            t = torch.from_numpy(flat.reshape(self.shape).copy()).to(self.ctx.torch_device)
             self.tensor_value = NDArray(t, self.ctx)
 
     # -- model-parallel sharding (reference Variable.py:83-123) ----------------
