@@ -78,6 +78,9 @@ def gradients(output_node, node_list: List[Op], insert_grad: Optional[Op] = None
         grad = sum_node_list(node_to_grads[node], node.raw_ctx)
         if grad is None:
             continue
+        if getattr(grad, 'mp_state', None) != getattr(node, 'mp_state', None):
+            from ..parallel.mp_lowering import match_grad_state
+            grad = match_grad_state(grad, node)
         node_to_grad[node] = grad
         if not node.inputs:
             continue

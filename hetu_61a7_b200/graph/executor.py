@@ -99,7 +99,7 @@ class HetuConfig(object):
         'dist_strategy', 'pipeline', 'use_preduce', 'overlap', 'use_nccl_collectives', 'symm',
         'fuse_dp_update', 'use_cuda_graph', 'dp_rank', 'dp_nrank', 'mp_index', 'shard_dataloaders',
         'all_forward_nodes', 'lcm_dp_nrank', 'pp_rank', 'pp_nrank', 'stage_ranks', 'memory_pool',
-        'timing',
+        'timing', 'dropped_eval_nodes',
     ]
 
     def __init__(self, eval_node_list, train_name, val_name, ctx=None, seed=None, comm_mode=None,
@@ -230,6 +230,7 @@ class HetuConfig(object):
         self.dataloader_ops = []
         self.inference = False
         self.my_eval_nodes = eval_node_list
+        self.dropped_eval_nodes = []
         self.param_allreduce_group = {}
         self.placeholder_to_arr_map = {}
         self.gpipe = pipeline == 'gpipe'
@@ -331,9 +332,23 @@ class Executor(object):
             for n in v:
                 if n not in all_eval_nodes:
                     all_eval_nodes.append(n)
+        ancestors = {k: set(find_topo_sort(v)) for k, v in eval_node_dict.items()}
         if config is None:
             config = HetuConfig(eval_node_list=all_eval_nodes, train_name=train_name,
                                 val_name=val_name, timing=timing, **kargs)
+        if config.my_eval_nodes is not all_eval_nodes:
+            # placement pruned / extended this rank's graph: keep own nodes, add its p2p sends
+            from ..ops.comm import PipelineSendOp
+            new_dict = {}
+            for k, v in eval_node_dict.items():
+                keep = [n for n in v if n not in config.dropped_eval_nodes]
+                sends = [n for n in config.my_eval_nodes if isinstance(n, PipelineSendOp)
+                         and n.inputs[0] in ancestors[k] and n not in keep]
+                merged = [n for n in config.my_eval_nodes if n in keep or n in sends]
+                new_dict[k] = merged
+            self.full_eval_node_dict = eval_node_dict
+            eval_node_dict = new_dict
+            all_eval_nodes = config.my_eval_nodes
         assert isinstance(config, HetuConfig)
         self.eval_node_dict = eval_node_dict
         self.config = config
@@ -638,6 +653,8 @@ class SubExecutor(object):
         else:
             vals = self._run_eager(feeds)
         self.step_count += 1
+        from ..parallel.comm import drain_sends
+        drain_sends()
         results = []
         for n in eval_nodes:
             v = vals.get(n)

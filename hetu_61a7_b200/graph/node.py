@@ -25,7 +25,19 @@ def _next_id() -> int:
     return G_NODE_ID - 1
 
 
-class Op(object):
+class OpMeta(type):
+    """Runs the model-parallel state propagation once an op is fully constructed (sub-class
+    constructors set their attributes after ``Op.__init__``)."""
+
+    def __call__(cls, *args, **kwargs):
+        obj = super().__call__(*args, **kwargs)
+        if not obj._no_adapt and any(getattr(i, 'mp_state', None) is not None for i in obj.inputs if i is not None):
+            from ..parallel.mp_lowering import adapt
+            adapt(obj)
+        return obj
+
+
+class Op(object, metaclass=OpMeta):
     """Basic unit of the dataflow graph."""
 
     #: False for nodes that must touch the host every step (PS RPC, dataloaders,
@@ -33,8 +45,11 @@ class Op(object):
     #: captured into one CUDA graph.
     graph_safe = True
 
-    def __init__(self, op_type, inputs: List['Op'], ctx=None) -> None:
+    def __init__(self, op_type, inputs: List['Op'], ctx=None, _adapt=True) -> None:
         self.inputs: List[Op] = list(inputs)
+        self._no_adapt = not _adapt
+        self.mp_state = None          # see parallel/mp_lowering.py
+        self.mp_group = None
         self.raw_ctx: Optional[DeviceGroup] = (
             get_current_context() if ctx is None else DeviceGroup(ctx))
         self.ctx = ctx

@@ -257,21 +257,21 @@ class PipelineSendOp(Op):
         return self.name + '(send node %s to rank %s)' % (self.inputs[0].name, str(self.const_attr))
 
     def compute(self, input_vals, output_val=None, stream_handle=None):
+        from ..parallel.comm import isend
         v = input_vals[0]
-        comm = _comm_of(self)
         dst = self.const_attr[self.index]
+        d = getattr(self, 'direction', 0)
         if isinstance(v, IndexedSlices):
             ind, val = v._iv()
-            comm.send(torch.tensor([ind.numel(), val.shape[1]], dtype=torch.int64, device=val.device), dst)
-            comm.send(ind, dst)
-            comm.send(val, dst)
+            isend(torch.tensor([ind.numel(), val.shape[1]], dtype=torch.int64, device=val.device), dst, d)
+            isend(ind, dst, d)
+            isend(val, dst, d)
         elif v.device.type != 'meta':
-            if not getattr(self, 'static_shape', False):
-                hdr = torch.zeros(8, dtype=torch.int64, device=v.device)
-                hdr[0] = v.dim()
-                hdr[1:1 + v.dim()] = torch.tensor(list(v.shape), dtype=torch.int64)
-                comm.send(hdr, dst)
-            comm.send(v, dst)
+            hdr = torch.zeros(8, dtype=torch.int64)
+            hdr[0] = v.dim()
+            hdr[1:1 + v.dim()] = torch.tensor(list(v.shape), dtype=torch.int64)
+            isend(hdr.to(v.device), dst, d)
+            isend(v, dst, d)
         self.step_index()
         return None
 
@@ -302,30 +302,22 @@ class PipelineReceiveOp(Op):
         return self.name + '(receive from rank %s)' % str(self.const_attr)
 
     def compute(self, input_vals, output_val=None, stream_handle=None):
-        comm = _comm_of(self)
+        from ..parallel.comm import recv_now, world
         src = self.const_attr[self.index]
+        d = getattr(self, 'direction', 0)
         dev = self.ctx.torch_device
-        if comm.active and not torch.cuda.is_available():
+        if world().active and torch.distributed.get_backend() == 'gloo':
             dev = torch.device('cpu')
         if self.use_indexed_slices:
-            hdr = torch.zeros(2, dtype=torch.int64, device=dev)
-            comm.recv(hdr, src)
+            hdr = recv_now(torch.zeros(2, dtype=torch.int64, device=dev), src, d)
             n, w = [int(x) for x in hdr.tolist()]
-            ind = torch.empty(n, dtype=torch.int64, device=dev)
-            val = torch.empty((n, w), dtype=torch.float32, device=dev)
-            comm.recv(ind, src)
-            comm.recv(val, src)
+            ind = recv_now(torch.empty(n, dtype=torch.int64, device=dev), src, d)
+            val = recv_now(torch.empty((n, w), dtype=torch.float32, device=dev), src, d)
             out = IndexedSlices(ind, val, None)
         else:
-            if self.static_shape_value is None:
-                hdr = torch.zeros(8, dtype=torch.int64, device=dev)
-                comm.recv(hdr, src)
-                h = hdr.tolist()
-                shape = tuple(int(x) for x in h[1:1 + int(h[0])])
-            else:
-                shape = self.static_shape_value
-            out = torch.empty(shape, dtype=torch.float32, device=dev)
-            comm.recv(out, src)
+            h = recv_now(torch.zeros(8, dtype=torch.int64, device=dev), src, d).tolist()
+            shape = tuple(int(x) for x in h[1:1 + int(h[0])])
+            out = recv_now(torch.empty(shape, dtype=torch.float32, device=dev), src, d)
         self.step_index()
         return out
 
@@ -420,6 +412,14 @@ def pipeline_receive_op(source, comm=None, use_indexed_slices=False, ctx=None):
 
 
 def dispatch(node, parts={}):
+    """Declare how ``node`` is partitioned over the devices of the enclosing model-parallel
+    worker (tuple context).  ``parts`` = tuple with one entry per dim or {dim: n}."""
+    from ..context import get_current_context
+    from ..parallel.mp_lowering import lower_dispatch
+    pdict = dict(parts) if isinstance(parts, dict) else {i: p for i, p in enumerate(parts)}
+    lowered = lower_dispatch(node, pdict, get_current_context())
+    if lowered is not None:
+        return lowered
     return DispatchOp(node, parts)
 
 

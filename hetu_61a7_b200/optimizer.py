@@ -90,7 +90,7 @@ class Optimizer(object):
     # -- state ------------------------------------------------------------------
     def initiate_states(self, config):
         assert not self.initiated, "Optimizer already initiated."
-        self.tensors = [config.placeholder_to_arr_map[node] for node in self.params]
+        self.tensors = [config.placeholder_to_arr_map.get(node) for node in self.params]
         self.states = []
         for t in self.tensors:
             if isinstance(t, torch.Tensor):
@@ -420,6 +420,12 @@ class OptimizerOp(Op):
             cur_node = node
             if node is None or 'expert' in cur_param.name:
                 pass
+            elif getattr(cur_param, 'dp_group_ranks', None) is not None:
+                # placement pass decided the replica group of this parameter (DP x TP x PP)
+                ranks = cur_param.dp_group_ranks
+                if len(ranks) > 1:
+                    from .parallel.comm import new_group_comm
+                    cur_node = allreduceCommunicate_op(node, new_group_comm(list(ranks)))
             elif strategy == 'AllReduce' or (strategy == 'Hybrid' and not node.use_indexed_slices):
                 if config.symm is not None and not node.use_indexed_slices and config.fuse_dp_update:
                     fused_ids.append(i)

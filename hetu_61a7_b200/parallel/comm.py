@@ -281,6 +281,45 @@ def new_group_comm(devices_context=None) -> Communicator:
     return _GROUPS[key]
 
 
+_P2P = {}
+_PENDING = []
+
+
+def make_p2p_comms():
+    """Two extra world-spanning communicators, one per pipeline direction (activations forward,
+    gradients backward).  Collective: every rank must call it (the placement pass does)."""
+    comm = world()
+    if not comm.active or _P2P:
+        return
+    for d in (0, 1):
+        _P2P[d] = Communicator(group=dist.new_group(ranks=list(range(comm.world_size))))
+
+
+def p2p_comm(direction: int = 0) -> Communicator:
+    return _P2P.get(direction, world())
+
+
+def isend(t: torch.Tensor, dst: int, direction: int = 0):
+    comm = p2p_comm(direction)
+    t = t.contiguous()
+    req = dist.isend(t, dst=comm.world_of(dst), group=comm.group)
+    _PENDING.append((req, t))
+    if len(_PENDING) > 64:
+        drain_sends(keep=32)
+
+
+def recv_now(t: torch.Tensor, src: int, direction: int = 0):
+    comm = p2p_comm(direction)
+    dist.irecv(t, src=comm.world_of(src), group=comm.group).wait()
+    return t
+
+
+def drain_sends(keep: int = 0):
+    while len(_PENDING) > keep:
+        req, _ = _PENDING.pop(0)
+        req.wait()
+
+
 def device_max_ms(ms: float, device=None) -> float:
     """MAX over ranks of a device-measured duration."""
     comm = world()

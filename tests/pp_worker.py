@@ -1,0 +1,117 @@
+"""2-rank pipeline / model-parallel equivalence worker (gloo on CPU or NCCL on GPUs).
+Pattern: reference examples/runner/parallel/all_mlp_tests.sh + validate_results.py - same
+weights, same feeds, losses must equal the single-process run."""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+mode, case = sys.argv[1], sys.argv[2]
+if mode == 'cpu':
+    os.environ['HETU_COMM_BACKEND'] = 'gloo'
+import hetu as ht                                           # noqa: E402
+
+comm = ht.wrapped_mpi_nccl_init()
+rank = comm.rank
+rs = np.random.RandomState(0)
+W1, W2, W3 = (rs.randn(12, 16) * 0.3).astype(np.float32), (rs.randn(16, 16) * 0.3).astype(np.float32), (rs.randn(16, 4) * 0.3).astype(np.float32)
+X = rs.randn(4, 8, 12).astype(np.float32)                    # 4 micro-batches of 8
+Y = np.eye(4, dtype=np.float32)[rs.randint(0, 4, (4, 8))]
+dev = (lambda i: ht.gpu(i)) if mode == 'gpu' else (lambda i: ht.gpu(i))
+
+
+def oracle(steps, micro, per_micro_update):
+    w = [torch.tensor(a.copy(), requires_grad=True) for a in (W1, W2, W3)]
+    opt = torch.optim.SGD(w, 0.1)
+    losses = []
+    for _ in range(steps):
+        if not per_micro_update:
+            opt.zero_grad()
+        for m in range(micro):
+            if per_micro_update:
+                opt.zero_grad()
+            h = torch.relu(torch.relu(torch.tensor(X[m]) @ w[0]) @ w[1]) @ w[2]
+            l = torch.nn.functional.cross_entropy(h, torch.tensor(Y[m]).argmax(1))
+            l.backward()
+            losses.append(float(l))
+            if per_micro_update:
+                opt.step()
+        if not per_micro_update:
+            opt.step()
+    return losses, [t.detach().numpy() for t in w]
+
+
+def build(split=None):
+    with ht.context(dev(0)):
+        x = ht.Variable('x')
+        w1 = ht.Variable('w1', value=W1.copy())
+        a = ht.relu_op(ht.matmul_op(x, w1))
+    if split is None:
+        with ht.context(dev(1)):
+            w2 = ht.Variable('w2', value=W2.copy())
+            a = ht.relu_op(ht.matmul_op(a, w2))
+    else:
+        with ht.context((dev(0), dev(1))):
+            w2 = ht.Variable('w2', value=W2.copy())
+            act, wt = {'left': ((2, 1), (1, 1)), 'right': ((1, 1), (1, 2)), 'middle': ((1, 2), (2, 1))}[split]
+            a = ht.matmul_op(ht.dispatch(a, act), ht.dispatch(w2, wt))
+            a = ht.relu_op(a)
+    with ht.context(dev(1)):
+        if split is not None:
+            a = ht.dispatch(a, (1, 1))
+        w3 = ht.Variable('w3', value=W3.copy())
+        y_ = ht.Variable('y_')
+        loss = ht.reduce_mean_op(ht.softmaxcrossentropy_op(ht.matmul_op(a, w3), y_), [0])
+        train = ht.optim.SGDOptimizer(0.1).minimize(loss)
+    return x, y_, loss, train, (w1, w2, w3)
+
+
+def mine(ex, p):
+    t = ex.config.placeholder_to_arr_map.get(p)
+    return None if t is None else t.detach().cpu().numpy()
+
+
+if case == 'gpipe':
+    x, y_, loss, train, ws = build()
+    ex = ht.Executor({'train': [loss, train]}, pipeline='gpipe', seed=0)
+    got = []
+    for step in range(3):
+        out = ex.run('train', feed_dict={x: [X[m] for m in range(4)], y_: [Y[m] for m in range(4)]}, batch_num=4)
+        if out[0] is not None:
+            got += [float(o.asnumpy()) for o in out[0]]
+    # GPipe sums the micro-batch gradients before one update
+    ref_l, ref_w = oracle(3, 4, per_micro_update=False)
+elif case == 'pipedream':
+    x, y_, loss, train, ws = build()
+    ex = ht.Executor({'train': [loss, train]}, pipeline='pipedream', seed=0)
+    got = []
+    for step in range(3):
+        out = ex.run('train', feed_dict={x: [X[m] for m in range(4)], y_: [Y[m] for m in range(4)]}, batch_num=4)
+        if out[0] is not None:
+            got += [float(o.asnumpy()) for o in out[0]]
+    ref_l, ref_w = None, None
+else:
+    x, y_, loss, train, ws = build(split=case)
+    ex = ht.Executor({'train': [loss, train]}, seed=0)
+    got = []
+    for step in range(12):
+        out = ex.run('train', feed_dict={x: X[step % 4], y_: Y[step % 4]})
+        if out[0] is not None:
+            got.append(float(out[0].asnumpy()))
+    ref_l, ref_w = oracle(3, 4, per_micro_update=True)
+
+if ref_l is not None:
+    if got:
+        assert np.allclose(got, ref_l, rtol=2e-4, atol=1e-5), (got[:4], ref_l[:4])
+    for p, r in zip(ws, ref_w):
+        m = mine(ex, p)
+        if m is not None:
+            assert np.allclose(m, r, rtol=2e-3, atol=1e-5), (p.name, np.abs(m - r).max())
+else:
+    if got:
+        assert got[-1] < got[0], got
+comm.barrier()
+print('PP %s rank %d OK' % (case, rank), flush=True)

@@ -38,3 +38,16 @@ def test_multi_gpu_symm_paths():
     if n < 2:
         pytest.skip('needs >= 2 GPUs (gpurun --gpus 2)')
     _launch('gpu', min(n, 4), timeout=800)
+
+
+def _launch_pp(mode, case, timeout=600):
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2',
+           '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
+           os.path.join(ROOT, 'tests', 'pp_worker.py'), mode, case]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=dict(os.environ, OMP_NUM_THREADS='2'))
+    assert r.returncode == 0 and r.stdout.count('OK') == 2, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.parametrize('case', ['gpipe', 'pipedream', 'left', 'right', 'middle'])
+def test_pipeline_and_model_parallel_equivalence_gloo(case):
+    _launch_pp('cpu', case)
