@@ -25,6 +25,7 @@ from . import layers
 from . import distributed_strategies as dist
 from . import ndarray
 from . import stream
+from . import cpu_links
 from .utils import data
 from .utils import metrics
 from .utils.profiler import HetuProfiler, NCCLProfiler

@@ -1,0 +1,595 @@
+// CPU op library (OpenMP) behind the CPU executor and the numpy-oracle tests.
+//
+// reference: src/dnnl_ops/*.cpp (oneDNN primitives + OpenMP loops, 47 exported functions listed in
+// python/hetu/_base.py:16-58).  oneDNN is not part of this image; the primitives are written out as
+// cache-blocked OpenMP loops the compiler vectorises (AVX2/FMA).  All tensors are dense row-major
+// fp32; every function returns 0 on success.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <random>
+#include <vector>
+#include <omp.h>
+
+#define API extern "C" __attribute__((visibility("default")))
+
+// ------------------------------------------------------------------------------------------------
+// GEMM: C[M,N] = alpha * op(A) op(B) + beta * C          (reference MatrixMult.cpp:18-56)
+// Packs op(A) / op(B) panels so the micro-kernel always streams unit-stride data.
+namespace {
+constexpr int MC = 96, KC = 256, NC = 512, MR = 6, NR = 16;
+
+inline void micro_kernel(int kc, const float* __restrict a, const float* __restrict b, float* __restrict c,
+                         int ldc, int mr, int nr, float alpha, bool accumulate) {
+    float acc[MR][NR] = {};
+    for (int p = 0; p < kc; ++p) {
+        const float* bp = b + p * NR;
+        const float* ap = a + p * MR;
+        for (int i = 0; i < MR; ++i) {
+            float av = ap[i];
+#pragma omp simd
+            for (int j = 0; j < NR; ++j) acc[i][j] += av * bp[j];
+        }
+    }
+    for (int i = 0; i < mr; ++i)
+        for (int j = 0; j < nr; ++j) {
+            float v = alpha * acc[i][j];
+            c[i * ldc + j] = accumulate ? c[i * ldc + j] + v : v;
+        }
+}
+}  // namespace
+
+API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, int K, int transA, int transB,
+                        float alpha, float beta) {
+    if (beta == 0.f) {
+#pragma omp parallel for
+        for (int64_t i = 0; i < (int64_t)M * N; ++i) C[i] = 0.f;
+    } else if (beta != 1.f) {
+#pragma omp parallel for
+        for (int64_t i = 0; i < (int64_t)M * N; ++i) C[i] *= beta;
+    }
+    const int lda = transA ? M : K, ldb = transB ? K : N;
+    for (int jc = 0; jc < N; jc += NC) {
+        int nc = std::min(NC, N - jc);
+        int npanels = (nc + NR - 1) / NR;
+        for (int pc = 0; pc < K; pc += KC) {
+            int kc = std::min(KC, K - pc);
+            std::vector<float> bpack((size_t)npanels * kc * NR);
+#pragma omp parallel for
+            for (int jp = 0; jp < npanels; ++jp) {
+                float* dst = bpack.data() + (size_t)jp * kc * NR;
+                for (int p = 0; p < kc; ++p)
+                    for (int j = 0; j < NR; ++j) {
+                        int col = jc + jp * NR + j;
+                        float v = 0.f;
+                        if (col < N) v = transB ? B[(size_t)col * ldb + pc + p] : B[(size_t)(pc + p) * ldb + col];
+                        dst[p * NR + j] = v;
+                    }
+            }
+#pragma omp parallel
+            {
+                std::vector<float> apack((size_t)((MC + MR - 1) / MR) * MR * kc);
+#pragma omp for schedule(dynamic)
+                for (int ic = 0; ic < M; ic += MC) {
+                    int mc = std::min(MC, M - ic);
+                    int mpanels = (mc + MR - 1) / MR;
+                    for (int ip = 0; ip < mpanels; ++ip) {
+                        float* dst = apack.data() + (size_t)ip * kc * MR;
+                        for (int p = 0; p < kc; ++p)
+                            for (int i = 0; i < MR; ++i) {
+                                int row = ic + ip * MR + i;
+                                float v = 0.f;
+                                if (row < M) v = transA ? A[(size_t)(pc + p) * lda + row] : A[(size_t)row * lda + pc + p];
+                                dst[p * MR + i] = v;
+                            }
+                    }
+                    for (int jp = 0; jp < npanels; ++jp)
+                        for (int ip = 0; ip < mpanels; ++ip) {
+                            int row = ic + ip * MR, col = jc + jp * NR;
+                            micro_kernel(kc, apack.data() + (size_t)ip * kc * MR, bpack.data() + (size_t)jp * kc * NR,
+                                         C + (size_t)row * N + col, N, std::min(MR, M - row), std::min(NR, N - col),
+                                         alpha, true);
+                        }
+                }
+            }
+        }
+    }
+    return 0;
+}
+
+API int hetu_cpu_batch_matmul(const float* A, const float* B, float* C, int batch, int M, int N, int K, int transA,
+                              int transB) {
+    for (int b = 0; b < batch; ++b)
+        hetu_cpu_matmul(A + (size_t)b * M * K, B + (size_t)b * K * N, C + (size_t)b * M * N, M, N, K, transA, transB,
+                        1.f, 0.f);
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// element-wise (reference AddConst/AddElewise/MultiplyConst/MultiplyElewise/DivideConst/DivideElewise/
+// Opposite/Sqrt/Relu/Sigmoid/Tanh/Gelu .cpp).  op codes are private to this library.
+enum { U_RELU = 0, U_SIGMOID, U_TANH, U_GELU, U_SQRT, U_RSQRT, U_NEG, U_EXP, U_LOG, U_ABS, U_ADDC, U_MULC, U_CDIV };
+enum { B_ADD = 0, B_SUB, B_MUL, B_DIV, B_RELU_GRAD, B_SIGMOID_GRAD, B_TANH_GRAD, B_GELU_GRAD };
+
+API int hetu_cpu_unary(const float* x, float* y, int64_t n, int op, float c) {
+#pragma omp parallel for simd
+    for (int64_t i = 0; i < n; ++i) {
+        float v = x[i], r;
+        switch (op) {
+            case U_RELU: r = v > 0.f ? v : 0.f; break;
+            case U_SIGMOID: r = 1.f / (1.f + std::exp(-v)); break;
+            case U_TANH: r = std::tanh(v); break;
+            case U_GELU: r = 0.5f * v * (1.f + std::erf(v * 0.70710678118f)); break;
+            case U_SQRT: r = std::sqrt(v); break;
+            case U_RSQRT: r = 1.f / std::sqrt(v); break;
+            case U_NEG: r = -v; break;
+            case U_EXP: r = std::exp(v); break;
+            case U_LOG: r = std::log(v); break;
+            case U_ABS: r = std::fabs(v); break;
+            case U_ADDC: r = v + c; break;
+            case U_MULC: r = v * c; break;
+            default: r = c / v; break;
+        }
+        y[i] = r;
+    }
+    return 0;
+}
+
+// y = x (op) z ; for the *_GRAD codes x is the forward input (or output for sigmoid/tanh) and z the adjoint
+API int hetu_cpu_binary(const float* x, const float* z, float* y, int64_t n, int op) {
+#pragma omp parallel for simd
+    for (int64_t i = 0; i < n; ++i) {
+        float a = x[i], b = z[i], r;
+        switch (op) {
+            case B_ADD: r = a + b; break;
+            case B_SUB: r = a - b; break;
+            case B_MUL: r = a * b; break;
+            case B_DIV: r = a / b; break;
+            case B_RELU_GRAD: r = a > 0.f ? b : 0.f; break;
+            case B_SIGMOID_GRAD: r = b * a * (1.f - a); break;
+            case B_TANH_GRAD: r = b * (1.f - a * a); break;
+            default: {
+                float cdf = 0.5f * (1.f + std::erf(a * 0.70710678118f));
+                float pdf = 0.3989422804f * std::exp(-0.5f * a * a);
+                r = b * (cdf + a * pdf);
+            }
+        }
+        y[i] = r;
+    }
+    return 0;
+}
+
+API int hetu_cpu_array_set(float* x, int64_t n, float v) {
+#pragma omp parallel for simd
+    for (int64_t i = 0; i < n; ++i) x[i] = v;
+    return 0;
+}
+
+API int hetu_cpu_reshape(const float* x, float* y, int64_t n) {
+    if (x != y) std::memcpy(y, x, sizeof(float) * n);
+    return 0;
+}
+
+// bias-style broadcast of x[cols] (or x[rows/rep, cols]) over the leading dim (BroadcastTo.cpp)
+API int hetu_cpu_broadcast_to(const float* x, float* y, int64_t in_n, int64_t out_n) {
+#pragma omp parallel for
+    for (int64_t i = 0; i < out_n; ++i) y[i] = x[i % in_n];
+    return 0;
+}
+
+API int hetu_cpu_reduce_sum_axis0(const float* x, float* y, int64_t rows, int64_t cols) {
+#pragma omp parallel for
+    for (int64_t j = 0; j < cols; ++j) {
+        float s = 0.f;
+        for (int64_t i = 0; i < rows; ++i) s += x[i * cols + j];
+        y[j] = s;
+    }
+    return 0;
+}
+
+API int hetu_cpu_transpose(const float* x, float* y, const int64_t* in_shape, const int* perm, int ndim) {
+    int64_t in_stride[8], out_shape[8], n = 1;
+    in_stride[ndim - 1] = 1;
+    for (int d = ndim - 2; d >= 0; --d) in_stride[d] = in_stride[d + 1] * in_shape[d + 1];
+    for (int d = 0; d < ndim; ++d) { out_shape[d] = in_shape[perm[d]]; n *= out_shape[d]; }
+#pragma omp parallel for
+    for (int64_t o = 0; o < n; ++o) {
+        int64_t rem = o, src = 0;
+        for (int d = ndim - 1; d >= 0; --d) {
+            src += (rem % out_shape[d]) * in_stride[perm[d]];
+            rem /= out_shape[d];
+        }
+        y[o] = x[src];
+    }
+    return 0;
+}
+
+API int hetu_cpu_concat(const float* a, const float* b, float* y, int64_t outer, int64_t a_inner, int64_t b_inner) {
+#pragma omp parallel for
+    for (int64_t o = 0; o < outer; ++o) {
+        std::memcpy(y + o * (a_inner + b_inner), a + o * a_inner, sizeof(float) * a_inner);
+        std::memcpy(y + o * (a_inner + b_inner) + a_inner, b + o * b_inner, sizeof(float) * b_inner);
+    }
+    return 0;
+}
+
+API int hetu_cpu_concat_grad(const float* g, float* ga, int64_t outer, int64_t a_inner, int64_t total_inner,
+                             int64_t offset) {
+#pragma omp parallel for
+    for (int64_t o = 0; o < outer; ++o)
+        std::memcpy(ga + o * a_inner, g + o * total_inner + offset, sizeof(float) * a_inner);
+    return 0;
+}
+
+// NCHW zero padding of the two spatial dims (Pad.cpp)
+API int hetu_cpu_pad(const float* x, float* y, int64_t nc, int H, int W, int pt, int pb, int pl, int pr, float value) {
+    int Ho = H + pt + pb, Wo = W + pl + pr;
+#pragma omp parallel for
+    for (int64_t p = 0; p < nc; ++p)
+        for (int h = 0; h < Ho; ++h)
+            for (int w = 0; w < Wo; ++w) {
+                int hi = h - pt, wi = w - pl;
+                y[(p * Ho + h) * Wo + w] = (hi >= 0 && hi < H && wi >= 0 && wi < W) ? x[(p * H + hi) * W + wi] : value;
+            }
+    return 0;
+}
+
+API int hetu_cpu_pad_grad(const float* gy, float* gx, int64_t nc, int H, int W, int pt, int pb, int pl, int pr) {
+    int Ho = H + pt + pb, Wo = W + pl + pr;
+#pragma omp parallel for
+    for (int64_t p = 0; p < nc; ++p)
+        for (int h = 0; h < H; ++h)
+            for (int w = 0; w < W; ++w) gx[(p * H + h) * W + w] = gy[(p * Ho + h + pt) * Wo + w + pl];
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// softmax family (Softmax.cpp, SoftmaxCrossEntropy.cpp)
+API int hetu_cpu_softmax(const float* x, float* y, int64_t rows, int64_t cols) {
+#pragma omp parallel for
+    for (int64_t r = 0; r < rows; ++r) {
+        const float* xr = x + r * cols;
+        float* yr = y + r * cols;
+        float m = xr[0];
+        for (int64_t j = 1; j < cols; ++j) m = std::max(m, xr[j]);
+        float s = 0.f;
+        for (int64_t j = 0; j < cols; ++j) { yr[j] = std::exp(xr[j] - m); s += yr[j]; }
+        float inv = 1.f / s;
+        for (int64_t j = 0; j < cols; ++j) yr[j] *= inv;
+    }
+    return 0;
+}
+
+API int hetu_cpu_softmax_cross_entropy(const float* x, const float* label, float* loss, int64_t rows, int64_t cols) {
+#pragma omp parallel for
+    for (int64_t r = 0; r < rows; ++r) {
+        const float* xr = x + r * cols;
+        const float* lr = label + r * cols;
+        float m = xr[0];
+        for (int64_t j = 1; j < cols; ++j) m = std::max(m, xr[j]);
+        float s = 0.f;
+        for (int64_t j = 0; j < cols; ++j) s += std::exp(xr[j] - m);
+        float lse = m + std::log(s), acc = 0.f;
+        for (int64_t j = 0; j < cols; ++j) acc += lr[j] * (lse - xr[j]);
+        loss[r] = acc;
+    }
+    return 0;
+}
+
+API int hetu_cpu_softmax_cross_entropy_grad(const float* x, const float* label, const float* g, float* gx,
+                                            int64_t rows, int64_t cols) {
+#pragma omp parallel for
+    for (int64_t r = 0; r < rows; ++r) {
+        const float* xr = x + r * cols;
+        const float* lr = label + r * cols;
+        float* gr = gx + r * cols;
+        float m = xr[0];
+        for (int64_t j = 1; j < cols; ++j) m = std::max(m, xr[j]);
+        float s = 0.f, lsum = 0.f;
+        for (int64_t j = 0; j < cols; ++j) { gr[j] = std::exp(xr[j] - m); s += gr[j]; lsum += lr[j]; }
+        float inv = 1.f / s, gv = g[r];
+        for (int64_t j = 0; j < cols; ++j) gr[j] = gv * (gr[j] * inv * lsum - lr[j]);
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// convolution = im2col + GEMM (Conv2d.cpp uses dnnl::convolution_forward / backward_data / backward_weights)
+namespace {
+void im2col(const float* x, float* col, int C, int H, int W, int kh, int kw, int pad, int stride, int Ho, int Wo) {
+#pragma omp parallel for
+    for (int c = 0; c < C * kh * kw; ++c) {
+        int wk = c % kw, hk = (c / kw) % kh, ci = c / (kw * kh);
+        for (int ho = 0; ho < Ho; ++ho)
+            for (int wo = 0; wo < Wo; ++wo) {
+                int hi = ho * stride - pad + hk, wi = wo * stride - pad + wk;
+                col[((size_t)c * Ho + ho) * Wo + wo] =
+                    (hi >= 0 && hi < H && wi >= 0 && wi < W) ? x[((size_t)ci * H + hi) * W + wi] : 0.f;
+            }
+    }
+}
+
+void col2im(const float* col, float* x, int C, int H, int W, int kh, int kw, int pad, int stride, int Ho, int Wo) {
+    std::memset(x, 0, sizeof(float) * (size_t)C * H * W);
+#pragma omp parallel for
+    for (int ci = 0; ci < C; ++ci)
+        for (int hk = 0; hk < kh; ++hk)
+            for (int wk = 0; wk < kw; ++wk) {
+                int c = (ci * kh + hk) * kw + wk;
+                for (int ho = 0; ho < Ho; ++ho)
+                    for (int wo = 0; wo < Wo; ++wo) {
+                        int hi = ho * stride - pad + hk, wi = wo * stride - pad + wk;
+                        if (hi >= 0 && hi < H && wi >= 0 && wi < W)
+                            x[((size_t)ci * H + hi) * W + wi] += col[((size_t)c * Ho + ho) * Wo + wo];
+                    }
+            }
+}
+}  // namespace
+
+API int hetu_cpu_conv2d(const float* x, const float* w, float* y, int N, int C, int H, int W, int F, int kh, int kw,
+                        int pad, int stride) {
+    int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+    std::vector<float> col((size_t)C * kh * kw * Ho * Wo);
+    for (int n = 0; n < N; ++n) {
+        im2col(x + (size_t)n * C * H * W, col.data(), C, H, W, kh, kw, pad, stride, Ho, Wo);
+        hetu_cpu_matmul(w, col.data(), y + (size_t)n * F * Ho * Wo, F, Ho * Wo, C * kh * kw, 0, 0, 1.f, 0.f);
+    }
+    return 0;
+}
+
+API int hetu_cpu_conv2d_grad_data(const float* w, const float* gy, float* gx, int N, int C, int H, int W, int F,
+                                  int kh, int kw, int pad, int stride) {
+    int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+    std::vector<float> col((size_t)C * kh * kw * Ho * Wo);
+    for (int n = 0; n < N; ++n) {
+        hetu_cpu_matmul(w, gy + (size_t)n * F * Ho * Wo, col.data(), C * kh * kw, Ho * Wo, F, 1, 0, 1.f, 0.f);
+        col2im(col.data(), gx + (size_t)n * C * H * W, C, H, W, kh, kw, pad, stride, Ho, Wo);
+    }
+    return 0;
+}
+
+API int hetu_cpu_conv2d_grad_filter(const float* x, const float* gy, float* gw, int N, int C, int H, int W, int F,
+                                    int kh, int kw, int pad, int stride) {
+    int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+    std::vector<float> col((size_t)C * kh * kw * Ho * Wo);
+    for (int n = 0; n < N; ++n) {
+        im2col(x + (size_t)n * C * H * W, col.data(), C, H, W, kh, kw, pad, stride, Ho, Wo);
+        hetu_cpu_matmul(gy + (size_t)n * F * Ho * Wo, col.data(), gw, F, C * kh * kw, Ho * Wo, 0, 1, 1.f,
+                        n == 0 ? 0.f : 1.f);
+    }
+    return 0;
+}
+
+// pooling (MaxPool.cpp / AvgPool.cpp).  mode 0 = max, 1 = average (padding counted, as oneDNN
+// pooling_avg_include_padding which the reference selects)
+API int hetu_cpu_pool2d(const float* x, float* y, int64_t nc, int H, int W, int kh, int kw, int pad, int stride,
+                        int mode) {
+    int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+#pragma omp parallel for
+    for (int64_t p = 0; p < nc; ++p)
+        for (int ho = 0; ho < Ho; ++ho)
+            for (int wo = 0; wo < Wo; ++wo) {
+                float acc = mode == 0 ? -INFINITY : 0.f;
+                for (int i = 0; i < kh; ++i)
+                    for (int j = 0; j < kw; ++j) {
+                        int hi = ho * stride - pad + i, wi = wo * stride - pad + j;
+                        if (hi < 0 || hi >= H || wi < 0 || wi >= W) continue;
+                        float v = x[(p * H + hi) * W + wi];
+                        acc = mode == 0 ? std::max(acc, v) : acc + v;
+                    }
+                y[(p * Ho + ho) * Wo + wo] = mode == 0 ? acc : acc / (kh * kw);
+            }
+    return 0;
+}
+
+API int hetu_cpu_pool2d_grad(const float* x, const float* y, const float* gy, float* gx, int64_t nc, int H, int W,
+                             int kh, int kw, int pad, int stride, int mode) {
+    int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+#pragma omp parallel for
+    for (int64_t p = 0; p < nc; ++p) {
+        float* gp = gx + p * H * W;
+        std::memset(gp, 0, sizeof(float) * H * W);
+        for (int ho = 0; ho < Ho; ++ho)
+            for (int wo = 0; wo < Wo; ++wo) {
+                float g = gy[(p * Ho + ho) * Wo + wo], out = y[(p * Ho + ho) * Wo + wo];
+                bool done = false;
+                for (int i = 0; i < kh; ++i)
+                    for (int j = 0; j < kw; ++j) {
+                        int hi = ho * stride - pad + i, wi = wo * stride - pad + j;
+                        if (hi < 0 || hi >= H || wi < 0 || wi >= W) continue;
+                        if (mode == 1) gp[hi * W + wi] += g / (kh * kw);
+                        else if (!done && x[(p * H + hi) * W + wi] == out) { gp[hi * W + wi] += g; done = true; }
+                    }
+            }
+    }
+    return 0;
+}
+
+// batch norm over NCHW (BatchNorm.cpp).  Training mode: batch statistics, running stats updated with
+// ``momentum``; save_mean / save_invstd are kept for the backward pass.
+API int hetu_cpu_batch_norm(const float* x, const float* scale, const float* bias, float* y, float* running_mean,
+                            float* running_var, float* save_mean, float* save_invstd, int N, int C, int HW,
+                            float momentum, float eps, int training) {
+#pragma omp parallel for
+    for (int c = 0; c < C; ++c) {
+        float mean, invstd;
+        if (training) {
+            double s = 0, ss = 0;
+            for (int n = 0; n < N; ++n)
+                for (int i = 0; i < HW; ++i) { double v = x[((size_t)n * C + c) * HW + i]; s += v; ss += v * v; }
+            double cnt = (double)N * HW;
+            mean = (float)(s / cnt);
+            float var = (float)(ss / cnt - (s / cnt) * (s / cnt));
+            invstd = 1.f / std::sqrt(var + eps);
+            running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+            running_var[c] = (1.f - momentum) * running_var[c] + momentum * var;
+            save_mean[c] = mean;
+            save_invstd[c] = invstd;
+        } else {
+            mean = running_mean[c];
+            invstd = 1.f / std::sqrt(running_var[c] + eps);
+        }
+        for (int n = 0; n < N; ++n)
+            for (int i = 0; i < HW; ++i) {
+                size_t k = ((size_t)n * C + c) * HW + i;
+                y[k] = (x[k] - mean) * invstd * scale[c] + bias[c];
+            }
+    }
+    return 0;
+}
+
+API int hetu_cpu_batch_norm_grad(const float* x, const float* gy, const float* scale, const float* save_mean,
+                                 const float* save_invstd, float* gx, float* gscale, float* gbias, int N, int C,
+                                 int HW) {
+#pragma omp parallel for
+    for (int c = 0; c < C; ++c) {
+        double sg = 0, sgx = 0;
+        float mean = save_mean[c], invstd = save_invstd[c];
+        for (int n = 0; n < N; ++n)
+            for (int i = 0; i < HW; ++i) {
+                size_t k = ((size_t)n * C + c) * HW + i;
+                sg += gy[k];
+                sgx += gy[k] * (x[k] - mean) * invstd;
+            }
+        gbias[c] = (float)sg;
+        gscale[c] = (float)sgx;
+        float cnt = (float)N * HW;
+        for (int n = 0; n < N; ++n)
+            for (int i = 0; i < HW; ++i) {
+                size_t k = ((size_t)n * C + c) * HW + i;
+                float xh = (x[k] - mean) * invstd;
+                gx[k] = scale[c] * invstd * (gy[k] - (float)sg / cnt - xh * (float)sgx / cnt);
+            }
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// dropout: counter-based hash so the backward pass regenerates the mask from (seed, index)
+// (Dropout.cpp keeps the seed for the same purpose)
+static inline uint32_t mix32(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return (uint32_t)((z ^ (z >> 31)) >> 32);
+}
+
+API int hetu_cpu_dropout(const float* x, float* y, int64_t n, float keep_prob, uint64_t seed) {
+    float inv = 1.f / keep_prob;
+#pragma omp parallel for
+    for (int64_t i = 0; i < n; ++i) {
+        float u = mix32(seed * 0x100000001B3ull + (uint64_t)i) * (1.f / 4294967296.f);
+        y[i] = u < keep_prob ? x[i] * inv : 0.f;
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// embedding (EmbeddingLookup.cpp:15-35) and optimizers (Optimizers.cpp:19-60)
+API int hetu_cpu_embedding_lookup(const float* table, const int64_t* ids, float* out, int64_t nids, int64_t width,
+                                  int64_t nrows) {
+#pragma omp parallel for
+    for (int64_t i = 0; i < nids; ++i) {
+        int64_t r = ids[i];
+        if (r < 0 || r >= nrows) std::memset(out + i * width, 0, sizeof(float) * width);
+        else std::memcpy(out + i * width, table + r * width, sizeof(float) * width);
+    }
+    return 0;
+}
+
+API int hetu_cpu_sgd_update(float* p, const float* g, int64_t n, float lr, float l2) {
+#pragma omp parallel for simd
+    for (int64_t i = 0; i < n; ++i) p[i] -= lr * (g[i] + l2 * p[i]);
+    return 0;
+}
+
+// rows may repeat: serial over ids, parallel over the row (matches the reference's accumulate semantics)
+API int hetu_cpu_sgd_sparse_update(float* p, const int64_t* ids, const float* g, int64_t nids, int64_t width,
+                                   float lr) {
+    for (int64_t i = 0; i < nids; ++i) {
+        float* row = p + ids[i] * width;
+        const float* gr = g + i * width;
+#pragma omp simd
+        for (int64_t j = 0; j < width; ++j) row[j] -= lr * gr[j];
+    }
+    return 0;
+}
+
+API int hetu_cpu_momentum_update(float* p, const float* g, float* vel, int64_t n, float lr, float momentum,
+                                 int nesterov, float l2) {
+#pragma omp parallel for simd
+    for (int64_t i = 0; i < n; ++i) {
+        float gi = g[i] + l2 * p[i];
+        float v = momentum * vel[i] - lr * gi;
+        vel[i] = v;
+        p[i] += nesterov ? momentum * v - lr * gi : v;
+    }
+    return 0;
+}
+
+API int hetu_cpu_adagrad_update(float* p, const float* g, float* acc, int64_t n, float lr, float eps, float l2) {
+#pragma omp parallel for simd
+    for (int64_t i = 0; i < n; ++i) {
+        float gi = g[i] + l2 * p[i];
+        acc[i] += gi * gi;
+        p[i] -= lr * gi / (std::sqrt(acc[i]) + eps);
+    }
+    return 0;
+}
+
+API int hetu_cpu_adam_update(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
+                             float beta2, float eps, int64_t step, float l2, int amsgrad, float* vmax) {
+    float c1 = 1.f - std::pow(beta1, (float)step), c2 = 1.f - std::pow(beta2, (float)step);
+#pragma omp parallel for simd
+    for (int64_t i = 0; i < n; ++i) {
+        float gi = g[i] + l2 * p[i];
+        m[i] = beta1 * m[i] + (1.f - beta1) * gi;
+        v[i] = beta2 * v[i] + (1.f - beta2) * gi * gi;
+        float vh = v[i];
+        if (amsgrad) { vmax[i] = std::max(vmax[i], vh); vh = vmax[i]; }
+        p[i] -= lr * (m[i] / c1) / (std::sqrt(vh / c2) + eps);
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// initialisers (Initializers.cpp): one engine per thread, seeded from (seed, thread)
+API int hetu_cpu_uniform_init(float* x, int64_t n, float lo, float hi, uint64_t seed) {
+#pragma omp parallel
+    {
+        std::mt19937_64 gen(seed * 1000003ull + omp_get_thread_num());
+        std::uniform_real_distribution<float> d(lo, hi);
+#pragma omp for schedule(static)
+        for (int64_t i = 0; i < n; ++i) x[i] = d(gen);
+    }
+    return 0;
+}
+
+API int hetu_cpu_normal_init(float* x, int64_t n, float mean, float stddev, uint64_t seed) {
+#pragma omp parallel
+    {
+        std::mt19937_64 gen(seed * 1000003ull + omp_get_thread_num());
+        std::normal_distribution<float> d(mean, stddev);
+#pragma omp for schedule(static)
+        for (int64_t i = 0; i < n; ++i) x[i] = d(gen);
+    }
+    return 0;
+}
+
+API int hetu_cpu_truncated_normal_init(float* x, int64_t n, float mean, float stddev, uint64_t seed) {
+#pragma omp parallel
+    {
+        std::mt19937_64 gen(seed * 1000003ull + omp_get_thread_num());
+        std::normal_distribution<float> d(mean, stddev);
+#pragma omp for schedule(static)
+        for (int64_t i = 0; i < n; ++i) {
+            float v;
+            do { v = d(gen); } while (std::fabs(v - mean) > 2.f * stddev);
+            x[i] = v;
+        }
+    }
+    return 0;
+}
+
+API int hetu_cpu_num_threads() { return omp_get_max_threads(); }

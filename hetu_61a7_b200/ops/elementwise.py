@@ -69,6 +69,20 @@ def _k(*ts):
     return L.kernels_on(*ts) and all(t.dtype == _F32 for t in ts)
 
 
+#: GPU opcode -> CPU library opcode for the activations the CPU executor runs natively
+_CPU_UNARY = {U['RELU']: 0, U['SIGMOID']: 1, U['TANH']: 2, U['SQRT']: 4, U['RSQRT']: 5, U['OPPOSITE']: 6}
+_CPU_BINARY = {B['RELU_GRAD']: 4}
+_cpu_state = {}
+
+
+def _cpu_native() -> bool:
+    if 'on' not in _cpu_state:
+        import os
+        from .. import cpu_links
+        _cpu_state['on'] = os.environ.get('HETU_CPU_NATIVE', '1') == '1' and cpu_links.available()
+    return _cpu_state['on']
+
+
 # --------------------------------------------------------------------- unary
 class UnaryOp(Op):
     """y = f(x; a, b).  Sub-classes set ``code`` / ``fn`` / ``grad``."""
@@ -85,6 +99,13 @@ class UnaryOp(Op):
         x = input_vals[0]
         if _k(x):
             return _unary_kernel(self.code, x, float(self.a), float(self.b))
+        cpu_code = _CPU_UNARY.get(self.code)
+        if cpu_code is not None and x.device.type == 'cpu' and x.dtype == _F32 and _cpu_native():
+            from .. import cpu_links
+            x = x.contiguous()
+            y = torch.empty_like(x)
+            cpu_links._unary(cpu_code, x, y)
+            return y
         return self.fn(x)
 
     def infer_shape(self, input_shapes):
@@ -111,6 +132,14 @@ class BinaryOp(Op):
         x, y = input_vals
         if _k(x, y) and x.shape == y.shape:
             return _binary_kernel(self.code, x, y, float(self.a))
+        cpu_code = _CPU_BINARY.get(self.code)
+        if cpu_code is not None and x.device.type == 'cpu' and x.shape == y.shape and x.dtype == _F32 \
+                and y.dtype == _F32 and _cpu_native():
+            from .. import cpu_links
+            x, y = x.contiguous(), y.contiguous()
+            out = torch.empty_like(x)
+            cpu_links._binary(cpu_code, x, y, out)
+            return out
         return self.fn(x, y)
 
     def infer_shape(self, input_shapes):

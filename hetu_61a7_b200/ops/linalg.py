@@ -79,12 +79,26 @@ def gemm(a: torch.Tensor, b: torch.Tensor, trans_a=False, trans_b=False, bias=No
     return c
 
 
+def _cpu_native(*ts) -> bool:
+    """CPU executor: route through the OpenMP op library (csrc_cpu) when it is built."""
+    from .. import cpu_links
+    return (os.environ.get('HETU_CPU_NATIVE', '1') == '1' and cpu_links.available()
+            and all(t.device.type == 'cpu' and t.dtype == torch.float32 for t in ts))
+
+
 def _gemm_torch(a, b, trans_a, trans_b, bias, c_in, alpha, beta, act):
-    if trans_a:
-        a = a.transpose(-1, -2)
-    if trans_b:
-        b = b.transpose(-1, -2)
-    y = torch.matmul(a, b)
+    if a.dim() == 2 and b.dim() == 2 and _cpu_native(a, b):
+        from .. import cpu_links
+        m = a.shape[1] if trans_a else a.shape[0]
+        n = b.shape[0] if trans_b else b.shape[1]
+        y = torch.empty((m, n), dtype=torch.float32)
+        cpu_links.matrix_multiply(a.contiguous(), trans_a, b.contiguous(), trans_b, y)
+    else:
+        if trans_a:
+            a = a.transpose(-1, -2)
+        if trans_b:
+            b = b.transpose(-1, -2)
+        y = torch.matmul(a, b)
     if alpha != 1.0:
         y = y * alpha
     if c_in is not None and beta != 0.0:

@@ -21,6 +21,9 @@ def _k(*ts):
     return L.kernels_on(*ts) and all(t.dtype == torch.float32 for t in ts)
 
 
+from .elementwise import _cpu_native  # noqa: E402
+
+
 class SoftmaxCrossEntropyOp(Op):
     """loss[b] = -sum_c y_[b,c] * log softmax(x)[b,c]"""
 
@@ -38,6 +41,12 @@ class SoftmaxCrossEntropyOp(Op):
             loss = torch.empty(x.shape[:-1], dtype=x.dtype, device=x.device)
             L.call('softmax_xent', L.p(x), L.p(y_), L.p(loss), L.c_int(rows), L.c_int(cols),
                    L.stream_ptr(x.device))
+            return loss
+        if x.device.type == 'cpu' and x.dtype == torch.float32 and y_.dtype == torch.float32 \
+                and x.shape == y_.shape and _cpu_native():
+            from .. import cpu_links
+            loss = torch.empty(x.shape[:-1], dtype=x.dtype)
+            cpu_links.softmax_crossentropy(x.contiguous(), y_.contiguous(), loss)
             return loss
         return -(y_ * torch.log_softmax(x, dim=-1)).sum(dim=-1)
 

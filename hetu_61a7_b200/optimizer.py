@@ -265,6 +265,13 @@ class SGDOptimizer(Optimizer):
         super().__init__(learning_rate, l2reg)
 
     def _dense_torch(self, p, g, st):
+        if p.device.type == 'cpu' and p.dtype == torch.float32 and p.is_contiguous() and g.shape == p.shape \
+                and g.dtype == torch.float32:
+            from .ops.elementwise import _cpu_native
+            if _cpu_native():                          # CPU executor: OpenMP library (csrc_cpu)
+                from . import cpu_links
+                cpu_links.sgd_update(p, g.contiguous(), float(self.lr_t), float(self.l2reg))
+                return
         if self.l2reg > 0:
             g = g + self.l2reg * p
         p.sub_(self.lr_t.to(p.device) * g)
