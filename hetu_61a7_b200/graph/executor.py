@@ -122,6 +122,16 @@ class HetuConfig(object):
         if dist_strategy is None:
             if ctx is None:
                 ctx = get_current_context()
+            if ctx is None:
+                # executor built outside every ``with ht.context`` block: take the placement the
+                # graph itself carries (the reference asserts here; its scripts build the
+                # executor inside the last block)
+                flat_eval = [n for v in (eval_node_list.values() if isinstance(eval_node_list, dict)
+                                         else [eval_node_list]) for n in v]
+                for n in flat_eval:
+                    if n.raw_ctx is not None and len(n.raw_ctx) > 0 and not isinstance(n, OptimizerOp):
+                        ctx = n.raw_ctx
+                        break
         else:
             ctx = dist_strategy.set_raw_ctxs_n_states(eval_node_list, None)
         if ctx is None:
@@ -342,8 +352,9 @@ class Executor(object):
             new_dict = {}
             for k, v in eval_node_dict.items():
                 keep = [n for n in v if n not in config.dropped_eval_nodes]
-                sends = [n for n in config.my_eval_nodes if isinstance(n, PipelineSendOp)
-                         and n.inputs[0] in ancestors[k] and n not in keep]
+                sends = [n for n in config.my_eval_nodes if n not in keep and (
+                    (isinstance(n, PipelineSendOp) and n.inputs[0] in ancestors[k])
+                    or (n in ancestors[k] and n not in v and n not in all_eval_nodes))]
                 merged = [n for n in config.my_eval_nodes if n in keep or n in sends]
                 new_dict[k] = merged
             self.full_eval_node_dict = eval_node_dict
@@ -370,6 +381,9 @@ class Executor(object):
             return SubExecutor(name, nodes, config)
 
         self.subexecutor: Dict[str, SubExecutor] = {k: make(k, v) for k, v in eval_node_dict.items()}
+        for k, sub in self.subexecutor.items():
+            # results are always reported for the user's own list (None for nodes of other ranks)
+            sub.result_nodes = list(getattr(self, 'full_eval_node_dict', eval_node_dict)[k])
         self.topo_order = find_topo_sort(all_eval_nodes)
         self.param_nodes = [n for n in self.topo_order if isinstance(n, PlaceholderOp) and n.trainable]
 
@@ -508,6 +522,10 @@ class SubExecutor(object):
         self.inference = not any(isinstance(n, OptimizerOp) for n in eval_node_list)
         self.topo_order = (find_topo_sort_inference(self.eval_node_list) if self.inference
                            else find_topo_sort(self.eval_node_list))
+        if any(hasattr(n, 'global_order') for n in self.topo_order):
+            # placed graph: every rank walks its nodes in the order of the ONE global topological
+            # sort, so collectives and blocking receives pair up identically on all ranks
+            self.topo_order.sort(key=lambda n: getattr(n, 'global_order', float('inf')))
         self.dataloader_nodes = [n for n in self.topo_order
                                  if isinstance(n, (DataloaderOp, GNNDataLoaderOp))]
         self.param_nodes = [n for n in self.topo_order
@@ -638,7 +656,7 @@ class SubExecutor(object):
 
     # --------------------------------------------------------------------------- run
     def run(self, eval_node_list=[], feed_dict={}, convert_to_numpy_ret_vals=False, **kwargs):
-        eval_nodes = list(eval_node_list) if eval_node_list else self.eval_node_list
+        eval_nodes = list(eval_node_list) if eval_node_list else getattr(self, 'result_nodes', self.eval_node_list)
         feeds: Dict[Op, object] = {}
         for node, value in feed_dict.items():
             feeds[node] = self._feed_tensor(node, value)

@@ -268,7 +268,7 @@ def adapt(op) -> None:
     # everything else needs replicated inputs
     for k, i in enumerate(op.inputs):
         if i is not None and getattr(i, 'mp_state', None) is not None:
-            op.inputs[k] = to_replicated(i, getattr(i, 'mp_group', group), ctx=ctx)
+            op.inputs[k] = to_replicated(i, getattr(i, 'mp_group', group), ctx=i.raw_ctx)   # runs on the whole worker
     op.mp_state = None
 
 
@@ -286,7 +286,8 @@ def match_grad_state(grad, node):
     group = getattr(node, 'mp_group', None) or getattr(grad, 'mp_group', None)
     if group is None:
         return grad
-    ctx = node.raw_ctx if getattr(node, 'mp_group', None) is not None else grad.raw_ctx
+    # the conversion is a collective of the whole MP worker: run it under the tuple context
+    ctx = grad.raw_ctx if (grad.raw_ctx is not None and grad.raw_ctx.is_mp) else node.raw_ctx
     if want is None:
         out = to_replicated(grad, group, ctx=ctx)
     elif have is not None and have[0] == 'partial':

@@ -147,7 +147,7 @@ class SubExecutor4Gpipe(_PipeBase):
 
     def run(self, eval_node_list=[], feed_dict={}, convert_to_numpy_ret_vals=False, batch_num=None, **kwargs):
         M = batch_num or 1
-        eval_nodes = list(eval_node_list) if eval_node_list else self.eval_node_list
+        eval_nodes = list(eval_node_list) if eval_node_list else getattr(self, 'result_nodes', self.eval_node_list)
         self._pre_step()
         all_vals = []
         for m in range(M):
@@ -179,7 +179,7 @@ class SubExecutor4Pipedream(_PipeBase):
 
     def run(self, eval_node_list=[], feed_dict={}, convert_to_numpy_ret_vals=False, batch_num=None, **kwargs):
         M = batch_num or 1
-        eval_nodes = list(eval_node_list) if eval_node_list else self.eval_node_list
+        eval_nodes = list(eval_node_list) if eval_node_list else getattr(self, 'result_nodes', self.eval_node_list)
         cfg = self.config
         self._pre_step()
         vals_of: Dict[int, dict] = {}

@@ -101,6 +101,8 @@ def assign_placement(config, eval_nodes) -> None:
         members = w if isinstance(w, tuple) else (w,)
         return members[k % len(members)].device_id
 
+    for i, n in enumerate(topo):
+        n.global_order = float(i)
     recv_cache: Dict = {}
     sends: List = []
     sent = set()
@@ -124,6 +126,7 @@ def assign_placement(config, eval_nodes) -> None:
                                              ctx=v.raw_ctx)
                     rv.ctx = config.context
                     rv.name = 'recv_%s_from%d' % (u.name, src)
+                    rv.global_order = v.global_order - 0.5
                     recv_cache[u] = rv
                 v.inputs[idx] = recv_cache[u]
             # producer side
@@ -133,12 +136,19 @@ def assign_placement(config, eval_nodes) -> None:
                         sent.add((u, r))
                         sd = pipeline_send_op(u, r, config.nccl_comm, ctx=u.raw_ctx)
                         sd.name = 'send_%s_to%d' % (u.name, r)
+                        sd.global_order = v.global_order - 0.25
                         sends.append((topo.index(v), sd))
     # this rank evaluates: its own eval nodes + its sends, interleaved in topological position so
     # that both sides of every p2p pair issue them in the same relative order
     my_eval = [n for n in eval_nodes if mine(n)]
     order = {n: i for i, n in enumerate(topo)}
-    merged = [(order.get(n, len(topo)), 1, n) for n in my_eval] + [(pos, 0, sd) for pos, sd in sends]
+    # a collective of a model-parallel worker needs every member, also the ones whose own
+    # results do not depend on it (e.g. the all-gather that only feeds the next stage)
+    from .mp_lowering import MPAllGatherOp, MPAllReduceOp, MPReduceScatterOp
+    coll = [n for n in topo if isinstance(n, (MPAllGatherOp, MPAllReduceOp, MPReduceScatterOp))
+            and me in _ranks(n.raw_ctx) and n not in my_eval]
+    merged = [(order.get(n, len(topo)), 1, n) for n in my_eval] + [(pos, 0, sd) for pos, sd in sends] \
+        + [(order[n], 1, n) for n in coll]
     merged.sort(key=lambda t: (t[0], t[1]))
     config.my_eval_nodes = [n for _, _, n in merged]
     config.dropped_eval_nodes = [n for n in eval_nodes if not mine(n)]

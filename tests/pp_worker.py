@@ -103,6 +103,9 @@ else:
             got.append(float(out[0].asnumpy()))
     ref_l, ref_w = oracle(3, 4, per_micro_update=True)
 
+# the graph must really be cut: stage-0 weights live on rank 0 only, stage-2 weights on rank 1 only
+assert (mine(ex, ws[0]) is not None) == (rank == 0), 'placement did not prune w1 on rank %d' % rank
+assert (mine(ex, ws[2]) is not None) == (rank == 1), 'placement did not prune w3 on rank %d' % rank
 if ref_l is not None:
     if got:
         assert np.allclose(got, ref_l, rtol=2e-4, atol=1e-5), (got[:4], ref_l[:4])
