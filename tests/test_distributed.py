@@ -51,3 +51,12 @@ def _launch_pp(mode, case, timeout=600):
 @pytest.mark.parametrize('case', ['gpipe', 'pipedream', 'left', 'right', 'middle'])
 def test_pipeline_and_model_parallel_equivalence_gloo(case):
     _launch_pp('cpu', case)
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize('case', ['gpipe', 'pipedream', 'left', 'right', 'middle'])
+def test_pipeline_and_model_parallel_equivalence_nccl(case):
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs >= 2 GPUs (gpurun --gpus 2)')
+    _launch_pp('gpu', case)
