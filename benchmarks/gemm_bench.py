@@ -13,7 +13,8 @@ except Exception:
     pass
 shapes = [(32768, 2048, 2048, False, False), (32768, 2048, 2048, False, True), (2048, 2048, 32768, True, False),
           (16384, 2048, 2048, False, False), (4096, 4096, 1024, False, False), (4096, 1024, 4096, False, False),
-          (8192, 8192, 8192, False, False), (16384, 16, 2048, False, False)]
+          (8192, 8192, 8192, False, False), (16384, 16, 2048, False, False),
+          (2048, 2048, 16384, True, False), (16384, 2, 2048, False, False), (2048, 2, 16384, True, False)]
 flush = torch.empty(256 * 1024 * 1024 // 4, device=dev)
 for (m, n, k, tA, tB) in shapes:
     a = torch.randn((k, m) if tA else (m, k), device=dev)

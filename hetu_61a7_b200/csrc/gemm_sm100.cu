@@ -139,6 +139,8 @@ struct GemmParams {
     long long sC;
     int a_mn_major, b_mn_major;    // 1 = MN-major (A given as [K,M] / B given as [K,N])
     int a_batched, b_batched;
+    int dbg;                       // diagnostics: 1 = no TMA after the first ring fill, 2 = no MMA
+    int a_mn4, b_mn4;              // MN-major operand described by ONE 4-D box {32 mn, 32 k, 4 groups, 1}
     float alpha, beta;
     int act;
 };
@@ -324,6 +326,24 @@ static int make_tmap(CUtensorMap* map, const float* base, long long inner, long 
     return 0;
 }
 
+// MN-major operand stored [rows_k][inner_mn] with inner_mn % 32 == 0, viewed as {32, rows_k, inner_mn/32, batch}:
+// one box {32, 32, 4, 1} lands in shared memory as 4 groups of [32 k][128 B], exactly the UMMA MN-major
+// layout, with a single TMA instruction instead of four.
+static int make_tmap_mn4(CUtensorMap* map, const float* base, long long inner, long long rows, long long batch,
+                         long long batch_stride_elems) {
+    auto fn = get_encode_fn();
+    if (!fn) { hetu_set_error("cuTensorMapEncodeTiled entry point not found"); return -1; }
+    cuuint64_t dims[4] = {32, (cuuint64_t)rows, (cuuint64_t)(inner / 32), (cuuint64_t)(batch > 0 ? batch : 1)};
+    cuuint64_t strides[3] = {(cuuint64_t)inner * 4, 128, (cuuint64_t)(batch > 1 ? batch_stride_elems : inner * rows) * 4};
+    cuuint32_t box[4] = {32, 32, 4, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return -1;
+    return 0;
+}
+
 template <int BLOCK_N>
 static int launch_tc(const float* A, const float* B, GemmParams& p, int batch, long long sA, long long sB, cudaStream_t s) {
     using Cfg = GemmCfg<BLOCK_N>;
@@ -340,6 +360,371 @@ static int launch_tc(const float* A, const float* B, GemmParams& p, int batch, l
     }
     dim3 grid((p.N + BLOCK_N - 1) / BLOCK_N, (p.M + BLOCK_M - 1) / BLOCK_M, batch);
     gemm_tf32_tcgen05_kernel<BLOCK_N><<<grid, kGemmThreads, Cfg::kSmem, s>>>(tmA, tmB, p);
+    return 0;
+}
+
+// ============================================================ 2-SM persistent tcgen05 GEMM
+// Large problems: a CTA pair (cluster 2x1x1, the two SMs of a TPC) owns a 256x256 output tile.
+// Each CTA stages its own 128 rows of A and its own 128 columns of B (32 KB per k-block instead
+// of 48 KB for the 1-SM 128x256 tile, which is what bounds the tf32 kernel: L2 -> smem bytes);
+// the leader CTA issues tcgen05.mma.cta_group::2 (M = 256), which reads both CTAs' shared memory
+// and writes rows 0-127 to the leader's TMEM and rows 128-255 to the peer's.  The kernel is
+// persistent (static round-robin over tiles, M fastest so concurrent tiles share a B panel in
+// L2) and double-buffers the accumulator in TMEM (2 x 256 columns), so the epilogue of tile i
+// overlaps the main loop of tile i+1.
+//   barriers: full[s]   leader only, tx bytes of BOTH CTAs' TMA loads land here
+//             empty[s]  per CTA, armed by tcgen05.commit ... multicast::cluster (mask 0b11)
+//             tfull[a]  per CTA, multicast commit after the last k-block of a tile
+//             tempty[a] leader only, 8 arrivals = 4 epilogue warps x 2 CTAs (peer arrives remotely)
+constexpr int k2Stages = 6;
+constexpr int k2ABytes = BLOCK_M * BLOCK_K * 4;            // 16 KB : 128 rows of A
+constexpr int k2BBytes = 128 * BLOCK_K * 4;                // 16 KB : this CTA's 128 columns of B
+constexpr int k2StageBytes = k2ABytes + k2BBytes;
+constexpr int k2EpiBytes = 4 * 32 * 36 * 4;
+constexpr int k2Smem = k2Stages * k2StageBytes + k2EpiBytes + 1024 + 256;
+constexpr int k2TileN = 256;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_3d_2sm(void* dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* leader_bar) {
+    // peer bit (bit 24 of the shared::cluster address) cleared: the bytes are counted on CTA 0's barrier
+    asm volatile(
+        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(leader_bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_2sm(void* dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint64_t* leader_bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(leader_bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_2sm(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
+    asm volatile(
+        "{\n\t"
+        ".reg .b16 m;\n\t"
+        "mov.b16 m, 3;\n\t"
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n\t"
+        "}" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, 0;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t"
+        "}" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Tile order: bands of up to 8 N-tiles, N fastest inside a band, so the ~74 tiles in flight share a few
+// A panels and one band of B in L2 and A is streamed from HBM once per band (M fastest re-read A
+// once per N tile: 2.2 GB of DRAM reads for the 32768x2048x2048 case, measured with ncu).
+__device__ __forceinline__ void decode_tile(int tile, int tiles_m, int tiles_n, int& bz, int& tm, int& tn) {
+    const int tiles_mn = tiles_m * tiles_n;
+    bz = tile / tiles_mn;
+    int rem = tile - bz * tiles_mn;
+    const int band_sz = 8 * tiles_m;
+    const int band = rem / band_sz;
+    rem -= band * band_sz;
+    const int bw = min(8, tiles_n - band * 8);
+    tm = rem / bw;
+    tn = band * 8 + (rem - tm * bw);
+}
+
+// Work scheduler shared by the three warp roles.  Normal mode: whole tiles, round-robin over clusters.
+// Stream-K mode (few tiles, long K - weight gradients): the k-blocks of all tiles form one sequence
+// that is cut into equal contiguous ranges, one per cluster; a range that covers only part of a tile is
+// added into the zero-initialised C with red.global.add.v4.f32.
+struct TileSched {
+    int tile, step, num_tiles, num_kb, streamk;
+    long long pos, end;
+    __device__ __forceinline__ TileSched(int cluster_id, int num_clusters, int num_tiles_, int num_kb_, int kb_per_cluster)
+        : tile(cluster_id), step(num_clusters), num_tiles(num_tiles_), num_kb(num_kb_), streamk(kb_per_cluster > 0) {
+        pos = (long long)cluster_id * kb_per_cluster;
+        const long long total = (long long)num_tiles_ * num_kb_;
+        end = pos + kb_per_cluster < total ? pos + kb_per_cluster : total;
+    }
+    __device__ __forceinline__ bool next(int& t, int& kb0, int& kb1) {
+        if (!streamk) {
+            if (tile >= num_tiles) return false;
+            t = tile; kb0 = 0; kb1 = num_kb; tile += step;
+            return true;
+        }
+        if (pos >= end) return false;
+        t = (int)(pos / num_kb);
+        kb0 = (int)(pos - (long long)t * num_kb);
+        const long long left = end - pos;
+        kb1 = (num_kb - kb0) < left ? num_kb : kb0 + (int)left;
+        pos += kb1 - kb0;
+        return true;
+    }
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p,
+                     int tiles_m, int tiles_n, int num_tiles, int kb_per_cluster) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + k2Stages * k2ABytes;
+    float* smem_epi = reinterpret_cast<float*>(smem + k2Stages * k2StageBytes);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + k2Stages * k2StageBytes + k2EpiBytes);
+    uint64_t* empty_bar = full_bar + k2Stages;
+    uint64_t* tfull_bar = empty_bar + k2Stages;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+    const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+        for (int i = 0; i < k2Stages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 8); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_2sm(tmem_ptr_smem, 512);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                     // peer barriers are initialised before anyone signals them
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ TMA producer (both CTAs)
+        if (lane == 0) {
+            int it = 0, tile, kb0, kb1;
+            TileSched sched(cluster_id, num_clusters, num_tiles, num_kb, kb_per_cluster);
+            while (sched.next(tile, kb0, kb1)) {
+                int bz, tm, tn;
+                decode_tile(tile, tiles_m, tiles_n, bz, tm, tn);
+                const int m0 = tm * 256 + (int)rank * 128, nb0 = tn * k2TileN + (int)rank * 128;
+                const int ba = p.a_batched ? bz : 0, bb = p.b_batched ? bz : 0;
+                for (int kb = kb0; kb < kb1; ++kb, ++it) {
+                    const int st = it % k2Stages;
+                    if (it >= k2Stages) mbar_wait(&empty_bar[st], ((it / k2Stages) - 1) & 1);
+                    if (p.dbg == 1 && it >= k2Stages) {
+                        if (rank == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&full_bar[st])) : "memory");
+                        continue;
+                    }
+                    if (rank == 0) mbar_expect_tx(&full_bar[st], 2 * k2StageBytes);
+                    uint8_t* a_dst = smem_a + st * k2ABytes;
+                    uint8_t* b_dst = smem_b + st * k2BBytes;
+                    const int k0 = kb * BLOCK_K;
+                    if (!p.a_mn_major) {
+                        tma_load_3d_2sm(a_dst, &tmA, k0, m0, ba, &full_bar[st]);
+                    } else if (p.a_mn4) {
+                        tma_load_4d_2sm(a_dst, &tmA, 0, k0, m0 >> 5, ba, &full_bar[st]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            tma_load_3d_2sm(a_dst + j * (BLOCK_K * 128), &tmA, m0 + j * 32, k0, ba, &full_bar[st]);
+                    }
+                    if (!p.b_mn_major) {
+                        tma_load_3d_2sm(b_dst, &tmB, k0, nb0, bb, &full_bar[st]);
+                    } else if (p.b_mn4) {
+                        tma_load_4d_2sm(b_dst, &tmB, 0, k0, nb0 >> 5, bb, &full_bar[st]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            tma_load_3d_2sm(b_dst + j * (BLOCK_K * 128), &tmB, nb0 + j * 32, k0, bb, &full_bar[st]);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------ MMA issuer (leader CTA only)
+        if (lane == 0 && rank == 0) {
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)p.a_mn_major << 15) |
+                                   ((uint32_t)p.b_mn_major << 16) | ((uint32_t)(k2TileN >> 3) << 17) |
+                                   ((uint32_t)(256 >> 4) << 24);
+            int it = 0, t_iter = 0, tile, kb0, kb1;
+            TileSched sched(cluster_id, num_clusters, num_tiles, num_kb, kb_per_cluster);
+            for (; sched.next(tile, kb0, kb1); ++t_iter) {
+                const int acc = t_iter & 1;
+                if (t_iter >= 2) mbar_wait(&tempty_bar[acc], ((t_iter >> 1) - 1) & 1);   // epilogues drained this buffer
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * k2TileN);
+                for (int kb = kb0; kb < kb1; ++kb, ++it) {
+                    const int st = it % k2Stages;
+                    mbar_wait(&full_bar[st], (it / k2Stages) & 1);
+                    tc_fence_after();
+                    const uint32_t a_base = smem_u32(smem_a + st * k2ABytes);
+                    const uint32_t b_base = smem_u32(smem_b + st * k2BBytes);
+#pragma unroll
+                    for (int ki = 0; ki < BLOCK_K / UMMA_K; ++ki) {
+                        uint64_t a_desc = p.a_mn_major ? make_smem_desc(a_base + ki * (UMMA_K * 128), BLOCK_K * 128, 512, 1)
+                                                       : make_smem_desc(a_base + ki * (UMMA_K * 4), 16, 1024, 2);
+                        uint64_t b_desc = p.b_mn_major ? make_smem_desc(b_base + ki * (UMMA_K * 128), BLOCK_K * 128, 512, 1)
+                                                       : make_smem_desc(b_base + ki * (UMMA_K * 4), 16, 1024, 2);
+                        if (p.dbg != 2) umma_tf32_2sm(d_tmem, a_desc, b_desc, idesc, (kb > kb0 || ki > 0) ? 1u : 0u);
+                    }
+                    umma_commit_2sm(&empty_bar[st]);
+                }
+                umma_commit_2sm(&tfull_bar[acc]);
+            }
+        }
+    } else {
+        // ------------------------------------------------------------ epilogue (warps 2..5, both CTAs)
+        const int q = warp & 3;
+        float* tile_s = smem_epi + (warp - 2) * (32 * 36);
+        const int sub_row = lane >> 3, c4 = (lane & 7) * 4;
+        int t_iter = 0, tile, kb0, kb1;
+        TileSched sched(cluster_id, num_clusters, num_tiles, num_kb, kb_per_cluster);
+        for (; sched.next(tile, kb0, kb1); ++t_iter) {
+            const int acc = t_iter & 1;
+            const bool partial = kb0 != 0 || kb1 != num_kb;        // stream-K fragment: accumulate into C
+            int bz, tm, tn;
+            decode_tile(tile, tiles_m, tiles_n, bz, tm, tn);
+            const int m0 = tm * 256 + (int)rank * 128, n0 = tn * k2TileN;
+            mbar_wait(&tfull_bar[acc], (t_iter >> 1) & 1);
+            tc_fence_after();
+            float* Cb = p.C + (size_t)bz * p.sC;
+            const int row_base = m0 + q * 32;
+            const bool vec_ok = (p.N & 3) == 0 && ((reinterpret_cast<uintptr_t>(Cb) & 15) == 0);
+#pragma unroll 1
+            for (int c0 = 0; c0 < k2TileN; c0 += 32) {
+                if (n0 + c0 >= p.N || row_base >= p.M) break;
+                float v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * k2TileN + c0), v);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<float4*>(&tile_s[lane * 36 + j * 4]) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                __syncwarp();
+                const int col = n0 + c0 + c4;
+                if (partial) {
+                    for (int r = 0; r < 32; r += 4) {
+                        const int row = row_base + r + sub_row;
+                        if (row >= p.M) continue;
+                        float* dst = Cb + (size_t)row * p.N + col;
+                        const float* src = &tile_s[(r + sub_row) * 36 + c4];
+                        if (vec_ok && col + 3 < p.N) {
+                            float4 o = make_float4(p.alpha * src[0], p.alpha * src[1], p.alpha * src[2], p.alpha * src[3]);
+                            if (kb0 == 0 && p.bias != nullptr) {
+                                const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+                                o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+                            }
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(o.x), "f"(o.y), "f"(o.z), "f"(o.w) : "memory");
+                        } else {
+                            for (int u = 0; u < 4 && col + u < p.N; ++u)
+                                atomicAdd(dst + u, p.alpha * src[u] + ((kb0 == 0 && p.bias) ? __ldg(p.bias + col + u) : 0.f));
+                        }
+                    }
+                } else if (vec_ok && col + 3 < p.N) {
+                    float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (p.bias != nullptr) bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+#pragma unroll
+                    for (int r = 0; r < 32; r += 4) {
+                        const int row = row_base + r + sub_row;
+                        if (row < p.M) {
+                            float4 a = *reinterpret_cast<const float4*>(&tile_s[(r + sub_row) * 36 + c4]);
+                            float4 o = make_float4(p.alpha * a.x + bv.x, p.alpha * a.y + bv.y, p.alpha * a.z + bv.z, p.alpha * a.w + bv.w);
+                            float4* dst = reinterpret_cast<float4*>(Cb + (size_t)row * p.N + col);
+                            if (p.beta != 0.f) {
+                                float4 c = *dst;
+                                o.x += p.beta * c.x; o.y += p.beta * c.y; o.z += p.beta * c.z; o.w += p.beta * c.w;
+                            }
+                            if (p.act != ACT_NONE) { o.x = apply_act(o.x, p.act); o.y = apply_act(o.y, p.act); o.z = apply_act(o.z, p.act); o.w = apply_act(o.w, p.act); }
+                            *dst = o;
+                        }
+                    }
+                } else {
+                    for (int r = 0; r < 32; r += 4) {
+                        const int row = row_base + r + sub_row;
+                        if (row >= p.M) continue;
+                        for (int u = 0; u < 4; ++u) {
+                            const int cc = col + u;
+                            if (cc >= p.N) break;
+                            float o = p.alpha * tile_s[(r + sub_row) * 36 + c4 + u] + (p.bias ? __ldg(p.bias + cc) : 0.f);
+                            float* dst = Cb + (size_t)row * p.N + cc;
+                            if (p.beta != 0.f) o += p.beta * (*dst);
+                            *dst = apply_act(o, p.act);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(&tempty_bar[acc]);      // this warp no longer reads accumulator `acc`
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                     // the peer's smem / TMEM stay valid until the leader's MMAs retired
+    if (warp == 1) tmem_dealloc_2sm(tmem_base, 512);
+}
+
+static int launch_tc_2sm(const float* A, const float* B, GemmParams& p, int batch, long long sA, long long sB, cudaStream_t s) {
+    CUtensorMap tmA, tmB;
+    p.a_mn4 = p.b_mn4 = 0;
+    if (!p.a_mn_major) { if (make_tmap(&tmA, A, p.K, p.M, p.a_batched ? batch : 1, sA, BLOCK_M, false)) return -1; }
+    else if (p.M % 128 == 0 && make_tmap_mn4(&tmA, A, p.M, p.K, p.a_batched ? batch : 1, sA) == 0) p.a_mn4 = 1;
+    else { if (make_tmap(&tmA, A, p.M, p.K, p.a_batched ? batch : 1, sA, BLOCK_K, true)) return -1; }
+    if (!p.b_mn_major) { if (make_tmap(&tmB, B, p.K, p.N, p.b_batched ? batch : 1, sB, 128, false)) return -1; }
+    else if (p.N % 128 == 0 && make_tmap_mn4(&tmB, B, p.N, p.K, p.b_batched ? batch : 1, sB) == 0) p.b_mn4 = 1;
+    else { if (make_tmap(&tmB, B, p.N, p.K, p.b_batched ? batch : 1, sB, BLOCK_K, true)) return -1; }
+    static int max_clusters[64] = {0};
+    int dev = 0;
+    HETU_CUDA(cudaGetDevice(&dev));
+    if (max_clusters[dev & 63] == 0) {
+        HETU_CUDA(cudaFuncSetAttribute(gemm_tf32_2sm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, k2Smem));
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2, 1, 1);
+        cfg.blockDim = dim3(kGemmThreads, 1, 1);
+        cfg.dynamicSmemBytes = k2Smem;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, gemm_tf32_2sm_kernel, &cfg) != cudaSuccess || n <= 0) {
+            cudaGetLastError();
+            int sms = 0;
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            n = sms / 2;
+        }
+        max_clusters[dev & 63] = n;
+    }
+    const int tiles_m = (p.M + 255) / 256, tiles_n = (p.N + k2TileN - 1) / k2TileN;
+    const int num_tiles = tiles_m * tiles_n * batch;
+    const int maxc = max_clusters[dev & 63];
+    int clusters = num_tiles < maxc ? num_tiles : maxc;
+    const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+    // stream-K when whole-tile scheduling would leave >10% of the machine idle in the last wave
+    const int waves = (num_tiles + maxc - 1) / maxc;
+    const double eff = (double)num_tiles / ((double)waves * maxc);
+    int kb_per_cluster = 0;
+    static int use_streamk = -1;
+    if (use_streamk < 0) { const char* e = getenv("HETU_GEMM_STREAMK"); use_streamk = (e && e[0] == '1') ? 1 : 0; }   // opt-in: measured slower than whole tiles (atomics + lost L2 lockstep)
+    if (use_streamk && eff < 0.9 && p.beta == 0.f && p.act == ACT_NONE && num_kb >= 128 && (long long)num_tiles * num_kb >= 8LL * maxc) {
+        clusters = maxc;
+        const long long total = (long long)num_tiles * num_kb;
+        kb_per_cluster = (int)((total + clusters - 1) / clusters);
+        HETU_CUDA(cudaMemsetAsync(p.C, 0, sizeof(float) * (size_t)(batch > 1 ? p.sC * batch : (long long)p.M * p.N), s));
+    }
+    gemm_tf32_2sm_kernel<<<dim3(2 * clusters), kGemmThreads, k2Smem, s>>>(tmA, tmB, p, tiles_m, tiles_n, num_tiles, kb_per_cluster);
     return 0;
 }
 
@@ -545,6 +930,123 @@ static void launch_small(const float* A, const float* B, float* C, const float* 
         gemm_finish_kernel<<<ew_grid((size_t)M * N * batch, 256), 256, 0, s>>>(C, bias, (size_t)M * N * batch, N, act);
 }
 
+// ================================================================= skinny GEMM (N <= 8)
+// MoE gate / logistic-regression shapes: [tokens, d] @ [d, n_experts] and its weight gradient.  These are
+// bandwidth-bound reads of the big operand; a tile kernel wastes 8-32x of its columns on them.
+constexpr int kSkinnyN = 8;
+
+// A row-major [M, K] (not transposed): one warp per output row, lanes stride K with 128-bit loads.
+template <int TB>
+__global__ void __launch_bounds__(256) gemm_skinny_rows_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                               float* __restrict__ C, const float* __restrict__ bias,
+                                                               int M, int N, int K, float alpha, float beta, int act) {
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= M) return;
+    const float* a = A + (size_t)row * K;
+    float acc[kSkinnyN];
+#pragma unroll
+    for (int n = 0; n < kSkinnyN; ++n) acc[n] = 0.f;
+    const bool vec = (K & 3) == 0 && ((reinterpret_cast<uintptr_t>(A) & 15) == 0);
+    if (vec) {
+        for (int kb = lane * 4; kb < K; kb += 512) {
+            float4 av[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)             // four independent 128-bit loads in flight per lane
+                av[u] = (kb + u * 128 < K) ? __ldcs(reinterpret_cast<const float4*>(a + kb + u * 128)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int k = kb + u * 128;
+                if (k >= K) break;
+#pragma unroll
+                for (int n = 0; n < kSkinnyN; ++n) {
+                    if (n < N) {
+                        if (TB) {   // B stored [N, K]
+                            const float4 bv = __ldg(reinterpret_cast<const float4*>(B + (size_t)n * K + k));
+                            acc[n] += av[u].x * bv.x + av[u].y * bv.y + av[u].z * bv.z + av[u].w * bv.w;
+                        } else {    // B stored [K, N]
+                            const float* b = B + (size_t)k * N + n;
+                            acc[n] += av[u].x * __ldg(b) + av[u].y * __ldg(b + N) + av[u].z * __ldg(b + 2 * N) + av[u].w * __ldg(b + 3 * N);
+                        }
+                    }
+                }
+            }
+        }
+    } else {
+        for (int k = lane; k < K; k += 32) {
+            const float av = __ldg(a + k);
+#pragma unroll
+            for (int n = 0; n < kSkinnyN; ++n)
+                if (n < N) acc[n] += av * __ldg(TB ? B + (size_t)n * K + k : B + (size_t)k * N + n);
+        }
+    }
+#pragma unroll
+    for (int n = 0; n < kSkinnyN; ++n) {
+        float v = acc[n];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0 && n < N) {
+            float o = alpha * v + (bias ? __ldg(bias + n) : 0.f);
+            float* dst = C + (size_t)row * N + n;
+            if (beta != 0.f) o += beta * (*dst);
+            *dst = apply_act(o, act);
+        }
+    }
+}
+
+// A stored [K, M] (transposed operand): threads run along M (coalesced), 4 k-lanes per block, K split over
+// blockIdx.y; partial sums are added atomically into the zero-initialised C.
+template <int TB>
+__global__ void __launch_bounds__(256) gemm_skinny_cols_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                               float* __restrict__ C, int M, int N, int K, int kchunk,
+                                                               float alpha) {
+    __shared__ float red[4][64][kSkinnyN + 1];
+    const int mt = threadIdx.x & 63, kl = threadIdx.x >> 6;
+    const int m = blockIdx.x * 64 + mt;
+    const int k_beg = blockIdx.y * kchunk, k_end = min(K, k_beg + kchunk);
+    float acc[kSkinnyN];
+#pragma unroll
+    for (int n = 0; n < kSkinnyN; ++n) acc[n] = 0.f;
+    if (m < M) {
+#pragma unroll 8
+        for (int k = k_beg + kl; k < k_end; k += 4) {
+            const float av = __ldcs(A + (size_t)k * M + m);
+#pragma unroll
+            for (int n = 0; n < kSkinnyN; ++n)
+                if (n < N) acc[n] += av * __ldg(TB ? B + (size_t)n * K + k : B + (size_t)k * N + n);
+        }
+    }
+#pragma unroll
+    for (int n = 0; n < kSkinnyN; ++n) red[kl][mt][n] = acc[n];
+    __syncthreads();
+    if (kl == 0 && m < M) {
+#pragma unroll
+        for (int n = 0; n < kSkinnyN; ++n)
+            if (n < N) atomicAdd(C + (size_t)m * N + n, alpha * (red[0][mt][n] + red[1][mt][n] + red[2][mt][n] + red[3][mt][n]));
+    }
+}
+
+static void launch_skinny(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, int tA, int tB,
+                          float alpha, float beta, int act, cudaStream_t s) {
+    if (!tA) {
+        dim3 grid((M + 7) / 8);
+        if (tB) gemm_skinny_rows_kernel<1><<<grid, 256, 0, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
+        else gemm_skinny_rows_kernel<0><<<grid, 256, 0, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
+        return;
+    }
+    const int mblocks = (M + 63) / 64;
+    int splits = (4 * kNumSMs + mblocks - 1) / mblocks;
+    int kchunk = (K + splits - 1) / splits;
+    kchunk = (kchunk + 63) / 64 * 64;
+    splits = (K + kchunk - 1) / kchunk;
+    cudaMemsetAsync(C, 0, sizeof(float) * (size_t)M * N, s);
+    dim3 grid(mblocks, splits);
+    if (tB) gemm_skinny_cols_kernel<1><<<grid, 256, 0, s>>>(A, B, C, M, N, K, kchunk, alpha);
+    else gemm_skinny_cols_kernel<0><<<grid, 256, 0, s>>>(A, B, C, M, N, K, kchunk, alpha);
+    if (bias || act != ACT_NONE)
+        gemm_finish_kernel<<<ew_grid((size_t)M * N, 256), 256, 0, s>>>(C, bias, (size_t)M * N, N, act);
+}
+
 // ============================================================================ dispatch
 static bool aligned16p(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
@@ -562,6 +1064,11 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
                   (sA % 4 == 0) && (sB % 4 == 0);
     const double macs = (double)M * N * K * batch;
     bool big = macs > (double)(1 << 25) && M >= 64 && N >= 8 && K >= 32;
+    if (N <= kSkinnyN && batch == 1 && (double)M * K >= (double)(1 << 20) && (!transA || beta == 0.f)) {
+        launch_skinny(A, B, C, bias, M, N, K, transA, transB, alpha, beta, act, s);
+        HETU_CHECK_LAUNCH("hetu_gemm(skinny)");
+        return 0;
+    }
     static int force_simt = -1;
     if (force_simt < 0) { const char* e = getenv("HETU_GEMM_FORCE_SIMT"); force_simt = (e && e[0] == '1') ? 1 : 0; }
     if (mode != 1 && tma_ok && big && !force_simt) {
@@ -572,8 +1079,14 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
         p.a_batched = (batch > 1 && sA != 0) ? 1 : 0;
         p.b_batched = (batch > 1 && sB != 0) ? 1 : 0;
         p.alpha = alpha; p.beta = beta; p.act = act;
+        p.a_mn4 = p.b_mn4 = 0;
+        { const char* e = getenv("HETU_GEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
         int rc;
-        if (N > 128) rc = launch_tc<256>(A, B, p, batch, sA, sB, s);
+        static int use_2sm = -1;
+        if (use_2sm < 0) { const char* e = getenv("HETU_GEMM_2SM"); use_2sm = (e && e[0] == '0') ? 0 : 1; }
+        if (use_2sm && M >= 512 && N >= 256 && (double)M * N * batch * K >= 74.0 * 256 * 256 * 1024)
+            rc = launch_tc_2sm(A, B, p, batch, sA, sB, s);
+        else if (N > 128) rc = launch_tc<256>(A, B, p, batch, sA, sB, s);
         else if (N > 64) rc = launch_tc<128>(A, B, p, batch, sA, sB, s);
         else if (N > 32) rc = launch_tc<64>(A, B, p, batch, sA, sB, s);
         else rc = launch_tc<32>(A, B, p, batch, sA, sB, s);

@@ -224,8 +224,49 @@ __global__ void __launch_bounds__(1024) cumsum_cols_kernel(const float* __restri
             out[r * E + col] = run;
         }
 }
+// Few columns (MoE gates: E = number of experts): one CTA per column, 1024 threads each own a run of
+// consecutive rows; thread sums -> block-wide exclusive scan (shuffle + one smem hop) -> rescan.
+__global__ void __launch_bounds__(1024) cumsum_fewcols_kernel(const float* __restrict__ x, float* __restrict__ out,
+                                                              size_t T, size_t E, float bias) {
+    __shared__ float wsum[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t col = blockIdx.x;
+    const size_t chunk = (T + 1023) / 1024;
+    const size_t r0 = (size_t)threadIdx.x * chunk, r1 = r0 + chunk < T ? r0 + chunk : T;
+    float acc = 0.f;
+    for (size_t r = r0; r < r1; ++r) acc += __ldg(x + r * E + col);
+    float incl = acc;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        float v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        float w = wsum[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            float v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += v;
+        }
+        wsum[lane] = wi - w;                       // exclusive prefix of the warp totals
+    }
+    __syncthreads();
+    float run = wsum[warp] + (incl - acc) + bias;
+    for (size_t r = r0; r < r1; ++r) {
+        run += __ldg(x + r * E + col);
+        out[r * E + col] = run;
+    }
+}
+
 HETU_API int hetu_cumsum_cols(const float* x, float* out, size_t T, size_t E, float bias, cudaStream_t s) {
     if (T == 0 || E == 0) return 0;
+    if (E <= 64 && T >= 2048) {
+        cumsum_fewcols_kernel<<<(int)E, 1024, 0, s>>>(x, out, T, E, bias);
+        HETU_CHECK_LAUNCH("hetu_cumsum_cols(few)");
+        return 0;
+    }
     cumsum_cols_kernel<<<(int)((E + 31) / 32), 1024, 0, s>>>(x, out, T, E, bias);
     HETU_CHECK_LAUNCH("hetu_cumsum_cols");
     return 0;

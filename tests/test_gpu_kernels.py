@@ -89,10 +89,14 @@ def test_reduce_topk_cumsum(L):
     cs = R.CumsumOp.__new__(R.CumsumOp)
     cs.bias, cs.dim = -1, 0
     torch.testing.assert_close(R.CumsumOp.compute(cs, [mask]), torch.cumsum(mask, 0) - 1)
+    for T, E in [(33001, 2), (1500, 100)]:                      # few-column and many-column kernels
+        m2 = (torch.rand(T, E, device='cuda') < 0.3).float()
+        torch.testing.assert_close(R.CumsumOp.compute(cs, [m2]), torch.cumsum(m2, 0) - 1)
 
 
 # ------------------------------------------------------------------------ GEMM
 GEMM_SHAPES = [(128, 128, 128), (256, 384, 512), (1000, 520, 264), (2048, 2048, 2048), (128, 256, 256),
+               (4096, 1024, 512), (1160, 776, 2048), (16384, 2, 2048), (2048, 3, 16384), (5000, 7, 1001),
                (96, 40, 72), (128, 1, 3584), (128, 256, 13), (4096, 64, 1024), (300, 32, 2048)]
 
 
@@ -126,6 +130,17 @@ def test_gemm_fp32_mode_and_epilogue(L):
     out = gemm(a, b, bias=bias, act=ACT_RELU)
     ref = torch.relu(a @ b + bias)
     assert (out - ref).abs().max().item() / ref.abs().max().item() < 2e-3      # tf32 operands
+    # persistent 2-SM (cta_group::2) kernel: fused epilogue, odd edges, batched operands
+    a, b, bias, c = rnd(1100, 4096), rnd(4096, 1032, seed=1), rnd(1032, seed=2), rnd(1100, 1032, seed=3)
+    out = gemm(a, b, bias=bias, c_in=c, alpha=0.5, beta=2.0, act=ACT_RELU)
+    ref = torch.relu(0.5 * (a.double() @ b.double()) + 2.0 * c.double() + bias.double())
+    assert (out.double() - ref).abs().max().item() / ref.abs().max().item() < 2e-3
+    a, b = rnd(3, 1024, 2048), rnd(3, 2048, 512, seed=1)
+    ref = torch.bmm(a.double(), b.double())
+    assert (gemm(a, b).double() - ref).abs().max().item() / ref.abs().max().item() < 2e-3
+    w = rnd(2048, 512, seed=4)                                                  # shared (un-batched) B
+    ref = a.double() @ w.double()
+    assert (gemm(a, w).double() - ref).abs().max().item() / ref.abs().max().item() < 2e-3
 
 
 def test_gemm_batched(L):
