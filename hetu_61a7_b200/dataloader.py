@@ -16,9 +16,12 @@ from .ndarray import cpu
 
 
 class Dataloader(object):
-    def __init__(self, raw_data, batch_size, name='default', func=None, drop_last=True):
+    def __init__(self, raw_data, batch_size, name='default', func=None, drop_last=True, dtype=np.float32):
+        """``dtype``: the reference stores every batch as float32 (ids included, dataloader.py:16);
+        pass ``np.int64`` to keep embedding ids exact beyond 2**24."""
         self.func = func if func else (lambda x: x)
-        self.raw_data = np.ascontiguousarray(self.func(raw_data), dtype=np.float32)
+        self.raw_data = np.ascontiguousarray(self.func(raw_data), dtype=dtype)
+        self.dtype = torch.from_numpy(np.empty(0, dtype=dtype)).dtype
         self.batch_size = int(batch_size)
         self.drop_last = drop_last
         self.name = str(name)
@@ -48,9 +51,18 @@ class Dataloader(object):
         self.index = 0
         self.batch_index = 0
         pin = torch.cuda.is_available()
-        self.ring = [torch.empty(self.reshape_shape(self.shape), dtype=torch.float32, pin_memory=pin)
+        # small enough datasets are pinned once as a whole: a batch is then a VIEW of pinned memory and
+        # the per-step host memcpy into the ring disappears (HETU_PIN_DATASET_MB, default 4096)
+        import os
+        limit = float(os.environ.get('HETU_PIN_DATASET_MB', '4096')) * (1 << 20)
+        self.pinned_all = None
+        if pin and not self.parts and self.raw_data.nbytes <= limit:
+            self.pinned_all = torch.from_numpy(self.raw_data).pin_memory()
+        self.ring = [None if self.pinned_all is not None else
+                     torch.empty(self.reshape_shape(self.shape), dtype=self.dtype, pin_memory=pin)
                      for _ in range(self.queue_size)]
         self.ring_rows = [0] * self.queue_size
+        self.inflight = [None] * self.queue_size
         self.rd = 0
         self.reads = 0
         for i in range(self.queue_size):
@@ -70,10 +82,17 @@ class Dataloader(object):
         if res + self.batch_size > self.samples_num and self.drop_last:
             res = 0
         end = min(res + self.batch_size, self.samples_num)
-        batch = self.raw_data[res:end]
-        batch = self.reshape_tensor(batch)
-        rows = batch.shape[0]
-        self.ring[slot][:rows].copy_(torch.from_numpy(np.ascontiguousarray(batch)))
+        if self.inflight[slot] is not None:              # an async H2D may still be reading this slot
+            self.inflight[slot].synchronize()
+            self.inflight[slot] = None
+        if self.pinned_all is not None:
+            self.ring[slot] = self.pinned_all[res:end]
+            rows = end - res
+        else:
+            batch = self.raw_data[res:end]
+            batch = self.reshape_tensor(batch)
+            rows = batch.shape[0]
+            self.ring[slot][:rows].copy_(torch.from_numpy(np.ascontiguousarray(batch)))
         self.ring_rows[slot] = rows
         self.index = end if end < self.samples_num else 0
         if self.drop_last and self.index + self.batch_size > self.samples_num:
@@ -98,6 +117,11 @@ class Dataloader(object):
     def get_next_arr(self):
         slot = self.rd
         return self.ring[slot][:self.ring_rows[slot]]
+
+    def mark_inflight(self, event):
+        """The executor started an async H2D of the NEXT batch; its slot must not be refilled before
+        ``event`` has completed."""
+        self.inflight[self.rd] = event
 
     def set_dp_rank(self, dp_rank, dp_nrank):
         if self.dp_nrank is not None:
@@ -158,6 +182,9 @@ class DataloaderOp(Op):
 
     def get_next_arr(self, name):
         return self.dataloaders[name].get_next_arr()
+
+    def mark_inflight(self, name, event):
+        self.dataloaders[name].mark_inflight(event)
 
     def get_cur_shape(self, name):
         return self.dataloaders[name].get_cur_shape()

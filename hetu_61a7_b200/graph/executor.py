@@ -660,9 +660,9 @@ class SubExecutor(object):
         feeds: Dict[Op, object] = {}
         for node, value in feed_dict.items():
             feeds[node] = self._feed_tensor(node, value)
-        for node in self.dataloader_nodes:
-            if node not in feeds:
-                feeds[node] = node.get_arr(self.name)
+        self._from_loader = [n for n in self.dataloader_nodes if n not in feeds]
+        for node in self._from_loader:
+            feeds[node] = self._next_batch(node)
         for node in self.need_feed_nodes:
             assert node in feeds, 'placeholder %s must be fed' % node.name
         self._pre_step()
@@ -670,6 +670,7 @@ class SubExecutor(object):
             vals = self._run_graph(feeds)
         else:
             vals = self._run_eager(feeds)
+        self._prefetch_batches()
         self.step_count += 1
         from ..parallel.comm import drain_sends
         drain_sends()
@@ -686,6 +687,60 @@ class SubExecutor(object):
                 results.append(NDArray(v, n.ctx if isinstance(n.ctx, DLContext) else None))
         return results
 
+    # ---- dataloader prefetch: the NEXT batch's H2D copy runs on the copy stream while this step
+    # computes (reference dataloader.py keeps a queue of pre-built batches for the same purpose)
+    def _next_batch(self, node):
+        arr = node.get_arr(self.name)
+        pre = getattr(self, '_pf', {}).pop(node, None)
+        if pre is not None:
+            buf, ev, key = pre
+            if key == (arr.data_ptr(), tuple(arr.shape)):
+                torch.cuda.current_stream(self.device).wait_event(ev)
+                return buf
+        return arr
+
+    def _prefetch_batches(self):
+        cfg = self.config
+        if self.device.type != 'cuda' or cfg.h2d_stream is None or not getattr(self, '_from_loader', None) \
+                or os.environ.get('HETU_PREFETCH_BATCHES', '1') != '1':
+            return
+        if not hasattr(self, '_pf'):
+            self._pf, self._pf_bufs, self._pf_turn, self._pf_ptrs = {}, {}, {}, set()
+        comp = torch.cuda.current_stream(self.device)
+        h2d = cfg.h2d_stream.handle
+        for node in self._from_loader:
+            if not hasattr(node, 'mark_inflight'):
+                continue
+            nxt = node.get_next_arr(self.name)
+            if not isinstance(nxt, torch.Tensor) or nxt.device.type != 'cpu' or not nxt.is_pinned():
+                continue
+            if nxt.numel() * nxt.element_size() < (1 << 20):
+                continue        # tiny batches: the event/stream bookkeeping costs more than the copy it hides
+            turn = self._pf_turn.get(node, 0)
+            self._pf_turn[node] = turn ^ 1
+            bufs = self._pf_bufs.setdefault(node, [None, None])
+            if bufs[turn] is None or bufs[turn][0].shape[1:] != nxt.shape[1:] or bufs[turn][0].shape[0] < nxt.shape[0]:
+                bufs[turn] = [torch.empty(tuple(nxt.shape), dtype=nxt.dtype, device=self.device), None]
+                self._pf_ptrs.add(bufs[turn][0].data_ptr())
+            full, consumed = bufs[turn]
+            buf = full[:nxt.shape[0]]
+            if consumed is not None:
+                h2d.wait_event(consumed)                 # the step that read this buffer has copied it out
+            with torch.cuda.stream(h2d):
+                buf.copy_(nxt, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(h2d)
+            node.mark_inflight(self.name, ev)
+            done = torch.cuda.Event()
+            bufs[turn][1] = done                         # recorded by the consuming step
+            self._pf[node] = (buf, ev, (nxt.data_ptr(), tuple(nxt.shape)))
+            self._pf_done = getattr(self, '_pf_done', {})
+            self._pf_done[node] = done
+
+    def _mark_feeds_consumed(self):
+        for node, done in getattr(self, '_pf_done', {}).items():
+            done.record(torch.cuda.current_stream(self.device))
+
     def _run_eager(self, feeds):
         vals: Dict[Op, object] = {}
         use_stream = self.config.comp_stream is not None and self.device.type == 'cuda'
@@ -694,10 +749,11 @@ class SubExecutor(object):
         for node, t in feeds.items():
             vals[node] = self._to_device(t)
         self._compute_all(vals, release=True)
+        self._mark_feeds_consumed()
         return vals
 
     def _graph_signature(self, feeds):
-        return tuple((id(n), tuple(t.shape), str(t.dtype), t.device.type) for n, t in feeds.items())
+        return tuple((id(n), tuple(t.shape), str(t.dtype)) for n, t in feeds.items())
 
     def _run_graph(self, feeds):
         key = self._graph_signature(feeds)
@@ -711,14 +767,13 @@ class SubExecutor(object):
                 self._graph_key = key
                 return self._run_eager(feeds)
             self._capture(feeds, key)
-        # stage inputs
+        # stage inputs: straight into the graph's static buffers on the compute stream (a pinned
+        # source makes this a true async H2D; no intermediate host copy, no memcpy node in the graph)
         for node, t in feeds.items():
-            if t.device.type == 'cpu':
-                self._stage[node].copy_(t)
-            else:
-                st = self._static_in[node]
-                if st.data_ptr() != t.data_ptr():
-                    st.copy_(t, non_blocking=True)
+            st = self._static_in[node]
+            if st.data_ptr() != t.data_ptr():
+                st.copy_(t, non_blocking=True)
+        self._mark_feeds_consumed()
         self._graph.replay()
         return self._static_out
 
@@ -726,20 +781,19 @@ class SubExecutor(object):
         dev = self.device
         torch.cuda.synchronize(dev)
         self._static_in, self._stage = {}, {}
+        pf_ptrs = getattr(self, '_pf_ptrs', set())
         for node, t in feeds.items():
-            if t.device.type == 'cpu':
-                self._stage[node] = torch.empty(tuple(t.shape), dtype=t.dtype, pin_memory=True)
-                self._stage[node].copy_(t)
+            if t.device.type == 'cpu' or t.data_ptr() in pf_ptrs or t.device != dev:
                 self._static_in[node] = torch.empty(tuple(t.shape), dtype=t.dtype, device=dev)
+                self._static_in[node].copy_(t, non_blocking=True)
             else:
-                self._static_in[node] = t
+                self._static_in[node] = t               # device-resident feed: the graph reads it in place
+        torch.cuda.synchronize(dev)
         graph = torch.cuda.CUDAGraph()
         vals: Dict[Op, object] = {}
         launches_before = L.launch_count
         with torch.cuda.graph(graph):
             for node, st in self._static_in.items():
-                if node in self._stage:
-                    st.copy_(self._stage[node], non_blocking=True)
                 vals[node] = st
             self._compute_all(vals, release=False)
         self._graph = graph

@@ -1,12 +1,11 @@
-"""Fused multi-head attention (new capability).
+"""Multi-head attention as one graph op (new capability).
 
-The reference has no fused attention: BERT builds it from five ops -
-batch_matmul, additive mask, softmax, dropout, batch_matmul - materialising the
-[B, heads, S, S] score tensor in fp32 (examples/nlp/bert/hetu_bert.py:220-270;
-SURVEY.md 5.7).  ``fused_attention_op(q, k, v, mask)`` computes
-softmax(q k^T * scale + mask) v in one flash-style kernel (csrc/attention.cu:
-online softmax, scores never leave the SM) and its backward recomputes the
-probabilities from the saved log-sum-exp.
+The reference has no attention op: BERT builds it from five ops - batch_matmul, additive mask,
+softmax, dropout, batch_matmul (examples/nlp/bert/hetu_bert.py:220-270) - and
+autodiff adds six more for the backward pass.  ``fused_attention_op(q, k, v, mask)`` computes
+softmax(q k^T * scale + mask) v with two batched tcgen05 GEMMs and ONE row kernel in between
+(csrc/attention.cu: scale + key mask + softmax + log-sum-exp in place on the score buffer); the
+backward pass is four batched GEMMs and one row kernel (ds = p * (dp - <dp, p>) * scale in place).
 """
 from __future__ import annotations
 
@@ -29,6 +28,7 @@ class FusedAttentionOp(Op):
         super().__init__(FusedAttentionOp, [q, k, v] + ([mask] if mask is not None else []), ctx)
         self.scale = scale
         self.lse = None
+        self.probs = None
 
     def compute(self, input_vals, output_val=None, stream_handle=None):
         q, k, v = input_vals[:3]
@@ -38,15 +38,16 @@ class FusedAttentionOp(Op):
         scale = self.scale if self.scale is not None else 1.0 / math.sqrt(q.shape[-1])
         B, H, S, D = q.shape
         Sk = k.shape[2]
-        if _k(q, k, v) and D in (32, 64, 128) and (mask is None or mask.numel() == B * Sk):
-            q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
-            out = torch.empty_like(q)
+        if _k(q, k, v) and (mask is None or mask.numel() == B * Sk):
+            from .linalg import gemm
+            q3, k3, v3 = (t.contiguous().view(B * H, t.shape[2], D) for t in (q, k, v))
+            p = gemm(q3, k3, False, True)                       # [B*H, S, Sk] scores
             self.lse = torch.empty((B, H, S), dtype=torch.float32, device=q.device)
             m = mask.contiguous() if mask is not None else None
-            L.call('attention_fwd', L.p(q), L.p(k), L.p(v), L.p(m), L.p(out), L.p(self.lse),
-                   L.c_int(B), L.c_int(H), L.c_int(S), L.c_int(Sk), L.c_int(D), L.c_f32(scale),
-                   L.stream_ptr(q.device))
-            return out
+            L.call('attn_softmax', L.p(p), L.p(m), L.p(self.lse), L.c_i64(B * H * S), L.c_int(Sk),
+                   L.c_i64(H * S), L.c_f32(scale), L.stream_ptr(q.device))
+            self.probs = p
+            return gemm(p, v3).view(B, H, S, D)
         s = torch.matmul(q, k.transpose(-1, -2)) * scale
         if mask is not None:
             s = s + mask.reshape(B, 1, 1, Sk) if mask.numel() == B * Sk else s + mask
@@ -77,14 +78,17 @@ class FusedAttentionGradOp(Op):
         scale = fwd.scale if fwd.scale is not None else 1.0 / math.sqrt(q.shape[-1])
         B, H, S, D = q.shape
         Sk = k.shape[2]
-        if _k(q, k, v, do, o) and D in (32, 64, 128) and (mask is None or mask.numel() == B * Sk):
-            q, k, v, do, o = [t.contiguous() for t in (q, k, v, do, o)]
-            dq = torch.zeros_like(q)
-            dk, dv = torch.empty_like(k), torch.empty_like(v)
-            m = mask.contiguous() if mask is not None else None
-            L.call('attention_bwd', L.p(q), L.p(k), L.p(v), L.p(m), L.p(o), L.p(do), L.p(fwd.lse),
-                   L.p(dq), L.p(dk), L.p(dv), L.c_int(B), L.c_int(H), L.c_int(S), L.c_int(Sk),
-                   L.c_int(D), L.c_f32(scale), L.stream_ptr(q.device))
+        if _k(q, k, v, do, o) and getattr(fwd, 'probs', None) is not None \
+                and (mask is None or mask.numel() == B * Sk):
+            from .linalg import gemm
+            q3, k3, v3, do3 = (t.contiguous().view(B * H, t.shape[2], D) for t in (q, k, v, do))
+            p = fwd.probs
+            dv = gemm(p, do3, True, False).view(B, H, Sk, D)     # P^T dO
+            ds = gemm(do3, v3, False, True)                      # dP = dO V^T, turned into dS in place
+            L.call('attn_softmax_bwd', L.p(p), L.p(ds), L.c_i64(B * H * S), L.c_int(Sk), L.c_f32(scale),
+                   L.stream_ptr(q.device))
+            dq = gemm(ds, k3).view(B, H, S, D)
+            dk = gemm(ds, q3, True, False).view(B, H, Sk, D)
         else:
             s = torch.matmul(q, k.transpose(-1, -2)) * scale
             if mask is not None:

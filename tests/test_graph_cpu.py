@@ -339,3 +339,22 @@ def test_metrics_tokenizer():
     assert tok.tokenize('Hello, worlds foo') == ['hello', ',', 'world', '##s', '[UNK]']
     ids, types, mask = tok.encode('hello world', 'hello', max_seq_length=8)
     assert ids[:6] == [2, 4, 5, 3, 4, 3] and sum(mask) == 6 and types[4] == 1
+
+
+def test_fused_attention_matches_autograd():
+    rs = np.random.RandomState(0)
+    B, H, S, D = 2, 3, 16, 8
+    qv, kv, vv = [rs.randn(B, H, S, D).astype(np.float32) for _ in range(3)]
+    mv = (rs.rand(B, 1, 1, S) > 0.8).astype(np.float32) * -1e4
+    q, k, v, m = ht.Variable('q', value=qv), ht.Variable('k', value=kv), ht.Variable('v', value=vv), ht.Variable('m')
+    out = ht.fused_attention_op(q, k, v, m)
+    loss = ht.reduce_sum_op(ht.mul_op(out, out), [0, 1, 2, 3])
+    grads = ht.gradients(loss, [q, k, v])
+    ex = ht.Executor([out] + grads, ctx=ht.cpu(0))
+    res = [r.asnumpy() for r in ex.run(feed_dict={m: mv})]
+    tq, tk, tv = [torch.tensor(a, requires_grad=True) for a in (qv, kv, vv)]
+    s = tq @ tk.transpose(-1, -2) / np.sqrt(D) + torch.tensor(mv)
+    o = torch.softmax(s, -1) @ tv
+    (o * o).sum().backward()
+    for got, ref in zip(res, [o.detach(), tq.grad, tk.grad, tv.grad]):
+        np.testing.assert_allclose(got, ref.numpy(), rtol=1e-4, atol=1e-5)
