@@ -26,6 +26,8 @@ from . import distributed_strategies as dist
 from . import ndarray
 from . import stream
 from . import cpu_links
+from . import onnx
+from . import graphboard
 from .utils import data
 from .utils import metrics
 from .utils.profiler import HetuProfiler, NCCLProfiler
