@@ -139,6 +139,13 @@ struct GemmParams {
     long long sC;
     int a_mn_major, b_mn_major;    // 1 = MN-major (A given as [K,M] / B given as [K,N])
     int a_batched, b_batched;
+    // tensor-parallel fusions over the symmetric heap (2-SM kernel only):
+    //  ag_world > 1: A is row-sharded over ag_world GPUs, rows [r*ag_rows, (r+1)*ag_rows) live on rank r and
+    //                are read in place through that rank's peer-mapped tensor map (all-gather -> GEMM)
+    //  rs_world > 1: row block r of the partial product is reduced into rank r's buffer rs_out[r] with
+    //                red.global.add.v4.f32 over NVLink (GEMM -> reduce-scatter)
+    int ag_world, ag_rows, rs_world, rs_rows;
+    float* rs_out[8];
     int dbg;                       // diagnostics: 1 = no TMA after the first ring fill, 2 = no MMA
     int a_mn4, b_mn4;              // MN-major operand described by ONE 4-D box {32 mn, 32 k, 4 groups, 1}
     float alpha, beta;
@@ -478,8 +485,11 @@ struct TileSched {
     }
 };
 
+struct PeerMaps { CUtensorMap m[8]; };
+
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
-gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p,
+gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const __grid_constant__ PeerMaps peerA, GemmParams p,
                      int tiles_m, int tiles_n, int num_tiles, int kb_per_cluster) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -519,8 +529,15 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             while (sched.next(tile, kb0, kb1)) {
                 int bz, tm, tn;
                 decode_tile(tile, tiles_m, tiles_n, bz, tm, tn);
-                const int m0 = tm * 256 + (int)rank * 128, nb0 = tn * k2TileN + (int)rank * 128;
+                int m0 = tm * 256 + (int)rank * 128;
+                const int nb0 = tn * k2TileN + (int)rank * 128;
                 const int ba = p.a_batched ? bz : 0, bb = p.b_batched ? bz : 0;
+                const CUtensorMap* mapA = &tmA;
+                if (p.ag_world > 1) {                  // this CTA's 128 rows live on one peer: read them in place
+                    const int owner = min(m0 / p.ag_rows, p.ag_world - 1);
+                    mapA = &peerA.m[owner];
+                    m0 -= owner * p.ag_rows;
+                }
                 for (int kb = kb0; kb < kb1; ++kb, ++it) {
                     const int st = it % k2Stages;
                     if (it >= k2Stages) mbar_wait(&empty_bar[st], ((it / k2Stages) - 1) & 1);
@@ -533,7 +550,7 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                     uint8_t* b_dst = smem_b + st * k2BBytes;
                     const int k0 = kb * BLOCK_K;
                     if (!p.a_mn_major) {
-                        tma_load_3d_2sm(a_dst, &tmA, k0, m0, ba, &full_bar[st]);
+                        tma_load_3d_2sm(a_dst, mapA, k0, m0, ba, &full_bar[st]);
                     } else if (p.a_mn4) {
                         tma_load_4d_2sm(a_dst, &tmA, 0, k0, m0 >> 5, ba, &full_bar[st]);
                     } else {
@@ -594,7 +611,7 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         TileSched sched(cluster_id, num_clusters, num_tiles, num_kb, kb_per_cluster);
         for (; sched.next(tile, kb0, kb1); ++t_iter) {
             const int acc = t_iter & 1;
-            const bool partial = kb0 != 0 || kb1 != num_kb;        // stream-K fragment: accumulate into C
+            const bool partial = kb0 != 0 || kb1 != num_kb || p.rs_world > 1;   // accumulate into C (stream-K / reduce-scatter)
             int bz, tm, tn;
             decode_tile(tile, tiles_m, tiles_n, bz, tm, tn);
             const int m0 = tm * 256 + (int)rank * 128, n0 = tn * k2TileN;
@@ -618,6 +635,10 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                         const int row = row_base + r + sub_row;
                         if (row >= p.M) continue;
                         float* dst = Cb + (size_t)row * p.N + col;
+                        if (p.rs_world > 1) {              // row block owner's buffer, over NVLink
+                            const int owner = min(row / p.rs_rows, p.rs_world - 1);
+                            dst = p.rs_out[owner] + (size_t)(row - owner * p.rs_rows) * p.N + col;
+                        }
                         const float* src = &tile_s[(r + sub_row) * 36 + c4];
                         if (vec_ok && col + 3 < p.N) {
                             float4 o = make_float4(p.alpha * src[0], p.alpha * src[1], p.alpha * src[2], p.alpha * src[3]);
@@ -676,8 +697,10 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     if (warp == 1) tmem_dealloc_2sm(tmem_base, 512);
 }
 
-static int launch_tc_2sm(const float* A, const float* B, GemmParams& p, int batch, long long sA, long long sB, cudaStream_t s) {
+static int launch_tc_2sm(const float* A, const float* B, GemmParams& p, int batch, long long sA, long long sB, cudaStream_t s,
+                         const PeerMaps* peers = nullptr) {
     CUtensorMap tmA, tmB;
+    static PeerMaps no_peers;
     p.a_mn4 = p.b_mn4 = 0;
     if (!p.a_mn_major) { if (make_tmap(&tmA, A, p.K, p.M, p.a_batched ? batch : 1, sA, BLOCK_M, false)) return -1; }
     else if (p.M % 128 == 0 && make_tmap_mn4(&tmA, A, p.M, p.K, p.a_batched ? batch : 1, sA) == 0) p.a_mn4 = 1;
@@ -724,7 +747,8 @@ static int launch_tc_2sm(const float* A, const float* B, GemmParams& p, int batc
         kb_per_cluster = (int)((total + clusters - 1) / clusters);
         HETU_CUDA(cudaMemsetAsync(p.C, 0, sizeof(float) * (size_t)(batch > 1 ? p.sC * batch : (long long)p.M * p.N), s));
     }
-    gemm_tf32_2sm_kernel<<<dim3(2 * clusters), kGemmThreads, k2Smem, s>>>(tmA, tmB, p, tiles_m, tiles_n, num_tiles, kb_per_cluster);
+    gemm_tf32_2sm_kernel<<<dim3(2 * clusters), kGemmThreads, k2Smem, s>>>(tmA, tmB, peers ? *peers : no_peers, p, tiles_m, tiles_n,
+                                                                          num_tiles, kb_per_cluster);
     return 0;
 }
 
@@ -1080,6 +1104,7 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
         p.b_batched = (batch > 1 && sB != 0) ? 1 : 0;
         p.alpha = alpha; p.beta = beta; p.act = act;
         p.a_mn4 = p.b_mn4 = 0;
+        p.ag_world = p.rs_world = 0; p.ag_rows = p.rs_rows = 1;
         { const char* e = getenv("HETU_GEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
         int rc;
         static int use_2sm = -1;
@@ -1102,6 +1127,49 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
     dim3 grid((N + 63) / 64, (M + 63) / 64, batch);
     gemm_fp32_simt_kernel<<<grid, 256, 0, s>>>(A, B, C, bias, M, N, K, transA, transB, sA, sB, sC, alpha, beta, act);
     HETU_CHECK_LAUNCH("hetu_gemm(simt)");
+    return 0;
+}
+
+// ============================================================ tensor-parallel fused GEMMs
+// reference: the model-parallel split/datatransfer ops of BASELINE.json (all-gather -> GEMM and
+// GEMM -> reduce-scatter).  Both reuse the persistent 2-SM kernel; the collective is not a separate
+// step but the operand fetch (TMA over peer-mapped memory) / the epilogue (NVLink reductions).
+// The caller brackets each call with hetu_symm_barrier (inputs complete / outputs complete).
+
+// C[M_total, N] = allgather_rows(A_shards) @ op(B); a_peers[r] = rank r's [M_total/world, K] shard.
+HETU_API int hetu_gemm_ag(void* const* a_peers, int world, const float* B, float* C, const float* bias, int M_total,
+                          int N, int K, int transB, float alpha, int act, cudaStream_t s) {
+    if (world < 1 || world > 8 || M_total % world) { hetu_set_error("hetu_gemm_ag: bad world / M"); return -1; }
+    const int rows = M_total / world;
+    if (rows % 128 || K % 4 || (transB ? K : N) % 4) { hetu_set_error("hetu_gemm_ag: shard rows must be a multiple of 128"); return -1; }
+    GemmParams p = {};
+    p.C = C; p.bias = bias; p.M = M_total; p.N = N; p.K = K; p.sC = 0;
+    p.a_mn_major = 0; p.b_mn_major = transB ? 0 : 1;
+    p.alpha = alpha; p.beta = 0.f; p.act = act;
+    p.ag_world = world; p.ag_rows = rows; p.rs_rows = 1;
+    PeerMaps peers;
+    for (int r = 0; r < world; ++r)
+        if (make_tmap(&peers.m[r], (const float*)a_peers[r], K, rows, 1, 0, BLOCK_M, false)) return -1;
+    // tmA itself is never dereferenced in this mode; describe shard 0 so the map is valid
+    if (launch_tc_2sm((const float*)a_peers[0], B, p, 1, 0, 0, s, &peers)) return -1;
+    HETU_CHECK_LAUNCH("hetu_gemm_ag");
+    return 0;
+}
+
+// partial = op(A) @ op(B) [M, N]; rows [r*M/world, (r+1)*M/world) are added into out_peers[r] ([M/world, N],
+// zeroed by its owner before the opening barrier).
+HETU_API int hetu_gemm_rs(const float* A, const float* B, void* const* out_peers, int world, int M, int N, int K,
+                          int transA, int transB, float alpha, cudaStream_t s) {
+    if (world < 1 || world > 8 || M % world) { hetu_set_error("hetu_gemm_rs: bad world / M"); return -1; }
+    if ((transA ? M : K) % 4 || (transB ? K : N) % 4 || N % 4) { hetu_set_error("hetu_gemm_rs: dims must be multiples of 4"); return -1; }
+    GemmParams p = {};
+    p.C = (float*)out_peers[0]; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.sC = 0;
+    p.a_mn_major = transA ? 1 : 0; p.b_mn_major = transB ? 0 : 1;
+    p.alpha = alpha; p.beta = 0.f; p.act = ACT_NONE;
+    p.rs_world = world; p.rs_rows = M / world; p.ag_rows = 1;
+    for (int r = 0; r < world; ++r) p.rs_out[r] = (float*)out_peers[r];
+    if (launch_tc_2sm(A, B, p, 1, 0, 0, s)) return -1;
+    HETU_CHECK_LAUNCH("hetu_gemm_rs");
     return 0;
 }
 

@@ -33,7 +33,9 @@ class OpMeta(type):
         obj = super().__call__(*args, **kwargs)
         if not obj._no_adapt and any(getattr(i, 'mp_state', None) is not None for i in obj.inputs if i is not None):
             from ..parallel.mp_lowering import adapt
-            adapt(obj)
+            repl = adapt(obj)
+            if repl is not None:          # a fused communication+compute node takes the op's place
+                return repl
         return obj
 
 

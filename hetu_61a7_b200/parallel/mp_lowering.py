@@ -26,6 +26,7 @@ from typing import Optional, Tuple
 import torch
 
 from ..graph.node import Op
+import os
 
 
 def _group_of(op) -> Optional[tuple]:
@@ -168,6 +169,143 @@ class MPReduceScatterOp(Op):
         return [MPAllGatherOp(g, self.dim, self.n, self.group, ctx=self.raw_ctx)]
 
 
+def _symm_for(group):
+    """Symmetric-heap engine when the MP worker spans the whole (single-node) world, else None."""
+    comm = group.resolve()
+    if not comm.multi or not torch.cuda.is_available():
+        return None
+    from .comm import world
+    if comm is not world() or comm.nrank > 8:
+        return None
+    from .symm import SymmEngine
+    return SymmEngine.get(comm)
+
+
+class MPAllGatherMatMulOp(Op):
+    """Y = allgather_rows(X_shard) @ op(W) - sequence-parallel input of a column-parallel (or replicated)
+    linear layer.  On B200 one kernel (csrc/gemm_sm100.cu hetu_gemm_ag): the TMA producer of the
+    persistent 2-SM GEMM reads each 128-row block straight from its owner's HBM over NVLink, so the
+    gather overlaps the MMAs tile by tile and the gathered activation is never materialised."""
+
+    def __init__(self, shard, weight, trans_B, n, group, ctx=None):
+        super().__init__(MPAllGatherMatMulOp, [shard, weight], ctx, _adapt=False)
+        self.trans_B, self.n, self.group = trans_B, n, group
+        self.mp_group = group
+        self.mp_state = getattr(weight, 'mp_state', None)       # col-parallel weight -> split(1)
+        if self.mp_state is not None:
+            self.mp_state = ('split', 1, self.mp_state[2])
+        self.fused_launches = 0
+
+    def compute(self, input_vals, output_val=None, stream_handle=None):
+        x, w = input_vals
+        if x.device.type == 'meta':
+            return torch.empty((x.shape[0] * self.n, w.shape[0] if self.trans_B else w.shape[1]), device='meta')
+        from ..ops.linalg import gemm
+        comm = self.group.resolve()
+        if not comm.multi:
+            return gemm(x, w, False, self.trans_B)
+        eng = _symm_for(self.group) if x.is_cuda else None
+        m, k = x.shape
+        nn = w.shape[0] if self.trans_B else w.shape[1]
+        if eng is not None and m % 128 == 0 and k % 4 == 0 and nn % 4 == 0 and x.dtype == torch.float32 \
+                and (m * self.n) >= 512 and nn >= 256:
+            from .. import _lib as L
+            buf = eng.buffer(('tp_ag', self.id), m * k * 4)
+            buf.tensor(numel=m * k).copy_(x.reshape(-1))
+            out = torch.empty((m * self.n, nn), dtype=torch.float32, device=x.device)
+            eng.barrier()                                         # every shard is in place
+            L.call('gemm_ag', buf.ptrs, L.c_int(self.n), L.p(w.contiguous()), L.p(out), L.p(None),
+                   L.c_int(m * self.n), L.c_int(nn), L.c_int(k), L.c_int(int(self.trans_B)), L.c_f32(1.0),
+                   L.c_int(0), L.stream_ptr(x.device))
+            eng.barrier()                                         # peers are done reading my shard
+            self.fused_launches += 1
+            return out
+        return gemm(comm.allgather(x.contiguous()), w, False, self.trans_B)
+
+    def gradient(self, g):
+        from ..ops.linalg import matmul_op
+        shard, w = self.inputs
+        c = self.raw_ctx
+        d_full = matmul_op(g, w, False, not self.trans_B, ctx=c)          # partial sum or replicated
+        gathered = MPAllGatherOp(shard, 0, self.n, self.group, ctx=c)
+        if self.trans_B:
+            d_w = matmul_op(g, gathered, True, False, ctx=c)
+        else:
+            d_w = matmul_op(gathered, g, True, False, ctx=c)
+        return [d_full, d_w]                     # autodiff re-lays d_full out as split(0) (reduce-scatter / slice)
+
+
+class MPMatMulReduceScatterOp(Op):
+    """Y_shard = reduce_scatter_rows(op(A) @ op(B)) - output of a row-parallel linear layer handed to a
+    sequence-parallel region.  On B200 one kernel (hetu_gemm_rs): the epilogue of the 2-SM GEMM adds each
+    row block into its owner's buffer with red.global.add.v4.f32 over NVLink."""
+
+    def __init__(self, a, b, trans_A, trans_B, n, group, ctx=None):
+        super().__init__(MPMatMulReduceScatterOp, [a, b], ctx, _adapt=False)
+        self.trans_A, self.trans_B, self.n, self.group = trans_A, trans_B, n, group
+        self.mp_group = group
+        self.mp_state = ('split', 0, n)
+        self.fused_launches = 0
+
+    def compute(self, input_vals, output_val=None, stream_handle=None):
+        a, b = input_vals
+        m = a.shape[1] if self.trans_A else a.shape[0]
+        k = a.shape[0] if self.trans_A else a.shape[1]
+        nn = b.shape[0] if self.trans_B else b.shape[1]
+        if a.device.type == 'meta':
+            return torch.empty((m // self.n, nn), device='meta')
+        from ..ops.linalg import gemm
+        comm = self.group.resolve()
+        if not comm.multi:
+            return gemm(a, b, self.trans_A, self.trans_B)
+        eng = _symm_for(self.group) if a.is_cuda else None
+        if eng is not None and m % self.n == 0 and nn % 4 == 0 and k % 4 == 0 and m % 4 == 0 and a.dtype == torch.float32 \
+                and m >= 512 and nn >= 256:
+            from .. import _lib as L
+            rows = m // self.n
+            buf = eng.buffer(('tp_rs', self.id), rows * nn * 4)
+            acc = buf.tensor(numel=rows * nn)
+            acc.zero_()
+            eng.barrier()                                         # every accumulator is zeroed
+            L.call('gemm_rs', L.p(a.contiguous()), L.p(b.contiguous()), buf.ptrs, L.c_int(self.n), L.c_int(m),
+                   L.c_int(nn), L.c_int(k), L.c_int(int(self.trans_A)), L.c_int(int(self.trans_B)), L.c_f32(1.0),
+                   L.stream_ptr(a.device))
+            eng.barrier()                                         # all partial sums have landed
+            self.fused_launches += 1
+            return acc.view(rows, nn).clone()
+        return comm.reducescatter(gemm(a, b, self.trans_A, self.trans_B))
+
+    def gradient(self, g):
+        from ..ops.linalg import matmul_op
+        a, b = self.inputs
+        c = self.raw_ctx
+        if not self.trans_A:
+            d_a = MPAllGatherMatMulOp(g, b, not self.trans_B, self.n, self.group, ctx=c)     # AG(g) @ op(B)^T
+            d_a.mp_state = getattr(a, 'mp_state', None)
+        else:
+            full = MPAllGatherOp(g, 0, self.n, self.group, ctx=c)
+            d_a = matmul_op(b, full, self.trans_B, True, ctx=c)
+        full = MPAllGatherOp(g, 0, self.n, self.group, ctx=c)
+        if not self.trans_A and not self.trans_B:
+            d_b = matmul_op(a, full, True, False, ctx=c)
+        elif not self.trans_A and self.trans_B:
+            d_b = matmul_op(full, a, True, False, ctx=c)
+        elif self.trans_A and not self.trans_B:
+            d_b = matmul_op(a, full, False, False, ctx=c)
+        else:
+            d_b = matmul_op(full, a, True, True, ctx=c)
+        return [d_a, d_b]
+
+
+def reduce_scatter_of(node, d, n, group, ctx=None):
+    """partial -> split(d): fused into the producing GEMM when that is a plain matmul and d == 0."""
+    if d == 0 and node.op_type == 'MatMulOp' and len(node.inputs) == 2 and os.environ.get('HETU_TP_FUSE', '1') == '1':
+        a, b = node.inputs
+        return MPMatMulReduceScatterOp(a, b, node.matmul_attr_trans_A, node.matmul_attr_trans_B, n, group,
+                                       ctx=ctx if ctx is not None else node.raw_ctx)
+    return MPReduceScatterOp(node, d, n, group, ctx=ctx)
+
+
 _GROUPS = {}
 
 
@@ -213,7 +351,7 @@ def lower_dispatch(node, parts, ctx_group):
         elif st[0] == 'split' and st[1] == d and st[2] == n:
             out = node
         elif st[0] == 'partial':
-            out = MPReduceScatterOp(node, d, n, group, ctx=ctx)
+            out = reduce_scatter_of(node, d, n, group, ctx=ctx)
         else:
             out = MPSliceOp(to_replicated(node, src_group or group, ctx=ctx), d, n, group, ctx=ctx)
     if out is not node or getattr(out, 'mp_group', None) is None:
@@ -251,6 +389,10 @@ def adapt(op) -> None:
         if b is None and a and a[0] == 'split' and a[1] == a_m:
             op.mp_state = ('split', 0, a[2])             # row (batch) parallel
             return
+        if a and a[0] == 'split' and a[1] == a_m and not tA and b and b[0] == 'split' and b[1] == b_n \
+                and a[2] == b[2] and os.environ.get('HETU_TP_FUSE', '1') == '1':
+            # sequence-parallel activation into a column-parallel weight: all-gather -> GEMM, one kernel
+            return MPAllGatherMatMulOp(ins[0], ins[1], tB, a[2], group, ctx=ctx)
     if len(ins) == 1 and name in _ELEMENTWISE_UNARY:
         s = states[0]
         if s[0] == 'split' or name in _LINEAR_UNARY and name != 'AddByConstOp':
@@ -291,7 +433,7 @@ def match_grad_state(grad, node):
     if want is None:
         out = to_replicated(grad, group, ctx=ctx)
     elif have is not None and have[0] == 'partial':
-        out = MPReduceScatterOp(grad, want[1], want[2], group, ctx=ctx)
+        out = reduce_scatter_of(grad, want[1], want[2], group, ctx=ctx)
     else:
         out = MPSliceOp(to_replicated(grad, group, ctx=ctx), want[1], want[2], group, ctx=ctx)
     out.mp_group = group

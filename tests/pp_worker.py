@@ -74,6 +74,69 @@ def mine(ex, p):
     return None if t is None else t.detach().cpu().numpy()
 
 
+if case == 'sp':
+    # sequence parallel + tensor parallel block: rows-split activation -> (all-gather -> GEMM) column-parallel
+    # -> row-parallel (GEMM -> reduce-scatter) -> rows-split activation.  On GPUs both pairs must run as ONE
+    # fused kernel each (hetu_gemm_ag / hetu_gemm_rs over the symmetric heap).
+    from hetu_61a7_b200.parallel.mp_lowering import MPAllGatherMatMulOp, MPMatMulReduceScatterOp
+    from hetu_61a7_b200.graph.autodiff import find_topo_sort
+    Bn, Hd = (512, 256) if mode == 'gpu' else (8, 16)
+    rs2 = np.random.RandomState(1)
+    V1, V2, V3, V4 = [(rs2.randn(*shp) * sc).astype(np.float32) for shp, sc in
+                      (((12, Hd), 0.3), ((Hd, Hd), 0.08 if mode == 'gpu' else 0.3), ((Hd, Hd), 0.08 if mode == 'gpu' else 0.3), ((Hd, 4), 0.1))]
+    Xs = rs2.randn(4, Bn, 12).astype(np.float32)
+    Ys = np.eye(4, dtype=np.float32)[rs2.randint(0, 4, (4, Bn))]
+    with ht.context(dev(0)):
+        x = ht.Variable('x')
+        w1 = ht.Variable('w1', value=V1.copy())
+        a = ht.relu_op(ht.matmul_op(x, w1))
+    with ht.context((dev(0), dev(1))):
+        w2 = ht.Variable('w2', value=V2.copy())
+        w3 = ht.Variable('w3', value=V3.copy())
+        a = ht.dispatch(a, (2, 1))
+        h = ht.relu_op(ht.matmul_op(a, ht.dispatch(w2, (1, 2))))
+        o = ht.matmul_op(h, ht.dispatch(w3, (2, 1)))
+        o = ht.relu_op(ht.dispatch(o, (2, 1)))
+    with ht.context(dev(1)):
+        o = ht.dispatch(o, (1, 1))
+        w4 = ht.Variable('w4', value=V4.copy())
+        y_ = ht.Variable('y_')
+        loss = ht.reduce_mean_op(ht.softmaxcrossentropy_op(ht.matmul_op(o, w4), y_), [0])
+        train = ht.optim.SGDOptimizer(0.1).minimize(loss)
+    topo = find_topo_sort([loss, train])
+    fused = [n for n in topo if isinstance(n, (MPAllGatherMatMulOp, MPMatMulReduceScatterOp))]
+    assert len([n for n in fused if isinstance(n, MPAllGatherMatMulOp)]) >= 2, [n.name for n in fused]
+    assert len([n for n in fused if isinstance(n, MPMatMulReduceScatterOp)]) >= 2, [n.name for n in fused]
+    ex = ht.Executor([loss, train], seed=0)
+    got = []
+    for step in range(8):
+        out = ex.run(feed_dict={x: Xs[step % 4], y_: Ys[step % 4]})
+        if out[0] is not None:
+            got.append(float(out[0].asnumpy()))
+    tw = [torch.tensor(a.copy(), requires_grad=True) for a in (V1, V2, V3, V4)]
+    opt = torch.optim.SGD(tw, 0.1)
+    ref = []
+    for step in range(8):
+        opt.zero_grad()
+        hh = torch.relu(torch.relu(torch.relu(torch.tensor(Xs[step % 4]) @ tw[0]) @ tw[1]) @ tw[2])
+        l = torch.nn.functional.cross_entropy(torch.relu(hh) @ tw[3] if False else hh @ tw[3], torch.tensor(Ys[step % 4]).argmax(1))
+        l.backward()
+        opt.step()
+        ref.append(float(l))
+    tol = 2e-2 if mode == 'gpu' else 2e-4                       # tf32 tensor cores on the GPU path
+    if got:
+        assert np.allclose(got, ref, rtol=tol, atol=1e-4), (got, ref)
+    for p, r in zip((w1, w2, w3, w4), tw):
+        m = mine(ex, p)
+        if m is not None:
+            assert np.allclose(m, r.detach().numpy(), rtol=5 * tol, atol=5e-3 if mode == 'gpu' else 1e-5), p.name
+    if mode == 'gpu':
+        launched = sum(n.fused_launches for n in fused)
+        assert launched > 0, 'fused TP kernels did not run'
+        print('fused TP kernel launches on rank %d: %d' % (rank, launched), flush=True)
+    comm.barrier()
+    print('PP %s rank %d OK' % (case, rank), flush=True)
+    sys.exit(0)
 if case == 'gpipe':
     x, y_, loss, train, ws = build()
     ex = ht.Executor({'train': [loss, train]}, pipeline='gpipe', seed=0)

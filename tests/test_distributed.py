@@ -48,14 +48,14 @@ def _launch_pp(mode, case, timeout=600):
     assert r.returncode == 0 and r.stdout.count('OK') == 2, r.stdout[-2000:] + r.stderr[-4000:]
 
 
-@pytest.mark.parametrize('case', ['gpipe', 'pipedream', 'left', 'right', 'middle'])
+@pytest.mark.parametrize('case', ['gpipe', 'pipedream', 'left', 'right', 'middle', 'sp'])
 def test_pipeline_and_model_parallel_equivalence_gloo(case):
     _launch_pp('cpu', case)
 
 
 @pytest.mark.gpu
 @pytest.mark.timeout(900)
-@pytest.mark.parametrize('case', ['gpipe', 'pipedream', 'left', 'right', 'middle'])
+@pytest.mark.parametrize('case', ['gpipe', 'pipedream', 'left', 'right', 'middle', 'sp'])
 def test_pipeline_and_model_parallel_equivalence_nccl(case):
     if torch.cuda.device_count() < 2:
         pytest.skip('needs >= 2 GPUs (gpurun --gpus 2)')
