@@ -140,11 +140,16 @@ struct GemmParams {
     int a_mn_major, b_mn_major;    // 1 = MN-major (A given as [K,M] / B given as [K,N])
     int a_batched, b_batched;
     // tensor-parallel fusions over the symmetric heap (2-SM kernel only):
-    //  ag_world > 1: A is row-sharded over ag_world GPUs, rows [r*ag_rows, (r+1)*ag_rows) live on rank r and
-    //                are read in place through that rank's peer-mapped tensor map (all-gather -> GEMM)
+    //  ag_world > 1: A is row-sharded over ag_world GPUs (all-gather -> GEMM).  Every rank holds a full-size
+    //                gathered buffer; the epilogue warps first PUSH this rank's shard to all peers in
+    //                128-row blocks (posted NVLink stores + a release flag per block) while the producer /
+    //                MMA warps already work on the locally owned tiles; tiles of remote rows wait for
+    //                their block's flag.  Each byte crosses NVLink once.
     //  rs_world > 1: row block r of the partial product is reduced into rank r's buffer rs_out[r] with
     //                red.global.add.v4.f32 over NVLink (GEMM -> reduce-scatter)
-    int ag_world, ag_rows, rs_world, rs_rows;
+    int ag_world, ag_rows, ag_rank, rs_world, rs_rows;
+    float* ag_buf[8];              // gathered buffer of every rank (peer-mapped)
+    unsigned* ag_flag[8];          // flags[world][ag_rows / 128] of every rank
     float* rs_out[8];
     int dbg;                       // diagnostics: 1 = no TMA after the first ring fill, 2 = no MMA
     int a_mn4, b_mn4;              // MN-major operand described by ONE 4-D box {32 mn, 32 k, 4 groups, 1}
@@ -485,11 +490,15 @@ struct TileSched {
     }
 };
 
-struct PeerMaps { CUtensorMap m[8]; };
+// all-gather mode: start with the row tiles this rank owns (no waiting), then walk the peers' rows
+__device__ __forceinline__ int ag_rotate(int tm, int tiles_m, const GemmParams& p) {
+    const int first = (p.ag_rank * p.ag_rows) >> 8;
+    const int t = tm + first;
+    return t >= tiles_m ? t - tiles_m : t;
+}
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
-gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                     const __grid_constant__ PeerMaps peerA, GemmParams p,
+gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p,
                      int tiles_m, int tiles_n, int num_tiles, int kb_per_cluster) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -529,14 +538,19 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             while (sched.next(tile, kb0, kb1)) {
                 int bz, tm, tn;
                 decode_tile(tile, tiles_m, tiles_n, bz, tm, tn);
-                int m0 = tm * 256 + (int)rank * 128;
+                if (p.ag_world > 1) tm = ag_rotate(tm, tiles_m, p);
+                const int m0 = tm * 256 + (int)rank * 128;
                 const int nb0 = tn * k2TileN + (int)rank * 128;
                 const int ba = p.a_batched ? bz : 0, bb = p.b_batched ? bz : 0;
                 const CUtensorMap* mapA = &tmA;
-                if (p.ag_world > 1) {                  // this CTA's 128 rows live on one peer: read them in place
+                if (p.ag_world > 1 && m0 < p.M) {      // rows pushed by a peer: wait until that 128-row block has landed
                     const int owner = min(m0 / p.ag_rows, p.ag_world - 1);
-                    mapA = &peerA.m[owner];
-                    m0 -= owner * p.ag_rows;
+                    if (owner != p.ag_rank) {
+                        const unsigned* f = p.ag_flag[p.ag_rank] + owner * (p.ag_rows >> 7) + ((m0 - owner * p.ag_rows) >> 7);
+                        unsigned v;
+                        do { asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory"); } while (v == 0);
+                        asm volatile("fence.proxy.async.global;" ::: "memory");     // generic-proxy writes -> TMA reads
+                    }
                 }
                 for (int kb = kb0; kb < kb1; ++kb, ++it) {
                     const int st = it % k2Stages;
@@ -607,6 +621,33 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         const int q = warp & 3;
         float* tile_s = smem_epi + (warp - 2) * (32 * 36);
         const int sub_row = lane >> 3, c4 = (lane & 7) * 4;
+        if (p.ag_world > 1) {
+            // ---- all-gather push phase (128 threads): my shard -> every peer's gathered buffer
+            const int et = threadIdx.x - 64;
+            const int blocks = p.ag_rows >> 7;
+            const int items = blocks * (p.ag_world - 1);
+            const size_t blk_f4 = (size_t)128 * p.K / 4;
+            for (int item = blockIdx.x; item < items; item += gridDim.x) {
+                const int pi = item / blocks, blk = item - pi * blocks;
+                const int peer = pi + (pi >= p.ag_rank ? 1 : 0);
+                const size_t off = ((size_t)p.ag_rank * p.ag_rows + (size_t)blk * 128) * p.K;
+                const float4* src = reinterpret_cast<const float4*>(p.ag_buf[p.ag_rank] + off);
+                float4* dst = reinterpret_cast<float4*>(p.ag_buf[peer] + off);
+                for (size_t i = et; i < blk_f4; i += 128 * 8) {
+                    float4 v[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) if (i + u * 128 < blk_f4) v[u] = __ldg(src + i + u * 128);
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) if (i + u * 128 < blk_f4) dst[i + u * 128] = v[u];
+                }
+                __threadfence_system();
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (et == 0) {
+                    unsigned* f = p.ag_flag[peer] + p.ag_rank * blocks + blk;
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(1u) : "memory");
+                }
+            }
+        }
         int t_iter = 0, tile, kb0, kb1;
         TileSched sched(cluster_id, num_clusters, num_tiles, num_kb, kb_per_cluster);
         for (; sched.next(tile, kb0, kb1); ++t_iter) {
@@ -614,6 +655,7 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             const bool partial = kb0 != 0 || kb1 != num_kb || p.rs_world > 1;   // accumulate into C (stream-K / reduce-scatter)
             int bz, tm, tn;
             decode_tile(tile, tiles_m, tiles_n, bz, tm, tn);
+            if (p.ag_world > 1) tm = ag_rotate(tm, tiles_m, p);
             const int m0 = tm * 256 + (int)rank * 128, n0 = tn * k2TileN;
             mbar_wait(&tfull_bar[acc], (t_iter >> 1) & 1);
             tc_fence_after();
@@ -697,10 +739,8 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     if (warp == 1) tmem_dealloc_2sm(tmem_base, 512);
 }
 
-static int launch_tc_2sm(const float* A, const float* B, GemmParams& p, int batch, long long sA, long long sB, cudaStream_t s,
-                         const PeerMaps* peers = nullptr) {
+static int launch_tc_2sm(const float* A, const float* B, GemmParams& p, int batch, long long sA, long long sB, cudaStream_t s) {
     CUtensorMap tmA, tmB;
-    static PeerMaps no_peers;
     p.a_mn4 = p.b_mn4 = 0;
     if (!p.a_mn_major) { if (make_tmap(&tmA, A, p.K, p.M, p.a_batched ? batch : 1, sA, BLOCK_M, false)) return -1; }
     else if (p.M % 128 == 0 && make_tmap_mn4(&tmA, A, p.M, p.K, p.a_batched ? batch : 1, sA) == 0) p.a_mn4 = 1;
@@ -747,8 +787,7 @@ static int launch_tc_2sm(const float* A, const float* B, GemmParams& p, int batc
         kb_per_cluster = (int)((total + clusters - 1) / clusters);
         HETU_CUDA(cudaMemsetAsync(p.C, 0, sizeof(float) * (size_t)(batch > 1 ? p.sC * batch : (long long)p.M * p.N), s));
     }
-    gemm_tf32_2sm_kernel<<<dim3(2 * clusters), kGemmThreads, k2Smem, s>>>(tmA, tmB, peers ? *peers : no_peers, p, tiles_m, tiles_n,
-                                                                          num_tiles, kb_per_cluster);
+    gemm_tf32_2sm_kernel<<<dim3(2 * clusters), kGemmThreads, k2Smem, s>>>(tmA, tmB, p, tiles_m, tiles_n, num_tiles, kb_per_cluster);
     return 0;
 }
 
@@ -1136,9 +1175,11 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
 // step but the operand fetch (TMA over peer-mapped memory) / the epilogue (NVLink reductions).
 // The caller brackets each call with hetu_symm_barrier (inputs complete / outputs complete).
 
-// C[M_total, N] = allgather_rows(A_shards) @ op(B); a_peers[r] = rank r's [M_total/world, K] shard.
-HETU_API int hetu_gemm_ag(void* const* a_peers, int world, const float* B, float* C, const float* bias, int M_total,
-                          int N, int K, int transB, float alpha, int act, cudaStream_t s) {
+// C[M_total, N] = allgather_rows(A) @ op(B).  gathered[r] = rank r's [M_total, K] gathered buffer (this rank's
+// own rows already in place at row rank*M_total/world), flags[r] = rank r's zeroed flag array
+// [world][M_total/world/128].  One opening barrier (flags zeroed + shards in place everywhere) must precede.
+HETU_API int hetu_gemm_ag(void* const* gathered, void* const* flags, int rank, int world, const float* B, float* C,
+                          const float* bias, int M_total, int N, int K, int transB, float alpha, int act, cudaStream_t s) {
     if (world < 1 || world > 8 || M_total % world) { hetu_set_error("hetu_gemm_ag: bad world / M"); return -1; }
     const int rows = M_total / world;
     if (rows % 128 || K % 4 || (transB ? K : N) % 4) { hetu_set_error("hetu_gemm_ag: shard rows must be a multiple of 128"); return -1; }
@@ -1146,12 +1187,9 @@ HETU_API int hetu_gemm_ag(void* const* a_peers, int world, const float* B, float
     p.C = C; p.bias = bias; p.M = M_total; p.N = N; p.K = K; p.sC = 0;
     p.a_mn_major = 0; p.b_mn_major = transB ? 0 : 1;
     p.alpha = alpha; p.beta = 0.f; p.act = act;
-    p.ag_world = world; p.ag_rows = rows; p.rs_rows = 1;
-    PeerMaps peers;
-    for (int r = 0; r < world; ++r)
-        if (make_tmap(&peers.m[r], (const float*)a_peers[r], K, rows, 1, 0, BLOCK_M, false)) return -1;
-    // tmA itself is never dereferenced in this mode; describe shard 0 so the map is valid
-    if (launch_tc_2sm((const float*)a_peers[0], B, p, 1, 0, 0, s, &peers)) return -1;
+    p.ag_world = world; p.ag_rows = rows; p.ag_rank = rank; p.rs_rows = 1;
+    for (int r = 0; r < world; ++r) { p.ag_buf[r] = (float*)gathered[r]; p.ag_flag[r] = (unsigned*)flags[r]; }
+    if (launch_tc_2sm((const float*)gathered[rank], B, p, 1, 0, 0, s)) return -1;
     HETU_CHECK_LAUNCH("hetu_gemm_ag");
     return 0;
 }

@@ -210,14 +210,16 @@ class MPAllGatherMatMulOp(Op):
         if eng is not None and m % 128 == 0 and k % 4 == 0 and nn % 4 == 0 and x.dtype == torch.float32 \
                 and (m * self.n) >= 512 and nn >= 256:
             from .. import _lib as L
-            buf = eng.buffer(('tp_ag', self.id), m * k * 4)
-            buf.tensor(numel=m * k).copy_(x.reshape(-1))
+            rank = comm.rank
+            buf = eng.buffer(('tp_ag', self.id), m * self.n * k * 4)           # full gathered activation
+            flg = eng.buffer(('tp_ag_flags', self.id), self.n * (m // 128) * 4)
+            buf.tensor(numel=m * self.n * k)[rank * m * k:(rank + 1) * m * k].copy_(x.reshape(-1))
+            flg.tensor(dtype=torch.int32, numel=self.n * (m // 128)).zero_()
             out = torch.empty((m * self.n, nn), dtype=torch.float32, device=x.device)
-            eng.barrier()                                         # every shard is in place
-            L.call('gemm_ag', buf.ptrs, L.c_int(self.n), L.p(w.contiguous()), L.p(out), L.p(None),
-                   L.c_int(m * self.n), L.c_int(nn), L.c_int(k), L.c_int(int(self.trans_B)), L.c_f32(1.0),
+            eng.barrier()                                         # shards in place, flags zeroed, last round's readers done
+            L.call('gemm_ag', buf.ptrs, flg.ptrs, L.c_int(rank), L.c_int(self.n), L.p(w.contiguous()), L.p(out),
+                   L.p(None), L.c_int(m * self.n), L.c_int(nn), L.c_int(k), L.c_int(int(self.trans_B)), L.c_f32(1.0),
                    L.c_int(0), L.stream_ptr(x.device))
-            eng.barrier()                                         # peers are done reading my shard
             self.fused_launches += 1
             return out
         return gemm(comm.allgather(x.contiguous()), w, False, self.trans_B)
