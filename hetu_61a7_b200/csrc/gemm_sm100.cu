@@ -145,9 +145,10 @@ struct GemmParams {
     //                128-row blocks (posted NVLink stores + a release flag per block) while the producer /
     //                MMA warps already work on the locally owned tiles; tiles of remote rows wait for
     //                their block's flag.  Each byte crosses NVLink once.
-    //  rs_world > 1: row block r of the partial product is reduced into rank r's buffer rs_out[r] with
-    //                red.global.add.v4.f32 over NVLink (GEMM -> reduce-scatter)
-    int ag_world, ag_rows, ag_rank, rs_world, rs_rows;
+    //  rs_world > 1: row block r of the partial product is stored into slice `rs_rank` of rank r's staging
+    //                buffer rs_out[r] ([world][rs_rows][N]) with plain 128-bit NVLink stores from the epilogue;
+    //                the owner sums its `world` slices after the closing barrier (GEMM -> reduce-scatter)
+    int ag_world, ag_rows, ag_rank, rs_world, rs_rows, rs_rank;
     float* ag_buf[8];              // gathered buffer of every rank (peer-mapped)
     unsigned* ag_flag[8];          // flags[world][ag_rows / 128] of every rank
     float* rs_out[8];
@@ -677,11 +678,17 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                         const int row = row_base + r + sub_row;
                         if (row >= p.M) continue;
                         float* dst = Cb + (size_t)row * p.N + col;
-                        if (p.rs_world > 1) {              // row block owner's buffer, over NVLink
-                            const int owner = min(row / p.rs_rows, p.rs_world - 1);
-                            dst = p.rs_out[owner] + (size_t)(row - owner * p.rs_rows) * p.N + col;
-                        }
                         const float* src = &tile_s[(r + sub_row) * 36 + c4];
+                        if (p.rs_world > 1) {              // my slice of the row owner's staging buffer, over NVLink
+                            const int owner = min(row / p.rs_rows, p.rs_world - 1);
+                            dst = p.rs_out[owner] + ((size_t)p.rs_rank * p.rs_rows + (row - owner * p.rs_rows)) * p.N + col;
+                            if (vec_ok && col + 3 < p.N) {
+                                *reinterpret_cast<float4*>(dst) = make_float4(p.alpha * src[0], p.alpha * src[1], p.alpha * src[2], p.alpha * src[3]);
+                            } else {
+                                for (int u = 0; u < 4 && col + u < p.N; ++u) dst[u] = p.alpha * src[u];
+                            }
+                            continue;
+                        }
                         if (vec_ok && col + 3 < p.N) {
                             float4 o = make_float4(p.alpha * src[0], p.alpha * src[1], p.alpha * src[2], p.alpha * src[3]);
                             if (kb0 == 0 && p.bias != nullptr) {
@@ -1003,15 +1010,43 @@ template <int TB>
 __global__ void __launch_bounds__(256) gemm_skinny_rows_kernel(const float* __restrict__ A, const float* __restrict__ B,
                                                                float* __restrict__ C, const float* __restrict__ bias,
                                                                int M, int N, int K, float alpha, float beta, int act) {
+    extern __shared__ float4 skinny_smem[];
+    float* Bs = reinterpret_cast<float*>(skinny_smem);      // [N][K] when it fits (bs_ok), else unused
     const int lane = threadIdx.x & 31;
-    const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (row >= M) return;
+    const bool bs_ok = (size_t)N * K * 4 <= 48 * 1024 && (K & 3) == 0;
+    if (bs_ok) {
+        for (int i = threadIdx.x; i < N * K; i += 256) {
+            const int n = i / K, k = i - n * K;
+            Bs[i] = TB ? __ldg(B + i) : __ldg(B + (size_t)k * N + n);
+        }
+        __syncthreads();
+    }
+    for (int row = blockIdx.x * 8 + (threadIdx.x >> 5); row < M; row += gridDim.x * 8) {
     const float* a = A + (size_t)row * K;
     float acc[kSkinnyN];
 #pragma unroll
     for (int n = 0; n < kSkinnyN; ++n) acc[n] = 0.f;
     const bool vec = (K & 3) == 0 && ((reinterpret_cast<uintptr_t>(A) & 15) == 0);
-    if (vec) {
+    if (vec && bs_ok) {
+        for (int kb = lane * 4; kb < K; kb += 512) {
+            float4 av[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                av[u] = (kb + u * 128 < K) ? __ldcs(reinterpret_cast<const float4*>(a + kb + u * 128)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int k = kb + u * 128;
+                if (k >= K) break;
+#pragma unroll
+                for (int n = 0; n < kSkinnyN; ++n) {
+                    if (n < N) {
+                        const float4 bv = *reinterpret_cast<const float4*>(Bs + n * K + k);
+                        acc[n] += av[u].x * bv.x + av[u].y * bv.y + av[u].z * bv.z + av[u].w * bv.w;
+                    }
+                }
+            }
+        }
+    } else if (vec) {
         for (int kb = lane * 4; kb < K; kb += 512) {
             float4 av[4];
 #pragma unroll
@@ -1055,6 +1090,7 @@ __global__ void __launch_bounds__(256) gemm_skinny_rows_kernel(const float* __re
             *dst = apply_act(o, act);
         }
     }
+    }   // row loop
 }
 
 // A stored [K, M] (transposed operand): threads run along M (coalesced), 4 k-lanes per block, K split over
@@ -1089,12 +1125,29 @@ __global__ void __launch_bounds__(256) gemm_skinny_cols_kernel(const float* __re
     }
 }
 
+// K <= 8: a sum of a few outer products (gradient of a [*, d] x [d, 1] projection); one thread per output.
+__global__ void __launch_bounds__(256) gemm_tinyk_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                         float* __restrict__ C, const float* __restrict__ bias, int M, int N,
+                                                         int K, int tA, int tB, float alpha, float beta, int act) {
+    const size_t total = (size_t)M * N;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int m = (int)(i / N), n = (int)(i - (size_t)m * N);
+        float acc = 0.f;
+        for (int k = 0; k < K; ++k)
+            acc += __ldg(tA ? A + (size_t)k * M + m : A + (size_t)m * K + k) * __ldg(tB ? B + (size_t)n * K + k : B + (size_t)k * N + n);
+        float o = alpha * acc + (bias ? __ldg(bias + n) : 0.f);
+        if (beta != 0.f) o += beta * C[i];
+        C[i] = apply_act(o, act);
+    }
+}
+
 static void launch_skinny(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, int tA, int tB,
                           float alpha, float beta, int act, cudaStream_t s) {
     if (!tA) {
-        dim3 grid((M + 7) / 8);
-        if (tB) gemm_skinny_rows_kernel<1><<<grid, 256, 0, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
-        else gemm_skinny_rows_kernel<0><<<grid, 256, 0, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
+        dim3 grid(std::min((M + 7) / 8, kNumSMs * 6));
+        const size_t sm = ((size_t)N * K * 4 <= 48 * 1024 && (K & 3) == 0) ? (size_t)N * K * 4 : 0;
+        if (tB) gemm_skinny_rows_kernel<1><<<grid, 256, sm, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
+        else gemm_skinny_rows_kernel<0><<<grid, 256, sm, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
         return;
     }
     const int mblocks = (M + 63) / 64;
@@ -1127,7 +1180,12 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
                   (sA % 4 == 0) && (sB % 4 == 0);
     const double macs = (double)M * N * K * batch;
     bool big = macs > (double)(1 << 25) && M >= 64 && N >= 8 && K >= 32;
-    if (N <= kSkinnyN && batch == 1 && (double)M * K >= (double)(1 << 20) && (!transA || beta == 0.f)) {
+    if (K <= 8 && batch == 1) {
+        gemm_tinyk_kernel<<<ew_grid((size_t)M * N, 256), 256, 0, s>>>(A, B, C, bias, M, N, K, transA, transB, alpha, beta, act);
+        HETU_CHECK_LAUNCH("hetu_gemm(tiny-k)");
+        return 0;
+    }
+    if (N <= kSkinnyN && batch == 1 && (double)M * K >= (double)(1 << 16) && (!transA || beta == 0.f)) {
         launch_skinny(A, B, C, bias, M, N, K, transA, transB, alpha, beta, act, s);
         HETU_CHECK_LAUNCH("hetu_gemm(skinny)");
         return 0;
@@ -1194,9 +1252,10 @@ HETU_API int hetu_gemm_ag(void* const* gathered, void* const* flags, int rank, i
     return 0;
 }
 
-// partial = op(A) @ op(B) [M, N]; rows [r*M/world, (r+1)*M/world) are added into out_peers[r] ([M/world, N],
-// zeroed by its owner before the opening barrier).
-HETU_API int hetu_gemm_rs(const float* A, const float* B, void* const* out_peers, int world, int M, int N, int K,
+// partial = op(A) @ op(B) [M, N]; rows [r*M/world, (r+1)*M/world) are stored into slice `rank` of out_peers[r]
+// (a [world][M/world][N] staging buffer on rank r).  The caller brackets the call with two barriers and sums
+// its own staging slices afterwards.
+HETU_API int hetu_gemm_rs(const float* A, const float* B, void* const* out_peers, int rank, int world, int M, int N, int K,
                           int transA, int transB, float alpha, cudaStream_t s) {
     if (world < 1 || world > 8 || M % world) { hetu_set_error("hetu_gemm_rs: bad world / M"); return -1; }
     if ((transA ? M : K) % 4 || (transB ? K : N) % 4 || N % 4) { hetu_set_error("hetu_gemm_rs: dims must be multiples of 4"); return -1; }
@@ -1204,7 +1263,7 @@ HETU_API int hetu_gemm_rs(const float* A, const float* B, void* const* out_peers
     p.C = (float*)out_peers[0]; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.sC = 0;
     p.a_mn_major = transA ? 1 : 0; p.b_mn_major = transB ? 0 : 1;
     p.alpha = alpha; p.beta = 0.f; p.act = ACT_NONE;
-    p.rs_world = world; p.rs_rows = M / world; p.ag_rows = 1;
+    p.rs_world = world; p.rs_rows = M / world; p.rs_rank = rank; p.ag_rows = 1;
     for (int r = 0; r < world; ++r) p.rs_out[r] = (float*)out_peers[r];
     if (launch_tc_2sm(A, B, p, 1, 0, 0, s)) return -1;
     HETU_CHECK_LAUNCH("hetu_gemm_rs");

@@ -119,9 +119,10 @@ class MatMulOp(Op):
         super().__init__(MatMulOp, [node_A, node_B], ctx)
         self.matmul_attr_trans_A = trans_A
         self.matmul_attr_trans_B = trans_B
+        self.act = ACT_NONE          # set by the executor's epilogue-fusion pass (graph/fusion.py)
 
     def compute(self, input_vals, output_val=None, stream_handle=None):
-        return gemm(input_vals[0], input_vals[1], self.matmul_attr_trans_A, self.matmul_attr_trans_B)
+        return gemm(input_vals[0], input_vals[1], self.matmul_attr_trans_A, self.matmul_attr_trans_B, act=self.act)
 
     def gradient(self, g):
         A, B = self.inputs

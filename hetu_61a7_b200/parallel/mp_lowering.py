@@ -265,16 +265,16 @@ class MPMatMulReduceScatterOp(Op):
                 and m >= 512 and nn >= 256:
             from .. import _lib as L
             rows = m // self.n
-            buf = eng.buffer(('tp_rs', self.id), rows * nn * 4)
-            acc = buf.tensor(numel=rows * nn)
-            acc.zero_()
-            eng.barrier()                                         # every accumulator is zeroed
-            L.call('gemm_rs', L.p(a.contiguous()), L.p(b.contiguous()), buf.ptrs, L.c_int(self.n), L.c_int(m),
-                   L.c_int(nn), L.c_int(k), L.c_int(int(self.trans_A)), L.c_int(int(self.trans_B)), L.c_f32(1.0),
-                   L.stream_ptr(a.device))
-            eng.barrier()                                         # all partial sums have landed
+            buf = eng.buffer(('tp_rs', self.id), self.n * rows * nn * 4)        # [world][rows][N] staging
+            eng.barrier()                                         # last round's staging has been consumed everywhere
+            L.call('gemm_rs', L.p(a.contiguous()), L.p(b.contiguous()), buf.ptrs, L.c_int(comm.rank), L.c_int(self.n),
+                   L.c_int(m), L.c_int(nn), L.c_int(k), L.c_int(int(self.trans_A)), L.c_int(int(self.trans_B)),
+                   L.c_f32(1.0), L.stream_ptr(a.device))
+            eng.barrier()                                         # every rank's partial rows have landed
+            from ..ops.reduce import _reduce
+            acc = _reduce(buf.tensor(numel=self.n * rows * nn).view(self.n, rows, nn), [0], False, 0)
             self.fused_launches += 1
-            return acc.view(rows, nn).clone()
+            return acc
         return comm.reducescatter(gemm(a, b, self.trans_A, self.trans_B))
 
     def gradient(self, g):

@@ -358,3 +358,29 @@ def test_fused_attention_matches_autograd():
     (o * o).sum().backward()
     for got, ref in zip(res, [o.detach(), tq.grad, tk.grad, tv.grad]):
         np.testing.assert_allclose(got, ref.numpy(), rtol=1e-4, atol=1e-5)
+
+
+def test_matmul_relu_epilogue_fusion_matches_oracle():
+    """graph/fusion.py moves relu into the GEMM epilogue; forward and backward must be unchanged."""
+    rs = np.random.RandomState(0)
+    W1, W2, W3 = [(rs.randn(*s) * 0.3).astype(np.float32) for s in ((12, 16), (16, 16), (16, 4))]
+    X = rs.randn(8, 12).astype(np.float32)
+    Y = np.eye(4, dtype=np.float32)[rs.randint(0, 4, 8)]
+    x, y_ = ht.Variable('x'), ht.Variable('y_')
+    w1, w2, w3 = ht.Variable('w1', value=W1.copy()), ht.Variable('w2', value=W2.copy()), ht.Variable('w3', value=W3.copy())
+    h = ht.relu_op(ht.matmul_op(ht.relu_op(ht.matmul_op(x, w1)), w2))
+    loss = ht.reduce_mean_op(ht.softmaxcrossentropy_op(ht.matmul_op(h, w3), y_), [0])
+    train = ht.optim.SGDOptimizer(0.1).minimize(loss)
+    ex = ht.Executor([loss, train], ctx=ht.cpu(0))
+    assert ex.fused_epilogues == 2
+    got = [float(ex.run(feed_dict={x: X, y_: Y})[0].asnumpy()) for _ in range(5)]
+    tw = [torch.tensor(a.copy(), requires_grad=True) for a in (W1, W2, W3)]
+    opt = torch.optim.SGD(tw, 0.1)
+    ref = []
+    for _ in range(5):
+        opt.zero_grad()
+        l = torch.nn.functional.cross_entropy(torch.relu(torch.relu(torch.tensor(X) @ tw[0]) @ tw[1]) @ tw[2], torch.tensor(Y).argmax(1))
+        l.backward()
+        opt.step()
+        ref.append(float(l))
+    np.testing.assert_allclose(got, ref, rtol=1e-4, atol=1e-6)
