@@ -140,6 +140,55 @@ int hetu_moe_combine_peer(void* const* idx, void* const* loc, void* const* gate,
                           void* const* peer_bases, int world, int rank, float* out, int T, int d, int capacity,
                           int e_local, cudaStream_t s);
 
+int hetu_moe_gate_grad_peer(const float* dout, const float* idx, const float* loc, void* const* peer_bases,
+                            int world, int rank, float* out, int T, int d, int capacity, int e_local,
+                            cudaStream_t s);
+
+/* ---- attention: examples/nlp/bert/hetu_bert.py:249-264 builds it from 5 graph ops; here the two
+ *      batched GEMMs run on hetu_gemm and everything between them is one in-place row kernel ---- */
+int hetu_attn_softmax(float* s, const float* mask, float* lse, long long rows, int cols, long long rows_per_batch,
+                      float scale, cudaStream_t st);
+int hetu_attn_softmax_bwd(const float* p, float* dp, long long rows, int cols, float scale, cudaStream_t st);
+
+/* ---- symmetric heap + in-kernel NVLink collectives (csrc/collectives.cu) ----------------------
+ * reference: src/communication/mpi_nccl_communication.cu:31-483 (NCCL wrappers) and
+ * gpu_ops/{AllReduceCommunicate,AllGatherCommunicate,ReduceScatterCommunicate,AllToAll}.py.
+ * Buffers come from hetu_symm_alloc (cudaMalloc + CUDA IPC handle); every rank opens its peers'
+ * handles and passes the table of base pointers (`*_ptrs`, up to 16 entries).  `flag_ptrs` is the
+ * table of each rank's flag page, `epoch`/`gate` are device counters owned by the caller.  Every
+ * collective opens and closes with a cross-GPU barrier, so buffers are reusable on return and the
+ * launches are CUDA-graph replay safe. */
+int hetu_symm_alloc(size_t bytes, void** ptr, void* handle64);
+int hetu_symm_open(const void* handle64, void** ptr);
+int hetu_symm_close(void* ptr);
+int hetu_symm_free(void* ptr);
+int hetu_symm_barrier(void* const* flag_ptrs, int rank, int world, void* epoch, cudaStream_t s);
+int hetu_pack_tensors(int ntensors, void* const* srcs, const long long* offsets, const long long* sizes, float* dst,
+                      float scale, cudaStream_t s);
+int hetu_symm_allreduce(void* const* arena_ptrs, size_t byte_off, void* const* flag_ptrs, int rank, int world,
+                        void* epoch, void* gate, long long n, float* out, cudaStream_t s);
+/* all-reduce fused with the optimizer update of `ntensors` parameters (kind = OPT_* of multi_tensor_opt) */
+int hetu_symm_allreduce_opt(void* const* arena_ptrs, size_t byte_off, void* const* flag_ptrs, int rank, int world,
+                            void* epoch, void* gate, int kind, int ntensors, void* const* params, void* const* s1,
+                            void* const* s2, const long long* offsets, const long long* sizes, const float* lr_p,
+                            const void* step_p, float h0, float h1, float h2, float h3, float l2reg, cudaStream_t s);
+/* same_chunk = 1: all-gather (every peer receives `chunk` floats from me); 0: all-to-all of `chunk` floats per peer */
+int hetu_symm_exchange(const float* send, void* const* recv_ptrs, size_t byte_off, void* const* flag_ptrs, int rank,
+                       int world, void* epoch, void* gate, long long chunk, int same_chunk, cudaStream_t s);
+int hetu_symm_reduce_scatter(void* const* arena_ptrs, size_t byte_off, void* const* flag_ptrs, int rank, int world,
+                             void* epoch, void* gate, long long chunk, float* out, cudaStream_t s);
+
+/* ---- tensor-parallel GEMMs fused with their collective (persistent 2-SM tcgen05 kernel) ---------
+ * reference: the model-parallel split / datatransfer ops (gpu_ops/Dispatch.py marker; lowering absent
+ * upstream).  hetu_gemm_ag: C = allgather_rows(A) @ op(B); the epilogue warps push this rank's shard to
+ * every peer's gathered buffer in 128-row blocks while the MMA warps start on the local rows; remote
+ * tiles wait for their block's flag.  hetu_gemm_rs: partial = op(A) @ op(B); row block r is stored into
+ * slice `rank` of rank r's [world][M/world][N] staging buffer straight from the epilogue. */
+int hetu_gemm_ag(void* const* gathered, void* const* flags, int rank, int world, const float* B, float* C,
+                 const float* bias, int M_total, int N, int K, int transB, float alpha, int act, cudaStream_t s);
+int hetu_gemm_rs(const float* A, const float* B, void* const* out_peers, int rank, int world, int M, int N, int K,
+                 int transA, int transB, float alpha, cudaStream_t s);
+
 /* ---- parameter initialisation: Initializers.cu ------------------------------------------
  * kind 0 constant(a) 1 uniform[a,b) 2 normal(mean a, std b) 3 truncated normal (|z| <= 2). */
 int hetu_init_random(float* out, size_t n, int kind, float a, float b, unsigned long long seed, cudaStream_t s);
