@@ -809,7 +809,7 @@ class SubExecutor(object):
     # ----------------------------------------------------------------------------- misc
     def profile(self, feed_shapes, log_file, profiler='cpu'):
         from ..utils.profiler import HetuProfiler
-        prof = HetuProfiler(self.computing_nodes, feed_shapes, self.node_to_shape_map,
+        prof = HetuProfiler(self.computing_nodes, feed_shapes, self.infer_shape(feed_shapes),
                             ctx=self.config.context)
         prof.profile_n_log(log_file, profiler=profiler)
 

@@ -1,0 +1,87 @@
+"""Auxiliary subsystems: per-node timer executor, op micro-profiler, collective profiler (loop-back
+world), distribution strategies, GNN ops.  Pattern: reference tests/test_profiler.py (smoke) and
+examples/gnn scripts."""
+import numpy as np
+import scipy.sparse as sp
+import torch
+
+import hetu as ht
+
+
+def _mlp():
+    x, y_ = ht.Variable('x'), ht.Variable('y_')
+    h = ht.relu_op(ht.matmul_op(x, ht.init.xavier_normal((20, 16), name='w1')))
+    logits = ht.matmul_op(h, ht.init.xavier_normal((16, 4), name='w2'))
+    loss = ht.reduce_mean_op(ht.softmaxcrossentropy_op(logits, y_), [0])
+    return x, y_, loss, ht.optim.SGDOptimizer(0.1).minimize(loss)
+
+
+def test_timer_executor_and_profiler(tmp_path):
+    rs = np.random.RandomState(0)
+    x, y_, loss, train = _mlp()
+    ex = ht.Executor([loss, train], ctx=ht.cpu(0), timing='cpu')
+    X, Y = rs.randn(8, 20).astype(np.float32), np.eye(4, dtype=np.float32)[rs.randint(0, 4, 8)]
+    for _ in range(3):
+        ex.run(feed_dict={x: X, y_: Y})
+    for level in ('node', 'type'):
+        path = str(tmp_path / ('timer_%s.txt' % level))
+        ex.logOut(path, log_level=level)
+        txt = open(path).read()
+        assert 'MatMulOp' in txt and 'ms' in txt
+    # op micro-profiler (Executor.profile -> HetuProfiler.profile_n_log)
+    x, y_, loss, train = _mlp()
+    ex = ht.Executor([loss, train], ctx=ht.cpu(0))
+    ex.run(feed_dict={x: X, y_: Y})
+    path = str(tmp_path / 'profile.txt')
+    ex.profile({x: (8, 20), y_: (8, 4)}, path, profiler='cpu')
+    lines = open(path).read().strip().splitlines()
+    assert len(lines) >= 3 and all(l.endswith('ms') for l in lines)
+
+
+def test_nccl_profiler_loopback():
+    prof = ht.NCCLProfiler()
+    for prim in ('allreduce', 'allgather', 'reducescatter', 'broadcast', 'reduce', 'alltoall'):
+        res = prof.profile(prim, [1024, 4096])
+        assert set(res) == {1024, 4096} and all(v >= 0 for v in res.values())
+
+
+def test_strategies_assign_contexts(monkeypatch):
+    from hetu_61a7_b200.distributed_strategies import hybrid, simple
+    x, y_, loss, train = _mlp()
+    monkeypatch.setattr(simple.DataParallel, 'worker_devices', lambda self: ['gpu:0', 'gpu:1', 'gpu:2', 'gpu:3'], raising=False)
+    monkeypatch.setattr(hybrid.ModelParallel, 'worker_devices', lambda self: ['gpu:0', 'gpu:1', 'gpu:2', 'gpu:3'], raising=False)
+    mp = hybrid.ModelParallel(tp=2)
+    ctx = mp.set_raw_ctxs_n_states([loss, train])
+    assert ctx.is_mp and ctx.worker_num == 2 and all(isinstance(w, tuple) and len(w) == 2 for w in ctx.workers)
+    assert loss.raw_ctx is ctx
+    plan = hybrid.LayerPlan(dp=2, tp=2, pp_stage=1)
+    assert 'tp=2' in repr(plan)
+    g = hybrid._stage_group(['gpu:0', 'gpu:1', 'gpu:2', 'gpu:3'], 2, 2)
+    assert g.worker_num == 2 and g.mp_dev_num == 2
+
+
+def test_gnn_ops_match_dense():
+    rs = np.random.RandomState(0)
+    N, F, O = 30, 8, 5
+    A = sp.random(N, N, 0.2, random_state=rs, format='coo', dtype=np.float32)
+    H, W = rs.randn(N, F).astype(np.float32), rs.randn(F, O).astype(np.float32)
+    adj = ht.Variable('adj', trainable=False)
+    h, w = ht.Variable('h', value=H), ht.Variable('w', value=W)
+    out = ht.csrmm_op(adj, ht.matmul_op(h, w))
+    loss = ht.reduce_sum_op(ht.mul_op(out, out), [0, 1])
+    gh, gw = ht.gradients(loss, [h, w])
+    ex = ht.Executor([out, gh, gw], ctx=ht.cpu(0))
+    mp = ht.sparse_array(A.data, (A.row, A.col), shape=(N, N), ctx=ht.cpu(0))
+    o, g1, g2 = [r.asnumpy() for r in ex.run(feed_dict={adj: mp})]
+    Ad = torch.tensor(A.toarray())
+    th, tw = torch.tensor(H, requires_grad=True), torch.tensor(W, requires_grad=True)
+    ref = Ad @ (th @ tw)
+    (ref * ref).sum().backward()
+    np.testing.assert_allclose(o, ref.detach().numpy(), rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(g1, th.grad.numpy(), rtol=1e-3, atol=1e-3)
+    np.testing.assert_allclose(g2, tw.grad.numpy(), rtol=1e-3, atol=1e-3)
+    # 1.5-D distributed GCN layer on a single-rank world == plain A (H W)
+    comm = ht.wrapped_mpi_nccl_init()
+    z = ht.distgcn_15d_op(adj, h, w, N, N, 1, 1, 0, comm, [None, None], True)
+    ex = ht.Executor([z], ctx=ht.cpu(0))
+    np.testing.assert_allclose(ex.run(feed_dict={adj: mp})[0].asnumpy(), (Ad @ torch.tensor(H)) @ torch.tensor(W), rtol=1e-4, atol=1e-4)
