@@ -68,13 +68,14 @@ def _emit(c: _Ctx, node, ins: List[str], out: str):
         c.add('Mul', [ins[0], c.const(np.float32(node.a))], [out])
     elif t == 'MatMulOp' or t == 'LinearOp':
         tA, tB = int(node.matmul_attr_trans_A), int(node.matmul_attr_trans_B)
+        act = getattr(node, 'act', 0)               # epilogue-fused activation (graph/fusion.py)
+        mm_out = c.tmp('mm') if act else out
         if t == 'LinearOp' or tA or tB:
-            c.add('Gemm', ins, [out], transA=tA, transB=tB, alpha=1.0, beta=1.0)
+            c.add('Gemm', ins, [mm_out], transA=tA, transB=tB, alpha=1.0, beta=1.0)
         else:
-            c.add('MatMul', ins, [out])
-        act = getattr(node, 'act', 0)
+            c.add('MatMul', ins, [mm_out])
         if act:
-            raise NotImplementedError('fused activation in LinearOp')
+            c.add({1: 'Relu', 2: 'Gelu', 3: 'Sigmoid'}[act], [mm_out], [out])
     elif t == 'BatchMatMulOp':
         a, b = ins
         if getattr(node, 'trans_A', False) or getattr(node, 'trans_B', False):
