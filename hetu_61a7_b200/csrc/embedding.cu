@@ -77,10 +77,12 @@ HETU_API int hetu_gather_rows_sharded(void* const* bases, int nshard, const void
     return 0;
 }
 
-// Sorted ids -> per-run sums.  Warp i handles position i: a run head (first occurrence in the
-// sorted order) sums its run's rows (through the sort permutation) and keeps its id; every
-// other position gets id -1 and is skipped by the optimizer kernel.  Static shapes, so the
-// step stays CUDA-graph capturable (torch.unique is data-dependent).
+// Sorted ids -> per-run sums.  Warp i handles position i of the sorted order.  The run [lo, hi) of equal
+// ids is found by binary search.  Short runs (<= 16 rows) are summed by the run head alone, in a fixed
+// order; long runs (BERT position / token-type tables: thousands of duplicates of a handful of ids) are
+// accumulated by all their members with atomic adds into the head's zero-initialised row, so no warp
+// ever walks a long run serially.  Non-head positions get id -1 and are skipped by the optimizer
+// kernel.  Static shapes: the step stays CUDA-graph capturable (torch.unique is data-dependent).
 __global__ void __launch_bounds__(256) dedup_sorted_rows_kernel(const long long* __restrict__ sidx,
                                                                 const long long* __restrict__ perm,
                                                                 const float* __restrict__ vals, long long* __restrict__ didx,
@@ -89,25 +91,32 @@ __global__ void __launch_bounds__(256) dedup_sorted_rows_kernel(const long long*
     int lane = threadIdx.x & 31;
     size_t nwarp = ((size_t)gridDim.x * blockDim.x) >> 5;
     for (size_t i = warp; i < n; i += nwarp) {
-        long long id = sidx[i];
-        bool head = (i == 0) || (sidx[i - 1] != id);
-        if (!head) {
-            if (lane == 0) didx[i] = -1;
-            continue;
+        const long long id = sidx[i];
+        size_t lo = 0, hi = i;                                  // first position holding id
+        while (lo < hi) { size_t mid = (lo + hi) >> 1; if (sidx[mid] < id) lo = mid + 1; else hi = mid; }
+        const size_t head = lo;
+        size_t l2 = i + 1, h2 = n;                              // one past the last position holding id
+        while (l2 < h2) { size_t mid = (l2 + h2) >> 1; if (sidx[mid] <= id) l2 = mid + 1; else h2 = mid; }
+        const size_t end = l2;
+        if (lane == 0) didx[i] = (i == head) ? id : -1;
+        if (end - head <= 16) {
+            if (i != head) continue;
+            for (int j = lane; j < width; j += 32) {
+                float acc = 0.f;
+                for (size_t k = head; k < end; ++k) acc += vals[(size_t)perm[k] * width + j];
+                dval[head * width + j] = acc;
+            }
+        } else {
+            const float* src = vals + (size_t)perm[i] * width;
+            float* dst = dval + head * width;
+            for (int j = lane; j < width; j += 32) atomicAdd(dst + j, src[j]);
         }
-        size_t end = i + 1;
-        while (end < n && sidx[end] == id) ++end;
-        for (int j = lane; j < width; j += 32) {
-            float acc = 0.f;
-            for (size_t k = i; k < end; ++k) acc += vals[(size_t)perm[k] * width + j];
-            dval[i * width + j] = acc;
-        }
-        if (lane == 0) didx[i] = id;
     }
 }
 HETU_API int hetu_dedup_sorted_rows(const void* sidx, const void* perm, const float* vals, void* didx, float* dval,
                                     size_t n, int width, cudaStream_t s) {
     if (n == 0) return 0;
+    HETU_CUDA(cudaMemsetAsync(dval, 0, sizeof(float) * n * (size_t)width, s));
     dedup_sorted_rows_kernel<<<ew_grid(n * 32, 256, 16), 256, 0, s>>>((const long long*)sidx, (const long long*)perm, vals,
                                                                       (long long*)didx, dval, n, width);
     HETU_CHECK_LAUNCH("hetu_dedup_sorted_rows");

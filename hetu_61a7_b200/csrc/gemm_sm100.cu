@@ -788,7 +788,11 @@ static int launch_tc_2sm(const float* A, const float* B, GemmParams& p, int batc
     int kb_per_cluster = 0;
     static int use_streamk = -1;
     if (use_streamk < 0) { const char* e = getenv("HETU_GEMM_STREAMK"); use_streamk = (e && e[0] == '1') ? 1 : 0; }   // opt-in: measured slower than whole tiles (atomics + lost L2 lockstep)
-    if (use_streamk && eff < 0.9 && p.beta == 0.f && p.act == ACT_NONE && num_kb >= 128 && (long long)num_tiles * num_kb >= 8LL * maxc) {
+    // few output tiles but a very long K (weight gradients of convolutions / small layers): without
+    // splitting K only num_tiles CTA pairs would work, so stream-K is always used there
+    const bool starved = num_tiles * 4 <= maxc && num_kb >= 256;
+    if ((starved || (use_streamk && eff < 0.9 && num_kb >= 128)) && p.beta == 0.f && p.act == ACT_NONE && p.rs_world <= 1 &&
+        p.ag_world <= 1 && (long long)num_tiles * num_kb >= 8LL * maxc) {
         clusters = maxc;
         const long long total = (long long)num_tiles * num_kb;
         kb_per_cluster = (int)((total + clusters - 1) / clusters);
@@ -1206,7 +1210,14 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
         int rc;
         static int use_2sm = -1;
         if (use_2sm < 0) { const char* e = getenv("HETU_GEMM_2SM"); use_2sm = (e && e[0] == '0') ? 0 : 1; }
-        if (use_2sm && M >= 512 && N >= 256 && (double)M * N * batch * K >= 74.0 * 256 * 256 * 1024)
+        // persistent 2-SM kernel: large problems; tall problems with few output columns (conv forward: the
+        // per-CTA set-up of the one-shot kernel costs more than the MMAs wasted on the empty part of the
+        // 256-wide tile); and few-tile / long-K products, which it runs as stream-K
+        const long long tiles_256 = (long long)((M + 255) / 256) * ((N + 255) / 256) * batch;
+        const bool big2 = M >= 512 && N >= 256 && (double)M * N * batch * K >= 74.0 * 256 * 256 * 1024;
+        const bool tall = M >= 8192 && N >= 64 && K >= 64;
+        const bool starved = tiles_256 * 4 <= 74 && K >= 8192 && M >= 32 && N >= 32 && beta == 0.f && act == ACT_NONE;
+        if (use_2sm && (big2 || tall || starved))
             rc = launch_tc_2sm(A, B, p, batch, sA, sB, s);
         else if (N > 128) rc = launch_tc<256>(A, B, p, batch, sA, sB, s);
         else if (N > 64) rc = launch_tc<128>(A, B, p, batch, sA, sB, s);

@@ -310,10 +310,44 @@ __global__ void __launch_bounds__(256) im2col_kernel(const float* __restrict__ x
         col[i] = (h >= 0 && h < H && w >= 0 && w < W) ? x[(((size_t)n * C + c) * H + h) * W + w] : 0.f;
     }
 }
+// Tiled variant: one CTA per (image, output row).  The kh input rows of every channel that this output
+// row touches are staged in shared memory with coalesced row reads, then the OW x K patch rows are
+// written out coalesced (K fastest).  All index math is 32-bit.
+__global__ void __launch_bounds__(256) im2col_tiled_kernel(const float* __restrict__ x, float* __restrict__ col, int C, int H,
+                                                           int W, int kh, int kw, int ph, int pw, int sh, int sw, int OH,
+                                                           int OW) {
+    extern __shared__ float im2col_smem[];               // [C][kh][W]
+    const int n = blockIdx.x / OH, oh = blockIdx.x - n * OH;
+    const int K = C * kh * kw, rows = C * kh;
+    const float* xn = x + (size_t)n * C * H * W;
+    for (int i = threadIdx.x; i < rows * W; i += 256) {
+        const int r = i / W, w = i - r * W;
+        const int c = r / kh, ky = r - c * kh;
+        const int h = oh * sh - ph + ky;
+        im2col_smem[i] = (h >= 0 && h < H) ? __ldg(xn + ((size_t)c * H + h) * W + w) : 0.f;
+    }
+    __syncthreads();
+    float* out = col + (size_t)blockIdx.x * OW * K;
+    const int khw = kh * kw;
+    for (int i = threadIdx.x; i < OW * K; i += 256) {
+        const int ow = i / K, kk = i - ow * K;
+        const int c = kk / khw, rem = kk - c * khw;
+        const int ky = rem / kw, kx = rem - ky * kw;
+        const int w = ow * sw - pw + kx;
+        out[i] = (w >= 0 && w < W) ? im2col_smem[(c * kh + ky) * W + w] : 0.f;
+    }
+}
+
 HETU_API int hetu_im2col(const float* x, float* col, int N, int C, int H, int W, int kh, int kw, int ph, int pw,
                          int sh, int sw, int OH, int OW, cudaStream_t s) {
     size_t total = (size_t)N * OH * OW * C * kh * kw;
     if (total == 0) return 0;
+    const size_t smem = (size_t)C * kh * W * sizeof(float);
+    if (smem <= 48 * 1024 && (size_t)OW * C * kh * kw < (1u << 30)) {
+        im2col_tiled_kernel<<<N * OH, 256, smem, s>>>(x, col, C, H, W, kh, kw, ph, pw, sh, sw, OH, OW);
+        HETU_CHECK_LAUNCH("hetu_im2col(tiled)");
+        return 0;
+    }
     im2col_kernel<<<ew_grid(total, 256, 16), 256, 0, s>>>(x, col, N, C, H, W, kh, kw, ph, pw, sh, sw, OH, OW);
     HETU_CHECK_LAUNCH("hetu_im2col");
     return 0;

@@ -20,7 +20,9 @@
 namespace {
 constexpr int MC = 96, KC = 256, NC = 512, MR = 6, NR = 16;
 
-inline void micro_kernel(int kc, const float* __restrict a, const float* __restrict b, float* __restrict c,
+// function multi-versioning: the AVX-512 clone is picked at load time when the CPU has it
+__attribute__((target_clones("avx512f", "default"), noinline))
+void micro_kernel(int kc, const float* __restrict a, const float* __restrict b, float* __restrict c,
                          int ldc, int mr, int nr, float alpha, bool accumulate) {
     float acc[MR][NR] = {};
     for (int p = 0; p < kc; ++p) {
@@ -67,12 +69,16 @@ API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, 
                         dst[p * NR + j] = v;
                     }
             }
+            // row-block height: small M (batch-sized activations) is cut finer so every thread gets a block
+            const int nthr = omp_get_max_threads();
+            int mcb = ((M + nthr - 1) / nthr + MR - 1) / MR * MR;
+            mcb = std::max(MR, std::min(MC, mcb));
 #pragma omp parallel
             {
                 std::vector<float> apack((size_t)((MC + MR - 1) / MR) * MR * kc);
 #pragma omp for schedule(dynamic)
-                for (int ic = 0; ic < M; ic += MC) {
-                    int mc = std::min(MC, M - ic);
+                for (int ic = 0; ic < M; ic += mcb) {
+                    int mc = std::min(mcb, M - ic);
                     int mpanels = (mc + MR - 1) / MR;
                     for (int ip = 0; ip < mpanels; ++ip) {
                         float* dst = apack.data() + (size_t)ip * kc * MR;

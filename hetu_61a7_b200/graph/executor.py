@@ -654,9 +654,11 @@ class SubExecutor(object):
                         vals[inp] = None
 
     def _pre_step(self):
-        for node in self.topo_order:
-            if isinstance(node, OptimizerOp):
-                node.optimizer.sync_lr()
+        opts = getattr(self, '_opt_nodes', None)
+        if opts is None:
+            opts = self._opt_nodes = [n for n in self.topo_order if isinstance(n, OptimizerOp)]
+        for node in opts:
+            node.optimizer.sync_lr()
 
     # --------------------------------------------------------------------------- run
     def run(self, eval_node_list=[], feed_dict={}, convert_to_numpy_ret_vals=False, **kwargs):
@@ -705,8 +707,10 @@ class SubExecutor(object):
 
     def _prefetch_batches(self):
         cfg = self.config
-        if self.device.type != 'cuda' or cfg.h2d_stream is None or not getattr(self, '_from_loader', None) \
-                or os.environ.get('HETU_PREFETCH_BATCHES', '1') != '1':
+        if getattr(self, '_pf_off', False) or not getattr(self, '_from_loader', None):
+            return
+        if self.device.type != 'cuda' or cfg.h2d_stream is None or os.environ.get('HETU_PREFETCH_BATCHES', '1') != '1':
+            self._pf_off = True
             return
         if not hasattr(self, '_pf'):
             self._pf, self._pf_bufs, self._pf_turn, self._pf_ptrs = {}, {}, {}, set()
@@ -719,7 +723,12 @@ class SubExecutor(object):
             if not isinstance(nxt, torch.Tensor) or nxt.device.type != 'cpu' or not nxt.is_pinned():
                 continue
             if nxt.numel() * nxt.element_size() < (1 << 20):
-                continue        # tiny batches: the event/stream bookkeeping costs more than the copy it hides
+                # tiny batches: the event/stream bookkeeping costs more than the copy it hides
+                self._pf_small = getattr(self, '_pf_small', set())
+                self._pf_small.add(node)
+                if all(n in self._pf_small for n in self.dataloader_nodes):
+                    self._pf_off = True
+                continue
             turn = self._pf_turn.get(node, 0)
             self._pf_turn[node] = turn ^ 1
             bufs = self._pf_bufs.setdefault(node, [None, None])

@@ -49,6 +49,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, trans_a=False, trans_b=False, bias=No
         return _gemm_torch(a, b, trans_a, trans_b, bias, c_in, alpha, beta, act)
     a = a if a.is_contiguous() else a.contiguous()
     b = b if b.is_contiguous() else b.contiguous()
+    if a.dim() == 2 and b.dim() == 2 and _PRECISION['mode'] != 'fp32':
+        padded = _pad_for_tma(a, b, trans_a, trans_b, bias, c_in, alpha, beta, act)
+        if padded is not None:
+            return padded
     batched = a.dim() == 3
     if batched:
         batch = a.shape[0]
@@ -84,6 +88,45 @@ def _cpu_native(*ts) -> bool:
     from .. import cpu_links
     return (os.environ.get('HETU_CPU_NATIVE', '1') == '1' and cpu_links.available()
             and all(t.device.type == 'cpu' and t.dtype == torch.float32 for t in ts))
+
+
+def _pad4(t, dim):
+    n = t.shape[dim]
+    if n % 4 == 0:
+        return t
+    shp = list(t.shape)
+    shp[dim] = (n + 3) // 4 * 4
+    out = torch.zeros(shp, dtype=t.dtype, device=t.device)
+    out.narrow(dim, 0, n).copy_(t)
+    return out
+
+
+def _pad_for_tma(a, b, trans_a, trans_b, bias, c_in, alpha, beta, act):
+    """TMA needs 16-byte row pitches.  Large products whose contiguous dimension is not a multiple of
+    four floats (first conv layer: K = 27; BERT vocabulary 30522) would otherwise fall to the CUDA-core
+    kernel at a few percent of tensor-core speed: zero-pad the odd dimension instead (a copy of one
+    operand) and slice the result."""
+    m, k = (a.shape[1], a.shape[0]) if trans_a else (a.shape[0], a.shape[1])
+    n = b.shape[0] if trans_b else b.shape[1]
+    a_inner, b_inner = (m if trans_a else k), (k if trans_b else n)
+    if a_inner % 4 == 0 and b_inner % 4 == 0:
+        return None                                  # already eligible
+    if float(m) * n * k < float(1 << 27) or m < 64 or k < 8 or n <= 8:
+        return None                                  # small / skinny: dedicated CUDA-core kernels
+    a2 = _pad4(_pad4(a, 0), 1)
+    b2 = _pad4(_pad4(b, 0), 1)
+    n2 = b2.shape[0] if trans_b else b2.shape[1]
+    m2 = a2.shape[1] if trans_a else a2.shape[0]
+    bias2 = None
+    if bias is not None:
+        bias2 = _pad4(bias.reshape(-1), 0)
+    c2 = None
+    if c_in is not None and beta != 0.0:
+        c2 = _pad4(_pad4(c_in.expand(m, n).contiguous(), 0), 1)
+    out = gemm(a2, b2, trans_a, trans_b, bias=bias2, c_in=c2, alpha=alpha, beta=beta, act=act)
+    if m2 != m or n2 != n:
+        out = out[:m, :n].contiguous()
+    return out
 
 
 def _gemm_torch(a, b, trans_a, trans_b, bias, c_in, alpha, beta, act):
