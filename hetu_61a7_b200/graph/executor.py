@@ -529,7 +529,10 @@ class SubExecutor(object):
         if any(hasattr(n, 'global_order') for n in self.topo_order):
             # placed graph: every rank walks its nodes in the order of the ONE global topological
             # sort, so collectives and blocking receives pair up identically on all ranks
-            self.topo_order.sort(key=lambda n: getattr(n, 'global_order', float('inf')))
+            for n in self.topo_order:          # nodes added after placement (gradient all-reduces): right after their inputs
+                if not hasattr(n, 'global_order'):
+                    n.global_order = max([getattr(i, 'global_order', 0.0) for i in n.inputs if i is not None] or [0.0]) + 0.01
+            self.topo_order.sort(key=lambda n: n.global_order)
         self.dataloader_nodes = [n for n in self.topo_order
                                  if isinstance(n, (DataloaderOp, GNNDataLoaderOp))]
         self.param_nodes = [n for n in self.topo_order

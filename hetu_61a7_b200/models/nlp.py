@@ -24,7 +24,8 @@ class BertConfig(object):
     def __init__(self, vocab_size=30522, hidden_size=768, num_hidden_layers=12, num_attention_heads=12,
                  intermediate_size=3072, hidden_act='gelu', hidden_dropout_prob=0.1,
                  attention_probs_dropout_prob=0.1, max_position_embeddings=512, type_vocab_size=2,
-                 initializer_range=0.02, batch_size=32, seq_len=128, fused_attention=True):
+                 initializer_range=0.02, batch_size=32, seq_len=128, fused_attention=True, tp=1,
+                 tie_word_embeddings=True):
         self.vocab_size, self.hidden_size = vocab_size, hidden_size
         self.num_hidden_layers, self.num_attention_heads = num_hidden_layers, num_attention_heads
         self.intermediate_size, self.hidden_act = intermediate_size, hidden_act
@@ -34,6 +35,12 @@ class BertConfig(object):
         self.initializer_range = initializer_range
         self.batch_size, self.seq_len = batch_size, seq_len
         self.fused_attention = fused_attention
+        #: tensor-parallel degree of the feed-forward block (build the model inside a tuple context;
+        #: w1 is column-parallel, w2 row-parallel, Megatron style) - see parallel/mp_lowering.py
+        self.tp = tp
+        #: the MLM decoder shares the word-embedding matrix (reference hetu_bert.py); pipeline-parallel
+        #: layouts untie it so the table does not travel between the first and the last stage
+        self.tie_word_embeddings = tie_word_embeddings
 
     @classmethod
     def base(cls, **kw):
@@ -99,8 +106,18 @@ class BertModel(object):
     """Embeddings + encoder stack + pooler.  ``__call__(input_ids, token_type_ids, attention_mask)``
     returns (sequence_output [B*S, H], pooled_output [B, H])."""
 
-    def __init__(self, config: BertConfig, name='bert'):
+    def __init__(self, config: BertConfig, name='bert', stage_contexts=None):
+        """``stage_contexts``: list of contexts (anything ``ht.context`` accepts), one per pipeline stage;
+        the encoder layers are split evenly, embeddings go to the first and the pooler to the last."""
         self.cfg, self.name = config, name
+        self.stage_contexts = list(stage_contexts) if stage_contexts else None
+
+    def _stage(self, i):
+        import contextlib
+        if not self.stage_contexts:
+            return contextlib.nullcontext()
+        S, L = len(self.stage_contexts), self.cfg.num_hidden_layers
+        return ht.context(self.stage_contexts[min(S - 1, i * S // max(L, 1))] if i >= 0 else self.stage_contexts[0])
 
     def embeddings(self, input_ids, token_type_ids):
         c = self.cfg
@@ -125,9 +142,26 @@ class BertModel(object):
                       c.seq_len, c.seq_len, fused=c.fused_attention, attn_dropout=c.attention_probs_dropout_prob
                       if not c.fused_attention else 0.0)
         x = _layer_norm(x + _dropout(a, c.hidden_dropout_prob), c.hidden_size, n + '_attn_ln')
-        h = _dense(x, c.hidden_size, c.intermediate_size, n + '_intermediate', std, act=c.hidden_act)
-        h = _dense(h, c.intermediate_size, c.hidden_size, n + '_ffn_output', std)
+        if c.tp > 1:
+            h = self._ffn_tp(x, n, std)
+        else:
+            h = _dense(x, c.hidden_size, c.intermediate_size, n + '_intermediate', std, act=c.hidden_act)
+            h = _dense(h, c.intermediate_size, c.hidden_size, n + '_ffn_output', std)
         return _layer_norm(x + _dropout(h, c.hidden_dropout_prob), c.hidden_size, n + '_ffn_ln')
+
+    def _ffn_tp(self, x, n, std):
+        """Column-parallel w1 / row-parallel w2: one all-reduce of the block output per direction."""
+        c = self.cfg
+        t = c.tp
+        w1 = init.truncated_normal((c.hidden_size, c.intermediate_size), stddev=std, name=n + '_intermediate_weight')
+        b1 = init.zeros((c.intermediate_size,), name=n + '_intermediate_bias')
+        w2 = init.truncated_normal((c.intermediate_size, c.hidden_size), stddev=std, name=n + '_ffn_output_weight')
+        b2 = init.zeros((c.hidden_size,), name=n + '_ffn_output_bias')
+        h = ht.matmul_op(x, ht.dispatch(w1, (1, t)))
+        h = h + ht.broadcastto_op(ht.dispatch(b1, (t,)), h)
+        h = ht.gelu_op(h) if c.hidden_act == 'gelu' else ht.relu_op(h)
+        out = ht.dispatch(ht.matmul_op(h, ht.dispatch(w2, (t, 1))), (1, 1))        # partial sums -> all-reduce
+        return out + ht.broadcastto_op(b2, out)
 
     def __call__(self, input_ids, token_type_ids, attention_mask=None):
         c = self.cfg
@@ -135,31 +169,47 @@ class BertModel(object):
         if attention_mask is not None:                       # 1 = attend, 0 = pad  ->  additive -10000
             m = ht.array_reshape_op(attention_mask, [c.batch_size, 1, 1, c.seq_len])
             mask = ht.mul_byconst_op(ht.addbyconst_op(m, -1.0), 10000.0)
-        x = self.embeddings(input_ids, token_type_ids)
+        with self._stage(-1):
+            x = self.embeddings(input_ids, token_type_ids)
         for i in range(c.num_hidden_layers):
-            x = self.layer(x, mask, i)
+            with self._stage(i):
+                x = self.layer(x, mask, i)
+        if self.stage_contexts:
+            with ht.context(self.stage_contexts[-1]):
+                return x, self._pool(x)
+        return x, self._pool(x)
+
+    def _pool(self, x):
+        c = self.cfg
         first = ht.slice_op(ht.array_reshape_op(x, [c.batch_size, c.seq_len, c.hidden_size]), (0, 0, 0),
                             (-1, 1, -1))
         first = ht.array_reshape_op(first, [c.batch_size, c.hidden_size])
-        pooled = _dense(first, c.hidden_size, c.hidden_size, self.name + '_pooler', c.initializer_range, act='tanh')
-        return x, pooled
+        return _dense(first, c.hidden_size, c.hidden_size, self.name + '_pooler', c.initializer_range, act='tanh')
 
 
 class BertForPreTraining(object):
     """MLM (decoder tied to the word embeddings) + NSP heads.  Returns (mlm_logits, nsp_logits,
     mlm_loss, nsp_loss); total loss = mlm_loss + nsp_loss (reference hetu_bert.py:618-660)."""
 
-    def __init__(self, config: BertConfig):
+    def __init__(self, config: BertConfig, stage_contexts=None):
         self.cfg = config
-        self.bert = BertModel(config)
+        self.bert = BertModel(config, stage_contexts=stage_contexts)
 
     def __call__(self, input_ids, token_type_ids, attention_mask, masked_lm_labels=None, next_sentence_label=None):
+        import contextlib
+        sc = self.bert.stage_contexts
+        with (ht.context(sc[-1]) if sc else contextlib.nullcontext()):
+            return self._build(input_ids, token_type_ids, attention_mask, masked_lm_labels, next_sentence_label)
+
+    def _build(self, input_ids, token_type_ids, attention_mask, masked_lm_labels, next_sentence_label):
         c = self.cfg
         seq, pooled = self.bert(input_ids, token_type_ids, attention_mask)
         h = _dense(seq, c.hidden_size, c.hidden_size, 'cls_transform', c.initializer_range, act=c.hidden_act)
         h = _layer_norm(h, c.hidden_size, 'cls_transform_ln')
         bias = init.zeros((c.vocab_size,), name='cls_decoder_bias')
-        mlm_logits = ht.linear_op(h, self.bert.word_embeddings, bias, trans_B=True)      # [B*S, vocab]
+        decoder = self.bert.word_embeddings if c.tie_word_embeddings else \
+            init.truncated_normal((c.vocab_size, c.hidden_size), stddev=c.initializer_range, name='cls_decoder_weight')
+        mlm_logits = ht.linear_op(h, decoder, bias, trans_B=True)                        # [B*S, vocab]
         nsp_logits = _dense(pooled, c.hidden_size, 2, 'cls_seq_relationship', c.initializer_range)
         out = [mlm_logits, nsp_logits]
         if masked_lm_labels is not None and next_sentence_label is not None:

@@ -41,10 +41,16 @@ def _group_of(op) -> Optional[tuple]:
 
 
 class _MPComm(object):
-    """Lazily resolved communicator of one MP worker (group of device ids on this node)."""
+    """Lazily resolved communicator of the model-parallel worker THIS rank belongs to.  A context with
+    several tuple workers (data-parallel replicas of a tensor-parallel group) yields one process group
+    per tuple; every rank creates all of them (group creation is collective) and keeps its own."""
 
-    def __init__(self, devices):
-        self.devices = tuple(devices)
+    def __init__(self, workers):
+        workers = list(workers)
+        if workers and not isinstance(workers[0], tuple):
+            workers = [tuple(workers)]                     # a single tuple was passed
+        self.workers = [tuple(w) for w in workers]
+        self.devices = self.workers[0]
         self._comm = None
 
     def resolve(self):
@@ -54,8 +60,13 @@ class _MPComm(object):
             if not w.multi:
                 self._comm = w
             else:
-                ranks = sorted(d.device_id for d in self.devices)
-                self._comm = new_group_comm(ranks)
+                mine = None
+                for tup in self.workers:
+                    ranks = sorted(d.device_id for d in tup)
+                    comm = new_group_comm(ranks)
+                    if w.world_rank in ranks:
+                        mine = comm
+                self._comm = mine if mine is not None else new_group_comm(sorted(d.device_id for d in self.workers[0]))
         return self._comm
 
     @property
@@ -311,10 +322,10 @@ def reduce_scatter_of(node, d, n, group, ctx=None):
 _GROUPS = {}
 
 
-def _group(devices) -> _MPComm:
-    key = tuple(devices)
+def _group(workers) -> _MPComm:
+    key = tuple(tuple(w) if isinstance(w, tuple) else w for w in workers)
     if key not in _GROUPS:
-        _GROUPS[key] = _MPComm(devices)
+        _GROUPS[key] = _MPComm(workers)
     return _GROUPS[key]
 
 
@@ -331,7 +342,7 @@ def lower_dispatch(node, parts, ctx_group):
     """Implementation of ``ht.dispatch`` inside an MP context."""
     devices = None
     if ctx_group is not None and ctx_group.is_mp:
-        devices = next(w for w in ctx_group.workers if isinstance(w, tuple))
+        devices = [w for w in ctx_group.workers if isinstance(w, tuple)]
     src_group = getattr(node, 'mp_group', None)
     if devices is None and src_group is None:
         return None                                       # not model parallel: marker only
@@ -404,6 +415,21 @@ def adapt(op) -> None:
             and (states[0][0] == 'split' or name in ('AddOp', 'MinusOp')):
         op.mp_state = states[0]
         return
+    if name == 'BroadcastToOp' and len(ins) == 2:
+        a, like = states
+        if like is not None and like[0] == 'split' and (
+                (a is None and like[1] == 0) or (a is not None and a[0] == 'split' and a[2] == like[2] and like[1] != 0)):
+            op.mp_state = like                 # bias shard broadcast over a column shard / replicated bias over row shards
+            return
+    if name == 'ReduceToShapeOp' and len(ins) == 2:
+        g, like = states
+        if g is not None and g[0] == 'split':
+            if like is not None and like[0] == 'split' and g[1] != 0 and g[2] == like[2]:
+                op.mp_state = like             # column-sharded gradient summed over rows -> shard of the bias gradient
+                return
+            if like is None and g[1] == 0:
+                op.mp_state = ('partial', g[2])    # rows are sharded: every member holds a partial sum
+                return
     from ..ops.elementwise import BinaryOp
     if isinstance(op, BinaryOp) and len(ins) == 2 and states[0] == states[1] and states[0][0] == 'split' \
             and name not in ('BoolMatrixOp',):

@@ -71,6 +71,16 @@ class _PipeBase(SubExecutor):
                 if n not in grad_side and any(i in grad_side for i in n.inputs if i is not None):
                     grad_side.add(n)
                     changed = True
+        if any(hasattr(n, 'pp_forward') for n in self.topo_order):
+            # the placement pass classified every node on the global graph: use that (ranks must agree on
+            # which pass a collective belongs to); nodes created later follow their inputs
+            grad_side = set()
+            for n in self.topo_order:
+                flag = getattr(n, 'pp_forward', None)
+                if flag is None:
+                    flag = not (isinstance(n, OptimizerOp) or any(i in grad_side for i in n.inputs if i is not None))
+                if not flag:
+                    grad_side.add(n)
         self.forward_nodes = [n for n in self.topo_order if n not in grad_side]
         self.backward_nodes = [n for n in self.topo_order if n in grad_side and not isinstance(n, OptimizerOp)]
         for n in self.topo_order:

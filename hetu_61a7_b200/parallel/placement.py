@@ -66,8 +66,22 @@ def assign_placement(config, eval_nodes) -> None:
     pure_dp = len(stages) <= 1 and not any(s.is_mp for s in stages)
     if pure_dp:
         return
-    from .comm import make_p2p_comms
+    from .comm import make_p2p_comms, new_group_comm
     make_p2p_comms()
+    # process groups are created collectively: EVERY rank walks all stages in the same order and creates
+    # each tensor-parallel group (one per tuple worker) and each data-parallel replica group (same member
+    # index across the workers of a stage), also the ones it is not a member of
+    for s in stages:
+        pos = _positions(s)
+        for w in s.workers:
+            if isinstance(w, tuple) and len(w) > 1:
+                new_group_comm(sorted(d.device_id for d in w))
+        width = max(len(w) if isinstance(w, tuple) else 1 for w in s.workers)
+        if s.worker_num > 1:
+            for k in range(width):
+                ranks = sorted(r for _, kk, r in pos if kk == k)
+                if len(ranks) > 1:
+                    new_group_comm(ranks)
     me = config.rank
     mine = lambda n: isinstance(n, OptimizerOp) or n.raw_ctx is None or me in _ranks(n.raw_ctx)   # noqa: E731
     my_stage_ids = [i for i, s in enumerate(stages) if me in _ranks(s)]
@@ -103,6 +117,11 @@ def assign_placement(config, eval_nodes) -> None:
 
     for i, n in enumerate(topo):
         n.global_order = float(i)
+    # forward / backward side of every node, decided ONCE on the global graph so that all ranks agree
+    # (the pipeline executors run the two sides in separate passes)
+    fwd_set = set(find_topo_sort([n for n in eval_nodes if not isinstance(n, OptimizerOp)]))
+    for n in topo:
+        n.pp_forward = n in fwd_set
     recv_cache: Dict = {}
     sends: List = []
     sent = set()
@@ -127,6 +146,7 @@ def assign_placement(config, eval_nodes) -> None:
                     rv.ctx = config.context
                     rv.name = 'recv_%s_from%d' % (u.name, src)
                     rv.global_order = v.global_order - 0.5
+                    rv.pp_forward = getattr(v, 'pp_forward', True)
                     recv_cache[u] = rv
                 v.inputs[idx] = recv_cache[u]
             # producer side
@@ -137,6 +157,7 @@ def assign_placement(config, eval_nodes) -> None:
                         sd = pipeline_send_op(u, r, config.nccl_comm, ctx=u.raw_ctx)
                         sd.name = 'send_%s_to%d' % (u.name, r)
                         sd.global_order = v.global_order - 0.25
+                        sd.pp_forward = getattr(v, 'pp_forward', True)
                         sends.append((topo.index(v), sd))
     # this rank evaluates: its own eval nodes + its sends, interleaved in topological position so
     # that both sides of every p2p pair issue them in the same relative order

@@ -60,3 +60,33 @@ def test_pipeline_and_model_parallel_equivalence_nccl(case):
     if torch.cuda.device_count() < 2:
         pytest.skip('needs >= 2 GPUs (gpurun --gpus 2)')
     _launch_pp('gpu', case)
+
+
+def _launch_hybrid(mode, pp, tp, dp, pipeline=None, timeout=900):
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(pp * tp * dp),
+           '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
+           os.path.join(ROOT, 'tests', 'bert_hybrid_worker.py'), mode, str(pp), str(tp), str(dp)]
+    if pipeline:
+        cmd.append(pipeline)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize('pp,tp,dp,pipeline', [(1, 2, 1, None), (2, 2, 1, 'gpipe'), (2, 2, 2, None)])
+def test_bert_hybrid_parallel_gloo(pp, tp, dp, pipeline):
+    """BERT with pipeline stages x tensor-parallel FFN x data-parallel replicas == single process
+    (BASELINE config 5 layout at toy size)."""
+    _launch_hybrid('cpu', pp, tp, dp, pipeline)
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(900)
+def test_bert_hybrid_parallel_nccl():
+    n = torch.cuda.device_count()
+    if n < 4:
+        pytest.skip('needs >= 4 GPUs')
+    if n >= 8:
+        _launch_hybrid('gpu', 2, 2, 2, 'gpipe')
+    else:
+        _launch_hybrid('gpu', 2, 2, 1, 'gpipe')
