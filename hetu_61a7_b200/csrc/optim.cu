@@ -12,20 +12,30 @@
 enum { OPT_SGD = 0, OPT_MOMENTUM, OPT_NESTEROV, OPT_ADAGRAD, OPT_ADAM, OPT_ADAMW, OPT_LAMB };
 constexpr int kMaxTensors = 48;
 
+constexpr int kOptChunk = 256 * 4 * 8;       // elements per CTA of the flattened element-wise update (8 float4 per thread)
+
 struct TensorList {
     float* p[kMaxTensors];
     const float* g[kMaxTensors];
     float* s1[kMaxTensors];
     float* s2[kMaxTensors];
     long long n[kMaxTensors];
+    int chunk_begin[kMaxTensors + 1];        // flattened schedule: CTA b works on tensor t with chunk_begin[t] <= b < chunk_begin[t+1]
 };
 
 template <int KIND>
 __global__ void __launch_bounds__(256) multi_tensor_opt_kernel(TensorList tl, const float* __restrict__ lr_p,
                                                                const long long* __restrict__ step_p, float h0, float h1,
                                                                float h2, float h3, float l2reg, float grad_scale) {
-    int t = blockIdx.y;
-    long long n = tl.n[t];
+    // flattened schedule: every CTA owns one kOptChunk-element chunk of one tensor, so a 31M-element
+    // embedding table and a 1024-element bias are both covered at full occupancy
+    int t = 0;
+    {
+        int lo = 0, hi = kMaxTensors;
+        while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (tl.chunk_begin[mid] <= (int)blockIdx.x) lo = mid; else hi = mid - 1; }
+        t = lo;
+    }
+    const long long n = tl.n[t];
     float* __restrict__ p = tl.p[t];
     const float* __restrict__ g = tl.g[t];
     float* __restrict__ s1 = tl.s1[t];
@@ -37,7 +47,9 @@ __global__ void __launch_bounds__(256) multi_tensor_opt_kernel(TensorList tl, co
         b1t = 1.f - powf(h0, st);
         b2t = 1.f - powf(h1, st);
     }
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long c0 = (long long)((int)blockIdx.x - tl.chunk_begin[t]) * kOptChunk;
+    const long long c1 = c0 + kOptChunk < n ? c0 + kOptChunk : n;
+    for (long long i = c0 + threadIdx.x; i < c1; i += blockDim.x) {
         float pv = p[i];
         float gv = g[i] * grad_scale + l2reg * pv;
         if (KIND == OPT_SGD) {
@@ -132,7 +144,15 @@ HETU_API int hetu_multi_tensor_opt(int kind, int ntensors, void* const* params, 
     int cap = (kNumSMs * 8 + ntensors - 1) / ntensors;
     if (gx > cap) gx = cap;
     if (gx < 1) gx = 1;
-    dim3 grid(gx, ntensors);
+    dim3 grid(gx, ntensors);                     // Lamb: (x-chunks, tensor) grid with grid-stride loops
+    int nchunks = 0;
+    for (int i = 0; i <= kMaxTensors; ++i) {
+        tl.chunk_begin[i] = nchunks;
+        if (i < ntensors) nchunks += (int)((sizes[i] + kOptChunk - 1) / kOptChunk);
+    }
+    for (int i = ntensors + 1; i <= kMaxTensors; ++i) tl.chunk_begin[i] = 0x7fffffff;   // never selected by the search
+    if (kind != OPT_LAMB) grid = dim3(nchunks > 0 ? nchunks : 1, 1);
+    if (kind != OPT_LAMB && nchunks == 0) return 0;
     const long long* st = (const long long*)step_p;
     switch (kind) {
         case OPT_SGD: multi_tensor_opt_kernel<OPT_SGD><<<grid, 256, 0, s>>>(tl, lr_p, st, h0, h1, h2, h3, l2reg, 1.f); break;

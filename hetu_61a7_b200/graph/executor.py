@@ -99,7 +99,7 @@ class HetuConfig(object):
         'dist_strategy', 'pipeline', 'use_preduce', 'overlap', 'use_nccl_collectives', 'symm',
         'fuse_dp_update', 'use_cuda_graph', 'dp_rank', 'dp_nrank', 'mp_index', 'shard_dataloaders',
         'all_forward_nodes', 'lcm_dp_nrank', 'pp_rank', 'pp_nrank', 'stage_ranks', 'memory_pool',
-        'timing', 'dropped_eval_nodes',
+        'timing', 'dropped_eval_nodes', '_running_name',
     ]
 
     def __init__(self, eval_node_list, train_name, val_name, ctx=None, seed=None, comm_mode=None,
@@ -669,6 +669,7 @@ class SubExecutor(object):
         feeds: Dict[Op, object] = {}
         for node, value in feed_dict.items():
             feeds[node] = self._feed_tensor(node, value)
+        self.config._running_name = self.name
         self._from_loader = [n for n in self.dataloader_nodes if n not in feeds]
         for node in self._from_loader:
             feeds[node] = self._next_batch(node)

@@ -47,6 +47,7 @@ class EmbeddingLookUp(Op):
             # PS / Hybrid: rows come from the parameter server (through the HET cache when one
             # is configured) every step -> host round trip, so this graph runs eagerly
             self._ps_comm = config.ps_comm
+            self._config = config
             self.graph_safe = False
 
     def _ps_lookup(self, idx):
@@ -58,10 +59,45 @@ class EmbeddingLookUp(Op):
         if cache is not None:
             rows = cache.embedding_lookup(ids, sync=True)
         else:
-            rows = self._ps_comm.SparsePull(emb.id, ids, width)
+            rows = self._take_prefetched(emb, ids, width)
+            if rows is None:
+                rows = self._ps_comm.SparsePull(emb.id, ids, width)
+            self._prefetch_next(emb, width)
         t = torch.from_numpy(np.asarray(rows).reshape(tuple(idx.shape) + (width,)))
         dev = self.ctx.torch_device if self.ctx is not None else idx.device
         return t.to(dev, non_blocking=True)
+
+    # ---- PS prefetch (reference executor.py prefetch=True + dataloader.get_next_arr): while this step
+    # computes, the rows of the NEXT batch are pulled on the worker's I/O thread.  ASP/SSP only - under
+    # BSP the pull has to see this step's update.
+    def _take_prefetched(self, emb, ids, width):
+        import numpy as np
+        pf = getattr(self, '_pf', None)
+        self._pf = None
+        if pf is None:
+            return None
+        next_ids, buf = pf
+        self._ps_comm.Wait(emb.id)
+        if next_ids.shape == ids.shape and np.array_equal(next_ids, ids):
+            self.prefetch_hits = getattr(self, 'prefetch_hits', 0) + 1
+            return buf
+        return None
+
+    def _prefetch_next(self, emb, width):
+        import numpy as np
+        cfg = getattr(self, '_config', None)
+        src = self.inputs[1]
+        if cfg is None or not getattr(cfg, 'prefetch', False) or getattr(cfg, 'bsp', -1) == 0 \
+                or not hasattr(src, 'get_next_arr'):
+            return
+        name = getattr(cfg, '_running_name', None) or next(iter(src.dataloaders))
+        if name not in src.dataloaders:
+            return
+        nxt = src.get_next_arr(name)
+        next_ids = np.asarray(nxt).astype(np.int64).reshape(-1)
+        buf = np.zeros((next_ids.size, width), dtype=np.float32)
+        self._ps_comm.SparsePullAsync(emb.id, next_ids, buf)
+        self._pf = (next_ids, buf)
 
     def compute(self, input_vals, output_val=None, stream_handle=None):
         table, idx = input_vals

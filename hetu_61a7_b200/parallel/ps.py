@@ -167,6 +167,14 @@ class PSWorker(object):
         self._keep.setdefault(int(node_id), []).append(out)
         _chk(self.lib.hps_pull_async(ctypes.c_uint64(node_id), out.ctypes.data_as(_F32P)), 'PullAsync')
 
+    def SparsePullAsync(self, node_id, rows, out: np.ndarray):
+        """Queue a row pull on the worker's I/O thread for ``node_id`` (ordered with the other async
+        requests of that key); ``out`` is filled once ``Wait(node_id)`` returns."""
+        r, rp = _i64(np.asarray(rows).reshape(-1))
+        self._keep.setdefault(int(node_id), []).extend([r, out])
+        _chk(self.lib.hps_sparse_pull_async(ctypes.c_uint64(node_id), rp, ctypes.c_uint64(r.size),
+                                            out.ctypes.data_as(_F32P)), 'SparsePullAsync')
+
     def Wait(self, node_id):
         _chk(self.lib.hps_wait(ctypes.c_uint64(node_id)), 'Wait')
         self._keep.pop(int(node_id), None)
