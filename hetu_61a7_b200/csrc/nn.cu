@@ -222,10 +222,121 @@ __global__ void __launch_bounds__(512) batchnorm_fwd_kernel(const float* __restr
         y[o] = (x[o] - mean) * rstd * g + b;
     }
 }
+// Cluster variant (training): a thread-block cluster of 8 CTAs owns one channel.  CTA r reduces images
+// n = r, r+8, ... (contiguous HW runs: coalesced, no integer division per element), publishes its partial
+// (sum, sum of squares) in shared memory, and after one cluster barrier every CTA reads the 8 partials
+// through distributed shared memory and normalises the images it has just touched (still in L1/L2).
+// One launch, C*8 CTAs instead of C, no workspace, no atomics.
+constexpr int kBnCluster = 8;
+
+__device__ __forceinline__ float2 block_sum2(float a, float b, float* sm /*64*/) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+    if (lane == 0) { sm[warp] = a; sm[32 + warp] = b; }
+    __syncthreads();
+    const int nw = blockDim.x >> 5;
+    a = lane < nw ? sm[lane] : 0.f;
+    b = lane < nw ? sm[32 + lane] : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+    __syncthreads();
+    return make_float2(a, b);
+}
+
+__device__ __forceinline__ float2 cluster_sum2(float2 mine, float2* slot /*shared*/) {
+    if (threadIdx.x == 0) *slot = mine;
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    float2 tot = make_float2(0.f, 0.f);
+    const uint32_t local = (uint32_t)__cvta_generic_to_shared(slot);
+#pragma unroll
+    for (int r = 0; r < kBnCluster; ++r) {
+        uint32_t remote;
+        float a, b;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(r));
+        asm volatile("ld.shared::cluster.v2.f32 {%0, %1}, [%2];" : "=f"(a), "=f"(b) : "r"(remote) : "memory");
+        tot.x += a; tot.y += b;
+    }
+    // nobody may leave (and free its shared memory) while peers still read it
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    return tot;
+}
+
+__global__ void __cluster_dims__(kBnCluster, 1, 1) __launch_bounds__(512)
+batchnorm_fwd_cluster_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                             float* __restrict__ y, float* __restrict__ run_mean, float* __restrict__ run_var,
+                             float* __restrict__ save_mean, float* __restrict__ save_rstd, int N, int C, int HW,
+                             float momentum, float eps) {
+    __shared__ float sm[64];
+    __shared__ float2 slot;
+    const int c = blockIdx.x / kBnCluster, r = blockIdx.x % kBnCluster;
+    float s = 0.f, ss = 0.f;
+    for (int n = r; n < N; n += kBnCluster) {
+        const float* xp = x + ((size_t)n * C + c) * HW;
+        for (int i = threadIdx.x; i < HW; i += blockDim.x) { const float v = xp[i]; s += v; ss += v * v; }
+    }
+    const float2 tot = cluster_sum2(block_sum2(s, ss, sm), &slot);
+    const float cnt = (float)N * HW;
+    const float mean = tot.x / cnt;
+    const float var = fmaxf(tot.y / cnt - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + eps);
+    if (r == 0 && threadIdx.x == 0) {
+        save_mean[c] = mean;
+        save_rstd[c] = rstd;
+        const float unbiased = cnt > 1.f ? var * cnt / (cnt - 1.f) : var;
+        run_mean[c] = (1.f - momentum) * run_mean[c] + momentum * mean;
+        run_var[c] = (1.f - momentum) * run_var[c] + momentum * unbiased;
+    }
+    const float g = gamma[c] * rstd, b = beta[c] - mean * rstd * gamma[c];
+    for (int n = r; n < N; n += kBnCluster) {
+        const size_t o = ((size_t)n * C + c) * HW;
+        for (int i = threadIdx.x; i < HW; i += blockDim.x) y[o + i] = x[o + i] * g + b;
+    }
+}
+
+__global__ void __cluster_dims__(kBnCluster, 1, 1) __launch_bounds__(512)
+batchnorm_bwd_cluster_kernel(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ gamma,
+                             const float* __restrict__ save_mean, const float* __restrict__ save_rstd, float* __restrict__ dx,
+                             float* __restrict__ dgamma, float* __restrict__ dbeta, int N, int C, int HW) {
+    __shared__ float sm[64];
+    __shared__ float2 slot;
+    const int c = blockIdx.x / kBnCluster, r = blockIdx.x % kBnCluster;
+    const float mean = save_mean[c], rstd = save_rstd[c];
+    float sb = 0.f, sg = 0.f;
+    for (int n = r; n < N; n += kBnCluster) {
+        const size_t o = ((size_t)n * C + c) * HW;
+        for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+            const float d = dy[o + i];
+            sb += d;
+            sg += d * (x[o + i] - mean) * rstd;
+        }
+    }
+    const float2 tot = cluster_sum2(block_sum2(sb, sg, sm), &slot);
+    if (r == 0 && threadIdx.x == 0) { dbeta[c] = tot.x; dgamma[c] = tot.y; }
+    const float cnt = (float)N * HW;
+    const float k = gamma[c] * rstd / cnt;
+    for (int n = r; n < N; n += kBnCluster) {
+        const size_t o = ((size_t)n * C + c) * HW;
+        for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+            const float h = (x[o + i] - mean) * rstd;
+            dx[o + i] = k * (cnt * dy[o + i] - tot.x - h * tot.y);
+        }
+    }
+}
+
 HETU_API int hetu_batchnorm_fwd(const float* x, const float* gamma, const float* beta, float* y, float* run_mean,
                                 float* run_var, float* save_mean, float* save_rstd, int N, int C, int HW,
                                 float momentum, float eps, int inference, cudaStream_t s) {
     if (C == 0) return 0;
+    if (!inference && N >= kBnCluster) {
+        const int threads = HW >= 512 ? 512 : (HW >= 128 ? 256 : 128);
+        batchnorm_fwd_cluster_kernel<<<C * kBnCluster, threads, 0, s>>>(x, gamma, beta, y, run_mean, run_var, save_mean,
+                                                                       save_rstd, N, C, HW, momentum, eps);
+        HETU_CHECK_LAUNCH("hetu_batchnorm_fwd(cluster)");
+        return 0;
+    }
     batchnorm_fwd_kernel<<<C, 512, 0, s>>>(x, gamma, beta, y, run_mean, run_var, save_mean, save_rstd, N, C, HW,
                                            momentum, eps, inference);
     HETU_CHECK_LAUNCH("hetu_batchnorm_fwd");
@@ -263,6 +374,13 @@ HETU_API int hetu_batchnorm_bwd(const float* dy, const float* x, const float* ga
                                 const float* save_rstd, float* dx, float* dgamma, float* dbeta, int N, int C, int HW,
                                 cudaStream_t s) {
     if (C == 0) return 0;
+    if (N >= kBnCluster) {
+        const int threads = HW >= 512 ? 512 : (HW >= 128 ? 256 : 128);
+        batchnorm_bwd_cluster_kernel<<<C * kBnCluster, threads, 0, s>>>(dy, x, gamma, save_mean, save_rstd, dx, dgamma, dbeta,
+                                                                       N, C, HW);
+        HETU_CHECK_LAUNCH("hetu_batchnorm_bwd(cluster)");
+        return 0;
+    }
     batchnorm_bwd_kernel<<<C, 512, 0, s>>>(dy, x, gamma, save_mean, save_rstd, dx, dgamma, dbeta, N, C, HW);
     HETU_CHECK_LAUNCH("hetu_batchnorm_bwd");
     return 0;
