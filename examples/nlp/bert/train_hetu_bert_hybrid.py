@@ -81,14 +81,21 @@ def main():
     for _ in range(3):
         out = step()
     comm.barrier()
-    torch.cuda.synchronize()
-    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s.record()
-    for _ in range(args.steps):
-        out = step()
-    e.record()
-    torch.cuda.synchronize()
-    ms = device_max_ms(s.elapsed_time(e) / args.steps)
+    if torch.cuda.is_available():
+        torch.cuda.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(args.steps):
+            out = step()
+        e.record()
+        torch.cuda.synchronize()
+        ms = device_max_ms(s.elapsed_time(e) / args.steps)
+    else:                                               # CPU / gloo dry run of the same layout
+        import time
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            out = step()
+        ms = device_max_ms((time.perf_counter() - t0) * 1e3 / args.steps)
     tokens = args.batch_size * args.seq_len * M * args.dp
     l = out[0]
     if l is not None:

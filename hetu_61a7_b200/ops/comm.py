@@ -30,8 +30,16 @@ def _comm_of(op):
 
 
 def _symm_engine(op):
+    """The symmetric-heap engine spans the WORLD; a collective over a sub-group (data-parallel replicas of
+    one pipeline stage, a tensor-parallel worker) has to stay on its own NCCL communicator."""
     cfg = getattr(op, '_config', None)
-    return getattr(cfg, 'symm', None) if cfg is not None else None
+    eng = getattr(cfg, 'symm', None) if cfg is not None else None
+    if eng is None:
+        return None
+    comm = getattr(op, 'comm', None)
+    if comm is not None and (comm.nrank != eng.world or getattr(comm, 'group', None) is not None):
+        return None
+    return eng
 
 
 class _CommOp(Op):
