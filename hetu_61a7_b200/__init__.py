@@ -28,6 +28,8 @@ from . import stream
 from . import cpu_links
 from . import onnx
 from . import graphboard
+from . import memory_pool
+from .memory_pool import HetuMemoryPool
 from .utils import data
 from .utils import metrics
 from .utils.profiler import HetuProfiler, NCCLProfiler

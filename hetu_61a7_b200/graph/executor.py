@@ -820,6 +820,11 @@ class SubExecutor(object):
         torch.cuda.synchronize(dev)
 
     # ----------------------------------------------------------------------------- misc
+    def memory_plan(self, feed_shapes):
+        """Predicted memory of one step (reference SubExecutor.memory_plan / memory_pool.test_memory)."""
+        from ..memory_pool import HetuMemoryPool
+        return HetuMemoryPool().test_memory(self, feed_shapes)
+
     def profile(self, feed_shapes, log_file, profiler='cpu'):
         from ..utils.profiler import HetuProfiler
         prof = HetuProfiler(self.computing_nodes, feed_shapes, self.infer_shape(feed_shapes),

@@ -11,6 +11,7 @@ and python/hetu/optimizer.py:145-163 (one all-reduce op + one update per tensor)
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, List, Optional, Sequence
 
 import numpy as np
@@ -65,10 +66,26 @@ class SymmBuffer(object):
         return _PTRS16(*([a + offset_bytes for a in self.addrs] + [0] * (16 - len(self.addrs))))
 
 
+class _ArenaView(object):
+    """A sub-range of the arena with the SymmBuffer interface (tensor / ptrs / peer_ptrs)."""
+
+    def __init__(self, arena: SymmBuffer, offset: int, nbytes: int):
+        self.arena, self.offset, self.nbytes = arena, offset, nbytes
+        self.addrs = [a + offset for a in arena.addrs]
+        self.local_ptr = arena.local_ptr + offset
+        self.ptrs = _PTRS16(*(self.addrs + [0] * (16 - len(self.addrs))))
+
+    def tensor(self, dtype=torch.float32, offset_bytes: int = 0, numel: Optional[int] = None) -> torch.Tensor:
+        return self.arena.tensor(dtype, self.offset + offset_bytes, numel)
+
+    def peer_ptrs(self, offset_bytes: int = 0):
+        return _PTRS16(*([a + offset_bytes for a in self.addrs] + [0] * (16 - len(self.addrs))))
+
+
 class SymmEngine(object):
     """Per-process singleton bound to the world communicator."""
     _inst: Optional['SymmEngine'] = None
-    MAX_FUSED_BYTES = 64 << 20
+    MAX_FUSED_BYTES = int(os.environ.get('HETU_SYMM_MAX_FUSED_BYTES', str(64 << 20)))
 
     @staticmethod
     def get(comm) -> Optional['SymmEngine']:
@@ -99,9 +116,24 @@ class SymmEngine(object):
     def buffer(self, key, nbytes: int) -> SymmBuffer:
         """Symmetric scratch keyed by (op identity, size).  Single-buffered: every collective
         kernel closes with a cross-GPU barrier, so the buffer is free again when it returns
-        (needed because CUDA-graph replays bake the address in)."""
+        (needed because CUDA-graph replays bake the address in).
+
+        With ``HETU_SYMM_ARENA_MB=<n>`` all buffers are carved out of ONE symmetric arena by the
+        best-fit-with-coalescing allocator (memory_pool.BFCAllocator): a single cudaMalloc + IPC
+        exchange instead of one per buffer; every rank runs the same allocation sequence, so the
+        offsets agree on all GPUs."""
         k = (key, int(nbytes))
         if k not in self._bufs:
+            arena_mb = int(os.environ.get('HETU_SYMM_ARENA_MB', '0'))
+            if arena_mb > 0:
+                if getattr(self, '_arena', None) is None:
+                    from ..memory_pool import BFCAllocator
+                    self._arena = SymmBuffer(self, arena_mb << 20)
+                    self._arena_alloc = BFCAllocator(arena_mb << 20, 256)
+                off = self._arena_alloc.alloc(int(nbytes))
+                if off >= 0:
+                    self._bufs[k] = _ArenaView(self._arena, off, int(nbytes))
+                    return self._bufs[k]
             self._bufs[k] = SymmBuffer(self, int(nbytes))
         return self._bufs[k]
 
@@ -186,7 +218,8 @@ class FusedDPUpdate(object):
             offs.append(off)
             sizes.append(n)
             off += (n + 3) // 4 * 4
-        self.total = off
+        quantum = 4 * self.engine.world                 # equal, 16-byte aligned slices for the two-shot path
+        self.total = (off + quantum - 1) // quantum * quantum
         self.offs, self.sizes = offs, sizes
         self.key = ('dp', id(self))
         self.buf = self.engine.buffer(self.key, self.total * 4)
@@ -232,9 +265,20 @@ class FusedDPUpdate(object):
                        L.c_f32(h[0]), L.c_f32(h[1]), L.c_f32(h[2]), L.c_f32(h[3]), L.c_f32(float(optimizer.l2reg)),
                        eng._stream())
         else:
-            out = torch.empty(self.total, dtype=torch.float32, device=eng.device)
-            L.call('symm_allreduce', self.buf.ptrs, L.c_sz(off), eng.flags.ptrs, L.c_int(eng.rank),
-                   L.c_int(eng.world), L.p(eng.epoch), L.p(eng.gate), L.c_i64(self.total), L.p(out), eng._stream())
+            if self.total * 4 > SymmEngine.MAX_FUSED_BYTES:
+                # large models: two-shot all-reduce.  The one-shot kernels make every rank read every
+                # peer's whole buffer ((world-1) x N bytes inbound - fine for latency-bound small models,
+                # 9.4 GB per step for BERT-large on 8 GPUs); reduce-scatter by peer loads + all-gather by
+                # peer stores moves 2 (world-1)/world x N instead.
+                chunk = self.total // eng.world
+                red = torch.empty(chunk, dtype=torch.float32, device=eng.device)
+                L.call('symm_reduce_scatter', self.buf.ptrs, L.c_sz(off), eng.flags.ptrs, L.c_int(eng.rank),
+                       L.c_int(eng.world), L.p(eng.epoch), L.p(eng.gate), L.c_i64(chunk), L.p(red), eng._stream())
+                out = eng.allgather(red, key=('dp_ag', id(self))).reshape(-1)
+            else:
+                out = torch.empty(self.total, dtype=torch.float32, device=eng.device)
+                L.call('symm_allreduce', self.buf.ptrs, L.c_sz(off), eng.flags.ptrs, L.c_int(eng.rank),
+                       L.c_int(eng.world), L.p(eng.epoch), L.p(eng.gate), L.c_i64(self.total), L.p(out), eng._stream())
             ps = [optimizer.tensors[i] for i in ids]
             gs = [out[o:o + sz].view(p.shape) for o, sz, p in zip(self.offs, self.sizes, ps)]
             optimizer._dense_kernel(ps, gs, [optimizer.states[i] for i in ids])

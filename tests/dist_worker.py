@@ -68,7 +68,10 @@ data_rng = np.random.RandomState(42)
 X = data_rng.randn(nrank * 16, 20).astype(np.float32)
 Y = np.eye(4, dtype=np.float32)[data_rng.randint(0, 4, nrank * 16)]
 for opt_name, mk in (('sgd', lambda: ht.optim.SGDOptimizer(0.1 / nrank)), ('adam', lambda: ht.optim.AdamOptimizer(0.01))):
-    for engine in (['nccl', 'symm'] if gpu else ['nccl']):
+    for engine in (['nccl', 'symm', 'symm2shot'] if gpu else ['nccl']):
+        if gpu:          # 'symm2shot': force the large-model path (reduce-scatter + all-gather, then the optimizer)
+            from hetu_61a7_b200.parallel.symm import SymmEngine
+            SymmEngine.MAX_FUSED_BYTES = 0 if engine == 'symm2shot' else (64 << 20)
         x, y_, loss, params = build_mlp(0)
         # sum-all-reduce of per-shard mean losses == nrank * full-batch mean gradient
         train = mk().minimize(loss)

@@ -2,6 +2,7 @@
 world), distribution strategies, GNN ops.  Pattern: reference tests/test_profiler.py (smoke) and
 examples/gnn scripts."""
 import numpy as np
+import pytest
 import scipy.sparse as sp
 import torch
 
@@ -85,3 +86,32 @@ def test_gnn_ops_match_dense():
     z = ht.distgcn_15d_op(adj, h, w, N, N, 1, 1, 0, comm, [None, None], True)
     ex = ht.Executor([z], ctx=ht.cpu(0))
     np.testing.assert_allclose(ex.run(feed_dict={adj: mp})[0].asnumpy(), (Ad @ torch.tensor(H)) @ torch.tensor(W), rtol=1e-4, atol=1e-4)
+
+
+def test_bfc_allocator_and_memory_plan():
+    from hetu_61a7_b200.memory_pool import BFCAllocator, HetuMemoryPool
+    a = BFCAllocator(1 << 20, alignment=256)
+    o1, o2, o3 = a.alloc(1000), a.alloc(5000), a.alloc(300)
+    assert o1 == 0 and o2 == 1024 and o3 == 1024 + 5120
+    a.free(o2)
+    assert a.alloc(4096) == o2                          # best fit reuses the hole
+    assert a.alloc(2048) == o3 + 512                    # the hole's 1 KB remainder is too small
+    st = a.stats()
+    assert st['live_blocks'] == 4 and st['in_use'] == 1024 + 4096 + 512 + 2048
+    for o in (o1, o2, o3, o3 + 512):
+        a.free(o)
+    st = a.stats()
+    assert st['in_use'] == 0 and st['free_fragments'] == 1 and st['largest_free'] == 1 << 20     # fully coalesced
+    assert BFCAllocator(4096).alloc(8192) == -1
+    with pytest.raises(ValueError):
+        a.free(12345)
+    # planner: peak of a 3-layer MLP step is far below the sum of all buffers
+    x, y_, loss, train = _mlp()
+    ex = ht.Executor([loss, train], ctx=ht.cpu(0))
+    rep = ex.subexecutor['default'].memory_plan({x: (4096, 20), y_: (4096, 4)})
+    pool = HetuMemoryPool()
+    shapes = ex.subexecutor['default'].infer_shape({x: (4096, 20), y_: (4096, 4)})
+    plan = pool.memory_plan(ex.subexecutor['default'].topo_order, shapes, eval_nodes=[loss])
+    total = sum(sz for _, sz in plan.values())
+    assert rep['parameter_bytes'] == (20 * 16 + 16 * 4) * 4
+    assert 0 < rep['activation_peak_bytes'] < total and rep['buffers'] == len(plan)
