@@ -288,6 +288,24 @@ def _post_hook(node: Op, config: HetuConfig) -> None:
 topo_sort_dfs_with_hook = topo_sort_with_hook
 
 
+def topo_sort_dfs(node, visited, topo_order) -> None:
+    """Post-order DFS of one root appended to ``topo_order`` (reference executor.py:1321-1328); iterative."""
+    if node in visited:
+        return
+    visited.add(node)
+    stack = [(node, 0)]
+    while stack:
+        n, i = stack.pop()
+        if i < len(n.inputs):
+            stack.append((n, i + 1))
+            c = n.inputs[i]
+            if c is not None and c not in visited:
+                visited.add(c)
+                stack.append((c, 0))
+        else:
+            topo_order.append(n)
+
+
 def topo_sort_register_ps(node_list, ps_comm, comm_mode, seed, cstable_policy):
     """Register every PS-resident parameter with the servers (InitTensor RPC)."""
     for node in find_topo_sort(node_list):

@@ -355,3 +355,8 @@ class IndexedSlices(object):
         ind, val = self._iv()
         oind, oval = other._iv()
         return IndexedSlices(torch.cat([ind, oind]), torch.cat([val, oval]), self.dense_shape)
+
+
+#: reference ndarray.py exposes the ctypes ``DLArray`` struct; tensors are torch tensors here and the C ABI
+#: takes raw pointers, so the name is kept as an alias of the array handle for isinstance checks
+DLArray = NDArray

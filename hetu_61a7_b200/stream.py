@@ -129,3 +129,8 @@ class CSEvent(object):
 
     def update(self):
         pass
+
+
+#: reference stream.py ctypes handles; here streams / events wrap torch.cuda objects
+DLStream = Stream
+DLEvent = Event

@@ -113,3 +113,49 @@ def criteo_synthetic(n, num_dense=13, num_sparse=26, vocab=33762577, seed=0, zip
     ids = (ranks - 1) % field + np.arange(num_sparse, dtype=np.int64)[None, :] * field
     labels = (rng.rand(n, 1) < 0.25).astype(np.float32)
     return dense, ids, labels
+
+
+# ---------------------------------------------------------------------------------------------
+def convert_to_one_hot(vals, max_val=0):
+    """Label vector -> one-hot matrix (reference data.py:250-256)."""
+    vals = np.asarray(vals).astype(np.int64).reshape(-1)
+    if max_val == 0:
+        max_val = int(vals.max()) + 1
+    out = np.zeros((vals.size, max_val), dtype=np.float32)
+    out[np.arange(vals.size), vals] = 1
+    return out
+
+
+def tf_normalize_cifar(num_class=10, onehot=True, directory=None, synthetic=False):
+    """CIFAR in NHWC layout with per-channel mean/std normalisation (reference data.py:221-247)."""
+    tx, ty, vx, vy = normalize_cifar(num_class=num_class, directory=directory, onehot=onehot, synthetic=synthetic)
+    tx = tx.reshape((-1, 3, 32, 32)).transpose(0, 2, 3, 1)
+    vx = vx.reshape((-1, 3, 32, 32)).transpose(0, 2, 3, 1)
+    return np.ascontiguousarray(tx), ty, np.ascontiguousarray(vx), vy
+
+
+def data_augmentation(images, mode='train', flip=False, crop=False, crop_shape=(24, 24, 3), whiten=False,
+                      noise=False, noise_mean=0, noise_std=0.01, rng=None):
+    """NHWC batch augmentation: random (train) / centre (test) crop, horizontal flip, per-image
+    whitening, additive Gaussian noise (reference data.py:263-338)."""
+    rng = rng if rng is not None else np.random
+    x = np.asarray(images, dtype=np.float32)
+    if crop:
+        n, h, w, _ = x.shape
+        ch, cw = crop_shape[0], crop_shape[1]
+        out = np.empty((n, ch, cw, x.shape[3]), dtype=np.float32)
+        for i in range(n):
+            top, left = ((rng.randint(0, h - ch + 1), rng.randint(0, w - cw + 1)) if mode == 'train'
+                         else ((h - ch) // 2, (w - cw) // 2))
+            out[i] = x[i, top:top + ch, left:left + cw]
+        x = out
+    if flip:
+        mask = rng.rand(x.shape[0]) < 0.5
+        x[mask] = x[mask, :, ::-1]
+    if whiten:
+        mean = x.mean(axis=(1, 2, 3), keepdims=True)
+        std = np.maximum(x.std(axis=(1, 2, 3), keepdims=True), 1.0 / np.sqrt(np.prod(x.shape[1:])))
+        x = (x - mean) / std
+    if noise:
+        x = x + rng.normal(noise_mean, noise_std, size=x.shape).astype(np.float32)
+    return x

@@ -93,3 +93,80 @@ def roc_auc_exact(y_pred, y_true):
         return float('nan')
     ranks = rankdata(y_pred)
     return float((ranks[y_true].sum() - n_pos * (n_pos + 1) / 2.0) / (n_pos * n_neg))
+
+
+# ---------------------------------------------------------------------------------------------
+# threshold / one-hot variants (reference metrics.py:17-359 spellings)
+def confusion_matrix_at_thresholds(labels, predictions, thresholds, includes=None):
+    """{'tp','fn','tn','fp'} -> arrays of shape [len(thresholds)] for binary ``labels`` and scores in [0, 1]."""
+    keys = ('tp', 'fn', 'tn', 'fp')
+    includes = keys if includes is None else tuple(includes)
+    for k in includes:
+        if k not in keys:
+            raise ValueError('Invalid key: %s.' % k)
+    y = _np(labels).reshape(-1).astype(bool)
+    p = _np(predictions).reshape(-1).astype(np.float64)
+    th = np.asarray(list(thresholds), dtype=np.float64).reshape(-1, 1)
+    pred_pos = p[None, :] > th                                   # [T, n]
+    out = {}
+    if 'tp' in includes:
+        out['tp'] = (pred_pos & y[None, :]).sum(1).astype(np.float64)
+    if 'fn' in includes:
+        out['fn'] = (~pred_pos & y[None, :]).sum(1).astype(np.float64)
+    if 'tn' in includes:
+        out['tn'] = (~pred_pos & ~y[None, :]).sum(1).astype(np.float64)
+    if 'fp' in includes:
+        out['fp'] = (pred_pos & ~y[None, :]).sum(1).astype(np.float64)
+    return out
+
+
+def roc_pr_curve(values, curve='ROC'):
+    """(x, y) lists of the ROC (fpr, tpr) or PR (recall, precision) curve from confusion counts."""
+    for k in ('tp', 'fp', 'fn', 'tn'):
+        if k not in values:
+            raise ValueError('values must have the key %s' % k)
+    eps = 1e-6
+    tp, fp, fn, tn = (np.asarray(values[k], dtype=np.float64) for k in ('tp', 'fp', 'fn', 'tn'))
+    tpr = (tp + eps) / (tp + fn + eps)
+    if curve == 'ROC':
+        return list(fp / (fp + tn + eps)), list(tpr)
+    if curve == 'PR':
+        return list(tpr), list((tp + eps) / (tp + fp + eps))
+    raise ValueError("curve must be 'ROC' or 'PR'")
+
+
+def confusion_matrix_one_hot(labels, predictions):
+    """Per-class tp / tn / fp / fn for one-hot ``labels`` and score matrix ``predictions`` (argmax decides)."""
+    y = _np(labels).astype(bool)
+    p = _np(predictions)
+    hit = np.zeros_like(y)
+    hit[np.arange(p.shape[0]), p.argmax(1)] = True
+    return {'tp': (hit & y).sum(0).astype(np.float64), 'tn': (~hit & ~y).sum(0).astype(np.float64),
+            'fp': (hit & ~y).sum(0).astype(np.float64), 'fn': (~hit & y).sum(0).astype(np.float64)}
+
+
+def _avg_score(num, den, average):
+    if average is None:
+        return num / np.maximum(den, 1e-12)
+    if average == 'micro':
+        return float(num.sum() / max(den.sum(), 1e-12))
+    if average == 'macro':
+        return float(np.mean(num / np.maximum(den, 1e-12)))
+    raise ValueError("average must be None, 'micro' or 'macro'")
+
+
+def precision_score_one_hot(labels, predictions, average=None):
+    v = confusion_matrix_one_hot(labels, predictions)
+    return _avg_score(v['tp'], v['tp'] + v['fp'], average)
+
+
+def recall_score_one_hot(labels, predictions, average=None):
+    v = confusion_matrix_one_hot(labels, predictions)
+    return _avg_score(v['tp'], v['tp'] + v['fn'], average)
+
+
+def f_score_one_hot(labels, predictions, beta=1.0, average=None):
+    p = precision_score_one_hot(labels, predictions, average)
+    r = recall_score_one_hot(labels, predictions, average)
+    b2 = beta * beta
+    return (1 + b2) * p * r / np.maximum(b2 * p + r, 1e-12)

@@ -34,6 +34,37 @@ def _timeit(fn, device, warmup, iters):
     return (time.perf_counter() - t0) * 1000.0 / iters
 
 
+class NCCLOP(object):
+    """reference profiler.py:18-23 (an Enum there; plain ints keep ``NCCLOP.AllReduce.value``-free call sites simple)."""
+    AllReduce, AllGather, ReduceScatter, Reduce, Broadcast = range(5)
+    names = ('allreduce', 'allgather', 'reducescatter', 'reduce', 'broadcast')
+
+
+class BaseProfiler(object):
+    """Shared device / timing plumbing of the profilers (reference profiler.py:26-52)."""
+
+    def __init__(self):
+        self.idx = 0
+        self.ctx = None
+        self.use_gpu = False
+
+    def set_ctx(self, ctx):
+        from ..ndarray import is_gpu_ctx
+        self.ctx = ctx
+        self.use_gpu = is_gpu_ctx(ctx) and torch.cuda.is_available()
+        self.device = ctx.torch_device if self.use_gpu else torch.device('cpu')
+
+    def renew_instances(self):
+        raise NotImplementedError
+
+    def init_memory(self, shape, seed=0):
+        g = torch.Generator().manual_seed(int(seed))
+        return torch.randn(tuple(shape), generator=g).to(getattr(self, 'device', 'cpu'))
+
+    def time_fn(self, fn, warmup=5, iters=100):
+        return _timeit(fn, getattr(self, 'device', torch.device('cpu')), warmup, iters)
+
+
 class HetuProfiler(object):
     def __init__(self, computing_nodes, feed_shapes, node_to_shape_map, ctx=None, rank=-1,
                  warmup=5, iters=100):

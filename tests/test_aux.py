@@ -115,3 +115,26 @@ def test_bfc_allocator_and_memory_plan():
     total = sum(sz for _, sz in plan.values())
     assert rep['parameter_bytes'] == (20 * 16 + 16 * 4) * 4
     assert 0 < rep['activation_peak_bytes'] < total and rep['buffers'] == len(plan)
+
+
+def test_metric_and_data_helpers():
+    from hetu_61a7_b200.utils import metrics as M, data as D
+    y = np.eye(3)[[0, 1, 2, 1]]
+    p = np.array([[9.1, 5, 7.8], [.3, .7, 1.4], [4.3, 1.3, 5.3], [0, 3, 1]])
+    cm = M.confusion_matrix_one_hot(y, p)
+    assert cm['tp'].tolist() == [1, 1, 1] and cm['fp'].tolist() == [0, 0, 1] and cm['fn'].tolist() == [0, 1, 0]
+    assert abs(M.precision_score_one_hot(y, p, 'macro') - (1 + 1 + 0.5) / 3) < 1e-9
+    assert abs(M.recall_score_one_hot(y, p, 'micro') - 0.75) < 1e-9
+    assert abs(M.f_score_one_hot(y, p, average='micro') - 0.75) < 1e-9
+    v = M.confusion_matrix_at_thresholds([1, 0, 1, 0], [.9, .4, .6, .1], [0.0, 0.5, 1.0])
+    assert v['tp'].tolist() == [2, 2, 0] and v['fp'].tolist() == [2, 0, 0]
+    fpr, tpr = M.roc_pr_curve(v)
+    assert abs(fpr[0] - 1) < 1e-5 and abs(tpr[1] - 1) < 1e-5 and tpr[2] < 1e-5
+    assert D.convert_to_one_hot([0, 2, 1]).tolist() == [[1, 0, 0], [0, 0, 1], [0, 1, 0]]
+    aug = D.data_augmentation(np.random.rand(4, 32, 32, 3), flip=True, crop=True, whiten=True, noise=True)
+    assert aug.shape == (4, 24, 24, 3) and abs(float(aug.mean())) < 0.1
+    from hetu_61a7_b200.graph.executor import topo_sort_dfs
+    x = ht.Variable('x')
+    order = []
+    topo_sort_dfs(ht.relu_op(x), set(), order)
+    assert order[0] is x and len(order) == 2
