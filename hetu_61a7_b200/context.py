@@ -24,6 +24,11 @@ ContextUnit = Union[DLContext, Tuple[DLContext, ...]]
 class DeviceGroup(object):
     def __init__(self, ctxs) -> None:
         self._contexts: List[ContextUnit] = self.parse_contexts(ctxs)
+        self.get_servers_n_workers()
+
+    def get_servers_n_workers(self) -> None:
+        """Split the parsed contexts into workers (GPUs, or tuples = one model-parallel worker) and servers
+        (CPU contexts).  reference context.py:101-111."""
         workers, servers = [], []
         mp = 1
         for c in self._contexts:

@@ -114,6 +114,14 @@ class Dataloader(object):
         self.batch_index = (self.batch_index + 1) % self.batch_num
         return out
 
+    def _get_arr(self, batchind):
+        """Rows of batch ``batchind`` straight from the dataset (reference dataloader.py:88-99); does not
+        touch the staging ring."""
+        self.init_states()
+        beg = (batchind % self.batch_num) * self.batch_size
+        end = min(beg + self.batch_size, self.samples_num)
+        return self.reshape_tensor(self.raw_data[beg:end])
+
     def get_next_arr(self):
         slot = self.rd
         return self.ring[slot][:self.ring_rows[slot]]

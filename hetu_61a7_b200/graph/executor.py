@@ -837,6 +837,33 @@ class SubExecutor(object):
         self.graph_launches = L.launch_count - launches_before   # native kernels per replay
         torch.cuda.synchronize(dev)
 
+    # ------------------------------------------------------- reference-compatible helpers
+    def update_executor(self, eval_node_list):
+        """Re-target this sub-executor at another list of eval nodes (reference executor.py:717-760, marked
+        'not in use' upstream): topology, feed / parameter lists and the captured graph are rebuilt."""
+        self.__init__(self.name, list(eval_node_list), self.config)
+
+    def get_feed_value(self, arr_map, node, value):
+        """Stage one feed into ``arr_map`` on this executor's device; returns (shape, reallocated?)
+        like reference executor.py:875-915."""
+        t = self._to_device(self._feed_tensor(node, value))
+        old = arr_map.get(node)
+        shape = tuple(t.shape) if isinstance(t, torch.Tensor) else None
+        realloc = old is None or not isinstance(old, torch.Tensor) or tuple(old.shape) != shape
+        arr_map[node] = t
+        return shape, realloc
+
+    def compute(self, computing_nodes, arr_map):
+        """Evaluate ``computing_nodes`` in order, reading and writing values in ``arr_map``
+        (reference executor.py:1000-1056; values are torch tensors here)."""
+        for node in computing_nodes:
+            ins = [arr_map.get(i) if i is not None else None for i in node.inputs]
+            if getattr(node, 'takes_inference', False):
+                arr_map[node] = node.compute(ins, None, self.config.comp_stream, inference=self.inference)
+            else:
+                arr_map[node] = node.compute(ins, None, self.config.comp_stream)
+        return arr_map
+
     # ----------------------------------------------------------------------------- misc
     def memory_plan(self, feed_shapes):
         """Predicted memory of one step (reference SubExecutor.memory_plan / memory_pool.test_memory)."""

@@ -189,6 +189,11 @@ class Op(object, metaclass=OpMeta):
     def get_default_state(self, status=None, enforce_order=False):
         return None
 
+    def reset_status(self) -> None:
+        """Forget the model-parallel layout derived for this node (reference Node.py:218-220 placeholder)."""
+        self.mp_state = None
+        self.mp_group = None
+
 
 # ---------------------------------------------------------------------------
 # helpers shared by op modules

@@ -194,6 +194,87 @@ class Communicator(object):
         dist.all_gather_object(out, obj, group=self.group)
         return out
 
+    # reference MPI / NCCL communicator helpers (communicator/mpi_nccl_comm.py:62-336) ------------
+    # MPI is replaced by the launcher's environment + torch.distributed, so the bootstrap calls are
+    # no-ops that return what the launcher already decided.
+    def MPI_Init(self):
+        return self
+
+    def MPI_Finalize(self):
+        pass
+
+    def MPIGetComm(self):
+        return self
+
+    def MPI_Comm_rank(self):
+        return self.rank
+
+    def MPI_Comm_size(self):
+        return self.nrank
+
+    def MPI_Broadcast(self, arr, root=0):
+        """Host-side broadcast of a numpy array / python object from ``root`` (in place for arrays)."""
+        if not self.multi:
+            return arr
+        box = [arr if self.rank == root else None]
+        dist.broadcast_object_list(box, src=self.world_of(root), group=self.group)
+        if isinstance(arr, np.ndarray) and self.rank != root:
+            arr[...] = box[0]
+            return arr
+        return box[0]
+
+    def getLocalRank(self):
+        return self.local_rank
+
+    def getGlobalDevice(self):
+        return self.local_rank
+
+    def getDeviceFromLocalRank(self, local_rank):
+        return local_rank
+
+    def getLocalRankFromDevice(self, device_id):
+        return device_id
+
+    def getRankFromDevice(self, hostname_or_ctx, device_id=None):
+        """Rank that drives a device: on one node rank == device id (group-relative inside a sub-group)."""
+        dev = hostname_or_ctx.device_id if device_id is None else device_id
+        return self.ranks.index(dev) if dev in self.ranks else dev
+
+    def ncclGroupInit(self, devices_context, stream=None):
+        return new_group_comm(devices_context)
+
+    def ncclGetUniqueId(self, senderRank=0):
+        return None                 # rendezvous is torch.distributed's store
+
+    ncclGetGroupUniqueId = ncclGetUniqueId
+
+    def ncclCommInitRank(self):
+        return self
+
+    def ncclCommDestroy(self):
+        pass
+
+    def dlarrayNcclReduce(self, dlarray, out=None, root=0, datatype=None, reduceop=None, stream=None):
+        from ..ndarray import NDArray
+        t = dlarray.tensor if isinstance(dlarray, NDArray) else dlarray
+        self.reduce(t, root)
+        if out is not None and out is not dlarray and self.rank == root:
+            (out.tensor if isinstance(out, NDArray) else out).copy_(t)
+
+    # hierarchical all-to-all (reference mpi_nccl_communication.cu:152-244: gather to the node leader,
+    # leader exchange, scatter).  Inside one NVSwitch domain the hierarchy only adds copies, so the three
+    # steps collapse into one direct exchange issued by the last call.
+    def dlarrayHA2AGather(self, sendarr, recvarr, datatype=None, myrank=None, num_local_gpus=None, stream=None):
+        self._ha2a_src = sendarr
+
+    def dlarrayHAllToAll(self, sendarr, recvarr, datatype=None, num_local_gpus=None, stream=None):
+        pass
+
+    def dlarrayHA2AScatter(self, sendarr, recvarr, datatype=None, myrank=None, num_local_gpus=None, stream=None):
+        src = getattr(self, '_ha2a_src', None)
+        self._ha2a_src = None
+        self.dlarrayAllToAll(src if src is not None else sendarr, recvarr)
+
     # reference dlarray* spellings ------------------------------------------------
     def dlarrayNcclAllReduce(self, dlarray, out=None, datatype=None, reduceop=None, stream=None):
         from ..ndarray import NDArray
