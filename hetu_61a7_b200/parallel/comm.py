@@ -206,6 +206,20 @@ class Communicator(object):
     def MPIGetComm(self):
         return self
 
+    MPI_GetComm = MPIGetComm
+
+    def allReduce(self, arr):
+        """Host-side sum all-reduce of a numpy array in place (reference mpi_communication.cc:37-47)."""
+        if self.multi:
+            t = torch.from_numpy(arr)
+            if dist.get_backend() == 'nccl':
+                d = t.cuda()
+                dist.all_reduce(d, group=self.group)
+                t.copy_(d.cpu())
+            else:
+                dist.all_reduce(t, group=self.group)
+        return arr
+
     def MPI_Comm_rank(self):
         return self.rank
 

@@ -88,6 +88,23 @@ class PSWorker(object):
         self.lib.hps_worker_finalize()
 
     Finalize = finalize
+    finish = finalize
+
+    def Init(self):
+        """reference ``ps_comm.Init()``: the connection is made in the constructor; kept for scripts."""
+        return self
+
+    def StartServer(self):
+        """reference server-role entry (executor.py:113-121): run the local server shard until shutdown."""
+        start_server_from_env(block=True)
+
+    def PushData(self, node_id, rows, data, lengths=None):
+        """Row-addressed raw write (reference PushData, used by the graph/GNN stores): rows of
+        ``data`` replace nothing on their own - they are added, so callers push deltas."""
+        self.SparsePush(node_id, rows, data)
+
+    def PullData(self, node_id, rows, out=None, lengths=None):
+        return self.SparsePull(node_id, rows, out=out)
 
     def rank(self) -> int:
         return int(self.lib.hps_rank())
