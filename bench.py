@@ -50,12 +50,19 @@ class ClockSampler(object):
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ['nvidia-smi', '--query-gpu=' + self.Q, '--format=csv,noheader,nounits', '-lms', '100',
+                ['nvidia-smi', '--query-gpu=' + self.Q, '--format=csv,noheader,nounits', '-lms', '20',
                  '-i', str(self.gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
+            t0 = time.time()
+            while not self.rows and time.time() - t0 < 5.0:      # nvidia-smi needs a moment to start: the timed
+                time.sleep(0.01)                                  # region must not begin before it is sampling
         except Exception:
             self.proc = None
+
+    def mark(self):
+        """Timed region starts now: rows sampled before (idle clocks) only serve as a fallback."""
+        self.pre_rows, self.rows = self.rows, []
 
     def _read(self):
         for line in self.proc.stdout:
@@ -64,8 +71,13 @@ class ClockSampler(object):
     def stop(self):
         if self.proc is None:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
-        time.sleep(0.15)
+        n0 = len(self.rows)
+        t0 = time.time()
+        while len(self.rows) <= n0 and time.time() - t0 < 1.0:   # one more sample after the last timed step
+            time.sleep(0.01)
         self.proc.terminate()
+        if not self.rows:
+            self.rows = getattr(self, 'pre_rows', [])
         sm = sorted(float(r[1]) for r in self.rows if len(r) > 2 and r[1].replace('.', '').isdigit())
         mx = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace('.', '').isdigit()]
         reasons = set()
@@ -146,6 +158,9 @@ def bench_wdl(args, ht, torch, np, comm, device):
     sub = ex.subexecutor['train']
     sampler = ClockSampler(device.index)
     sampler.start()
+    for i in range(3):
+        step_dev(i)
+    sampler.mark()
     ms_dev = timed(step_dev, args.steps, torch, device, comm)
     # --- end to end: numpy batch -> pinned -> H2D, loss D2H every step ---------------------
     h2d = sum(a.nbytes for a in pool[0])
