@@ -1,12 +1,15 @@
 // Minimal blocking TCP transport + message framing for the parameter server
 // (replaces ps-lite's ZeroMQ "Van": ps-lite/src/zmq_van.h, p3_van.h).  One message =
-//   [u32 magic][u32 type][u64 key][i64 arg0][i64 arg1][u32 narrays] { [u64 nbytes][bytes] }*
+//   [u32 magic][u32 type][u64 key][i64 arg0][i64 arg1][u64 sig][u32 narrays] { [u64 nbytes][bytes] }*
+// `sig` = (sender uid << 32 | sequence number); 0 when the sender does not use the resend protocol
+// (ps-lite's Resender keys its duplicate filter on the same kind of signature, resender.h:15-148).
 #pragma once
 #include <arpa/inet.h>
 #include <netdb.h>
 #include <netinet/in.h>
 #include <netinet/tcp.h>
 #include <sys/socket.h>
+#include <sys/time.h>
 #include <unistd.h>
 
 #include <cerrno>
@@ -24,6 +27,7 @@ struct Message {
     uint32_t type = 0;
     uint64_t key = 0;
     int64_t arg0 = 0, arg1 = 0;
+    uint64_t sig = 0;
     std::vector<std::vector<char>> arrays;
 
     template <typename T> void add(const T* p, size_t n) {
@@ -34,7 +38,7 @@ struct Message {
     template <typename T> T* mdata(size_t i) { return reinterpret_cast<T*>(arrays[i].data()); }
     template <typename T> size_t count(size_t i) const { return arrays[i].size() / sizeof(T); }
     std::string str(size_t i) const { return std::string(arrays[i].begin(), arrays[i].end()); }
-    size_t bytes() const { size_t b = 36; for (auto& a : arrays) b += 8 + a.size(); return b; }
+    size_t bytes() const { size_t b = 44; for (auto& a : arrays) b += 8 + a.size(); return b; }
 };
 
 inline void write_all(int fd, const void* buf, size_t n) {
@@ -56,11 +60,11 @@ inline bool read_all(int fd, void* buf, size_t n) {
     return true;
 }
 inline void send_msg(int fd, const Message& m) {
-    char hdr[36];
+    char hdr[44];
     uint32_t na = (uint32_t)m.arrays.size();
     memcpy(hdr, &kMagic, 4); memcpy(hdr + 4, &m.type, 4); memcpy(hdr + 8, &m.key, 8);
-    memcpy(hdr + 16, &m.arg0, 8); memcpy(hdr + 24, &m.arg1, 8); memcpy(hdr + 32, &na, 4);
-    write_all(fd, hdr, 36);
+    memcpy(hdr + 16, &m.arg0, 8); memcpy(hdr + 24, &m.arg1, 8); memcpy(hdr + 32, &m.sig, 8); memcpy(hdr + 40, &na, 4);
+    write_all(fd, hdr, 44);
     for (auto& a : m.arrays) {
         uint64_t nb = a.size();
         write_all(fd, &nb, 8);
@@ -68,13 +72,13 @@ inline void send_msg(int fd, const Message& m) {
     }
 }
 inline bool recv_msg(int fd, Message* m) {
-    char hdr[36];
-    if (!read_all(fd, hdr, 36)) return false;
+    char hdr[44];
+    if (!read_all(fd, hdr, 44)) return false;
     uint32_t magic, na;
     memcpy(&magic, hdr, 4);
     if (magic != kMagic) return false;
     memcpy(&m->type, hdr + 4, 4); memcpy(&m->key, hdr + 8, 8);
-    memcpy(&m->arg0, hdr + 16, 8); memcpy(&m->arg1, hdr + 24, 8); memcpy(&na, hdr + 32, 4);
+    memcpy(&m->arg0, hdr + 16, 8); memcpy(&m->arg1, hdr + 24, 8); memcpy(&m->sig, hdr + 32, 8); memcpy(&na, hdr + 40, 4);
     m->arrays.clear();
     m->arrays.resize(na);
     for (uint32_t i = 0; i < na; ++i) {
@@ -84,6 +88,12 @@ inline bool recv_msg(int fd, Message* m) {
         if (nb && !read_all(fd, m->arrays[i].data(), nb)) return false;
     }
     return true;
+}
+// receive timeout in milliseconds (0 = block forever); a timed-out recv makes read_all return false
+inline void set_recv_timeout(int fd, int ms) {
+    timeval tv{};
+    tv.tv_sec = ms / 1000; tv.tv_usec = (ms % 1000) * 1000;
+    setsockopt(fd, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
 }
 inline int listen_on(int port, int* bound_port = nullptr) {
     int fd = ::socket(AF_INET, SOCK_STREAM, 0);

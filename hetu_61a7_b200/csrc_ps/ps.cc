@@ -11,6 +11,19 @@
 // per-server shards (AveragePartitioner semantics), async requests on the worker through
 // std::async with per-tensor Wait().  This is the host-DRAM tier; the B200 fast path for
 // embeddings is the NVLink-sharded table (parallel/sharded_embedding.py).
+//
+// Fault handling (reference: ps-lite/src/van.cc:23-27,132-162,334-336,567-579, resender.h:15-148,
+// postoffice.cc:201-221), same environment knobs:
+//   PS_HEARTBEAT_INTERVAL=<s>  workers and servers beat to the scheduler on a side connection;
+//   PS_HEARTBEAT_TIMEOUT=<s>   a node silent for longer is "dead" (hps_query_dead_nodes) and a node
+//                              of the same role that registers late takes over its rank (recovery;
+//                              parameter state is not restored - use LoadParam, as in the reference);
+//   PS_RESEND=1, PS_RESEND_TIMEOUT=<ms>  worker->server requests carry a signature; after a timeout
+//                              the worker reconnects and retransmits (up to 10 times), the server
+//                              answers a retransmitted signature from its reply cache instead of
+//                              applying the update twice;
+//   PS_DROP_MSG=<percent>      fault injection: the server loses that share of data-plane messages,
+//                              half before handling them (lost request), half after (lost reply).
 #include "net.h"
 
 #include <algorithm>
@@ -37,7 +50,7 @@ enum PsfType : uint32_t {
     kDensePull = 0, kDensePush, kDDPushPull, kSparsePull, kSparsePush, kSDPushPull, kSSPushPull, kParamInit,
     kParamClear, kParamSave, kParamLoad, kSyncEmbedding, kPushEmbedding, kPushSyncEmbedding, kSSPInit, kSSPSync,
     kPReduceGetPartner,
-    kRegister = 100, kBarrier, kTerminate, kHeartbeat, kOk, kError
+    kRegister = 100, kBarrier, kTerminate, kHeartbeat, kOk, kError, kGetDeadNodes, kGetServers
 };
 
 // ------------------------------------------------------------------------------- server state
@@ -219,6 +232,10 @@ class Server {
 // ---------------------------------------------------------------------------- scheduler state
 struct NodeInfo { int role; std::string host; int port; };
 
+static const char* env_or(const char* k, const char* d) { const char* v = getenv(k); return v ? v : d; }
+// ps-lite node ids: scheduler 1, server rank r -> 8 + 2r, worker rank r -> 9 + 2r
+inline int node_id_of(int role, int rank) { return (role == 1 ? 8 : 9) + 2 * rank; }
+
 class Scheduler {
   public:
     Scheduler(int nworkers, int nservers) : nworkers_(nworkers), nservers_(nservers) {}
@@ -234,19 +251,52 @@ class Scheduler {
             case kSSPSync: ssp_sync(req, rsp); break;
             case kPReduceGetPartner: preduce(req, rsp); break;
             case kHeartbeat: { std::unique_lock<std::mutex> l(mu_); heartbeat_[req.arg0] = std::chrono::steady_clock::now(); break; }
+            case kGetDeadNodes: {
+                std::unique_lock<std::mutex> l(mu_);
+                std::vector<int> dead = dead_nodes((double)req.arg0 / 1000.0);
+                rsp->add(dead.data(), dead.size());
+                break;
+            }
+            case kGetServers: {
+                std::unique_lock<std::mutex> l(mu_);
+                for (auto& sv : servers_) rsp->add_str(sv.host + ":" + std::to_string(sv.port));
+                break;
+            }
             default: rsp->type = kError; rsp->add_str("unknown scheduler request");
         }
     }
 
   private:
+    // ids registered so far whose last heartbeat is older than `timeout_s` (caller holds mu_)
+    std::vector<int> dead_nodes(double timeout_s) {
+        std::vector<int> dead;
+        auto now = std::chrono::steady_clock::now();
+        for (auto& kv : heartbeat_)
+            if (std::chrono::duration<double>(now - kv.second).count() > timeout_s) dead.push_back((int)kv.first);
+        std::sort(dead.begin(), dead.end());
+        return dead;
+    }
     void do_register(const Message& req, Message* rsp) {
         std::unique_lock<std::mutex> l(mu_);
         int role = (int)req.arg0;
-        int rank;
-        if (role == 1) { rank = (int)servers_.size(); servers_.push_back({role, req.str(0), (int)req.arg1}); }
-        else { rank = nworkers_seen_++; }
-        cv_.notify_all();
-        cv_.wait(l, [&] { return (int)servers_.size() == nservers_ && nworkers_seen_ >= nworkers_; });
+        int rank = -1;
+        bool full = (int)servers_.size() == nservers_ && nworkers_seen_ >= nworkers_;
+        if (full) {
+            // late registration = a restarted node: give it the rank of a dead node of its role
+            double timeout = atof(env_or("PS_HEARTBEAT_TIMEOUT", "0"));
+            if (timeout <= 0) throw std::runtime_error("cluster is complete and recovery is off (PS_HEARTBEAT_TIMEOUT unset)");
+            for (int id : dead_nodes(timeout))
+                if ((id % 2 == 0) == (role == 1)) { rank = (id - (role == 1 ? 8 : 9)) / 2; break; }
+            if (rank < 0) throw std::runtime_error("cluster is complete and no node of this role is dead");
+            if (role == 1) servers_[(size_t)rank] = {role, req.str(0), (int)req.arg1};
+            rsp->key = 1;                                        // is_recovery
+        } else {
+            if (role == 1) { rank = (int)servers_.size(); servers_.push_back({role, req.str(0), (int)req.arg1}); }
+            else { rank = nworkers_seen_++; }
+            cv_.notify_all();
+            cv_.wait(l, [&] { return (int)servers_.size() == nservers_ && nworkers_seen_ >= nworkers_; });
+        }
+        heartbeat_[node_id_of(role, rank)] = std::chrono::steady_clock::now();
         rsp->arg0 = rank;
         rsp->arg1 = nworkers_;
         for (auto& s : servers_) rsp->add_str(s.host + ":" + std::to_string(s.port));
@@ -313,7 +363,11 @@ class Scheduler {
 template <class H>
 class Listener {
   public:
-    Listener(std::shared_ptr<H> h, int port) : h_(h) { fd_ = listen_on(port, &port_); th_ = std::thread([this] { loop(); }); }
+    Listener(std::shared_ptr<H> h, int port) : h_(h) {
+        drop_pct_ = atoi(env_or("PS_DROP_MSG", "0"));
+        fd_ = listen_on(port, &port_);
+        th_ = std::thread([this] { loop(); });
+    }
     ~Listener() { stop(); }
     int port() const { return port_; }
     void stop() {
@@ -333,57 +387,171 @@ class Listener {
             setsockopt(c, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
             std::thread([this, c] {
                 Message req, rsp;
+                std::minstd_rand rng((unsigned)c * 2654435761u + 12345u);
                 while (recv_msg(c, &req)) {
                     rsp = Message();
                     if (req.type == kTerminate) { rsp.type = kOk; send_msg(c, rsp); stopped_ = true; ::shutdown(fd_, SHUT_RDWR); break; }
-                    try { h_->handle(req, &rsp); }
-                    catch (const std::exception& e) { rsp = Message(); rsp.type = kError; rsp.add_str(e.what()); }
+                    int fate = 0;                        // 1 = lose the request, 2 = lose the reply
+                    if (drop_pct_ > 0 && req.type < kRegister && (int)(rng() % 100) < drop_pct_) fate = 1 + (int)(rng() % 2);
+                    if (fate == 1) continue;
+                    if (req.sig == 0 || !replay(req.sig, &rsp)) {
+                        try { h_->handle(req, &rsp); }
+                        catch (const std::exception& e) { rsp = Message(); rsp.type = kError; rsp.add_str(e.what()); }
+                        if (req.sig != 0) remember(req.sig, rsp);
+                    }
+                    if (fate == 2) continue;
                     try { send_msg(c, rsp); } catch (...) { break; }
                 }
                 ::close(c);
             }).detach();
         }
     }
+    // Reply cache for the resend protocol: one slot per sender uid (a sender has one request in
+    // flight).  replay() returns true with the cached reply when `sig` was already handled; when
+    // the first copy is still being handled it waits for it.  Otherwise it claims the slot.
+    struct Slot { uint32_t seq = 0; bool done = false; Message rsp; };
+    bool replay(uint64_t sig, Message* rsp) {
+        uint32_t uid = (uint32_t)(sig >> 32), seq = (uint32_t)sig;
+        std::unique_lock<std::mutex> l(dd_mu_);
+        Slot& s = slots_[uid];
+        if (s.seq == seq) {
+            dd_cv_.wait(l, [&] { return slots_[uid].done || slots_[uid].seq != seq; });
+            if (slots_[uid].seq != seq) return false;
+            *rsp = slots_[uid].rsp;
+            return true;
+        }
+        s.seq = seq; s.done = false; s.rsp = Message();
+        return false;
+    }
+    void remember(uint64_t sig, const Message& rsp) {
+        uint32_t uid = (uint32_t)(sig >> 32), seq = (uint32_t)sig;
+        std::unique_lock<std::mutex> l(dd_mu_);
+        Slot& s = slots_[uid];
+        if (s.seq == seq) { s.rsp = rsp; s.done = true; }
+        dd_cv_.notify_all();
+    }
     std::shared_ptr<H> h_;
-    int fd_ = -1, port_ = 0;
+    int fd_ = -1, port_ = 0, drop_pct_ = 0;
     std::thread th_;
     std::atomic<bool> stopped_{false};
+    std::mutex dd_mu_;
+    std::condition_variable dd_cv_;
+    std::unordered_map<uint32_t, Slot> slots_;
 };
 
 // ------------------------------------------------------------------------------------ worker
 struct Conn {
     int fd = -1;
     std::mutex mu;
-    Message call(const Message& req) {
-        std::unique_lock<std::mutex> l(mu);
-        send_msg(fd, req);
-        Message rsp;
-        if (!recv_msg(fd, &rsp)) throw std::runtime_error("connection to PS lost");
+    // resend protocol (PS_RESEND=1): only on worker->server connections, whose handlers never block
+    bool resend = false;
+    int timeout_ms = 1000;
+    uint32_t uid = 0, seq = 0;
+    std::string host;
+    int port = 0;
+    std::function<bool(Conn*)> relocate;          // asks the scheduler where this server lives now
+    std::atomic<uint64_t>* retransmits = nullptr;
+
+    static Message& check(Message& rsp) {
         if (rsp.type == kError) throw std::runtime_error("PS error: " + (rsp.arrays.empty() ? std::string("?") : rsp.str(0)));
         return rsp;
+    }
+    void open(const std::string& h, int p, int retries = 600) {
+        host = h; port = p;
+        fd = connect_to(h, p, retries);
+        if (resend) set_recv_timeout(fd, timeout_ms);
+    }
+    Message call(Message& req) {
+        std::unique_lock<std::mutex> l(mu);
+        Message rsp;
+        if (!resend) {
+            send_msg(fd, req);
+            if (!recv_msg(fd, &rsp)) throw std::runtime_error("connection to PS lost");
+            return std::move(check(rsp));
+        }
+        if (++seq == 0) ++seq;
+        req.sig = ((uint64_t)uid << 32) | seq;
+        for (int attempt = 0; attempt <= 10; ++attempt) {
+            if (attempt > 0 && retransmits) ++*retransmits;
+            try {
+                if (fd >= 0) { send_msg(fd, req); if (recv_msg(fd, &rsp)) return std::move(check(rsp)); }
+            } catch (const std::runtime_error& e) {
+                if (strncmp(e.what(), "PS error", 8) == 0) throw;
+            }
+            // timed out, or the peer went away (possibly mid-frame): start over on a fresh connection
+            if (fd >= 0) ::close(fd);
+            fd = -1;
+            try { open(host, port, 5); }
+            catch (...) { if (relocate && relocate(this)) { try { open(host, port, 20); } catch (...) {} } }
+        }
+        throw std::runtime_error("PS request not acknowledged after 10 retransmissions");
     }
 };
 
 struct TensorMeta { int type; size_t len, width; };
 
+// Beat to the scheduler every PS_HEARTBEAT_INTERVAL seconds on a connection of its own (the main
+// scheduler connection may sit in a blocking barrier).  Returns an empty thread when disabled.
+inline std::thread start_heartbeat(const std::string& host, int port, int node_id, std::atomic<bool>* stop) {
+    double interval = atof(env_or("PS_HEARTBEAT_INTERVAL", "0"));
+    if (interval <= 0) return std::thread();
+    return std::thread([=] {
+        int fd = -1;
+        try { fd = connect_to(host, port, 50); } catch (...) { return; }
+        auto us = (long long)(interval * 1e6);
+        while (!*stop) {
+            Message m, r;
+            m.type = kHeartbeat; m.arg0 = node_id;
+            try { send_msg(fd, m); if (!recv_msg(fd, &r)) break; } catch (...) { break; }
+            for (long long t = 0; t < us && !*stop; t += 10000) usleep(10000);
+        }
+        ::close(fd);
+    });
+}
+
 class Worker {
   public:
-    Worker(const std::string& sched_host, int sched_port) {
-        sched_.fd = connect_to(sched_host, sched_port);
+    Worker(const std::string& sched_host, int sched_port) : sched_host_(sched_host), sched_port_(sched_port) {
+        sched_.open(sched_host, sched_port);
         Message req;
         req.type = kRegister; req.arg0 = 0; req.arg1 = 0; req.add_str("worker");
         Message rsp = sched_.call(req);
         rank_ = (int)rsp.arg0;
         nrank_ = (int)rsp.arg1;
+        is_recovery_ = rsp.key == 1;
+        bool resend = atoi(env_or("PS_RESEND", "0")) != 0;
+        int timeout_ms = std::max(1, atoi(env_or("PS_RESEND_TIMEOUT", "1000")));
+        std::random_device rd;
         for (size_t i = 0; i < rsp.arrays.size(); ++i) {
             std::string hp = rsp.str(i);
             size_t c = hp.rfind(':');
             auto conn = std::make_unique<Conn>();
-            conn->fd = connect_to(hp.substr(0, c), atoi(hp.substr(c + 1).c_str()));
+            conn->resend = resend; conn->timeout_ms = timeout_ms; conn->uid = (uint32_t)rd() | 1u;
+            conn->retransmits = &retransmits_;
+            conn->relocate = [this, i](Conn* cn) {
+                Message q; q.type = kGetServers;
+                Message a = sched_.call(q);
+                if (i >= a.arrays.size()) return false;
+                std::string now = a.str(i);
+                size_t k = now.rfind(':');
+                std::string h = now.substr(0, k); int p = atoi(now.substr(k + 1).c_str());
+                if (h == cn->host && p == cn->port) return false;
+                cn->host = h; cn->port = p;
+                return true;
+            };
+            conn->open(hp.substr(0, c), atoi(hp.substr(c + 1).c_str()));
             servers_.push_back(std::move(conn));
         }
+        hb_ = start_heartbeat(sched_host, sched_port, node_id_of(0, rank_), &hb_stop_);
     }
-    ~Worker() { for (auto& s : servers_) ::close(s->fd); ::close(sched_.fd); }
+    ~Worker() {
+        hb_stop_ = true;
+        if (hb_.joinable()) hb_.join();
+        for (auto& s : servers_) if (s->fd >= 0) ::close(s->fd);
+        ::close(sched_.fd);
+    }
+    bool is_recovery() const { return is_recovery_; }
+    std::atomic<uint64_t> retransmits_{0};
     int rank() const { return rank_; }
     int nrank() const { return nrank_; }
     int nservers() const { return (int)servers_.size(); }
@@ -547,6 +715,11 @@ class Worker {
   private:
     Conn sched_;
     std::vector<std::unique_ptr<Conn>> servers_;
+    std::string sched_host_;
+    int sched_port_ = 0;
+    bool is_recovery_ = false;
+    std::atomic<bool> hb_stop_{false};
+    std::thread hb_;
     int rank_ = 0, nrank_ = 1;
     std::mutex mu_;
     std::unordered_map<uint64_t, TensorMeta> meta_;
@@ -557,8 +730,8 @@ static std::unique_ptr<Worker> g_worker;
 static std::unique_ptr<Listener<Scheduler>> g_sched;
 static std::vector<std::unique_ptr<Listener<Server>>> g_servers;
 static thread_local std::string g_err;
-
-static const char* env_or(const char* k, const char* d) { const char* v = getenv(k); return v ? v : d; }
+static std::atomic<bool> g_server_hb_stop{false};
+static std::vector<std::thread> g_server_hb;
 
 }  // namespace hps
 
@@ -588,14 +761,29 @@ HPS_API int hps_start_server(const char* sched_host, int sched_port, const char*
         Message req;
         req.type = kRegister; req.arg0 = 1; req.arg1 = lst->port(); req.add_str(my_host);
         g_servers.push_back(std::move(lst));
-        std::thread([fd, req, srv] {
-            try { Message rsp; send_msg(fd, req); if (recv_msg(fd, &rsp)) srv->set_id((int)rsp.arg0); } catch (...) {}
+        std::string sh = sched_host;
+        g_server_hb_stop = false;
+        g_server_hb.emplace_back([fd, req, srv, sh, sched_port] {
+            int rank = -1;
+            try { Message rsp; send_msg(fd, req); if (recv_msg(fd, &rsp) && rsp.type == kOk) rank = (int)rsp.arg0; } catch (...) {}
             ::close(fd);
-        }).detach();
+            if (rank < 0) return;
+            srv->set_id(rank);
+            std::thread hb = start_heartbeat(sh, sched_port, node_id_of(1, rank), &g_server_hb_stop);
+            if (hb.joinable()) hb.join();
+        });
     });
 }
 HPS_API int hps_wait_servers() { for (auto& s : g_servers) s->wait(); return 0; }
-HPS_API int hps_stop_servers() { for (auto& s : g_servers) s->stop(); g_servers.clear(); return 0; }
+HPS_API int hps_stop_servers() {
+    g_server_hb_stop = true;
+    for (auto& s : g_servers) s->stop();
+    g_servers.clear();
+    // a registration that never completed (scheduler gone) would block join forever: detach those
+    for (auto& t : g_server_hb) if (t.joinable()) t.detach();
+    g_server_hb.clear();
+    return 0;
+}
 
 HPS_API int hps_worker_init(const char* sched_host, int sched_port) { HPS_TRY(g_worker = std::make_unique<Worker>(sched_host, sched_port)); }
 HPS_API int hps_worker_finalize() { g_worker.reset(); return 0; }
@@ -646,6 +834,25 @@ HPS_API int hps_preduce_get_partner(uint64_t key, int want, float wait_ms, int* 
 }
 HPS_API int hps_start_record() { if (g_worker) g_worker->record_ = true; return 0; }
 HPS_API int hps_get_loads(uint64_t* sent, uint64_t* recv) { if (!g_worker) return -1; *sent = g_worker->sent_; *recv = g_worker->recv_; return 0; }
+
+// ---- failure detection -------------------------------------------------------------------------
+// Node ids (ps-lite convention: server r -> 8+2r, worker r -> 9+2r) that registered with the
+// scheduler at host:port and have not sent a heartbeat for `timeout_s` seconds.  Callable from any
+// process (opens its own connection).  reference: Postoffice::GetDeadNodes, postoffice.cc:201-221.
+HPS_API int hps_query_dead_nodes(const char* sched_host, int sched_port, double timeout_s, int* out, int cap, int* n_out) {
+    HPS_TRY({
+        Conn c;
+        c.open(sched_host, sched_port, 50);
+        Message q; q.type = kGetDeadNodes; q.arg0 = (int64_t)(timeout_s * 1000.0);
+        Message r = c.call(q);
+        ::close(c.fd);
+        size_t k = r.count<int>(0);
+        *n_out = (int)k;
+        for (size_t i = 0; i < k && (int)i < cap; ++i) out[i] = r.data<int>(0)[i];
+    });
+}
+HPS_API int hps_is_recovery() { return g_worker && g_worker->is_recovery() ? 1 : 0; }
+HPS_API uint64_t hps_num_retransmits() { return g_worker ? g_worker->retransmits_.load() : 0; }
 
 // HET-cache RPCs used by cache.cc ---------------------------------------------------------------
 namespace hps {

@@ -70,6 +70,18 @@ def stop_local_servers():
     _lib().hps_stop_servers()
 
 
+def get_dead_nodes(timeout: float = 60.0, host: Optional[str] = None, port: Optional[int] = None):
+    """Ids of registered nodes (server r -> 8+2r, worker r -> 9+2r) whose last heartbeat is older
+    than ``timeout`` seconds.  Needs ``PS_HEARTBEAT_INTERVAL`` > 0 in the node processes.
+    reference: Postoffice::GetDeadNodes (ps-lite/src/postoffice.cc:201-221)."""
+    h, p, _, _ = _env()
+    out = (ctypes.c_int * 1024)()
+    n = ctypes.c_int(0)
+    _chk(_lib().hps_query_dead_nodes((host or h).encode(), int(port or p), ctypes.c_double(timeout), out, 1024,
+                                     ctypes.byref(n)), 'get_dead_nodes')
+    return [out[i] for i in range(min(n.value, 1024))]
+
+
 class PSWorker(object):
     """Worker-side agent.  Method names follow the reference C API."""
 
@@ -108,6 +120,19 @@ class PSWorker(object):
 
     def rank(self) -> int:
         return int(self.lib.hps_rank())
+
+    def is_recovery(self) -> bool:
+        """True when this worker registered after the cluster was complete and took over the rank
+        of a dead worker (reference ``is_recovery``, ps-lite/src/van.cc:132-162)."""
+        return bool(self.lib.hps_is_recovery())
+
+    def num_retransmits(self) -> int:
+        """Requests sent again after ``PS_RESEND_TIMEOUT`` ms without a reply (``PS_RESEND=1``)."""
+        self.lib.hps_num_retransmits.restype = ctypes.c_uint64
+        return int(self.lib.hps_num_retransmits())
+
+    def get_dead_nodes(self, timeout: float = 60.0):
+        return get_dead_nodes(timeout)
 
     def nrank(self) -> int:
         return int(self.lib.hps_nrank())

@@ -37,3 +37,95 @@ def test_ps_scheduler_2servers_2workers():
         finally:
             for p in procs:
                 p.terminate()
+
+
+def _spawn(code, env, **kw):
+    return subprocess.Popen([sys.executable, '-c', code], env=env, **kw)
+
+
+def test_ps_resend_survives_dropped_messages():
+    """PS_DROP_MSG loses requests and replies at the server; PS_RESEND retransmits and the server's
+    reply cache keeps pushes exactly-once (reference: resender.h:15-148, van.cc:334-336)."""
+    port = _free_port()
+    env = dict(os.environ, DMLC_PS_ROOT_URI='127.0.0.1', DMLC_PS_ROOT_PORT=str(port), DMLC_NUM_WORKER='1',
+               DMLC_NUM_SERVER='1', PYTHONPATH=ROOT + os.pathsep + os.environ.get('PYTHONPATH', ''))
+    procs = []
+    try:
+        procs.append(_spawn('import hetu_61a7_b200.launcher as l; l.start_sched()', env))
+        time.sleep(0.5)
+        procs.append(_spawn('import hetu_61a7_b200.launcher as l; l.start_server()', dict(env, PS_DROP_MSG='25')))
+        w = subprocess.Popen([sys.executable, os.path.join(ROOT, 'tests', 'ps_fault_worker.py')],
+                             env=dict(env, PS_RESEND='1', PS_RESEND_TIMEOUT='60'),
+                             stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        out = w.communicate(timeout=300)[0]
+        assert w.returncode == 0 and 'OK' in out, out[-3000:]
+    finally:
+        for p in procs:
+            p.terminate()
+
+
+def test_ps_heartbeat_dead_node_and_recovery():
+    """A server that stops beating shows up in get_dead_nodes; a replacement server that registers
+    late takes over its rank and the worker finds it through the scheduler
+    (reference: van.cc:132-162,567-579, postoffice.cc:201-221)."""
+    port = _free_port()
+    env = dict(os.environ, DMLC_PS_ROOT_URI='127.0.0.1', DMLC_PS_ROOT_PORT=str(port), DMLC_NUM_WORKER='1',
+               DMLC_NUM_SERVER='1', PS_HEARTBEAT_INTERVAL='0.1', PS_HEARTBEAT_TIMEOUT='0.6',
+               PS_RESEND='1', PS_RESEND_TIMEOUT='200',
+               PYTHONPATH=ROOT + os.pathsep + os.environ.get('PYTHONPATH', ''))
+    code = r'''
+import os, sys, time, subprocess, numpy as np
+sys.path.insert(0, %r)
+from hetu_61a7_b200.parallel.ps import PSWorker, get_dead_nodes
+w = PSWorker.from_env()
+w.InitTensor(1, 0, 16, 1, 0, 2.0, 2.0, 1)
+assert np.allclose(w.Pull(1), 2.0)
+assert get_dead_nodes(0.6) == []
+print('READY', flush=True)
+sys.stdin.readline()                       # parent kills the server, then pokes us
+deadline = time.time() + 20
+dead = []
+while time.time() < deadline and 8 not in dead:
+    time.sleep(0.2); dead = get_dead_nodes(0.6)
+assert dead == [8], dead                  # server rank 0; this worker (id 9) still beats
+print('DEAD', flush=True)
+sys.stdin.readline()                       # parent has started the replacement server
+w.InitTensor(1, 0, 16, 1, 0, 5.0, 5.0, 1)  # state is not restored: re-initialise, as after LoadParam
+assert np.allclose(w.Pull(1), 5.0)
+assert get_dead_nodes(0.6) == []
+print('OK', flush=True)
+w.finalize()
+''' % ROOT
+    procs = []
+    try:
+        procs.append(_spawn('import hetu_61a7_b200.launcher as l; l.start_sched()', env))
+        time.sleep(0.5)
+        srv = _spawn('import hetu_61a7_b200.launcher as l; l.start_server()', env)
+        procs.append(srv)
+        w = subprocess.Popen([sys.executable, '-c', code], env=env, stdin=subprocess.PIPE, stdout=subprocess.PIPE,
+                             stderr=subprocess.STDOUT, text=True)
+        procs.append(w)
+
+        def expect(tag):
+            lines = []
+            while True:
+                line = w.stdout.readline()
+                if not line:
+                    raise AssertionError('worker ended before %s:\n%s' % (tag, ''.join(lines)[-3000:]))
+                lines.append(line)
+                if line.strip() == tag:
+                    return
+        expect('READY')
+        srv.kill()
+        srv.wait()
+        w.stdin.write('\n'); w.stdin.flush()
+        expect('DEAD')
+        procs.append(_spawn('import hetu_61a7_b200.launcher as l; l.start_server()', env))
+        time.sleep(0.5)
+        w.stdin.write('\n'); w.stdin.flush()
+        expect('OK')
+        assert w.wait(timeout=60) == 0
+    finally:
+        for p in procs:
+            if p.poll() is None:
+                p.terminate()
