@@ -129,3 +129,15 @@ w.finalize()
         for p in procs:
             if p.poll() is None:
                 p.terminate()
+
+
+def test_cpu_ring_allreduce_three_ranks():
+    """Legacy CPU data-parallel path: TCP ring reduce-scatter + all-gather
+    (reference src/communication/c_communication_nthread.cc)."""
+    base = _free_port()
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get('PYTHONPATH', ''), OMP_NUM_THREADS='2')
+    ws = [subprocess.Popen([sys.executable, os.path.join(ROOT, 'tests', 'ring_worker.py'), str(r), '3', str(base)], env=env,
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for r in range(3)]
+    outs = [w.communicate(timeout=120)[0] for w in ws]
+    for w, o in zip(ws, outs):
+        assert w.returncode == 0 and 'OK' in o, o[-3000:]
