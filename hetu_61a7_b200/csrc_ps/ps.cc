@@ -29,6 +29,7 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <cmath>
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
@@ -60,6 +61,33 @@ struct Param {
     std::vector<float> data;
     std::vector<int64_t> ver;
     std::shared_mutex mu;
+    // optional server-side optimizer (reference include/ps/server/optimizer.h:36-357): when set, pushed
+    // values are gradients.  0 none (server does +=), 1 SGD, 2 Momentum, 3 Nesterov, 4 AdaGrad, 5 Adam.
+    int opt = 0;
+    double lr = 0, h0 = 0, h1 = 0, eps = 1e-7;
+    std::vector<float> s1, s2;          // velocity / accumulator / m, v
+    std::vector<int64_t> step;          // Adam step per element block (one per row for 2-D, one for dense)
+    void apply(size_t off, const float* g, size_t n, size_t row) {
+        float* w = data.data() + off;
+        switch (opt) {
+            case 0: for (size_t i = 0; i < n; ++i) w[i] += g[i]; break;
+            case 1: for (size_t i = 0; i < n; ++i) w[i] -= (float)lr * g[i]; break;
+            case 2: { float* v = s1.data() + off; for (size_t i = 0; i < n; ++i) { v[i] = (float)h0 * v[i] - (float)lr * g[i]; w[i] += v[i]; } break; }
+            case 3: { float* v = s1.data() + off; for (size_t i = 0; i < n; ++i) { float nv = (float)h0 * v[i] - (float)lr * g[i]; w[i] += (float)h0 * nv - (float)lr * g[i]; v[i] = nv; } break; }
+            case 4: { float* a = s1.data() + off; for (size_t i = 0; i < n; ++i) { a[i] += g[i] * g[i]; w[i] -= (float)lr * g[i] / (std::sqrt(a[i]) + (float)eps); } break; }
+            case 5: {
+                float* m = s1.data() + off; float* v = s2.data() + off;
+                int64_t t = ++step[row];
+                double c1 = 1.0 - std::pow(h0, (double)t), c2 = 1.0 - std::pow(h1, (double)t);
+                for (size_t i = 0; i < n; ++i) {
+                    m[i] = (float)h0 * m[i] + (1.f - (float)h0) * g[i];
+                    v[i] = (float)h1 * v[i] + (1.f - (float)h1) * g[i] * g[i];
+                    w[i] -= (float)(lr * (m[i] / c1) / (std::sqrt(v[i] / c2) + eps));
+                }
+                break;
+            }
+        }
+    }
 };
 
 class Server {
@@ -108,6 +136,15 @@ class Server {
         p->data.resize(n);
         if (p->type == 2) p->ver.assign(p->len, 0);
         int init_type = (int)h[3];
+        p->opt = (int)h[4];
+        if (p->opt != 0 && req.arrays.size() > 3) {
+            const double* o = req.data<double>(3);
+            size_t no = req.count<double>(3);
+            p->lr = no > 0 ? o[0] : 0; p->h0 = no > 1 ? o[1] : 0; p->h1 = no > 2 ? o[2] : 0;
+            if (no > 3 && o[3] > 0) p->eps = o[3];
+            if (p->opt >= 2) p->s1.assign(n, 0.f);
+            if (p->opt == 5) { p->s2.assign(n, 0.f); p->step.assign(p->type == 0 ? 1 : p->len, 0); }
+        }
         std::mt19937_64 rng(seed * 1000003ull + (uint64_t)id_.load());
         if (init_type == 0) {
             std::fill(p->data.begin(), p->data.end(), (float)ab[0]);
@@ -135,7 +172,7 @@ class Server {
         std::unique_lock<std::shared_mutex> l(p->mu);
         const float* g = req.data<float>(0);
         size_t n = std::min(p->data.size(), req.count<float>(0));
-        for (size_t i = 0; i < n; ++i) p->data[i] += g[i];
+        p->apply(0, g, n, 0);
     }
     void sparse_pull(const Message& req, size_t off_idx, Message* rsp) {
         auto p = get(req.key);
@@ -158,8 +195,7 @@ class Server {
         for (size_t i = 0; i < n; ++i) {
             int64_t r = rows[i];
             if (r < 0 || (size_t)r >= p->len) continue;
-            float* dst = &p->data[(size_t)r * w];
-            for (size_t j = 0; j < w; ++j) dst[j] += g[i * w + j];
+            p->apply((size_t)r * w, g + i * w, w, (size_t)r);
         }
     }
     // arrays: rows(i64), versions(i64); arg0 = bound.  response: idx(i64), versions(i64), data(f32)
@@ -562,16 +598,18 @@ class Worker {
         *beg = total * (size_t)s / S;
         *end = total * (size_t)(s + 1) / S;
     }
-    void init_tensor(uint64_t key, int type, size_t len, size_t width, int init_type, double a, double b, uint64_t seed) {
+    void init_tensor(uint64_t key, int type, size_t len, size_t width, int init_type, double a, double b, uint64_t seed,
+                     int opt_type = 0, const double* opt_args = nullptr, int n_opt = 0) {
         { std::unique_lock<std::mutex> l(mu_); meta_[key] = {type, len, width}; }
         for (int s = 0; s < nservers(); ++s) {
             size_t beg, end;
             shard(len, s, &beg, &end);
             Message req;
             req.type = kParamInit; req.key = key;
-            int64_t h[5] = {type, (int64_t)(end - beg), (int64_t)width, init_type, 0};
+            int64_t h[5] = {type, (int64_t)(end - beg), (int64_t)width, init_type, opt_type};
             double ab[2] = {a, b};
             req.add(h, 5); req.add(ab, 2); req.add(&seed, 1);
+            if (opt_type != 0 && opt_args && n_opt > 0) req.add(opt_args, (size_t)n_opt);
             count(req, servers_[s]->call(req));
         }
         barrier(0);
@@ -794,6 +832,12 @@ HPS_API int hps_nservers() { return g_worker ? g_worker->nservers() : 0; }
 // ---- PS functions (synchronous; *_async variants enqueue and are joined by hps_wait(key)) -------
 HPS_API int hps_init_tensor(uint64_t key, int type, uint64_t len, uint64_t width, int init_type, double a, double b, uint64_t seed) {
     HPS_TRY(g_worker->init_tensor(key, type, len, width, init_type, a, b, seed));
+}
+// same, with a server-side optimizer: pushes are then gradients.  opt_type 1 SGD, 2 Momentum, 3 Nesterov,
+// 4 AdaGrad, 5 Adam; opt_args = {lr, h0 (momentum / beta1), h1 (beta2), eps}
+HPS_API int hps_init_tensor_opt(uint64_t key, int type, uint64_t len, uint64_t width, int init_type, double a, double b, uint64_t seed,
+                                int opt_type, const double* opt_args, int n_opt) {
+    HPS_TRY(g_worker->init_tensor(key, type, len, width, init_type, a, b, seed, opt_type, opt_args, n_opt));
 }
 HPS_API int hps_pull(uint64_t key, float* out) { HPS_TRY(g_worker->dense(kDensePull, key, nullptr, out)); }
 HPS_API int hps_push(uint64_t key, const float* grad) { HPS_TRY(g_worker->dense(kDensePush, key, grad, nullptr)); }

@@ -140,6 +140,17 @@ class PSWorker(object):
     # -- tensors ------------------------------------------------------------------------------
     def InitTensor(self, node_id, param_type, length, width, init_type, a, b, seed, opt=None):
         self._meta[int(node_id)] = (int(param_type), int(length), int(width))
+        if opt is not None:
+            # server-side optimizer: (kind, [lr, h0, h1, eps]); pushes to this tensor are then gradients
+            # (reference ps-lite include/ps/server/optimizer.h; the stock path keeps "server does +=")
+            kind, args = opt
+            kinds = {'sgd': 1, 'momentum': 2, 'nesterov': 3, 'adagrad': 4, 'adam': 5}
+            code = kinds[kind.lower()] if isinstance(kind, str) else int(kind)
+            arr = (ctypes.c_double * len(args))(*[float(v) for v in args])
+            _chk(self.lib.hps_init_tensor_opt(ctypes.c_uint64(node_id), int(param_type), ctypes.c_uint64(int(length)),
+                                              ctypes.c_uint64(int(width)), int(init_type), ctypes.c_double(a), ctypes.c_double(b),
+                                              ctypes.c_uint64(int(seed) & 0xFFFFFFFFFFFFFFFF), code, arr, len(args)), 'InitTensor')
+            return
         _chk(self.lib.hps_init_tensor(ctypes.c_uint64(node_id), int(param_type), ctypes.c_uint64(int(length)),
                                       ctypes.c_uint64(int(width)), int(init_type), ctypes.c_double(a),
                                       ctypes.c_double(b), ctypes.c_uint64(int(seed) & 0xFFFFFFFFFFFFFFFF)), 'InitTensor')

@@ -1,0 +1,49 @@
+"""Worker for the server-side optimizer test: one step sequence per optimizer against numpy."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from hetu_61a7_b200.parallel.ps import PSWorker          # noqa: E402
+
+w = PSWorker.from_env()
+rng = np.random.RandomState(0)
+grads = [rng.standard_normal(64).astype(np.float32) for _ in range(4)]
+lr, mom, b1, b2, eps = 0.1, 0.9, 0.9, 0.999, 1e-7
+
+
+def oracle(kind):
+    x = np.full(64, 1.0)
+    v = np.zeros(64); m = np.zeros(64); acc = np.zeros(64)
+    for t, g in enumerate(grads, 1):
+        g = g.astype(np.float64)
+        if kind == 'sgd':
+            x -= lr * g
+        elif kind == 'momentum':
+            v = mom * v - lr * g; x += v
+        elif kind == 'nesterov':
+            v = mom * v - lr * g; x += mom * v - lr * g
+        elif kind == 'adagrad':
+            acc += g * g; x -= lr * g / (np.sqrt(acc) + eps)
+        elif kind == 'adam':
+            m = b1 * m + (1 - b1) * g; v = b2 * v + (1 - b2) * g * g
+            x -= lr * (m / (1 - b1 ** t)) / (np.sqrt(v / (1 - b2 ** t)) + eps)
+    return x
+
+
+for key, (kind, args) in enumerate([('sgd', [lr]), ('momentum', [lr, mom]), ('nesterov', [lr, mom]),
+                                    ('adagrad', [lr, 0, 0, eps]), ('adam', [lr, b1, b2, eps])], start=20):
+    w.InitTensor(key, 0, 64, 1, 0, 1.0, 1.0, 0, opt=(kind, args))
+    for g in grads:
+        w.Push(key, g)
+    np.testing.assert_allclose(w.Pull(key), oracle(kind), rtol=2e-5, atol=2e-5, err_msg=kind)
+# sparse rows: Adam keeps a step count per row
+w.InitTensor(40, 1, 10, 4, 0, 0.0, 0.0, 0, opt=('adam', [lr, b1, b2, eps]))
+w.SparsePush(40, np.array([2, 7]), np.ones((2, 4), np.float32))
+w.SparsePush(40, np.array([2]), np.ones((1, 4), np.float32))
+rows = w.SparsePull(40, np.array([2, 7, 3]))
+assert np.allclose(rows[0], -2 * lr, atol=1e-5) and np.allclose(rows[1], -lr, atol=1e-5) and np.allclose(rows[2], 0)
+print('OK')
+w.finalize()

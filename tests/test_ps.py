@@ -141,3 +141,24 @@ def test_cpu_ring_allreduce_three_ranks():
     outs = [w.communicate(timeout=120)[0] for w in ws]
     for w, o in zip(ws, outs):
         assert w.returncode == 0 and 'OK' in o, o[-3000:]
+
+
+def test_ps_server_side_optimizers():
+    """SGD / Momentum / Nesterov / AdaGrad / Adam applied by the server to pushed gradients
+    (reference ps-lite include/ps/server/optimizer.h:36-357), against numpy."""
+    port = _free_port()
+    env = dict(os.environ, DMLC_PS_ROOT_URI='127.0.0.1', DMLC_PS_ROOT_PORT=str(port), DMLC_NUM_WORKER='1',
+               DMLC_NUM_SERVER='2', PYTHONPATH=ROOT + os.pathsep + os.environ.get('PYTHONPATH', ''))
+    procs = []
+    try:
+        procs.append(_spawn('import hetu_61a7_b200.launcher as l; l.start_sched()', env))
+        time.sleep(0.5)
+        for _ in range(2):
+            procs.append(_spawn('import hetu_61a7_b200.launcher as l; l.start_server()', env))
+        w = subprocess.Popen([sys.executable, os.path.join(ROOT, 'tests', 'ps_opt_worker.py')], env=env,
+                             stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        out = w.communicate(timeout=120)[0]
+        assert w.returncode == 0 and 'OK' in out, out[-3000:]
+    finally:
+        for p in procs:
+            p.terminate()
