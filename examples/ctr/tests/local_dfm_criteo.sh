@@ -1,0 +1,6 @@
+#!/bin/bash
+# reference: examples/ctr/tests/local_dfm_criteo.sh
+workdir=$(cd "$(dirname "$0")"; pwd)
+mainpy=${workdir}/../run_hetu.py
+heturun=${workdir}/../../../bin/heturun
+python ${mainpy} --model dfm_criteo --nepoch ${1:-1} --all

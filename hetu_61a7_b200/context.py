@@ -205,7 +205,8 @@ def get_launch_config_by_traverse_nodes(node_list, default_ctx: DeviceGroup):
         if rc is not None and not isinstance(node, (OptimizerOp, DataloaderOp)):
             devices.update(rc.flat_devices())
         stack.extend(node.inputs)
-    launchPS = default_ctx.server_num > 0 or any(s == 'PS' for s in node_strategy.values())
+    # a group of CPU contexts only (e.g. ``with ht.context(ht.cpu(0))``) is a local CPU run, not a server without workers
+    launchPS = (default_ctx.server_num > 0 and default_ctx.worker_num > 0) or any(s == 'PS' for s in node_strategy.values())
     launchMPI = ((not launchPS) and min_worker_num > 1) or any(
         s == 'AllReduce' for s in node_strategy.values())
     return launchMPI, launchPS, node_strategy, devices, min_worker_num
