@@ -7,7 +7,7 @@ from hetu_61a7_b200 import (optim, lr, init, layers, dist, ndarray, stream, data
 
 for _name in ('layers', 'optimizer', 'lr_scheduler', 'initializers', 'ndarray', 'stream', 'context',
               'dataloader', 'distributed_strategies', 'ops', 'graph', 'parallel', 'utils', 'models',
-              'launcher', 'runner', 'cpu_links', 'onnx', 'graphboard', 'memory_pool'):
+              'launcher', 'runner', 'cpu_links', 'gpu_links', 'onnx', 'graphboard', 'memory_pool'):
     try:
         _mod = __import__('hetu_61a7_b200.' + _name, fromlist=['_'])
         _sys.modules['hetu.' + _name] = _mod

@@ -38,3 +38,4 @@ from .parallel.cstable import CacheSparseTable
 from .parallel.preduce import PartialReduce
 
 __version__ = '0.1.0'
+from . import gpu_links
