@@ -33,13 +33,27 @@ def main():
     ap.add_argument('--iters', type=int, default=200, help='synthetic batches per epoch')
     ap.add_argument('--all', action='store_true', help='report AUC')
     ap.add_argument('--cpu', action='store_true')
+    ap.add_argument('--data-dir', default=None, help='directory with Criteo train.csv / train.txt (or the processed .npy files); '
+                    'synthetic Criteo-shaped data when omitted')
+    ap.add_argument('--head', type=int, default=0, help='with --data-dir: use only the first N rows')
     args = ap.parse_args()
 
     comm = ht.wrapped_mpi_nccl_init() if args.comm in ('Hybrid', 'AllReduce') else None
     rank = comm.rank if comm is not None else int(os.environ.get('DMLC_WORKER_ID', os.environ.get('RANK', 0)))
     ctx = ht.cpu(0) if args.cpu else ht.gpu(int(os.environ.get('LOCAL_RANK', 0)))
     n = args.iters * args.batch_size
-    dense_v, sparse_v, label_v = ht.data.criteo_synthetic(n, vocab=args.vocab, seed=rank)
+    if args.data_dir:
+        from hetu_61a7_b200.utils import ctr_data
+        if args.head:
+            dense_v, sparse_v, label_v = ctr_data.process_head_criteo_data(args.data_dir, nrows=args.head, return_val=False)
+        else:
+            dense_v, sparse_v, label_v = ctr_data.process_all_criteo_data(args.data_dir, return_val=False)
+        nw = int(os.environ.get('WORLD_SIZE', os.environ.get('DMLC_NUM_WORKER', 1)))
+        dense_v, sparse_v, label_v = dense_v[rank::nw], sparse_v[rank::nw].astype(np.int64), label_v[rank::nw].astype(np.float32)
+        args.vocab = int(sparse_v.max()) + 1 if args.head else args.vocab
+        n = len(label_v) // args.batch_size * args.batch_size
+    else:
+        dense_v, sparse_v, label_v = ht.data.criteo_synthetic(n, vocab=args.vocab, seed=rank)
     dense = ht.dataloader_op([ht.Dataloader(dense_v, args.batch_size, 'train')])
     sparse = ht.dataloader_op([ht.Dataloader(sparse_v, args.batch_size, 'train', dtype=np.int64)])
     y_ = ht.dataloader_op([ht.Dataloader(label_v, args.batch_size, 'train')])

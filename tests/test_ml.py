@@ -281,3 +281,23 @@ def test_parallel_models_over_parameter_server(tmp_path):
     np.testing.assert_array_equal(t0, t1)
     blocks = t0.reshape(3, 3, 10).sum(axis=2)
     assert np.all(blocks.max(axis=1) > 0.85), blocks
+
+
+@pytest.mark.gpu
+def test_knn_gpu_distance_gemm_matches_cpu():
+    """KNN(device='gpu'): distances from the tcgen05 GEMM, same votes as the sparse CPU core
+    (rows whose k-th and (k+1)-th neighbour are within tf32 rounding of each other may differ)."""
+    rng = np.random.RandomState(7)
+    Xl = sp.random(3000, 200, density=0.2, random_state=rng, format='csr', dtype=np.float32)
+    yl = rng.randint(0, 5, 3000).astype(np.float32)
+    Xq = sp.random(500, 200, density=0.2, random_state=rng, format='csr', dtype=np.float32)
+    cpu = KNN(num_label=5, num_neighbor=9, device='cpu').predict_score((Xl, yl), Xq)
+    gpu = KNN(num_label=5, num_neighbor=9, device='gpu').predict_score((Xl, yl), Xq)
+    assert gpu.shape == cpu.shape and np.all(gpu.sum(1) == 9)
+    assert np.mean(np.abs(gpu - cpu).sum(1) == 0) > 0.97
+    small_l = sp.random(400, 30, density=0.3, random_state=rng, format='csr', dtype=np.float32)
+    small_q = sp.random(50, 30, density=0.3, random_state=rng, format='csr', dtype=np.float32)
+    ys = rng.randint(0, 3, 400).astype(np.float32)
+    a = KNN(num_label=3, num_neighbor=5, device='cpu').predict_score((small_l, ys), small_q)
+    b = KNN(num_label=3, num_neighbor=5, device='gpu').predict_score((small_l, ys), small_q)      # exact fp32 path (K <= 64)
+    assert np.mean(np.abs(a - b).sum(1) == 0) > 0.97
