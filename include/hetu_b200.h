@@ -18,6 +18,37 @@ extern "C" {
 #endif
 
 /* ---- runtime ------------------------------------------------------------------ */
+/* Array / stream / event ABI: reference src/common/dlarray.h:22-65, c_runtime_api.cc:93-142,
+ * src/cuda_common/gpu_runtime.cc:61-118.  Arrays are dense row-major fp32; device arrays come from
+ * the device's stream-ordered memory pool, host arrays are pinned. */
+typedef enum { kDLCPU = 1, kDLGPU = 2 } DLDeviceType;
+typedef struct { int device_id; int device_type; } DLContext;
+typedef struct { void* data; DLContext ctx; int ndim; long long* shape; long long* stride; } DLArray;
+typedef DLArray* DLArrayHandle;
+typedef struct { int device_id; void* handle; } DLStream;
+typedef DLStream* DLStreamHandle;
+typedef struct { int device_id; void* handle; } DLEvent;
+typedef DLEvent* DLEventHandle;
+int DLArrayAlloc(const long long* shape, int ndim, DLContext ctx, DLArrayHandle* out);
+int DLArrayFree(DLArrayHandle handle);
+/* any of host->device, device->host, device->device (same or peer GPU), host->host; stream NULL = blocking */
+int DLArrayCopyFromTo(DLArrayHandle from, DLArrayHandle to, DLStreamHandle stream);
+int DLStreamCreate(int device_id, DLStreamHandle* out);
+int DLStreamDestroy(DLStreamHandle handle);
+int DLStreamSync(DLStreamHandle handle);
+int DLEventCreate(int device_id, DLEventHandle* out);
+int DLEventDestroy(DLEventHandle handle);
+int DLEventRecord(DLStreamHandle stream, DLEventHandle event);
+int DLEventSync(DLEventHandle event);
+int DLStreamWaitEvent(DLStreamHandle stream, DLEventHandle event);
+int DLEventElapsedTime(DLEventHandle start, DLEventHandle end, float* ms);
+/* workspace chunk cache: reference src/cuda_common/gpu_chunk.cc:18-86 (find_chunk / del_chunk).
+ * hetu_find_chunk returns NULL on failure; hetu_del_chunk returns the chunk to the cache. */
+void* hetu_find_chunk(size_t bytes, int device_id);
+int hetu_del_chunk(void* ptr, int device_id);
+size_t hetu_chunk_cache_bytes(int device_id);
+int hetu_chunk_cache_release(int device_id);
+
 const char* hetu_last_error(void);
 int hetu_version(void);
 /* *p += 1 on the device (step counters read by dropout / Adam; graph-capturable). */
