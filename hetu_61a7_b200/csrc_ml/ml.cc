@@ -877,6 +877,32 @@ HML_API int hml_gbdt_predict(void* h, const int64_t* indptr, const int32_t* indi
 HML_API int hml_gbdt_save(void* h, const char* path) { HML_TRY(gbdt_save(*static_cast<Gbdt*>(h), path)); }
 HML_API int hml_gbdt_load(void* h, const char* path) { HML_TRY(gbdt_load(*static_cast<Gbdt*>(h), path)); }
 
+// Candidate cuts and the bin of every stored entry, for trainers that run elsewhere (the device GBDT):
+// off [dim + 1] offsets into cut_vals (capacity `cap`); returns the number of cuts, or -1 - needed when cap is short.
+HML_API int64_t hml_gbdt_cuts(const int64_t* indptr, const int32_t* indices, const float* vals, int64_t n, int64_t dim,
+                              int num_split, int64_t* off, float* cut_vals, int64_t cap) {
+    try {
+        Cuts c = build_cuts(Csr{indptr, indices, vals, n}, dim, num_split, nullptr);
+        if ((int64_t)c.vals.size() > cap) return -1 - (int64_t)c.vals.size();
+        std::copy(c.off.begin(), c.off.end(), off);
+        std::copy(c.vals.begin(), c.vals.end(), cut_vals);
+        return (int64_t)c.vals.size();
+    } catch (const std::exception& e) { g_err = e.what(); return INT64_MIN; }
+}
+HML_API int hml_gbdt_bins(const int64_t* indptr, const int32_t* indices, const float* vals, int64_t n, int64_t dim,
+                          const int64_t* off, const float* cut_vals, uint8_t* bins) {
+    HML_TRY({
+        for (int64_t i = 0; i < n; ++i)
+            for (int64_t q = indptr[i]; q < indptr[i + 1]; ++q) {
+                int32_t f = indices[q];
+                if (f >= dim) { bins[q] = 0; continue; }
+                const float* b = cut_vals + off[f];
+                const float* e = cut_vals + off[f + 1];
+                bins[q] = (uint8_t)(std::lower_bound(b, e, vals[q]) - b);
+            }
+    });
+}
+
 HML_API int hml_knn_predict(const int64_t* lptr, const int32_t* lidx, const float* lval, const float* labels, int64_t nl,
                             const int64_t* qptr, const int32_t* qidx, const float* qval, int64_t nq, int64_t dim, int k,
                             int num_label, float* out) {

@@ -29,7 +29,11 @@ class GBDT(SupervisedMLBase):
                  ins_sp_ratio: float = 1.0, feat_sp_ratio: float = 1.0, is_regression: bool = False, num_label: int = 2,
                  num_round: int = 10, learning_rate: float = 0.1, min_split_gain: float = 0.0, min_node_ins: int = 1024,
                  min_child_weight: float = 0, reg_alpha: float = 0, reg_lambda: float = 0, max_leaf_weight: float = 0,
-                 multi_tree: bool = False, loss: str = 'auto', metrics: str = 'auto', parallel=False, aux_args=None):
+                 multi_tree: bool = False, loss: str = 'auto', metrics: str = 'auto', parallel=False, aux_args=None,
+                 device: str = 'auto'):
+        """``device``: 'cpu' (native OpenMP trainer), 'gpu' (level-at-a-time trainer on the CUDA kernels of
+        csrc/gbdt.cu; level-wise scalar-leaf trees) or 'auto' (GPU for large inputs when one is present)."""
+        assert device in ('auto', 'cpu', 'gpu')
         assert max_depth > 0, 'Maximum tree depth should be positive'
         if max_node_num == -1:
             max_node_num = (2 ** (max_depth + 1)) - 1
@@ -53,6 +57,7 @@ class GBDT(SupervisedMLBase):
                          reg_alpha=reg_alpha, reg_lambda=reg_lambda, max_leaf_weight=max_leaf_weight, multi_tree=multi_tree,
                          loss=loss, metrics=metrics, parallel=parallel, majority_voting=self._MAJORITY)
         args.setdefault('seed', 42)
+        args['device'] = device
         super().__init__(args)
         self._handle = None
 
@@ -69,7 +74,26 @@ class GBDT(SupervisedMLBase):
         vals = (ctypes.c_double * len(_ORDER))(*[float(self._args[k]) for k in _ORDER])
         self._handle = C.lib().hml_gbdt_create(vals, len(_ORDER))
 
+    def _on_gpu(self, train: Dataset) -> bool:
+        mode = self._args.get('device', 'auto')
+        if mode == 'cpu' or self._args.get('parallel', False):
+            return False
+        import torch
+        from . import _gbdt_gpu
+        if not torch.cuda.is_available() or not _gbdt_gpu.supported(self._args):
+            if mode == 'gpu':
+                raise RuntimeError("GBDT(device='gpu') needs a CUDA device and level-wise scalar-leaf trees "
+                                   "(leafwise=False; multi_tree=True for more than two labels)")
+            return False
+        return mode == 'gpu' or train.X.indices.size >= (1 << 22)
+
     def _fit(self, train: Dataset, valid: Optional[Dataset]) -> None:
+        self._gpu_curve = None
+        if self._on_gpu(train):
+            from . import _gbdt_gpu
+            _gbdt_gpu.fit(self, train, train.get_max_dim())
+            self._log_metrics('fit', train, valid)
+            return
         comm = self._comm()
         self._new_handle()
         dim = train.get_max_dim()
@@ -97,6 +121,8 @@ class GBDT(SupervisedMLBase):
 
     def train_loss_curve(self) -> np.ndarray:
         """Mean training loss after every boosting round."""
+        if getattr(self, '_gpu_curve', None) is not None:
+            return self._gpu_curve
         out = (ctypes.c_double * int(self._args['num_round']))()
         n = C.lib().hml_gbdt_round_metric(ctypes.c_void_p(self._handle), out, len(out))
         return np.array(out[:n])
@@ -138,10 +164,11 @@ class RandomForest(GBDT):
                  ins_sp_ratio: float = 0.3, feat_sp_ratio: float = 0.3, is_regression: bool = False, num_label: int = 2,
                  num_round: int = 100, learning_rate: float = 0.1, min_split_gain: float = 0.0, min_node_ins: int = 1024,
                  min_child_weight: float = 0, reg_alpha: float = 0, reg_lambda: float = 0, max_leaf_weight: float = 0,
-                 multi_tree: bool = False, loss: str = 'auto', metrics: str = 'auto', parallel=False, aux_args=None):
+                 multi_tree: bool = False, loss: str = 'auto', metrics: str = 'auto', parallel=False, aux_args=None,
+                 device: str = 'auto'):
         super().__init__(max_depth, max_node_num, leafwise, num_split, ins_sp_ratio, feat_sp_ratio, is_regression, num_label,
                          num_round, learning_rate, min_split_gain, min_node_ins, min_child_weight, reg_alpha, reg_lambda,
-                         max_leaf_weight, multi_tree, loss, metrics, parallel, aux_args)
+                         max_leaf_weight, multi_tree, loss, metrics, parallel, aux_args, device)
 
 
 RanomBoostedForest = RandomForest          # the reference's (misspelt) class name

@@ -224,6 +224,18 @@ int hetu_gemm_rs(const float* A, const float* B, void* const* out_peers, int ran
  * kind 0 constant(a) 1 uniform[a,b) 2 normal(mean a, std b) 3 truncated normal (|z| <= 2). */
 int hetu_init_random(float* out, size_t n, int kind, float a, float b, unsigned long long seed, cudaStream_t s);
 
+/* ---- hetuml GBDT on the device: reference third_party/HetuML/hetuml/cc/ml/include/model/gbdt/{hist,helper}/ ----
+ * One launch per tree level.  hist [num_slots, total_bins, 2] (g, h) must be zeroed by the caller; only stored
+ * CSR entries are visited (bins[q] = bin of stored entry q, rows sorted by column).  node_of[i] = node of
+ * instance i (-1 = ignore); slot_of_node maps node id -> histogram slot (-1 = inactive). */
+int hetu_gbdt_hist(const long long* indptr, const int* indices, const unsigned char* bins, const int* node_of,
+                   const int* slot_of_node, const float* g, const float* h, const long long* bin_off,
+                   const unsigned char* feat_on, float* hist, long long total_bins, long long n, cudaStream_t s);
+/* move instances of split nodes to left_child[node] (bin <= split_bin[node]) or left_child[node] + 1 */
+int hetu_gbdt_route(const long long* indptr, const int* indices, const unsigned char* bins, int* node_of,
+                    const int* split_feat, const int* split_bin, const int* zero_bin, const int* left_child,
+                    long long n, cudaStream_t s);
+
 #ifdef __cplusplus
 }
 #endif

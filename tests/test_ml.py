@@ -301,3 +301,55 @@ def test_knn_gpu_distance_gemm_matches_cpu():
     a = KNN(num_label=3, num_neighbor=5, device='cpu').predict_score((small_l, ys), small_q)
     b = KNN(num_label=3, num_neighbor=5, device='gpu').predict_score((small_l, ys), small_q)      # exact fp32 path (K <= 64)
     assert np.mean(np.abs(a - b).sum(1) == 0) > 0.97
+
+
+def _gbdt_level_trainer_matches_node_trainer(dev):
+    from hetu_61a7_b200.ml import _gbdt_gpu
+    rng = np.random.RandomState(11)
+    n, d = 3000, 12
+    Xd = rng.standard_normal((n, d)).astype(np.float32)
+    Xd[rng.rand(n, d) < 0.5] = 0
+    y = ((Xd[:, 0] > 0.3) ^ (Xd[:, 1] < -0.2) | (Xd[:, 2] * Xd[:, 3] > 0.5)).astype(np.float32)
+    X = sp.csr_matrix(Xd)
+    kw = dict(max_depth=4, num_round=8, learning_rate=0.3, num_split=16, min_node_ins=20, reg_lambda=1.0)
+    ref = GBDT(device='cpu', **kw)
+    ref.fit((X, y))
+    lvl = GBDT(device='cpu', **kw)
+    ds = Dataset.from_data((X, y))
+    _gbdt_gpu.fit(lvl, ds, ds.get_max_dim(), dev=dev)
+    # float32 histograms vs double: same trees unless two splits tie within rounding
+    np.testing.assert_allclose(lvl.train_loss_curve(), ref.train_loss_curve(), rtol=2e-3, atol=2e-3)
+    a, b = lvl.predict_score(X), ref.predict_score(X)
+    # (on the GPU the float atomics also reorder the sums, so a near-tie may pick the other split in some tree)
+    assert np.mean(np.abs(a - b) < 1e-3) > (0.98 if dev == 'cpu' else 0.85), np.abs(a - b).max()
+    assert abs(lvl.evaluate((X, y), 'log-loss')['log-loss'] - ref.evaluate((X, y), 'log-loss')['log-loss']) < 5e-3
+    assert lvl.num_trees() == 8 and lvl.evaluate((X, y), 'error')['error'] < 0.12
+    # regression, sampling, multi-class with one tree per class
+    target = (np.sin(2 * Xd[:, 0]) + Xd[:, 1]).astype(np.float32)
+    reg = GBDT(device='cpu', is_regression=True, max_depth=4, num_round=20, learning_rate=0.3, num_split=16, min_node_ins=20,
+               ins_sp_ratio=0.8, feat_sp_ratio=0.9)
+    dr = Dataset.from_data((X, target))
+    curve = _gbdt_gpu.fit(reg, dr, dr.get_max_dim(), dev=dev)
+    assert curve[-1] < 0.3 * curve[0] and reg.evaluate((X, target), 'mse')['mse'] < 0.3 * float(np.var(target))
+    lab = ((Xd[:, 0] > 0).astype(np.int64) + (Xd[:, 1] > 0).astype(np.int64)).astype(np.float32)
+    mc = GBDT(device='cpu', num_label=3, multi_tree=True, max_depth=3, num_round=10, learning_rate=0.5, num_split=16, min_node_ins=20)
+    dm = Dataset.from_data((X, lab))
+    _gbdt_gpu.fit(mc, dm, dm.get_max_dim(), dev=dev)
+    assert mc.num_trees() == 30 and mc.evaluate((X, lab), 'precision')['precision'] > 0.95
+
+
+def test_gbdt_level_trainer_host_oracle():
+    """The level-at-a-time trainer (device GBDT) with torch stand-ins for its two kernels agrees
+    with the node-at-a-time native trainer."""
+    _gbdt_level_trainer_matches_node_trainer('cpu')
+
+
+@pytest.mark.gpu
+def test_gbdt_level_trainer_on_b200():
+    _gbdt_level_trainer_matches_node_trainer('cuda')
+    rng = np.random.RandomState(12)
+    Xd = (rng.rand(2000, 30) < 0.2).astype(np.float32)
+    y = (Xd[:, :5].sum(1) > 1).astype(np.float32)
+    gb = GBDT(device='gpu', max_depth=3, num_round=5, min_node_ins=10)      # public entry point
+    gb.fit((sp.csr_matrix(Xd), y))
+    assert gb.evaluate((sp.csr_matrix(Xd), y), 'error')['error'] < 0.1
