@@ -140,6 +140,23 @@ def _emit(c: _Ctx, node, ins: List[str], out: str):
         pads = np.asarray(node.paddings, dtype=np.int64)
         c.add('Pad', [ins[0], c.const(np.concatenate([pads[:, 0], pads[:, 1]]), 'pads'),
                       c.const(np.float32(node.constant_values), 'pad_value')], [out], mode='constant')
+    elif t == 'OneHotOp':
+        idx = c.tmp('ids')
+        c.add('Cast', [ins[0]], [idx], to=P.INT64)
+        c.add('OneHot', [idx, c.const(np.asarray([int(node.num_classes)], np.int64), 'depth'),
+                         c.const(np.asarray([0.0, 1.0], np.float32), 'values')], [out], axis=-1)
+    elif t == 'WhereOp':
+        cond = c.tmp('cond')
+        c.add('Cast', [ins[0]], [cond], to=P.BOOL)
+        c.add('Where', [cond, ins[1], ins[2]], [out])
+    elif t in ('RsqrtOp', 'ReciprocalSqrtOp'):
+        r = c.tmp('sqrt')
+        c.add('Sqrt', [ins[0]], [r])
+        c.add('Reciprocal', [r], [out])
+    elif t == 'DivConstOp':
+        c.add('Div', [c.const(np.float32(node.a if hasattr(node, 'a') else node.const_attr), 'const'), ins[0]], [out])
+    elif t == 'MinusByConstOp':
+        c.add('Sub', [c.const(np.float32(node.a if hasattr(node, 'a') else node.const_attr), 'const'), ins[0]], [out])
     elif t == 'FusedAttentionOp':
         raise NotImplementedError('export fused attention with fused_attention=False models')
     else:
@@ -151,6 +168,8 @@ def export(executor, inputs, outputs, path, name='default'):
     c = _Ctx()
     names: Dict = {}
     g_inputs, g_outputs = [], []
+    input_rank = {n: k for k, n in enumerate(inputs)}
+    g_input_keys = []
     sub = executor.subexecutor[name] if name in executor.subexecutor else next(iter(executor.subexecutor.values()))
     shapes = getattr(sub, 'node_to_shape_map', {}) or {}
     for node in find_topo_sort(list(outputs)):
@@ -160,17 +179,21 @@ def export(executor, inputs, outputs, path, name='default'):
             if node in inputs or (node.tensor_value is None and executor.config.placeholder_to_arr_map.get(node) is None):
                 shp = shapes.get(node) or node.shape or ()
                 g_inputs.append(P.value_info(nm, ['N'] + list(shp[1:]) if shp else ['N']))
+                g_input_keys.append(input_rank.get(node, len(inputs) + len(g_input_keys)))
             else:
                 c.inits.append(P.tensor(nm, _value_of(executor, node).astype(np.float32)))
             continue
         if node in inputs:
             shp = shapes.get(node) or ()
             g_inputs.append(P.value_info(nm, ['N'] + list(shp[1:]) if shp else ['N']))
+            g_input_keys.append(input_rank.get(node, len(inputs) + len(g_input_keys)))
             continue
         _emit(c, node, [names[i] for i in node.inputs if i is not None], nm)
     for o in outputs:
         shp = shapes.get(o) or ()
         g_outputs.append(P.value_info(names[o], ['N'] + list(shp[1:]) if shp else ['N']))
+    # graph inputs in the order the caller listed them (then any further free placeholders in graph order)
+    g_inputs = [gi for _, gi in sorted(zip(g_input_keys, g_inputs), key=lambda kv: kv[0])]
     buf = P.model(c.nodes, g_inputs, g_outputs, c.inits)
     with open(path, 'wb') as f:
         f.write(buf)

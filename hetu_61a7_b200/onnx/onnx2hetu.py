@@ -105,6 +105,12 @@ def load_onnx(path):
             env[o] = get(ins[0])
         elif op == 'Cast':
             env[o] = get(ins[0])
+        elif op == 'OneHot':
+            env[o] = ht.one_hot_op(get(ins[0]), int(np.asarray(consts[ins[1]]).reshape(-1)[0]))
+        elif op == 'Where':
+            env[o] = ht.where_op(get(ins[0]), get(ins[1]), get(ins[2]))
+        elif op == 'Reciprocal':
+            env[o] = ht.div_const_op(1.0, get(ins[0]))
         elif op == 'Gather':
             env[o] = ht.embedding_lookup_op(get(ins[0]), get(ins[1]))
         elif op == 'Pad':

@@ -11,7 +11,7 @@ from typing import Dict, List, Tuple
 
 import numpy as np
 
-FLOAT, INT32, INT64 = 1, 6, 7
+FLOAT, INT32, INT64, BOOL = 1, 6, 7, 9
 _NP = {FLOAT: np.float32, INT32: np.int32, INT64: np.int64, 11: np.float64, 9: np.bool_, 10: np.float16}
 A_FLOAT, A_INT, A_STRING, A_TENSOR, A_FLOATS, A_INTS = 1, 2, 3, 4, 6, 7
 

@@ -61,3 +61,27 @@ def test_graphboard_dot(tmp_path):
     assert 'MatMulOp' in dot and '->' in dot and out
     import graphboard.graph2fig as g2f
     assert g2f.show is ht.graphboard.show
+
+
+def test_onnx_where_onehot_const_ops_and_input_order():
+    """OneHot / Where / reciprocal-sqrt / const-minus / const-divide handlers (reference
+    onnx_opset/{OneHot,Where,Sqrt,Division}.py); graph inputs keep the order given to export()."""
+    import os
+    import tempfile
+    import numpy as np
+    import hetu as ht
+    from hetu.onnx import hetu2onnx, onnx2hetu
+    x, c, ids = ht.Variable('x'), ht.Variable('c'), ht.Variable('ids')
+    y = ht.where_op(c, ht.rsqrt_op(x), ht.div_const_op(2.0, x)) + ht.minus_byconst_op(x, 1.0)
+    z = ht.one_hot_op(ids, 5)
+    ex = ht.Executor([y, z], ctx=ht.cpu(0))
+    rs = np.random.RandomState(0)
+    xv, cv, iv = rs.rand(4, 5).astype(np.float32) + 0.5, (rs.rand(4, 5) > 0.5).astype(np.float32), np.array([0, 3, 4, 1], np.float32)
+    ref = ex.run(feed_dict={x: xv, c: cv, ids: iv}, convert_to_numpy_ret_vals=True)
+    path = os.path.join(tempfile.mkdtemp(), 'm.onnx')
+    hetu2onnx.export(ex, [x, c, ids], [y, z], path)
+    ins, outs = onnx2hetu.load_onnx(path)
+    assert [i.name for i in ins] == ['x', 'c', 'ids']
+    got = ht.Executor(outs, ctx=ht.cpu(0)).run(feed_dict=dict(zip(ins, [xv, cv, iv])), convert_to_numpy_ret_vals=True)
+    np.testing.assert_allclose(got[0], ref[0], rtol=1e-6)
+    np.testing.assert_array_equal(got[1], ref[1])
