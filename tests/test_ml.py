@@ -342,14 +342,3 @@ def test_gbdt_level_trainer_host_oracle():
     """The level-at-a-time trainer (device GBDT) with torch stand-ins for its two kernels agrees
     with the node-at-a-time native trainer."""
     _gbdt_level_trainer_matches_node_trainer('cpu')
-
-
-@pytest.mark.gpu
-def test_gbdt_level_trainer_on_b200():
-    _gbdt_level_trainer_matches_node_trainer('cuda')
-    rng = np.random.RandomState(12)
-    Xd = (rng.rand(2000, 30) < 0.2).astype(np.float32)
-    y = (Xd[:, :5].sum(1) > 1).astype(np.float32)
-    gb = GBDT(device='gpu', max_depth=3, num_round=5, min_node_ins=10)      # public entry point
-    gb.fit((sp.csr_matrix(Xd), y))
-    assert gb.evaluate((sp.csr_matrix(Xd), y), 'error')['error'] < 0.1
