@@ -2,11 +2,12 @@
 //
 // reference: src/dnnl_ops/*.cpp (oneDNN primitives + OpenMP loops, 47 exported functions listed in
 // python/hetu/_base.py:16-58).  oneDNN is not part of this image; the primitives are written out as
-// cache-blocked OpenMP loops the compiler vectorises (AVX2/FMA).  All tensors are dense row-major
+// cache-blocked OpenMP loops the compiler vectorises (AVX2/FMA); the GEMM has hand-written AVX-512 / AVX2 micro-kernels.  All tensors are dense row-major
 // fp32; every function returns 0 on success.
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <random>
 #include <vector>
@@ -16,90 +17,217 @@
 
 // ------------------------------------------------------------------------------------------------
 // GEMM: C[M,N] = alpha * op(A) op(B) + beta * C          (reference MatrixMult.cpp:18-56)
-// Packs op(A) / op(B) panels so the micro-kernel always streams unit-stride data.
-namespace {
-constexpr int MC = 96, KC = 256, NC = 512, MR = 6, NR = 16;
+//
+// C is cut into tiles that are handed to the OpenMP threads; a thread walks K in chunks, packs the
+// op(A) / op(B) sub-panels of its tile into thread-local buffers (so the micro-kernel streams
+// unit-stride data whatever the transposes are) and runs a register-blocked micro-kernel:
+// 12 x 32 on AVX-512 (24 zmm accumulators + 2 B vectors + 1 broadcast), 6 x 16 on AVX2.
+// The instruction set is picked once at run time.
+#include <immintrin.h>
 
-// function multi-versioning: the AVX-512 clone is picked at load time when the CPU has it
-__attribute__((target_clones("avx512f", "default"), noinline))
-void micro_kernel(int kc, const float* __restrict a, const float* __restrict b, float* __restrict c,
-                         int ldc, int mr, int nr, float alpha, bool accumulate) {
-    float acc[MR][NR] = {};
+namespace {
+constexpr int KC = 384;
+
+struct Kern { int MR, NR; void (*fn)(int, const float*, const float*, int, float*, int, int, int, float, float); };
+
+// a: packed [kc][MR], b: packed [kc][NR]; C tile (mr x nr valid) = alpha * a.b + beta * C
+__attribute__((target("avx512f"), noinline))
+void kern_avx512(int kc, const float* __restrict a, const float* __restrict b, int ldbk, float* __restrict c, int ldc, int mr,
+                 int nr, float alpha, float beta) {
+    constexpr int MR = 12;
+    __m512 acc0[MR], acc1[MR];
+    for (int i = 0; i < MR; ++i) { acc0[i] = _mm512_setzero_ps(); acc1[i] = _mm512_setzero_ps(); }
     for (int p = 0; p < kc; ++p) {
-        const float* bp = b + p * NR;
+        __m512 b0 = _mm512_loadu_ps(b + (size_t)p * ldbk), b1 = _mm512_loadu_ps(b + (size_t)p * ldbk + 16);
         const float* ap = a + p * MR;
+#pragma GCC unroll 12
         for (int i = 0; i < MR; ++i) {
-            float av = ap[i];
-#pragma omp simd
-            for (int j = 0; j < NR; ++j) acc[i][j] += av * bp[j];
+            __m512 av = _mm512_set1_ps(ap[i]);
+            acc0[i] = _mm512_fmadd_ps(av, b0, acc0[i]);
+            acc1[i] = _mm512_fmadd_ps(av, b1, acc1[i]);
         }
     }
-    for (int i = 0; i < mr; ++i)
-        for (int j = 0; j < nr; ++j) {
-            float v = alpha * acc[i][j];
-            c[i * ldc + j] = accumulate ? c[i * ldc + j] + v : v;
+    __m512 va = _mm512_set1_ps(alpha), vb = _mm512_set1_ps(beta);
+    __mmask16 m0 = nr >= 16 ? (__mmask16)0xffff : (__mmask16)((1u << nr) - 1);
+    __mmask16 m1 = nr >= 32 ? (__mmask16)0xffff : (nr > 16 ? (__mmask16)((1u << (nr - 16)) - 1) : (__mmask16)0);
+    for (int i = 0; i < mr; ++i) {
+        float* cr = c + (size_t)i * ldc;
+        __m512 r0 = _mm512_mul_ps(va, acc0[i]), r1 = _mm512_mul_ps(va, acc1[i]);
+        if (beta != 0.f) {
+            r0 = _mm512_fmadd_ps(vb, _mm512_maskz_loadu_ps(m0, cr), r0);
+            if (m1) r1 = _mm512_fmadd_ps(vb, _mm512_maskz_loadu_ps(m1, cr + 16), r1);
         }
+        _mm512_mask_storeu_ps(cr, m0, r0);
+        if (m1) _mm512_mask_storeu_ps(cr + 16, m1, r1);
+    }
 }
+
+__attribute__((target("avx2,fma"), noinline))
+void kern_avx2(int kc, const float* __restrict a, const float* __restrict b, int ldbk, float* __restrict c, int ldc, int mr,
+               int nr, float alpha, float beta) {
+    constexpr int MR = 6;
+    __m256 acc0[MR], acc1[MR];
+    for (int i = 0; i < MR; ++i) { acc0[i] = _mm256_setzero_ps(); acc1[i] = _mm256_setzero_ps(); }
+    for (int p = 0; p < kc; ++p) {
+        __m256 b0 = _mm256_loadu_ps(b + (size_t)p * ldbk), b1 = _mm256_loadu_ps(b + (size_t)p * ldbk + 8);
+        const float* ap = a + p * MR;
+#pragma GCC unroll 6
+        for (int i = 0; i < MR; ++i) {
+            __m256 av = _mm256_broadcast_ss(ap + i);
+            acc0[i] = _mm256_fmadd_ps(av, b0, acc0[i]);
+            acc1[i] = _mm256_fmadd_ps(av, b1, acc1[i]);
+        }
+    }
+    alignas(32) float tmp[16];
+    for (int i = 0; i < mr; ++i) {
+        _mm256_store_ps(tmp, acc0[i]);
+        _mm256_store_ps(tmp + 8, acc1[i]);
+        float* cr = c + (size_t)i * ldc;
+        for (int j = 0; j < nr; ++j) cr[j] = alpha * tmp[j] + (beta != 0.f ? beta * cr[j] : 0.f);
+    }
+}
+
+void kern_scalar(int kc, const float* a, const float* b, int ldbk, float* c, int ldc, int mr, int nr, float alpha, float beta) {
+    constexpr int MR = 4, NR = 8;
+    float acc[MR][NR] = {};
+    for (int p = 0; p < kc; ++p)
+        for (int i = 0; i < MR; ++i)
+            for (int j = 0; j < NR; ++j) acc[i][j] += a[p * MR + i] * b[(size_t)p * ldbk + j];
+    for (int i = 0; i < mr; ++i)
+        for (int j = 0; j < nr; ++j) c[(size_t)i * ldc + j] = alpha * acc[i][j] + (beta != 0.f ? beta * c[(size_t)i * ldc + j] : 0.f);
+}
+
+const Kern& pick_kernel() {
+    static const Kern k = [] {
+        __builtin_cpu_init();
+        if (__builtin_cpu_supports("avx512f")) return Kern{12, 32, kern_avx512};
+        if (__builtin_cpu_supports("avx2") && __builtin_cpu_supports("fma")) return Kern{6, 16, kern_avx2};
+        return Kern{4, 8, kern_scalar};
+    }();
+    return k;
+}
+
+inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
 }  // namespace
 
 API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, int K, int transA, int transB,
                         float alpha, float beta) {
-    if (beta == 0.f) {
+    if (M <= 0 || N <= 0) return 0;
+    const Kern& kr = pick_kernel();
+    const int MR = kr.MR, NR = kr.NR;
+    if (K <= 0) {
 #pragma omp parallel for
-        for (int64_t i = 0; i < (int64_t)M * N; ++i) C[i] = 0.f;
-    } else if (beta != 1.f) {
-#pragma omp parallel for
-        for (int64_t i = 0; i < (int64_t)M * N; ++i) C[i] *= beta;
+        for (int64_t i = 0; i < (int64_t)M * N; ++i) C[i] = beta == 0.f ? 0.f : beta * C[i];
+        return 0;
     }
     const int lda = transA ? M : K, ldb = transB ? K : N;
-    for (int jc = 0; jc < N; jc += NC) {
-        int nc = std::min(NC, N - jc);
-        int npanels = (nc + NR - 1) / NR;
-        for (int pc = 0; pc < K; pc += KC) {
-            int kc = std::min(KC, K - pc);
-            std::vector<float> bpack((size_t)npanels * kc * NR);
-#pragma omp parallel for
-            for (int jp = 0; jp < npanels; ++jp) {
-                float* dst = bpack.data() + (size_t)jp * kc * NR;
-                for (int p = 0; p < kc; ++p)
-                    for (int j = 0; j < NR; ++j) {
-                        int col = jc + jp * NR + j;
-                        float v = 0.f;
-                        if (col < N) v = transB ? B[(size_t)col * ldb + pc + p] : B[(size_t)(pc + p) * ldb + col];
-                        dst[p * NR + j] = v;
-                    }
-            }
-            // row-block height: small M (batch-sized activations) is cut finer so every thread gets a block
-            const int nthr = omp_get_max_threads();
-            int mcb = ((M + nthr - 1) / nthr + MR - 1) / MR * MR;
-            mcb = std::max(MR, std::min(MC, mcb));
+    const int mpanels = (M + MR - 1) / MR, npanels = (N + NR - 1) / NR;
+    // op(A) is packed once into row panels [panel][K][MR] (each element is copied once, in parallel).
+    // op(B) is read in place when it is row-major K x N (a panel row is 32 consecutive floats); only
+    // the ragged last panel and the transposed layout go through a packed copy [panel][K][NR].
+    static thread_local std::vector<float> apack_store, bpack_store;
+    std::vector<float>& apack = apack_store;
+    std::vector<float>& bpack = bpack_store;
+    apack.resize((size_t)mpanels * K * MR);
+    // in-place B rows are ldb floats apart: fine while a K chunk of a panel stays within a few pages per row group,
+    // but with many K steps the strided walk defeats the L1 prefetcher - pack then (one contiguous 128-byte row per step)
+    const bool pack_all_b = transB != 0 || (K >= 512 && getenv("HETU_CPU_GEMM_INPLACE_B") == nullptr);
+    const bool ragged_b = (N % NR) != 0;
+    if (pack_all_b) bpack.resize((size_t)npanels * K * NR);
+    else if (ragged_b) bpack.resize((size_t)K * NR);
+    float* ap_base = apack.data();
+    float* bp_base = bpack.data();
 #pragma omp parallel
-            {
-                std::vector<float> apack((size_t)((MC + MR - 1) / MR) * MR * kc);
-#pragma omp for schedule(dynamic)
-                for (int ic = 0; ic < M; ic += mcb) {
-                    int mc = std::min(mcb, M - ic);
-                    int mpanels = (mc + MR - 1) / MR;
-                    for (int ip = 0; ip < mpanels; ++ip) {
-                        float* dst = apack.data() + (size_t)ip * kc * MR;
-                        for (int p = 0; p < kc; ++p)
-                            for (int i = 0; i < MR; ++i) {
-                                int row = ic + ip * MR + i;
-                                float v = 0.f;
-                                if (row < M) v = transA ? A[(size_t)(pc + p) * lda + row] : A[(size_t)row * lda + pc + p];
-                                dst[p * MR + i] = v;
-                            }
+    {
+#pragma omp for schedule(static) nowait
+        for (int ip = 0; ip < mpanels; ++ip) {
+            float* dst = ap_base + (size_t)ip * K * MR;
+            const int row0 = ip * MR, hgt = std::min(MR, M - row0);
+            if (!transA) {
+                for (int i = 0; i < MR; ++i) {                       // contiguous reads along K, strided writes
+                    if (i < hgt) {
+                        const float* src = A + (size_t)(row0 + i) * lda;
+                        for (int p = 0; p < K; ++p) dst[(size_t)p * MR + i] = src[p];
+                    } else {
+                        for (int p = 0; p < K; ++p) dst[(size_t)p * MR + i] = 0.f;
                     }
-                    for (int jp = 0; jp < npanels; ++jp)
-                        for (int ip = 0; ip < mpanels; ++ip) {
-                            int row = ic + ip * MR, col = jc + jp * NR;
-                            micro_kernel(kc, apack.data() + (size_t)ip * kc * MR, bpack.data() + (size_t)jp * kc * NR,
-                                         C + (size_t)row * N + col, N, std::min(MR, M - row), std::min(NR, N - col),
-                                         alpha, true);
-                        }
+                }
+            } else {
+                for (int p = 0; p < K; ++p) {
+                    const float* src = A + (size_t)p * lda + row0;
+                    float* d = dst + (size_t)p * MR;
+                    for (int i = 0; i < hgt; ++i) d[i] = src[i];
+                    for (int i = hgt; i < MR; ++i) d[i] = 0.f;
                 }
             }
         }
+        if (pack_all_b) {
+#pragma omp for schedule(static)
+            for (int jp = 0; jp < npanels; ++jp) {
+                float* dst = bp_base + (size_t)jp * K * NR;
+                const int col0 = jp * NR, w = std::min(NR, N - col0);
+                if (transB) {
+                    for (int j = 0; j < NR; ++j) {                   // contiguous reads along K
+                        if (j < w) {
+                            const float* src = B + (size_t)(col0 + j) * ldb;
+                            for (int p = 0; p < K; ++p) dst[(size_t)p * NR + j] = src[p];
+                        } else {
+                            for (int p = 0; p < K; ++p) dst[(size_t)p * NR + j] = 0.f;
+                        }
+                    }
+                } else {
+                    for (int p = 0; p < K; ++p) {
+                        float* d = dst + (size_t)p * NR;
+                        const float* src = B + (size_t)p * ldb + col0;
+                        for (int j = 0; j < w; ++j) d[j] = src[j];
+                        for (int j = w; j < NR; ++j) d[j] = 0.f;
+                    }
+                }
+            }
+        } else if (ragged_b) {
+            const int col0 = (npanels - 1) * NR, w = N - col0;
+#pragma omp for schedule(static)
+            for (int p = 0; p < K; ++p) {
+                float* d = bp_base + (size_t)p * NR;
+                const float* src = B + (size_t)p * ldb + col0;
+                for (int j = 0; j < w; ++j) d[j] = src[j];
+                for (int j = w; j < NR; ++j) d[j] = 0.f;
+            }
+        } else {
+#pragma omp barrier
+        }
+        // tiles of C: a few row panels x a few column panels each, about two tiles per thread at least
+        const int nthr = omp_get_num_threads();
+        int tp_m = std::max(1, std::min(mpanels, 96 / MR)), tp_n = std::max(1, std::min(npanels, 128 / NR));
+        auto ntiles = [&](int a, int b) { return (int64_t)((mpanels + a - 1) / a) * ((npanels + b - 1) / b); };
+        while (ntiles(tp_m, tp_n) < 2 * (int64_t)nthr && (tp_m > 1 || tp_n > 1)) {
+            if (tp_n > 1 && (tp_n * NR >= tp_m * MR || tp_m == 1)) tp_n = (tp_n + 1) / 2;
+            else tp_m = (tp_m + 1) / 2;
+        }
+        const int tiles_m = (mpanels + tp_m - 1) / tp_m, tiles_n = (npanels + tp_n - 1) / tp_n;
+#pragma omp for schedule(dynamic) collapse(2)
+        for (int tm = 0; tm < tiles_m; ++tm)
+            for (int tn = 0; tn < tiles_n; ++tn) {
+                const int ip0 = tm * tp_m, ip1 = std::min(mpanels, ip0 + tp_m);
+                const int jp0 = tn * tp_n, jp1 = std::min(npanels, jp0 + tp_n);
+                for (int pc = 0; pc < K; pc += KC) {
+                    const int kc = std::min(KC, K - pc);
+                    const float b_eff = pc == 0 ? beta : 1.f;       // later K chunks accumulate
+                    for (int jp = jp0; jp < jp1; ++jp) {
+                        const int col = jp * NR, nr = std::min(NR, N - col);
+                        const float* bptr;
+                        int ldbk;
+                        if (pack_all_b) { bptr = bp_base + (size_t)jp * K * NR + (size_t)pc * NR; ldbk = NR; }
+                        else if (nr < NR) { bptr = bp_base + (size_t)pc * NR; ldbk = NR; }
+                        else { bptr = B + (size_t)pc * ldb + col; ldbk = ldb; }
+                        for (int ip = ip0; ip < ip1; ++ip) {
+                            const int row = ip * MR;
+                            kr.fn(kc, ap_base + (size_t)ip * K * MR + (size_t)pc * MR, bptr, ldbk, C + (size_t)row * N + col, N,
+                                  std::min(MR, M - row), nr, alpha, b_eff);
+                        }
+                    }
+                }
+            }
     }
     return 0;
 }
