@@ -62,7 +62,10 @@ class GBDT(SupervisedMLBase):
         self._handle = None
 
     def __del__(self):
-        self._free()
+        try:
+            self._free()
+        except Exception:                    # interpreter shutdown: module globals may already be gone
+            pass
 
     def _free(self):
         if getattr(self, '_handle', None):
