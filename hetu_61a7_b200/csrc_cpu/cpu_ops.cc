@@ -137,7 +137,8 @@ API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, 
     else if (ragged_b) bpack.resize((size_t)K * NR);
     float* ap_base = apack.data();
     float* bp_base = bpack.data();
-#pragma omp parallel
+    const bool go_parallel = (int64_t)M * N * K >= (1 << 18);          // tiny products: the fork/join costs more than it saves
+#pragma omp parallel if (go_parallel)
     {
 #pragma omp for schedule(static) nowait
         for (int ip = 0; ip < mpanels; ++ip) {
