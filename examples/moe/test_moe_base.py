@@ -1,0 +1,10 @@
+#!/usr/bin/env python
+"""reference examples/moe/test_moe_base.py: the base-gate MoE layer benchmark (same flags as test_moe.py).
+    heturun -w 8 python examples/moe/test_moe_base.py --top 2"""
+import sys
+
+from test_moe import main
+
+if '--gate' not in sys.argv:
+    sys.argv += '--gate base'.split()
+main()
