@@ -11,13 +11,14 @@ import numpy as np
 
 ap = argparse.ArgumentParser()
 ap.add_argument('--rtol', type=float, default=2e-3)
+ap.add_argument('--prefix', default='', help="compare only <prefix>*.npy against <prefix>base.npy (e.g. 'cnn_')")
 ap.add_argument('--dir', default=os.path.join(os.path.dirname(os.path.abspath(__file__)), 'results'))
 args = ap.parse_args()
-base = np.load(os.path.join(args.dir, 'base.npy'))
+base = np.load(os.path.join(args.dir, args.prefix + 'base.npy'))
 bad = 0
-for path in sorted(glob.glob(os.path.join(args.dir, '*.npy'))):
+for path in sorted(glob.glob(os.path.join(args.dir, args.prefix + '*.npy'))):
     name = os.path.basename(path)[:-4]
-    if name == 'base':
+    if name == args.prefix + 'base' or (not args.prefix and name.startswith('cnn_')):
         continue
     res = np.load(path)
     if '_gpipe' in name or '_pipedream' in name or '_hetpipe' in name:
