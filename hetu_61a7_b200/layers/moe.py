@@ -14,6 +14,7 @@ the expert GEMMs run as one grouped tcgen05 launch.
 from __future__ import annotations
 
 import math
+import os
 
 import numpy as np
 
@@ -85,8 +86,17 @@ def _slots(mask_topk, k):
 
 
 def topkgating(logits, k, capacity_factor, num_tokens, num_experts, embed_dim):
-    gates = ht.softmax_op(logits)
     capacity = k * math.ceil((num_tokens / num_experts) * capacity_factor)
+    if os.environ.get('HETU_MOE_FUSED_GATE', '1') == '1' and k <= 4:
+        # one op for softmax + top-k + slots + balance loss (ops/moe_gate.py); the pieces are columns of its output
+        packed = ht.fused_topk_gate_op(logits, k)
+        col = lambda c: ht.array_reshape_op(ht.slice_op(packed, (0, c), (num_tokens, 1)), [-1])     # noqa: E731
+        indices_s = [col(i) for i in range(k)]
+        location_s = [col(k + i) for i in range(k)]
+        gates_s = [col(2 * k + i) for i in range(k)]
+        l_aux = ht.array_reshape_op(ht.slice_op(packed, (num_tokens, 0), (1, 1)), [1])
+        return l_aux, indices_s, location_s, gates_s, capacity
+    gates = ht.softmax_op(logits)
     topk_indices = ht.topk_idx_op(gates, topk=k)
     indices_s = [ht.array_reshape_op(ht.split_op(topk_indices, axes=[1], indices=[i], splits=[k]), [-1])
                  for i in range(k)]

@@ -236,6 +236,13 @@ int hetu_gbdt_route(const long long* indptr, const int* indices, const unsigned 
                     const int* split_feat, const int* split_bin, const int* zero_bin, const int* left_child,
                     long long n, cudaStream_t s);
 
+/* ---- fused MoE gate: reference python/hetu/layers/TopGate.py:15-79 lowered through cudnnSoftmax, TopKIdx.cu,
+ * OneHot.cu, CumSum.cu, ReduceSum/ReduceMean (about 30 launches).  P [T + 1, 3k]: expert index, capacity slot,
+ * gate value per route; P[T][0] = balance loss.  Scratch: blk_cnt int[k * ceil(T / 256) * E], me float[E], cnt float[E]. */
+int hetu_moe_gate_fwd(const float* logits, float* P, int* blk_cnt, float* me, int T, int E, int k, cudaStream_t s);
+int hetu_moe_gate_bwd(const float* logits, const float* P, const float* dP, float* cnt, float* dlogits, int T, int E, int k,
+                      cudaStream_t s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -384,3 +384,39 @@ def test_matmul_relu_epilogue_fusion_matches_oracle():
         opt.step()
         ref.append(float(l))
     np.testing.assert_allclose(got, ref, rtol=1e-4, atol=1e-6)
+
+
+def _fused_gate_vs_composed(ctx, tol):
+    """ops/moe_gate.py: one op for softmax + top-k + slots + balance loss equals the ~30-op composed gate
+    (values, slots and the gradient w.r.t. the logits)."""
+    import os
+    from hetu_61a7_b200.layers import moe as M
+    rs = np.random.RandomState(0)
+    res = {}
+    for T, E, k in ((300, 8, 2), (1000, 16, 1), (517, 12, 3)):
+        lv = rs.randn(T, E).astype(np.float32)
+        for flag in ('0', '1'):
+            os.environ['HETU_MOE_FUSED_GATE'] = flag
+            try:
+                logits = ht.Variable('gate_logits_%s_%d' % (flag, T), value=lv.copy())
+                l_aux, idx, loc, gates, cap = M.topkgating(logits, k, 1.0, T, E, 16)
+                obj = l_aux
+                for i in range(k):
+                    r = ht.Variable('gate_r%d_%s_%d' % (i, flag, T), value=np.random.RandomState(1 + i).randn(T).astype(np.float32),
+                                    trainable=False)
+                    obj = obj + ht.reduce_sum_op(ht.mul_op(gates[i], r), axes=0)
+                g = ht.gradients(obj, [logits])[0]
+                ex = ht.Executor([l_aux] + idx + loc + gates + [g], ctx=ctx)
+                res[flag] = ex.run(convert_to_numpy_ret_vals=True)
+            finally:
+                os.environ.pop('HETU_MOE_FUSED_GATE', None)
+        for a, b in zip(res['0'], res['1']):
+            np.testing.assert_allclose(np.ravel(a), np.ravel(b), rtol=tol, atol=tol)
+        loc = np.stack(res['1'][1 + k:1 + 2 * k]).astype(np.int64)
+        idx = np.stack(res['1'][1:1 + k]).astype(np.int64)
+        pairs = set(zip(idx.reshape(-1).tolist(), loc.reshape(-1).tolist()))
+        assert len(pairs) == T * k                              # every (expert, slot) is used once
+
+
+def test_fused_moe_gate_matches_composed_gate():
+    _fused_gate_vs_composed(ht.cpu(0), 1e-6)
