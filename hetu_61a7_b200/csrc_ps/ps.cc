@@ -33,6 +33,7 @@
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
+#include <deque>
 #include <functional>
 #include <future>
 #include <map>
@@ -545,6 +546,71 @@ inline std::thread start_heartbeat(const std::string& host, int port, int node_i
     });
 }
 
+// Worker-side I/O pool for the *_async calls.  reference: ps-lite/src/worker.cc:25-34 + thread_pool.cc:4 (5 threads)
+// and the P3 van's priority queue (ps-lite/src/p3_van.h:12-68).  Requests of one key run in submission order
+// (a pull queued after a push of the same tensor sees that push); across keys the highest priority goes first
+// (hps_set_priority; default 0 = first come first served).  PS_WORKER_THREADS sets the pool size.
+class IoPool {
+  public:
+    ~IoPool() { shutdown(); }
+    std::future<void> submit(uint64_t key, std::function<void()> fn) {
+        std::unique_lock<std::mutex> l(mu_);
+        if (threads_.empty()) {
+            int n = std::max(1, atoi(env_or("PS_WORKER_THREADS", "5")));
+            for (int i = 0; i < n; ++i) threads_.emplace_back([this] { loop(); });
+        }
+        auto t = std::make_unique<Task>();
+        t->fn = std::move(fn);
+        t->seq = ++seq_;
+        std::future<void> fut = t->done.get_future();
+        keys_[key].q.push_back(std::move(t));
+        cv_.notify_one();
+        return fut;
+    }
+    void set_priority(uint64_t key, int prio) { std::unique_lock<std::mutex> l(mu_); keys_[key].prio = prio; }
+    void shutdown() {
+        { std::unique_lock<std::mutex> l(mu_); stop_ = true; cv_.notify_all(); }
+        for (auto& t : threads_) if (t.joinable()) t.join();
+        threads_.clear();
+    }
+
+  private:
+    struct Task { std::function<void()> fn; std::promise<void> done; uint64_t seq = 0; };
+    struct KeyQ { std::deque<std::unique_ptr<Task>> q; bool running = false; int prio = 0; };
+    KeyQ* pick() {
+        KeyQ* best = nullptr;
+        for (auto& kv : keys_) {
+            KeyQ& k = kv.second;
+            if (k.running || k.q.empty()) continue;
+            if (!best || k.prio > best->prio || (k.prio == best->prio && k.q.front()->seq < best->q.front()->seq)) best = &k;
+        }
+        return best;
+    }
+    void loop() {
+        std::unique_lock<std::mutex> l(mu_);
+        for (;;) {
+            KeyQ* k = nullptr;
+            cv_.wait(l, [&] { return (k = pick()) != nullptr || stop_; });
+            if (!k) return;                                     // stopping and nothing runnable
+            std::unique_ptr<Task> t = std::move(k->q.front());
+            k->q.pop_front();
+            k->running = true;
+            l.unlock();
+            try { t->fn(); t->done.set_value(); }
+            catch (...) { t->done.set_exception(std::current_exception()); }
+            l.lock();
+            k->running = false;
+            cv_.notify_all();
+        }
+    }
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::unordered_map<uint64_t, KeyQ> keys_;
+    std::vector<std::thread> threads_;
+    uint64_t seq_ = 0;
+    bool stop_ = false;
+};
+
 class Worker {
   public:
     Worker(const std::string& sched_host, int sched_port) : sched_host_(sched_host), sched_port_(sched_port) {
@@ -581,6 +647,7 @@ class Worker {
         hb_ = start_heartbeat(sched_host, sched_port, node_id_of(0, rank_), &hb_stop_);
     }
     ~Worker() {
+        pool_.shutdown();
         hb_stop_ = true;
         if (hb_.joinable()) hb_.join();
         for (auto& s : servers_) if (s->fd >= 0) ::close(s->fd);
@@ -739,8 +806,9 @@ class Worker {
     // async bookkeeping -----------------------------------------------------------------
     void submit(uint64_t key, std::function<void()> fn) {
         std::unique_lock<std::mutex> l(mu_);
-        pending_[key].push_back(std::async(std::launch::async, std::move(fn)));
+        pending_[key].push_back(pool_.submit(key, std::move(fn)));
     }
+    void set_priority(uint64_t key, int prio) { pool_.set_priority(key, prio); }
     void wait(uint64_t key) {
         std::vector<std::future<void>> fs;
         { std::unique_lock<std::mutex> l(mu_); fs.swap(pending_[key]); }
@@ -762,6 +830,7 @@ class Worker {
     std::mutex mu_;
     std::unordered_map<uint64_t, TensorMeta> meta_;
     std::unordered_map<uint64_t, std::vector<std::future<void>>> pending_;
+    IoPool pool_;
 };
 
 static std::unique_ptr<Worker> g_worker;
@@ -867,6 +936,8 @@ HPS_API int hps_sparse_pull_async(uint64_t key, const int64_t* rows, uint64_t n,
     HPS_TRY(g_worker->submit(key, [=] { g_worker->sparse(kSparsePull, key, rows, n, nullptr, nullptr, 0, out, nullptr); }));
 }
 HPS_API int hps_wait(uint64_t key) { HPS_TRY(g_worker->wait(key)); }
+// higher priority keys are served first by the async I/O pool (P3-style: front layers' parameters before back layers')
+HPS_API int hps_set_priority(uint64_t key, int prio) { HPS_TRY(g_worker->set_priority(key, prio)); }
 HPS_API int hps_clear(uint64_t key) { HPS_TRY(g_worker->simple(kParamClear, key, "")); }
 HPS_API int hps_save(uint64_t key, const char* dir) { HPS_TRY(g_worker->simple(kParamSave, key, dir)); }
 HPS_API int hps_load(uint64_t key, const char* dir) { HPS_TRY(g_worker->simple(kParamLoad, key, dir)); }

@@ -234,6 +234,11 @@ class PSWorker(object):
 
     WaitData = Wait
 
+    def SetPriority(self, node_id, priority: int):
+        """Async requests of higher-priority tensors are served first (P3 van behaviour, ps-lite/src/p3_van.h:12-68);
+        requests of one tensor always run in submission order."""
+        _chk(self.lib.hps_set_priority(ctypes.c_uint64(node_id), int(priority)), 'SetPriority')
+
     def pull_full(self, node):
         return self.Pull(node.id).reshape(node.shape)
 

@@ -45,5 +45,27 @@ w.SparsePush(40, np.array([2, 7]), np.ones((2, 4), np.float32))
 w.SparsePush(40, np.array([2]), np.ones((1, 4), np.float32))
 rows = w.SparsePull(40, np.array([2, 7, 3]))
 assert np.allclose(rows[0], -2 * lr, atol=1e-5) and np.allclose(rows[1], -lr, atol=1e-5) and np.allclose(rows[2], 0)
+# async pool: requests of one key keep their order (push, push, pull sees both), priorities reorder across keys
+import time
+w.InitTensor(60, 0, 1 << 16, 1, 0, 0.0, 0.0, 0)
+w.InitTensor(61, 0, 8, 1, 0, 0.0, 0.0, 0)
+one = np.ones(1 << 16, np.float32)
+out = np.empty(1 << 16, np.float32)
+for rep in range(20):
+    w.PushAsync(60, one)
+    w.PushAsync(60, one)
+    w.PullAsync(60, out)
+    w.Wait(60)
+    assert np.all(out == 2.0 * (rep + 1)), (rep, out[:3])
+w.SetPriority(61, 10)
+small = np.empty(8, np.float32)
+for _ in range(30):
+    w.PushAsync(60, one)
+w.PushAsync(61, np.ones(8, np.float32))
+w.PullAsync(61, small)
+w.Wait(61)
+assert np.all(small == 1.0)
+w.Wait(60)
+assert np.allclose(w.Pull(60), 2.0 * 20 + 30)
 print('OK')
 w.finalize()
