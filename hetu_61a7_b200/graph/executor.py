@@ -307,13 +307,18 @@ def topo_sort_dfs(node, visited, topo_order) -> None:
 
 
 def topo_sort_register_ps(node_list, ps_comm, comm_mode, seed, cstable_policy):
-    """Register every PS-resident parameter with the servers (InitTensor RPC)."""
+    """Register every PS-resident parameter with the servers (InitTensor RPC).  Parameters that come
+    earlier in the graph get the higher I/O priority: their pulls are needed first by the next step."""
+    order = 0
     for node in find_topo_sort(node_list):
         if isinstance(node, PlaceholderOp) and node.trainable and (
                 comm_mode == 'PS' or node.is_embed):
             ptype = 0 if not node.is_embed else (2 if cstable_policy is not None else 1)
             if node.initializer is not None:
                 node.initializer.init_on_ps(ps_comm, node.id, ptype, seed + node.id, None)
+            if hasattr(ps_comm, 'SetPriority'):
+                ps_comm.SetPriority(node.id, -order)
+            order += 1
 
 
 def get_pipeline_stage_info(node_list, ctx):
