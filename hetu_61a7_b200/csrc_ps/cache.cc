@@ -111,6 +111,31 @@ class Cache {
         apply_sync(uniq, idx, nver, data);
         scatter(pull_keys, n_pull, out);
     }
+    // Push every not-yet-pushed local update (lines below the push bound and evicted dirty lines) to the servers,
+    // so that a checkpoint taken right after sees them.  The reference's save does not do this (SURVEY 5.4:
+    // "dirty lines are not flushed by save").  Returns the number of rows pushed.
+    size_t flush() {
+        std::unique_lock<std::mutex> l(mu_);
+        std::vector<int64_t> prow, pupd;
+        std::vector<float> pdata;
+        for (auto& kv : lines_) {
+            Line* ln = kv.second.get();
+            if (ln->updates <= 0) continue;
+            prow.push_back(ln->key);
+            pdata.insert(pdata.end(), ln->grad.begin(), ln->grad.end());
+            pupd.push_back(ln->updates);
+            if (ln->version >= 0) ln->version += ln->updates;
+            ln->updates = 0;
+            std::fill(ln->grad.begin(), ln->grad.end(), 0.f);
+        }
+        take_evicted(&prow, &pdata, &pupd);
+        if (!prow.empty()) {
+            worker_sync_embedding(kPushEmbedding, node_, nullptr, nullptr, 0, 0, prow.data(), pdata.data(), pupd.data(),
+                                  prow.size(), nullptr, nullptr, nullptr);
+            perf_.pushed_rows += (int64_t)prow.size();
+        }
+        return prow.size();
+    }
     size_t size() const { return lines_.size(); }
     Perf perf_;
     bool bypass_ = false;
@@ -268,6 +293,10 @@ HPS_API int hcache_update(void* h, const int64_t* keys, uint64_t n, const float*
 HPS_API int hcache_push_pull(void* h, const int64_t* pull_keys, uint64_t n_pull, float* out, const int64_t* push_keys,
                              uint64_t n_push, const float* grads) {
     HC_TRY(static_cast<Cache*>(h)->push_pull(pull_keys, n_pull, out, push_keys, n_push, grads));
+}
+HPS_API int64_t hcache_flush(void* h) {
+    try { return (int64_t)static_cast<Cache*>(h)->flush(); }
+    catch (const std::exception& e) { g_cerr = e.what(); return -1; }
 }
 HPS_API uint64_t hcache_size(void* h) { return static_cast<Cache*>(h)->size(); }
 HPS_API void hcache_bypass(void* h, int on) { static_cast<Cache*>(h)->bypass_ = on != 0; }

@@ -449,6 +449,12 @@ class Executor(object):
         os.makedirs(file_path, exist_ok=True)
         cfg = self.config
         if cfg.ps_comm is not None:
+            # un-pushed updates sitting in the HET caches reach the servers before the shards are written
+            for sub in self.subexecutor.values():
+                for n in sub.topo_order:
+                    cache = getattr(n, 'cache', None)
+                    if cache is not None and hasattr(cache, 'flush'):
+                        cache.flush()
             cfg.ps_comm.BarrierWorker()
         state = {}
         for name, node in self._named_params().items():

@@ -113,6 +113,15 @@ class CacheSparseTable(object):
         names = ['num_lookup', 'num_miss', 'num_evict', 'num_transfered', 'num_pushed', 'num_requests']
         return dict(zip(names, [int(v) for v in out]))
 
+    def flush(self) -> int:
+        """Push every local update that is still below the push bound (and evicted dirty rows) to the servers;
+        ``Executor.save`` calls this so that a checkpoint contains them (the reference does not flush on save)."""
+        self.lib.hcache_flush.restype = ctypes.c_int64
+        n = int(self.lib.hcache_flush(self.handle))
+        if n < 0:
+            self._chk(-1)
+        return n
+
     def bypass(self):
         self.lib.hcache_bypass(self.handle, 1)
 
