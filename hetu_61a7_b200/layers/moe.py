@@ -90,6 +90,7 @@ def topkgating(logits, k, capacity_factor, num_tokens, num_experts, embed_dim):
     if os.environ.get('HETU_MOE_FUSED_GATE', '1') == '1' and k <= 4:
         # one op for softmax + top-k + slots + balance loss (ops/moe_gate.py); the pieces are columns of its output
         packed = ht.fused_topk_gate_op(logits, k)
+        packed.expected_tokens = num_tokens
         col = lambda c: ht.array_reshape_op(ht.slice_op(packed, (0, c), (num_tokens, 1)), [-1])     # noqa: E731
         indices_s = [col(i) for i in range(k)]
         location_s = [col(k + i) for i in range(k)]

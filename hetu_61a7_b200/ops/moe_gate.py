@@ -51,10 +51,15 @@ class FusedTopKGateOp(Op):
         super().__init__(FusedTopKGateOp, [logits], ctx)
         self.k = int(k)
         self.fused_launches = 0
+        #: set by layers.moe.topkgating: the row count its column slices were built for
+        self.expected_tokens = None
 
     def compute(self, input_vals, output_val=None, stream_handle=None):
         x = input_vals[0]
         T, E = x.shape
+        if self.expected_tokens is not None and int(self.expected_tokens) != int(T):
+            raise ValueError('gate was built for num_tokens=%d but the logits have %d rows (pass the total number of tokens '
+                             'per step, batch_size * tokens, to the gate)' % (self.expected_tokens, T))
         if x.device.type == 'meta':
             return torch.empty((T + 1, 3 * self.k), device='meta')
         if L.kernels_on(x) and x.dtype == torch.float32 and self.k <= 4 and E * (self.k + 1) * 4 <= 48 * 1024:
