@@ -34,7 +34,7 @@ namespace hgm {
 
 using hps::Message;
 
-enum MsgType : uint32_t { kMeta = 1, kPullNode, kPullLocal, kPullGraph, kBarrier, kStop, kOk = 200, kError };
+enum MsgType : uint32_t { kMeta = 1, kPullNode, kPullLocal, kPullGraph, kBarrier, kStop, kStats, kOk = 200, kError };
 enum SamplerType : int { kGraphSage = 0, kRandomWalk = 1, kGlobalNode = 2, kLocalNode = 3, kNumSampler = 4 };
 enum CachePolicy : int { kLRU = 0, kLFU = 1, kLFUOpt = 2 };
 
@@ -391,6 +391,7 @@ class Server {
         if (stopped_) throw std::runtime_error("graph server is shutting down");
         auto g = q->q.front();
         q->q.pop_front();
+        ++served_graphs_;
         q->cv.notify_all();
         return g;
     }
@@ -420,6 +421,13 @@ class Server {
                 int64_t gen = barrier_gen_;
                 if (++barrier_cnt_ >= want) { barrier_cnt_ = 0; ++barrier_gen_; barrier_cv_.notify_all(); }
                 else barrier_cv_.wait(l, [&] { return barrier_gen_ != gen || stopped_.load(); });
+                break;
+            }
+            case kStats: {
+                int64_t st[4] = {0, 0, 0, 0};
+                cache_stats(&st[0], &st[1], &st[2]);
+                st[3] = served_graphs_.load();
+                rsp->add(st, 4);
                 break;
             }
             default: rsp->type = kError; rsp->add_str("unknown graph request");
@@ -462,7 +470,7 @@ class Server {
     int fd_ = -1, port_ = 0;
     std::atomic<bool> stopped_{false};
     std::atomic<uint64_t> rr_{0};
-    std::atomic<int64_t> worker_seq_{0};
+    std::atomic<int64_t> worker_seq_{0}, served_graphs_{0};
     std::mutex ready_mu_, barrier_mu_;
     std::condition_variable ready_cv_, barrier_cv_;
     bool ready_ = false;
@@ -518,6 +526,11 @@ class Client {
         p.call(req);
     }
     void stop_server() { Message req; req.type = kStop; try { peer_.call(req); } catch (...) {} }
+    void server_stats(int64_t* out4) {
+        Message req; req.type = kStats;
+        Message rsp = peer_.call(req);
+        memcpy(out4, rsp.arrays[0].data(), 4 * sizeof(int64_t));
+    }
 
   private:
     // queries may be in flight concurrently: each gets a connection of its own from a small pool
@@ -653,4 +666,6 @@ HGM_API int hgm_client_fetch_node(void* h, int64_t q, float* f, int32_t* iv, int
     });
 }
 HGM_API int hgm_client_barrier(void* h, int64_t count, const char* host0, int port0) { HGM_TRY(static_cast<Client*>(h)->barrier(count, host0, port0)); }
+// out4 = {remote-node cache lookups, hits, cached nodes, sub-graphs served} of the server this client talks to
+HGM_API int hgm_client_server_stats(void* h, int64_t* out4) { HGM_TRY(static_cast<Client*>(h)->server_stats(out4)); }
 HGM_API int hgm_client_stop_server(void* h) { HGM_TRY(static_cast<Client*>(h)->stop_server()); }

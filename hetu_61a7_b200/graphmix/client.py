@@ -172,6 +172,13 @@ class Client(object):
                                               ptr.ctypes.data_as(C.I64P), nbr.ctypes.data_as(C.I64P)), 'pull_node')
         return NodePack(f.reshape(waitobj.n, -1) if waitobj.n else f.reshape(0, 0), i.reshape(waitobj.n, -1) if waitobj.n else i.reshape(0, 0), ptr, nbr)
 
+    def server_stats(self):
+        """Counters of the graph server this client is attached to: remote-node cache lookups / hits / size and the
+        number of sub-graphs it has handed out."""
+        out = (ctypes.c_int64 * 4)()
+        C.check(C.lib().hgm_client_server_stats(ctypes.c_void_p(self._h), out), 'server_stats')
+        return {'cache_lookups': out[0], 'cache_hits': out[1], 'cache_size': out[2], 'graphs_served': out[3]}
+
     def stop_server(self):
         C.lib().hgm_client_stop_server(ctypes.c_void_p(self._h))
 

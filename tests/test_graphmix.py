@@ -129,6 +129,9 @@ def _worker(args):
     for k in range(len(ids)):
         orig_u = int(pack.i_feat[k, -1])
         assert len(pack.neighbors(k)) == sum(1 for (a, b) in edge_set if a == orig_u)
+    st = comm.server_stats()
+    assert st['graphs_served'] >= 1 and st['cache_lookups'] > 0 and 0 < st['cache_hits'] <= st['cache_lookups'], st
+    assert 0 < st['cache_size'] <= 0.3 * 900 + 1
     comm.barrier()
     with open(os.path.join(args.out, 'ok_%d' % rank), 'w') as f:
         f.write('ok')
