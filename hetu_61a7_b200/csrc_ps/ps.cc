@@ -814,7 +814,13 @@ class Worker {
         { std::unique_lock<std::mutex> l(mu_); fs.swap(pending_[key]); }
         for (auto& f : fs) f.get();
     }
-    void count(const Message& req, const Message& rsp) { if (record_) { sent_ += req.bytes(); recv_ += rsp.bytes(); } }
+    void count(const Message& req, const Message& rsp) {
+        if (!record_) return;
+        sent_ += req.bytes(); recv_ += rsp.bytes();
+        if (req.type < kNumPsf) { sent_by_[req.type] += req.bytes(); recv_by_[req.type] += rsp.bytes(); calls_by_[req.type] += 1; }
+    }
+    static constexpr uint32_t kNumPsf = 17;                    // data-plane PS functions (PsfType 0..16)
+    std::atomic<uint64_t> sent_by_[17] = {}, recv_by_[17] = {}, calls_by_[17] = {};
     std::atomic<bool> record_{false};
     std::atomic<uint64_t> sent_{0}, recv_{0};
 
@@ -948,6 +954,12 @@ HPS_API int hps_preduce_get_partner(uint64_t key, int want, float wait_ms, int* 
     HPS_TRY({ auto v = g_worker->preduce(key, want, wait_ms); *n_out = (int)v.size(); for (size_t i = 0; i < v.size(); ++i) out[i] = v[i]; });
 }
 HPS_API int hps_start_record() { if (g_worker) g_worker->record_ = true; return 0; }
+// per PS function (index = PsfType 0..16): bytes sent, bytes received, number of requests; arrays of 17
+HPS_API int hps_get_loads_by_function(uint64_t* sent, uint64_t* recv, uint64_t* calls) {
+    if (!g_worker) return -1;
+    for (int i = 0; i < 17; ++i) { sent[i] = g_worker->sent_by_[i]; recv[i] = g_worker->recv_by_[i]; calls[i] = g_worker->calls_by_[i]; }
+    return 0;
+}
 HPS_API int hps_get_loads(uint64_t* sent, uint64_t* recv) { if (!g_worker) return -1; *sent = g_worker->sent_; *recv = g_worker->recv_; return 0; }
 
 // ---- failure detection -------------------------------------------------------------------------

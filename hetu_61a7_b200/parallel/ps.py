@@ -273,6 +273,16 @@ class PSWorker(object):
         self._record_path = path
         self.lib.hps_start_record()
 
+    PSF_NAMES = ('DensePull', 'DensePush', 'DDPushPull', 'SparsePull', 'SparsePush', 'SDPushPull', 'SSPushPull', 'ParamInit',
+                 'ParamClear', 'ParamSave', 'ParamLoad', 'SyncEmbedding', 'PushEmbedding', 'PushSyncEmbedding', 'SSPInit',
+                 'SSPSync', 'PReduceGetPartner')
+
+    def getLoadsByFunction(self):
+        """{PS function: (bytes sent, bytes received, requests)} since ``startRecord`` (reference kvworker.h:39-51)."""
+        arr = [(ctypes.c_uint64 * 17)() for _ in range(3)]
+        self.lib.hps_get_loads_by_function(*arr)
+        return {n: (int(arr[0][i]), int(arr[1][i]), int(arr[2][i])) for i, n in enumerate(self.PSF_NAMES) if arr[2][i]}
+
     def getLoads(self):
         s, r = ctypes.c_uint64(0), ctypes.c_uint64(0)
         self.lib.hps_get_loads(ctypes.byref(s), ctypes.byref(r))
@@ -281,4 +291,6 @@ class PSWorker(object):
             os.makedirs(path, exist_ok=True)
             with open(os.path.join(path, 'loads_%d.txt' % self.rank()), 'w') as fw:
                 fw.write('sent %d\nreceived %d\n' % (s.value, r.value))
+                for name, (bs, br, nc) in self.getLoadsByFunction().items():
+                    fw.write('%s: sent %d received %d requests %d\n' % (name, bs, br, nc))
         return s.value, r.value

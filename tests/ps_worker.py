@@ -93,6 +93,9 @@ w.startRecord(out_dir)
 w.Pull(1)
 s, r = w.getLoads()
 assert r > 4000
+by = w.getLoadsByFunction()
+assert set(by) == {'DensePull'} and by['DensePull'][1] == r and by['DensePull'][2] == 2          # one request per server
+assert 'DensePull:' in open(os.path.join(out_dir, 'loads_%d.txt' % rank)).read()
 w.BarrierWorker()
 print('PS WORKER %d OK' % rank, flush=True)
 w.finalize()
