@@ -213,7 +213,7 @@ def const_pow_gradient(in_arr, grad_arr, out_arr, val, stream=None):
 
 
 def bool(input, output, stream=None):
-    """1 where the input is non-zero... the reference kernel writes (input > 0)."""
+    """output = 1 where input > 0, else 0 (reference Bool.cu: bool_kernel)."""
     return _store(output, (_t(input) > 0).to(_t(output).dtype))
 
 

@@ -65,9 +65,19 @@ def test_transformer_data_pipeline(tmp_path):
     assert 'loss' in out
 
 
+def _free_port_block(span=4):
+    import socket
+    while True:
+        with socket.socket() as s:
+            s.bind(('127.0.0.1', 0))
+            p = s.getsockname()[1]
+        if p + span < 65000:
+            return p
+
+
 def test_gnn_on_sampled_subgraphs(tmp_path):
     _run(['-m', 'hetu_61a7_b200.graphmix.partition', '-d', 'Cora', '-n', '2', '-p', str(tmp_path), '--scale', '0.2'])
     out = _run([os.path.join(EX, 'gnn', 'run_dist.py'), '--data', os.path.join(str(tmp_path), 'Cora'), '--workers', '2', '--gpu', '-1',
-                '--steps', '15', '--port', '28111'])
+                '--steps', '15', '--port', str(_free_port_block())])
     accs = [float(l.rsplit(' ', 1)[1]) for l in out.splitlines() if 'held-out acc' in l]
     assert accs and max(accs) > 0.6, out[-1500:]
