@@ -20,9 +20,34 @@ import hetu as ht                                              # noqa: E402
 from hetu_61a7_b200.models import ctr                          # noqa: E402
 
 
+def run_adult(args, ctx, rank, n):
+    """Wide&Deep on Adult (reference models/wdl_adult.py): real files through --data-dir (adult.data / adult.test),
+    Adult-shaped random data otherwise."""
+    from hetu_61a7_b200.utils import ctr_data
+    if args.data_dir:
+        deep, wide, y = ctr_data.load_adult_data(args.data_dir, return_val=False)
+    else:
+        deep, wide, y = ctr_data.adult_synthetic(n, seed=rank)
+    n = len(y) // args.batch_size * args.batch_size
+    loader = lambda a: ht.dataloader_op([ht.Dataloader(np.asarray(a[:n], np.float32), args.batch_size, 'train')])   # noqa: E731
+    X_deep, X_wide, y_ = [loader(a) for a in deep], loader(wide), loader(y)
+    loss, pred, label, train_op = ctr.wdl_adult(X_deep, X_wide, y_, dim_wide=wide.shape[1])
+    ex = ht.Executor({'train': [loss, pred, label, train_op]}, ctx=ctx, comm_mode=args.comm, bsp=args.bsp, shard_dataloaders=False)
+    for ep in range(args.nepoch):
+        t0, losses, acc = time.time(), [], []
+        for _ in range(ex.get_batch_num('train')):
+            l, p, lab, _ = ex.run('train', convert_to_numpy_ret_vals=True)
+            losses.append(float(np.mean(l)))
+            acc.extend(np.argmax(p, 1) == np.argmax(lab, 1))
+        print('[rank %d] epoch %d loss %.4f acc %.4f  %.0f samples/s' % (rank, ep, np.mean(losses), np.mean(acc), n / (time.time() - t0)),
+              flush=True)
+    if args.comm in ('PS', 'Hybrid') and os.environ.get('DMLC_PS_ROOT_URI'):
+        ht.worker_finish()
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument('--model', default='wdl_criteo', choices=['wdl_criteo', 'dfm_criteo', 'dcn_criteo', 'dc_criteo'])
+    ap.add_argument('--model', default='wdl_criteo', choices=['wdl_criteo', 'dfm_criteo', 'dcn_criteo', 'dc_criteo', 'wdl_adult'])
     ap.add_argument('--batch-size', type=int, default=128)
     ap.add_argument('--vocab', type=int, default=33762577)
     ap.add_argument('--comm', default=None, choices=[None, 'PS', 'Hybrid', 'AllReduce'])
@@ -42,6 +67,8 @@ def main():
     rank = comm.rank if comm is not None else int(os.environ.get('DMLC_WORKER_ID', os.environ.get('RANK', 0)))
     ctx = ht.cpu(0) if args.cpu else ht.gpu(int(os.environ.get('LOCAL_RANK', 0)))
     n = args.iters * args.batch_size
+    if args.model == 'wdl_adult':
+        return run_adult(args, ctx, rank, n)
     if args.data_dir:
         from hetu_61a7_b200.utils import ctr_data
         if args.head:

@@ -21,15 +21,7 @@ import hetu as ht                                              # noqa: E402
 from hetu_61a7_b200.models import ctr                          # noqa: E402
 
 
-def synthetic_adult(n, seed=0):
-    rs = np.random.RandomState(seed)
-    cat = rs.randint(0, 50, (n, 8))
-    cont = rs.randn(n, 4).astype(np.float32)
-    wide = (rs.rand(n, 809) < 0.02).astype(np.float32)
-    score = (cat[:, 0] % 2) + cont[:, 0] + wide[:, :20].sum(1) - 1.0
-    y = np.eye(2, dtype=np.float32)[(score > 0).astype(np.int64)]
-    deep = [cat[:, i].astype(np.float32) for i in range(8)] + [cont[:, i] for i in range(4)]
-    return deep, wide, y
+from hetu_61a7_b200.utils.ctr_data import adult_synthetic as synthetic_adult   # noqa: E402
 
 
 if __name__ == '__main__':

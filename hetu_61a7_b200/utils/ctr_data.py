@@ -132,6 +132,19 @@ def load_adult_data(path, return_val=True):
     return ([d[:n_tr] for d in deep], [d[n_tr:] for d in deep]), (wide[:n_tr], wide[n_tr:]), (labels[:n_tr], labels[n_tr:])
 
 
+def adult_synthetic(n, seed=0):
+    """Adult-shaped random data (8 categorical + 4 continuous deep inputs, 809 wide columns, one-hot labels) for
+    runs without the UCI files."""
+    rs = np.random.RandomState(seed)
+    cat = rs.randint(0, 50, (n, 8))
+    cont = rs.randn(n, 4).astype(np.float32)
+    wide = (rs.rand(n, 809) < 0.02).astype(np.float32)
+    score = (cat[:, 0] % 2) + cont[:, 0] + wide[:, :20].sum(1) - 1.0
+    y = np.eye(2, dtype=np.float32)[(score > 0).astype(np.int64)]
+    deep = [cat[:, i].astype(np.float32) for i in range(8)] + [cont[:, i] for i in range(4)]
+    return deep, wide, y
+
+
 # ------------------------------------------------------------------------------------ avazu
 def process_avazu(path, nrows=None):
     """Avazu click logs (``train.csv``): every column but id / click is categorical."""

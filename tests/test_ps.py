@@ -121,7 +121,13 @@ w.finalize()
         w.stdin.write('\n'); w.stdin.flush()
         expect('DEAD')
         procs.append(_spawn('import hetu_61a7_b200.launcher as l; l.start_server()', env))
-        time.sleep(0.5)
+        # the replacement has taken over once the scheduler stops listing server 0 as dead (its start-up time varies with load)
+        sys.path.insert(0, ROOT)
+        from hetu_61a7_b200.parallel.ps import get_dead_nodes
+        deadline = time.time() + 120
+        while 8 in get_dead_nodes(2.0, '127.0.0.1', port):
+            assert time.time() < deadline, 'replacement server never registered'
+            time.sleep(0.3)
         w.stdin.write('\n'); w.stdin.flush()
         expect('OK')
         assert w.wait(timeout=60) == 0
