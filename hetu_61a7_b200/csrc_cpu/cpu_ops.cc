@@ -140,51 +140,56 @@ API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, 
     const bool go_parallel = (int64_t)M * N * K >= (1 << 18);          // tiny products: the fork/join costs more than it saves
 #pragma omp parallel if (go_parallel)
     {
-#pragma omp for schedule(static) nowait
-        for (int ip = 0; ip < mpanels; ++ip) {
-            float* dst = ap_base + (size_t)ip * K * MR;
-            const int row0 = ip * MR, hgt = std::min(MR, M - row0);
-            if (!transA) {
-                for (int i = 0; i < MR; ++i) {                       // contiguous reads along K, strided writes
-                    if (i < hgt) {
-                        const float* src = A + (size_t)(row0 + i) * lda;
-                        for (int p = 0; p < K; ++p) dst[(size_t)p * MR + i] = src[p];
-                    } else {
-                        for (int p = 0; p < K; ++p) dst[(size_t)p * MR + i] = 0.f;
-                    }
-                }
-            } else {
-                for (int p = 0; p < K; ++p) {
-                    const float* src = A + (size_t)p * lda + row0;
-                    float* d = dst + (size_t)p * MR;
-                    for (int i = 0; i < hgt; ++i) d[i] = src[i];
-                    for (int i = hgt; i < MR; ++i) d[i] = 0.f;
-                }
-            }
-        }
-        if (pack_all_b) {
-#pragma omp for schedule(static)
-            for (int jp = 0; jp < npanels; ++jp) {
-                float* dst = bp_base + (size_t)jp * K * NR;
-                const int col0 = jp * NR, w = std::min(NR, N - col0);
-                if (transB) {
-                    for (int j = 0; j < NR; ++j) {                   // contiguous reads along K
-                        if (j < w) {
-                            const float* src = B + (size_t)(col0 + j) * ldb;
-                            for (int p = 0; p < K; ++p) dst[(size_t)p * NR + j] = src[p];
+        const int kchunks = (K + KC - 1) / KC;                       // packing work items = panel x K chunk, so few panels still fill all threads
+#pragma omp for schedule(static) collapse(2) nowait
+        for (int ip = 0; ip < mpanels; ++ip)
+            for (int kb = 0; kb < kchunks; ++kb) {
+                const int p0 = kb * KC, p1 = std::min(K, p0 + KC);
+                float* dst = ap_base + (size_t)ip * K * MR;
+                const int row0 = ip * MR, hgt = std::min(MR, M - row0);
+                if (!transA) {
+                    for (int i = 0; i < MR; ++i) {                   // contiguous reads along K, strided writes
+                        if (i < hgt) {
+                            const float* src = A + (size_t)(row0 + i) * lda;
+                            for (int p = p0; p < p1; ++p) dst[(size_t)p * MR + i] = src[p];
                         } else {
-                            for (int p = 0; p < K; ++p) dst[(size_t)p * NR + j] = 0.f;
+                            for (int p = p0; p < p1; ++p) dst[(size_t)p * MR + i] = 0.f;
                         }
                     }
                 } else {
-                    for (int p = 0; p < K; ++p) {
-                        float* d = dst + (size_t)p * NR;
-                        const float* src = B + (size_t)p * ldb + col0;
-                        for (int j = 0; j < w; ++j) d[j] = src[j];
-                        for (int j = w; j < NR; ++j) d[j] = 0.f;
+                    for (int p = p0; p < p1; ++p) {
+                        const float* src = A + (size_t)p * lda + row0;
+                        float* d = dst + (size_t)p * MR;
+                        for (int i = 0; i < hgt; ++i) d[i] = src[i];
+                        for (int i = hgt; i < MR; ++i) d[i] = 0.f;
                     }
                 }
             }
+        if (pack_all_b) {
+#pragma omp for schedule(static) collapse(2)
+            for (int jp = 0; jp < npanels; ++jp)
+                for (int kb = 0; kb < kchunks; ++kb) {
+                    const int p0 = kb * KC, p1 = std::min(K, p0 + KC);
+                    float* dst = bp_base + (size_t)jp * K * NR;
+                    const int col0 = jp * NR, w = std::min(NR, N - col0);
+                    if (transB) {
+                        for (int j = 0; j < NR; ++j) {               // contiguous reads along K
+                            if (j < w) {
+                                const float* src = B + (size_t)(col0 + j) * ldb;
+                                for (int p = p0; p < p1; ++p) dst[(size_t)p * NR + j] = src[p];
+                            } else {
+                                for (int p = p0; p < p1; ++p) dst[(size_t)p * NR + j] = 0.f;
+                            }
+                        }
+                    } else {
+                        for (int p = p0; p < p1; ++p) {
+                            float* d = dst + (size_t)p * NR;
+                            const float* src = B + (size_t)p * ldb + col0;
+                            for (int j = 0; j < w; ++j) d[j] = src[j];
+                            for (int j = w; j < NR; ++j) d[j] = 0.f;
+                        }
+                    }
+                }
         } else if (ragged_b) {
             const int col0 = (npanels - 1) * NR, w = N - col0;
 #pragma omp for schedule(static)
