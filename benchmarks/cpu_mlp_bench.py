@@ -13,11 +13,18 @@ train = ht.optim.SGDOptimizer(0.01).minimize(loss)
 ex = ht.Executor([loss, train], ctx=ht.cpu(0))
 xs = [rs.randn(128, 3072).astype(np.float32) for _ in range(8)]
 ys = [np.eye(10, dtype=np.float32)[rs.randint(0, 10, 128)] for _ in range(8)]
-for i in range(20):
+t_w = time.time()
+i = 0
+while time.time() - t_w < 2.0:                      # time-based warm-up: the vCPUs of this kind of box ramp up slowly
     ex.run(feed_dict={x: xs[i % 8], y_: ys[i % 8]})
-t0 = time.time()
-for i in range(steps):
-    out = ex.run(feed_dict={x: xs[i % 8], y_: ys[i % 8]})
-l = float(out[0].asnumpy())
-dt = time.time() - t0
-print('cpu mlp: %.1f us/step, %.0f samples/s, loss %.4f' % (dt / steps * 1e6, 128 * steps / dt, l))
+    i += 1
+best = None
+for rep in range(3):                                # best of three timed repeats
+    t0 = time.time()
+    for i in range(steps):
+        out = ex.run(feed_dict={x: xs[i % 8], y_: ys[i % 8]})
+    l = float(out[0].asnumpy())
+    dt = time.time() - t0
+    best = dt if best is None else min(best, dt)
+    print('cpu mlp: %.1f us/step, %.0f samples/s, loss %.4f' % (dt / steps * 1e6, 128 * steps / dt, l), flush=True)
+print('best: %.0f samples/s' % (128 * steps / best))
