@@ -543,6 +543,10 @@ class Executor(object):
     def clearTimer(self, name='default'):
         self.subexecutor[name].clearTimer()
 
+    def export_chrome_trace(self, path, name='default', **kargs):
+        """With ``timing='cpu'|'gpu'``: write the per-node timeline as a Chrome / Perfetto trace file."""
+        return self.subexecutor[name].export_chrome_trace(path, **kargs)
+
     def __del__(self):
         pass
 

@@ -18,6 +18,10 @@ class TimerSubExecutor(SubExecutor):
         self.use_gpu = timing == 'gpu' and self.device.type == 'cuda'
         self.timer = defaultdict(float)
         self.counts = defaultdict(int)
+        #: (node name, op type, start offset in us, duration in us) of every node execution, for export_chrome_trace
+        self.trace = []
+        self.trace_limit = 200000
+        self._t_origin = time.perf_counter()
         self._wrap()
 
     def _wrap(self):
@@ -40,6 +44,9 @@ class TimerSubExecutor(SubExecutor):
                     ms = (time.perf_counter() - t0) * 1000.0
                 self.timer[_node] += ms
                 self.counts[_node] += 1
+                if len(self.trace) < self.trace_limit:
+                    end_us = (time.perf_counter() - self._t_origin) * 1e6
+                    self.trace.append((_node.name, _node.op_type, end_us - ms * 1e3, ms * 1e3))
                 return out
 
             node.compute = timed
@@ -62,6 +69,26 @@ class TimerSubExecutor(SubExecutor):
                     print(k, cnt[k], '%.6f ms' % agg[k], file=fw)
         if clear:
             self.clearTimer()
+
+    def export_chrome_trace(self, path, clear=True):
+        """Write the recorded node executions as a Chrome / Perfetto trace (``chrome://tracing``, ui.perfetto.dev):
+        one complete event per node run, one row per op type.  The reference has no trace export."""
+        import json
+        import os
+        pid = int(os.environ.get('RANK', '0'))
+        rows = {}
+        events = []
+        for name, op_type, start_us, dur_us in self.trace:
+            tid = rows.setdefault(op_type, len(rows))
+            events.append({'name': name, 'cat': op_type, 'ph': 'X', 'ts': round(start_us, 3), 'dur': round(dur_us, 3),
+                           'pid': pid, 'tid': tid})
+        for op_type, tid in rows.items():
+            events.append({'name': 'thread_name', 'ph': 'M', 'pid': pid, 'tid': tid, 'args': {'name': op_type}})
+        with open(path, 'w') as fw:
+            json.dump({'traceEvents': events, 'displayTimeUnit': 'ms'}, fw)
+        if clear:
+            self.trace = []
+        return len(events)
 
     def clearTimer(self):
         self.timer.clear()

@@ -24,6 +24,14 @@ def test_timer_executor_and_profiler(tmp_path):
     X, Y = rs.randn(8, 20).astype(np.float32), np.eye(4, dtype=np.float32)[rs.randint(0, 4, 8)]
     for _ in range(3):
         ex.run(feed_dict={x: X, y_: Y})
+    import json
+    trace_path = str(tmp_path / 'trace.json')
+    n_events = ex.export_chrome_trace(trace_path)
+    ev = json.load(open(trace_path))['traceEvents']
+    runs = [e for e in ev if e['ph'] == 'X']
+    assert n_events == len(ev) and len(runs) >= 3 * 5 and all(e['dur'] >= 0 for e in runs)
+    assert any(e['cat'] == 'MatMulOp' for e in runs) and any(e['ph'] == 'M' for e in ev)
+    assert [e['ts'] for e in runs] == sorted(e['ts'] for e in runs)
     for level in ('node', 'type'):
         path = str(tmp_path / ('timer_%s.txt' % level))
         ex.logOut(path, log_level=level)
