@@ -403,8 +403,9 @@ class Executor(object):
                 return SubExecutor4Pipedream(name, nodes, config)
             return SubExecutor(name, nodes, config)
 
-        from .fusion import fuse_matmul_relu
+        from .fusion import fuse_matmul_bias, fuse_matmul_relu
         keep = set(all_eval_nodes)
+        self.fused_biases = fuse_matmul_bias([n for n in find_topo_sort(all_eval_nodes) if n not in keep])
         self.fused_epilogues = fuse_matmul_relu([n for n in find_topo_sort(all_eval_nodes) if n not in keep or
                                                  n.op_type not in ('MatMulOp', 'LinearOp')])
         self.subexecutor: Dict[str, SubExecutor] = {k: make(k, v) for k, v in eval_node_dict.items()}

@@ -69,6 +69,10 @@ def _emit(c: _Ctx, node, ins: List[str], out: str):
     elif t == 'MatMulOp' or t == 'LinearOp':
         tA, tB = int(node.matmul_attr_trans_A), int(node.matmul_attr_trans_B)
         act = getattr(node, 'act', 0)               # epilogue-fused activation (graph/fusion.py)
+        if t == 'MatMulOp' and len(ins) == 3:
+            # bias folded into the GEMM by fuse_matmul_bias: the graph still holds the Add (and the Relu) that follow,
+            # and they are exported as themselves, so the product is exported bare
+            ins, act = ins[:2], 0
         mm_out = c.tmp('mm') if act else out
         if t == 'LinearOp' or tA or tB:
             c.add('Gemm', ins, [mm_out], transA=tA, transB=tB, alpha=1.0, beta=1.0)

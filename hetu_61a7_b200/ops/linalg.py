@@ -180,7 +180,7 @@ class MatMulOp(Op):
         return [matmul_op(B, g, True, True, ctx=c), matmul_op(g, A, True, True, ctx=c)]
 
     def infer_shape(self, input_shapes):
-        a, b = input_shapes
+        a, b = input_shapes[:2]                      # a fused bias may ride along as a third input (graph/fusion.py)
         m = a[1] if self.matmul_attr_trans_A else a[0]
         n = b[0] if self.matmul_attr_trans_B else b[1]
         return (m, n)

@@ -420,3 +420,49 @@ def _fused_gate_vs_composed(ctx, tol):
 
 def test_fused_moe_gate_matches_composed_gate():
     _fused_gate_vs_composed(ht.cpu(0), 1e-6)
+
+
+def test_matmul_bias_fusion_keeps_training_identical(tmp_path):
+    """graph/fusion.py::fuse_matmul_bias: matmul + broadcast bias (+ relu) folded into one GEMM on host executors -
+    same losses step by step, same outputs, and the ONNX export of the fused graph still computes the same function."""
+    import os
+    from hetu.onnx import hetu2onnx, onnx2hetu
+    from hetu_61a7_b200.models import cnn
+
+    def run(flag):
+        os.environ['HETU_FUSE_BIAS'] = flag
+        try:
+            np.random.seed(0)
+            rs = np.random.RandomState(0)
+            x, y_ = ht.Variable('x'), ht.Variable('y_')
+            loss, y = cnn.mlp(x, y_, in_dim=48)
+            train = ht.optim.SGDOptimizer(0.05).minimize(loss)
+            ex = ht.Executor([loss, train], ctx=ht.cpu(0), seed=0)
+            out = []
+            for _ in range(6):
+                xs = rs.randn(16, 48).astype(np.float32)
+                ys = np.eye(10, dtype=np.float32)[rs.randint(0, 10, 16)]
+                out.append(float(ex.run(feed_dict={x: xs, y_: ys}, convert_to_numpy_ret_vals=True)[0]))
+            return out, ex.fused_biases, ex.fused_epilogues
+        finally:
+            os.environ.pop('HETU_FUSE_BIAS', None)
+    plain, nb0, _ = run('0')
+    fused, nb1, ne1 = run('all')
+    assert nb0 == 0 and nb1 == 3 and ne1 == 2
+    np.testing.assert_allclose(fused, plain, rtol=1e-6)
+    os.environ['HETU_FUSE_BIAS'] = 'all'
+    try:
+        x, y_ = ht.Variable('x'), ht.Variable('y_')
+        _, y = cnn.mlp(x, y_, in_dim=48)
+        h = ht.relu_op(y)
+        ex = ht.Executor([h], ctx=ht.cpu(0))
+        xv = np.random.RandomState(1).randn(4, 48).astype(np.float32)
+        ref = ex.run(feed_dict={x: xv}, convert_to_numpy_ret_vals=True)[0]
+        assert ex.fused_biases == 3
+        path = str(tmp_path / 'mlp.onnx')
+        hetu2onnx.export(ex, [x], [h], path)
+        ins, outs = onnx2hetu.load_onnx(path)
+        got = ht.Executor(outs, ctx=ht.cpu(0)).run(feed_dict={ins[0]: xv}, convert_to_numpy_ret_vals=True)[0]
+        np.testing.assert_allclose(got, ref, rtol=1e-5, atol=1e-6)
+    finally:
+        os.environ.pop('HETU_FUSE_BIAS', None)
