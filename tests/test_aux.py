@@ -146,3 +146,24 @@ def test_metric_and_data_helpers():
     order = []
     topo_sort_dfs(ht.relu_op(x), set(), order)
     assert order[0] is x and len(order) == 2
+
+
+def test_step_monitor_jsonl_and_prometheus(tmp_path):
+    """utils/monitor.py: step metrics as JSON lines and Prometheus gauges (no counterpart in the reference)."""
+    import json
+    import socket
+    import urllib.request
+    from hetu_61a7_b200.utils.monitor import StepMonitor
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        port = s.getsockname()[1]
+    path = str(tmp_path / 'metrics.jsonl')
+    mon = StepMonitor(samples_per_step=128, log_path=path, prometheus_port=port, rank=0)
+    for i in range(3):
+        mon.observe(0.01 * (i + 1), loss=1.0 / (i + 1), lr=0.1)
+    mon.close()
+    rows = [json.loads(l) for l in open(path)]
+    assert [r['step'] for r in rows] == [1, 2, 3] and rows[-1]['lr'] == 0.1
+    assert abs(rows[-1]['samples_per_second'] - 128 / 0.02) < 1e-6
+    txt = urllib.request.urlopen('http://127.0.0.1:%d/metrics' % port).read().decode()
+    assert 'hetu_loss{rank="0"} 0.333' in txt and 'hetu_step{rank="0"} 3.0' in txt
