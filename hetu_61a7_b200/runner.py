@@ -60,6 +60,9 @@ def main(argv=None):
     parser.add_argument('-w', '--workers', type=int, default=0, help='shorthand: local workers')
     parser.add_argument('-s', '--servers', type=int, default=0, help='shorthand: local PS servers')
     parser.add_argument('-i', '--identify', default='', help='ssh identity file')
+    parser.add_argument('--max-restarts', type=int, default=0,
+                        help='relaunch ALL workers (new rendezvous, HETU_RESTART_COUNT=k) when one exits with an error; '
+                             'the script resumes from its own checkpoint (Executor.save / load).  Not for PS launches.')
     parser.add_argument('command', nargs=argparse.REMAINDER)
     args = parser.parse_args(argv)
     assert args.command, 'heturun: no command given'
@@ -87,17 +90,47 @@ def main(argv=None):
                 env = dict(base_env, DMLC_ROLE='server', DMLC_NODE_HOST='127.0.0.1' if single else host)
                 _spawn([sys.executable, '-c', 'import hetu_61a7_b200.launcher as l; l.start_server()'], env, host)
         time.sleep(0.3)
-    rank = 0
-    workers = []
-    for host, n in cfg.workers.items():
-        for local in range(n):
-            env = dict(base_env, RANK=str(rank), LOCAL_RANK=str(local), DMLC_ROLE='worker',
-                       HETU_LOCAL_WORLD=str(n))
-            workers.append(_spawn(args.command, env, host))
-            rank += 1
-    code = 0
-    for p in workers:
-        code = p.wait() or code
+    def launch_workers(restart):
+        env0 = dict(base_env, HETU_RESTART_COUNT=str(restart))
+        if restart:
+            env0['MASTER_PORT'] = str(_free_port())               # fresh rendezvous for the new incarnation
+        out, rank = [], 0
+        for host, n in cfg.workers.items():
+            for local in range(n):
+                env = dict(env0, RANK=str(rank), LOCAL_RANK=str(local), DMLC_ROLE='worker', HETU_LOCAL_WORLD=str(n))
+                out.append(_spawn(args.command, env, host))
+                rank += 1
+        return out
+
+    # Failure detection on the collective plane (the reference has none: NCCLCHECK aborts one rank and the others
+    # hang in their next collective).  Workers are polled; the first non-zero exit takes the rest down, and with
+    # --max-restarts the whole group is started again.
+    restart, code = 0, 0
+    while True:
+        workers = launch_workers(restart)
+        code, pending = 0, list(workers)
+        while pending and code == 0:
+            for p in list(pending):
+                rc = p.poll()
+                if rc is not None:
+                    pending.remove(p)
+                    code = code or rc
+            if pending and code == 0:
+                time.sleep(0.2)
+        if code != 0:
+            for p in pending:
+                p.terminate()
+            for p in pending:
+                try:
+                    p.wait(timeout=10)
+                except subprocess.TimeoutExpired:
+                    p.kill()
+            if restart < args.max_restarts and not cfg.enable_PS:
+                restart += 1
+                print('heturun: a worker failed with exit code %d; restarting all workers (%d of %d)' % (code, restart, args.max_restarts),
+                      flush=True)
+                continue
+        break
     for p in _children:
         if p.poll() is None:
             p.terminate()
