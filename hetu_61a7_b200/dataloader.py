@@ -69,6 +69,17 @@ class Dataloader(object):
             self._fill(i)
         self._inited = True
 
+    def seek(self, batch_index):
+        """Continue from batch ``batch_index`` of the epoch (checkpoint resume): the pinned ring is refilled from there."""
+        self.init_states()
+        b = int(batch_index) % self.batch_num
+        self.index = b * self.batch_size
+        self.batch_index = b
+        self.rd = 0
+        self.reads = 0
+        for i in range(self.queue_size):
+            self._fill(i)
+
     def reshape_shape(self, shape):
         if not self.parts:
             return tuple(shape)

@@ -482,6 +482,16 @@ class Executor(object):
                     for n in sub.topo_order:
                         if isinstance(n, OptimizerOp):
                             opt_state.update(n.optimizer.state_dict())
+                # where the run stands: position of every dataloader and the step counters (also dropped by the reference)
+                run = {'dataloaders': {}, 'step_count': {}}
+                for sname, sub in self.subexecutor.items():
+                    run['step_count'][sname] = int(getattr(sub, 'step_count', 0))
+                    # keyed by position in the sub-executor's loader list: node names carry process-local ids
+                    for pos_i, n in enumerate(getattr(sub, 'dataloader_nodes', [])):
+                        dls = getattr(n, 'dataloaders', None)
+                        if dls:
+                            run['dataloaders']['%s/%d' % (sname, pos_i)] = {k: int(getattr(d, 'batch_index', 0)) for k, d in dls.items()}
+                opt_state['__run__'] = run
                 with open(os.path.join(file_path, file_name + '.opt'), 'wb') as fw:
                     pickle.dump(opt_state, fw)
         if cfg.ps_comm is not None:
@@ -499,6 +509,20 @@ class Executor(object):
                 for n in sub.topo_order:
                     if isinstance(n, OptimizerOp):
                         n.optimizer.load_state_dict(opt_state)
+            run = opt_state.get('__run__')
+            if run:
+                for sname, sub in self.subexecutor.items():
+                    if sname in run.get('step_count', {}):
+                        sub.step_count = int(run['step_count'][sname])
+                    for pos_i, n in enumerate(getattr(sub, 'dataloader_nodes', [])):
+                        pos = run.get('dataloaders', {}).get('%s/%d' % (sname, pos_i))
+                        dls = getattr(n, 'dataloaders', None)
+                        if pos and dls:
+                            for k, d in dls.items():
+                                if k in pos and hasattr(d, 'seek'):
+                                    d.seek(pos[k])
+                    if hasattr(sub, '_pf'):
+                        sub._pf = {}                         # batches prefetched before the seek are stale
 
     def load_dict(self, state_dict, file_path: str = None, consider_splits: bool = False):
         cfg = self.config

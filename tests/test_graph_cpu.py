@@ -466,3 +466,27 @@ def test_matmul_bias_fusion_keeps_training_identical(tmp_path):
         np.testing.assert_allclose(got, ref, rtol=1e-5, atol=1e-6)
     finally:
         os.environ.pop('HETU_FUSE_BIAS', None)
+
+
+def test_checkpoint_resume_is_exact_with_run_state(tmp_path):
+    """save(..., save_optimizer=True) also records dataloader positions and step counters, so a fresh executor that
+    loads the checkpoint continues on the same batches with the same optimizer state (the reference drops all of this)."""
+    rs = np.random.RandomState(0)
+    X = rs.randn(80, 6).astype(np.float32)
+    Y = np.eye(3, dtype=np.float32)[rs.randint(0, 3, 80)]
+
+    def build():
+        x = ht.dataloader_op([ht.Dataloader(X, 8, 'train')])
+        y_ = ht.dataloader_op([ht.Dataloader(Y, 8, 'train')])
+        w = ht.Variable('w_resume', value=np.zeros((6, 3), np.float32))
+        loss = ht.reduce_mean_op(ht.softmaxcrossentropy_op(ht.matmul_op(x, w), y_), [0])
+        return ht.Executor({'train': [loss, ht.optim.AdamOptimizer(0.05).minimize(loss)]}, ctx=ht.cpu(0))
+    ex = build()
+    ref = [float(ex.run('train')[0].asnumpy()) for _ in range(13)]
+    ex = build()
+    first = [float(ex.run('train')[0].asnumpy()) for _ in range(7)]
+    ex.save(str(tmp_path), 'ckpt.pkl', save_optimizer=True)
+    ex2 = build()
+    ex2.load(str(tmp_path), 'ckpt.pkl')
+    rest = [float(ex2.run('train')[0].asnumpy()) for _ in range(6)]
+    np.testing.assert_allclose(first + rest, ref, rtol=1e-6)
