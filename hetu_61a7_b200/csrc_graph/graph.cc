@@ -196,6 +196,11 @@ class Server {
         ready_cv_.notify_all();
     }
     void wait() { if (accept_th_.joinable()) accept_th_.join(); }
+    // a client asked the server to stop: only flag it and close the listener; the owner's stop() / destructor does the joins
+    void stop_async() {
+        stop_flag_only_ = true;
+        if (fd_ >= 0) ::shutdown(fd_, SHUT_RDWR);
+    }
     void stop() {
         if (stopped_.exchange(true)) return;
         for (auto& q : queues_) { std::unique_lock<std::mutex> l(q->mu); q->cv.notify_all(); }
@@ -204,6 +209,11 @@ class Server {
         if (fd_ >= 0) { ::shutdown(fd_, SHUT_RDWR); ::close(fd_); }
         if (accept_th_.joinable() && std::this_thread::get_id() != accept_th_.get_id()) accept_th_.join();
         for (auto& t : threads_) if (t.joinable()) t.join();
+        // connection handlers run detached and use this object: wake them (their sockets are shut down) and wait
+        // until the last one has left before the caller may destroy the server
+        std::unique_lock<std::mutex> l(conn_mu_);
+        for (int c : conn_fds_) ::shutdown(c, SHUT_RDWR);
+        conn_cv_.wait(l, [&] { return active_conns_ == 0; });
     }
     void cache_stats(int64_t* lookups, int64_t* hits, int64_t* size) {
         *lookups = *hits = *size = 0;
@@ -437,19 +447,28 @@ class Server {
     void accept_loop() {
         while (!stopped_) {
             int c = ::accept(fd_, nullptr, nullptr);
-            if (c < 0) { if (stopped_) break; continue; }
+            if (c < 0) { if (stopped_ || stop_flag_only_) break; continue; }
             int one = 1;
             setsockopt(c, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+            { std::unique_lock<std::mutex> l(conn_mu_); conn_fds_.insert(c); ++active_conns_; }
             std::thread([this, c] {
                 Message req, rsp;
+                bool stop_requested = false;
                 while (hps::recv_msg(c, &req)) {
                     rsp = Message();
-                    if (req.type == kStop) { rsp.type = kOk; try { hps::send_msg(c, rsp); } catch (...) {} ::close(c); std::thread([this] { stop(); }).detach(); return; }
+                    if (req.type == kStop) { rsp.type = kOk; try { hps::send_msg(c, rsp); } catch (...) {} stop_requested = true; break; }
                     try { handle(req, &rsp); }
                     catch (const std::exception& e) { rsp = Message(); rsp.type = kError; rsp.add_str(e.what()); }
                     try { hps::send_msg(c, rsp); } catch (...) { break; }
                 }
-                ::close(c);
+                {
+                    std::unique_lock<std::mutex> l(conn_mu_);
+                    conn_fds_.erase(c);
+                    ::close(c);
+                    --active_conns_;
+                    conn_cv_.notify_all();
+                }
+                if (stop_requested) stop_async();
             }).detach();
         }
     }
@@ -468,7 +487,11 @@ class Server {
     std::vector<std::thread> threads_;
     std::thread accept_th_;
     int fd_ = -1, port_ = 0;
-    std::atomic<bool> stopped_{false};
+    std::atomic<bool> stopped_{false}, stop_flag_only_{false};
+    std::mutex conn_mu_;
+    std::condition_variable conn_cv_;
+    std::set<int> conn_fds_;
+    int active_conns_ = 0;
     std::atomic<uint64_t> rr_{0};
     std::atomic<int64_t> worker_seq_{0}, served_graphs_{0};
     std::mutex ready_mu_, barrier_mu_;

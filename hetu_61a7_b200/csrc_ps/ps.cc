@@ -400,41 +400,80 @@ class Scheduler {
 template <class H>
 class Listener {
   public:
-    Listener(std::shared_ptr<H> h, int port) : h_(h) {
-        drop_pct_ = atoi(env_or("PS_DROP_MSG", "0"));
-        fd_ = listen_on(port, &port_);
-        th_ = std::thread([this] { loop(); });
+    Listener(std::shared_ptr<H> h, int port) : st_(std::make_shared<Shared>()) {
+        st_->h = h;
+        st_->drop_pct = atoi(env_or("PS_DROP_MSG", "0"));
+        st_->fd = listen_on(port, &port_);
+        th_ = std::thread([st = st_] { loop(st); });
     }
     ~Listener() { stop(); }
     int port() const { return port_; }
     void stop() {
-        if (stopped_.exchange(true)) return;
-        ::shutdown(fd_, SHUT_RDWR);
-        ::close(fd_);
+        if (st_->stopped.exchange(true)) { if (th_.joinable()) th_.join(); return; }
+        ::shutdown(st_->fd, SHUT_RDWR);
+        ::close(st_->fd);
         if (th_.joinable()) th_.join();
     }
     void wait() { if (th_.joinable()) th_.join(); }
 
   private:
-    void loop() {
-        while (!stopped_) {
-            int c = ::accept(fd_, nullptr, nullptr);
-            if (c < 0) { if (stopped_) break; continue; }
+    // Everything a connection handler touches lives in this shared block, not in the Listener: handlers run
+    // detached and may sit in a blocking request (barrier, registration) after the Listener is gone.
+    struct Slot { uint32_t seq = 0; bool done = false; Message rsp; };
+    struct Shared {
+        std::shared_ptr<H> h;
+        int fd = -1, drop_pct = 0;
+        std::atomic<bool> stopped{false};
+        std::mutex dd_mu;
+        std::condition_variable dd_cv;
+        std::unordered_map<uint32_t, Slot> slots;
+        // Reply cache for the resend protocol: one slot per sender uid (a sender has one request in
+        // flight).  replay() returns true with the cached reply when `sig` was already handled; when
+        // the first copy is still being handled it waits for it.  Otherwise it claims the slot.
+        bool replay(uint64_t sig, Message* rsp) {
+            uint32_t uid = (uint32_t)(sig >> 32), seq = (uint32_t)sig;
+            std::unique_lock<std::mutex> l(dd_mu);
+            Slot& s = slots[uid];
+            if (s.seq == seq) {
+                dd_cv.wait(l, [&] { return slots[uid].done || slots[uid].seq != seq; });
+                if (slots[uid].seq != seq) return false;
+                *rsp = slots[uid].rsp;
+                return true;
+            }
+            s.seq = seq; s.done = false; s.rsp = Message();
+            return false;
+        }
+        void remember(uint64_t sig, const Message& rsp) {
+            uint32_t uid = (uint32_t)(sig >> 32), seq = (uint32_t)sig;
+            std::unique_lock<std::mutex> l(dd_mu);
+            Slot& s = slots[uid];
+            if (s.seq == seq) { s.rsp = rsp; s.done = true; }
+            dd_cv.notify_all();
+        }
+    };
+    static void loop(std::shared_ptr<Shared> st) {
+        while (!st->stopped) {
+            int c = ::accept(st->fd, nullptr, nullptr);
+            if (c < 0) { if (st->stopped) break; continue; }
             int one = 1;
             setsockopt(c, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
-            std::thread([this, c] {
+            std::thread([st, c] {
                 Message req, rsp;
                 std::minstd_rand rng((unsigned)c * 2654435761u + 12345u);
                 while (recv_msg(c, &req)) {
                     rsp = Message();
-                    if (req.type == kTerminate) { rsp.type = kOk; send_msg(c, rsp); stopped_ = true; ::shutdown(fd_, SHUT_RDWR); break; }
+                    if (req.type == kTerminate) {
+                        rsp.type = kOk; send_msg(c, rsp);
+                        if (!st->stopped.exchange(true)) ::shutdown(st->fd, SHUT_RDWR);      // wait() returns; the owner closes the socket
+                        break;
+                    }
                     int fate = 0;                        // 1 = lose the request, 2 = lose the reply
-                    if (drop_pct_ > 0 && req.type < kRegister && (int)(rng() % 100) < drop_pct_) fate = 1 + (int)(rng() % 2);
+                    if (st->drop_pct > 0 && req.type < kRegister && (int)(rng() % 100) < st->drop_pct) fate = 1 + (int)(rng() % 2);
                     if (fate == 1) continue;
-                    if (req.sig == 0 || !replay(req.sig, &rsp)) {
-                        try { h_->handle(req, &rsp); }
+                    if (req.sig == 0 || !st->replay(req.sig, &rsp)) {
+                        try { st->h->handle(req, &rsp); }
                         catch (const std::exception& e) { rsp = Message(); rsp.type = kError; rsp.add_str(e.what()); }
-                        if (req.sig != 0) remember(req.sig, rsp);
+                        if (req.sig != 0) st->remember(req.sig, rsp);
                     }
                     if (fate == 2) continue;
                     try { send_msg(c, rsp); } catch (...) { break; }
@@ -443,37 +482,9 @@ class Listener {
             }).detach();
         }
     }
-    // Reply cache for the resend protocol: one slot per sender uid (a sender has one request in
-    // flight).  replay() returns true with the cached reply when `sig` was already handled; when
-    // the first copy is still being handled it waits for it.  Otherwise it claims the slot.
-    struct Slot { uint32_t seq = 0; bool done = false; Message rsp; };
-    bool replay(uint64_t sig, Message* rsp) {
-        uint32_t uid = (uint32_t)(sig >> 32), seq = (uint32_t)sig;
-        std::unique_lock<std::mutex> l(dd_mu_);
-        Slot& s = slots_[uid];
-        if (s.seq == seq) {
-            dd_cv_.wait(l, [&] { return slots_[uid].done || slots_[uid].seq != seq; });
-            if (slots_[uid].seq != seq) return false;
-            *rsp = slots_[uid].rsp;
-            return true;
-        }
-        s.seq = seq; s.done = false; s.rsp = Message();
-        return false;
-    }
-    void remember(uint64_t sig, const Message& rsp) {
-        uint32_t uid = (uint32_t)(sig >> 32), seq = (uint32_t)sig;
-        std::unique_lock<std::mutex> l(dd_mu_);
-        Slot& s = slots_[uid];
-        if (s.seq == seq) { s.rsp = rsp; s.done = true; }
-        dd_cv_.notify_all();
-    }
-    std::shared_ptr<H> h_;
-    int fd_ = -1, port_ = 0, drop_pct_ = 0;
+    std::shared_ptr<Shared> st_;
+    int port_ = 0;
     std::thread th_;
-    std::atomic<bool> stopped_{false};
-    std::mutex dd_mu_;
-    std::condition_variable dd_cv_;
-    std::unordered_map<uint32_t, Slot> slots_;
 };
 
 // ------------------------------------------------------------------------------------ worker
