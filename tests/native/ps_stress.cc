@@ -28,6 +28,12 @@ int hps_pull_async(uint64_t key, float* out);
 int hps_wait(uint64_t key);
 int hps_set_priority(uint64_t key, int prio);
 int hps_barrier(int group);
+void* hcache_create(uint64_t limit, uint64_t length, uint64_t width, uint64_t node_id, int policy, int64_t pull_bound, int64_t push_bound);
+void hcache_destroy(void* h);
+int hcache_lookup(void* h, const int64_t* keys, uint64_t n, float* out);
+int hcache_update(void* h, const int64_t* keys, uint64_t n, const float* grads);
+int64_t hcache_flush(void* h);
+const char* hcache_last_error();
 }
 
 #define CHECK(x) do { if ((x) != 0) { fprintf(stderr, "FAILED %s: %s\n", #x, hps_last_error()); exit(1); } } while (0)
@@ -69,6 +75,33 @@ int main() {
     std::vector<float> so(8);
     CHECK(hps_sparse_pull(200, rows.data(), 1, so.data()));
     if (std::fabs(so[0] - 0.5f * T * ROUNDS) > 1e-2f) { fprintf(stderr, "sparse row ends at %f\n", so[0]); return 1; }
+    // HET cache in front of a versioned table: three policies, concurrent lookups / updates, then a flush
+    CHECK(hps_init_tensor(300, 2, 256, 4, 0, 0.0, 0.0, 1));
+    std::vector<std::thread> ct;
+    for (int pol = 0; pol < 3; ++pol)
+        ct.emplace_back([pol] {
+            void* c = hcache_create(40, 256, 4, 300, pol, 2, 2);
+            std::vector<int64_t> keys(16);
+            std::vector<float> rows(16 * 4), g(16 * 4, 0.25f);
+            unsigned state = 17u * (pol + 1);
+            for (int it = 0; it < 60; ++it) {
+                for (auto& k : keys) { state = state * 1664525u + 1013904223u; k = (int64_t)((state >> 8) % 256); }
+                if (hcache_lookup(c, keys.data(), keys.size(), rows.data()) != 0) { fprintf(stderr, "lookup: %s\n", hcache_last_error()); exit(1); }
+                if (hcache_update(c, keys.data(), keys.size(), g.data()) != 0) { fprintf(stderr, "update: %s\n", hcache_last_error()); exit(1); }
+            }
+            if (hcache_flush(c) < 0) { fprintf(stderr, "flush: %s\n", hcache_last_error()); exit(1); }
+            hcache_destroy(c);
+        });
+    for (auto& x : ct) x.join();
+    {
+        std::vector<int64_t> all(256);
+        for (int i = 0; i < 256; ++i) all[i] = i;
+        std::vector<float> tbl(256 * 4);
+        CHECK(hps_sparse_pull(300, all.data(), all.size(), tbl.data()));
+        double sum = 0;
+        for (float v : tbl) sum += v;
+        if (std::fabs(sum - 3.0 * 60 * 16 * 4 * 0.25) > 1e-2) { fprintf(stderr, "cache table sums to %f\n", sum); return 1; }
+    }
     hps_worker_finalize();
     hps_stop_servers();
     hps_stop_scheduler();
