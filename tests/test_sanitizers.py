@@ -20,6 +20,8 @@ CASES = {
                 'ML ASAN OK'),
     'gemm_asan': (['-fsanitize=address,undefined', '-fno-omit-frame-pointer', '-fopenmp', '-march=x86-64-v3'],
                   ['tests/native/cpu_gemm_asan.cc', 'csrc_cpu/cpu_ops.cc'], 'CPU GEMM ASAN OK'),
+    'cpu_ops_asan': (['-fsanitize=address,undefined', '-fno-omit-frame-pointer', '-fopenmp', '-march=x86-64-v3'],
+                     ['tests/native/cpu_ops_asan.cc', 'csrc_cpu/cpu_ops.cc', 'csrc_cpu/bfc_allocator.cc'], 'CPU OPS ASAN OK'),
 }
 
 
