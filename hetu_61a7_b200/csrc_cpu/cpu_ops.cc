@@ -26,7 +26,16 @@
 #include <immintrin.h>
 
 namespace {
-constexpr int KC = 384;
+// K chunk walked per micro-kernel call.  384 measured best on the MLP shapes of BASELINE config 1 (a sweep of
+// 96..384 on a shared 8-vCPU box stayed within noise); HETU_CPU_GEMM_KC overrides it (tuning knob).
+int kc_setting() {
+    static const int v = [] {
+        const char* e = getenv("HETU_CPU_GEMM_KC");
+        int k = e ? atoi(e) : 0;
+        return k >= 16 ? k : 384;
+    }();
+    return v;
+}
 
 struct Kern { int MR, NR; void (*fn)(int, const float*, const float*, int, float*, int, int, int, float, float); };
 
@@ -97,6 +106,67 @@ void kern_scalar(int kc, const float* a, const float* b, int ldbk, float* c, int
         for (int j = 0; j < nr; ++j) c[(size_t)i * ldc + j] = alpha * acc[i][j] + (beta != 0.f ? beta * c[(size_t)i * ldc + j] : 0.f);
 }
 
+// Packs up to 16 rows x columns [p0, p1) of a row-major matrix into a panel of width W: dst[(p - p0) * W + off + i]
+// (rows beyond hgt read as zero; the first popcount(sm) lanes of a column are stored).  16 x 16 blocks are transposed in registers - unpack 32-bit, unpack 64-bit, two
+// rounds of 128-bit lane shuffles - so both the reads and the writes are whole vectors instead of a 4-byte scatter.
+__attribute__((target("avx512f"), noinline))
+void pack_rows_avx512(const float* src, int ld, int hgt, int p0, int p1, float* dst, int W, int off, unsigned sm) {
+    for (int p = p0; p < p1; p += 16) {
+        const int cols = std::min(16, p1 - p);
+        const __mmask16 lm = cols >= 16 ? (__mmask16)0xffff : (__mmask16)((1u << cols) - 1);
+        __m512 r[16], t[16], u[16];
+        for (int i = 0; i < 16; ++i)
+            r[i] = i < hgt ? _mm512_maskz_loadu_ps(lm, src + (size_t)i * ld + p) : _mm512_setzero_ps();
+        for (int i = 0; i < 8; ++i) {
+            t[2 * i] = _mm512_unpacklo_ps(r[2 * i], r[2 * i + 1]);
+            t[2 * i + 1] = _mm512_unpackhi_ps(r[2 * i], r[2 * i + 1]);
+        }
+        for (int g = 0; g < 4; ++g) {                    // u[4g + j], lane L: rows 4g..4g+3 of column 4L + j
+            __m512d a0 = _mm512_castps_pd(t[4 * g]), a1 = _mm512_castps_pd(t[4 * g + 1]);
+            __m512d a2 = _mm512_castps_pd(t[4 * g + 2]), a3 = _mm512_castps_pd(t[4 * g + 3]);
+            u[4 * g] = _mm512_castpd_ps(_mm512_unpacklo_pd(a0, a2));
+            u[4 * g + 1] = _mm512_castpd_ps(_mm512_unpackhi_pd(a0, a2));
+            u[4 * g + 2] = _mm512_castpd_ps(_mm512_unpacklo_pd(a1, a3));
+            u[4 * g + 3] = _mm512_castpd_ps(_mm512_unpackhi_pd(a1, a3));
+        }
+        __m512 out[16];
+        for (int j = 0; j < 4; ++j) {
+            __m512 a = _mm512_shuffle_f32x4(u[j], u[4 + j], 0x88), b = _mm512_shuffle_f32x4(u[8 + j], u[12 + j], 0x88);
+            __m512 c = _mm512_shuffle_f32x4(u[j], u[4 + j], 0xdd), d = _mm512_shuffle_f32x4(u[8 + j], u[12 + j], 0xdd);
+            out[j] = _mm512_shuffle_f32x4(a, b, 0x88);
+            out[8 + j] = _mm512_shuffle_f32x4(a, b, 0xdd);
+            out[4 + j] = _mm512_shuffle_f32x4(c, d, 0x88);
+            out[12 + j] = _mm512_shuffle_f32x4(c, d, 0xdd);
+        }
+        for (int q = 0; q < cols; ++q) _mm512_mask_storeu_ps(dst + (size_t)(p - p0 + q) * W + off, (__mmask16)sm, out[q]);
+    }
+}
+
+// op(B)[p0:p1, col0:col0 + w] -> dst[(p - p0) * NR + j], columns beyond w zero-filled
+void pack_b_chunk(const float* B, int ldb, int transB, int col0, int w, int p0, int p1, int NR, float* dst) {
+    if (!transB) {
+        for (int p = p0; p < p1; ++p) {
+            float* d = dst + (size_t)(p - p0) * NR;
+            const float* src = B + (size_t)p * ldb + col0;
+            if (w == NR) { std::memcpy(d, src, sizeof(float) * NR); continue; }
+            for (int j = 0; j < w; ++j) d[j] = src[j];
+            for (int j = w; j < NR; ++j) d[j] = 0.f;
+        }
+    } else if (NR == 32) {                                           // AVX-512 kernel: two 16-row register transposes
+        for (int o = 0; o < 32; o += 16)
+            pack_rows_avx512(B + (size_t)(col0 + o) * ldb, ldb, std::max(0, std::min(16, w - o)), p0, p1, dst, 32, o, 0xffffu);
+    } else {
+        for (int j = 0; j < NR; ++j) {                               // contiguous reads along K
+            if (j < w) {
+                const float* src = B + (size_t)(col0 + j) * ldb;
+                for (int p = p0; p < p1; ++p) dst[(size_t)(p - p0) * NR + j] = src[p];
+            } else {
+                for (int p = p0; p < p1; ++p) dst[(size_t)(p - p0) * NR + j] = 0.f;
+            }
+        }
+    }
+}
+
 const Kern& pick_kernel() {
     static const Kern k = [] {
         __builtin_cpu_init();
@@ -114,7 +184,7 @@ API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, 
                         float alpha, float beta) {
     if (M <= 0 || N <= 0) return 0;
     const Kern& kr = pick_kernel();
-    const int MR = kr.MR, NR = kr.NR;
+    const int MR = kr.MR, NR = kr.NR, KC = kc_setting();
     if (K <= 0) {
 #pragma omp parallel for
         for (int64_t i = 0; i < (int64_t)M * N; ++i) C[i] = beta == 0.f ? 0.f : beta * C[i];
@@ -123,20 +193,15 @@ API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, 
     const int lda = transA ? M : K, ldb = transB ? K : N;
     const int mpanels = (M + MR - 1) / MR, npanels = (N + NR - 1) / NR;
     // op(A) is packed once into row panels [panel][K][MR] (each element is copied once, in parallel).
-    // op(B) is read in place when it is row-major K x N (a panel row is 32 consecutive floats); only
-    // the ragged last panel and the transposed layout go through a packed copy [panel][K][NR].
-    static thread_local std::vector<float> apack_store, bpack_store;
+    // op(B) is read in place when it is row-major K x N with a short K (a panel row is 32 consecutive floats).
+    // Otherwise - transposed layout, long K (rows ldb floats apart defeat the L1 prefetcher and collide in its
+    // sets), ragged last panel - the thread that is about to use a KC x NR chunk packs it into its own buffer
+    // right before the micro-kernel calls: the chunk stays in that core's L1/L2 and there is no B stage or barrier.
+    static thread_local std::vector<float> apack_store, bchunk_store;
     std::vector<float>& apack = apack_store;
-    std::vector<float>& bpack = bpack_store;
     apack.resize((size_t)mpanels * K * MR);
-    // in-place B rows are ldb floats apart: fine while a K chunk of a panel stays within a few pages per row group,
-    // but with many K steps the strided walk defeats the L1 prefetcher - pack then (one contiguous 128-byte row per step)
     const bool pack_all_b = transB != 0 || (K >= 512 && getenv("HETU_CPU_GEMM_INPLACE_B") == nullptr);
-    const bool ragged_b = (N % NR) != 0;
-    if (pack_all_b) bpack.resize((size_t)npanels * K * NR);
-    else if (ragged_b) bpack.resize((size_t)K * NR);
     float* ap_base = apack.data();
-    float* bp_base = bpack.data();
     const bool go_parallel = (int64_t)M * N * K >= (1 << 18);          // tiny products: the fork/join costs more than it saves
 #pragma omp parallel if (go_parallel)
     {
@@ -147,7 +212,9 @@ API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, 
                 const int p0 = kb * KC, p1 = std::min(K, p0 + KC);
                 float* dst = ap_base + (size_t)ip * K * MR;
                 const int row0 = ip * MR, hgt = std::min(MR, M - row0);
-                if (!transA) {
+                if (!transA && MR == 12) {
+                    pack_rows_avx512(A + (size_t)row0 * lda, lda, hgt, p0, p1, dst + (size_t)p0 * MR, 12, 0, 0x0fffu);
+                } else if (!transA) {
                     for (int i = 0; i < MR; ++i) {                   // contiguous reads along K, strided writes
                         if (i < hgt) {
                             const float* src = A + (size_t)(row0 + i) * lda;
@@ -165,43 +232,9 @@ API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, 
                     }
                 }
             }
-        if (pack_all_b) {
-#pragma omp for schedule(static) collapse(2)
-            for (int jp = 0; jp < npanels; ++jp)
-                for (int kb = 0; kb < kchunks; ++kb) {
-                    const int p0 = kb * KC, p1 = std::min(K, p0 + KC);
-                    float* dst = bp_base + (size_t)jp * K * NR;
-                    const int col0 = jp * NR, w = std::min(NR, N - col0);
-                    if (transB) {
-                        for (int j = 0; j < NR; ++j) {               // contiguous reads along K
-                            if (j < w) {
-                                const float* src = B + (size_t)(col0 + j) * ldb;
-                                for (int p = p0; p < p1; ++p) dst[(size_t)p * NR + j] = src[p];
-                            } else {
-                                for (int p = p0; p < p1; ++p) dst[(size_t)p * NR + j] = 0.f;
-                            }
-                        }
-                    } else {
-                        for (int p = p0; p < p1; ++p) {
-                            float* d = dst + (size_t)p * NR;
-                            const float* src = B + (size_t)p * ldb + col0;
-                            for (int j = 0; j < w; ++j) d[j] = src[j];
-                            for (int j = w; j < NR; ++j) d[j] = 0.f;
-                        }
-                    }
-                }
-        } else if (ragged_b) {
-            const int col0 = (npanels - 1) * NR, w = N - col0;
-#pragma omp for schedule(static)
-            for (int p = 0; p < K; ++p) {
-                float* d = bp_base + (size_t)p * NR;
-                const float* src = B + (size_t)p * ldb + col0;
-                for (int j = 0; j < w; ++j) d[j] = src[j];
-                for (int j = w; j < NR; ++j) d[j] = 0.f;
-            }
-        } else {
 #pragma omp barrier
-        }
+        bchunk_store.resize((size_t)KC * NR);                        // this thread's B chunk
+        float* bchunk = bchunk_store.data();
         // tiles of C: a few row panels x a few column panels each, about two tiles per thread at least
         const int nthr = omp_get_num_threads();
         int tp_m = std::max(1, std::min(mpanels, 96 / MR)), tp_n = std::max(1, std::min(npanels, 128 / NR));
@@ -223,9 +256,14 @@ API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, 
                         const int col = jp * NR, nr = std::min(NR, N - col);
                         const float* bptr;
                         int ldbk;
-                        if (pack_all_b) { bptr = bp_base + (size_t)jp * K * NR + (size_t)pc * NR; ldbk = NR; }
-                        else if (nr < NR) { bptr = bp_base + (size_t)pc * NR; ldbk = NR; }
-                        else { bptr = B + (size_t)pc * ldb + col; ldbk = ldb; }
+                        if (pack_all_b || nr < NR) {
+                            pack_b_chunk(B, ldb, transB, col, nr, pc, pc + kc, NR, bchunk);
+                            bptr = bchunk;
+                            ldbk = NR;
+                        } else {
+                            bptr = B + (size_t)pc * ldb + col;
+                            ldbk = ldb;
+                        }
                         for (int ip = ip0; ip < ip1; ++ip) {
                             const int row = ip * MR;
                             kr.fn(kc, ap_base + (size_t)ip * K * MR + (size_t)pc * MR, bptr, ldbk, C + (size_t)row * N + col, N,
@@ -249,60 +287,86 @@ API int hetu_cpu_batch_matmul(const float* A, const float* B, float* C, int batc
 // ------------------------------------------------------------------------------------------------
 // element-wise (reference AddConst/AddElewise/MultiplyConst/MultiplyElewise/DivideConst/DivideElewise/
 // Opposite/Sqrt/Relu/Sigmoid/Tanh/Gelu .cpp).  op codes are private to this library.
+// below this many elements an OpenMP region costs more than it saves (waking the pool takes tens of microseconds)
+constexpr int64_t kParallelMin = 1 << 16;
 enum { U_RELU = 0, U_SIGMOID, U_TANH, U_GELU, U_SQRT, U_RSQRT, U_NEG, U_EXP, U_LOG, U_ABS, U_ADDC, U_MULC, U_CDIV };
 enum { B_ADD = 0, B_SUB, B_MUL, B_DIV, B_RELU_GRAD, B_SIGMOID_GRAD, B_TANH_GRAD, B_GELU_GRAD };
 
-API int hetu_cpu_unary(const float* x, float* y, int64_t n, int op, float c) {
+// the op switch sits outside the loop: each instantiation is a straight-line loop the compiler vectorises
+namespace {
+template <class F>
+inline void map1(const float* x, float* y, int64_t n, F f) {
+    if (n < kParallelMin) {
+#pragma omp simd
+        for (int64_t i = 0; i < n; ++i) y[i] = f(x[i]);
+        return;
+    }
 #pragma omp parallel for simd
-    for (int64_t i = 0; i < n; ++i) {
-        float v = x[i], r;
-        switch (op) {
-            case U_RELU: r = v > 0.f ? v : 0.f; break;
-            case U_SIGMOID: r = 1.f / (1.f + std::exp(-v)); break;
-            case U_TANH: r = std::tanh(v); break;
-            case U_GELU: r = 0.5f * v * (1.f + std::erf(v * 0.70710678118f)); break;
-            case U_SQRT: r = std::sqrt(v); break;
-            case U_RSQRT: r = 1.f / std::sqrt(v); break;
-            case U_NEG: r = -v; break;
-            case U_EXP: r = std::exp(v); break;
-            case U_LOG: r = std::log(v); break;
-            case U_ABS: r = std::fabs(v); break;
-            case U_ADDC: r = v + c; break;
-            case U_MULC: r = v * c; break;
-            default: r = c / v; break;
-        }
-        y[i] = r;
+    for (int64_t i = 0; i < n; ++i) y[i] = f(x[i]);
+}
+template <class Body>
+inline void for_n(int64_t n, Body body) {
+    if (n < kParallelMin) {
+#pragma omp simd
+        for (int64_t i = 0; i < n; ++i) body(i);
+        return;
+    }
+#pragma omp parallel for simd
+    for (int64_t i = 0; i < n; ++i) body(i);
+}
+template <class F>
+inline void map2(const float* x, const float* z, float* y, int64_t n, F f) {
+    if (n < kParallelMin) {
+#pragma omp simd
+        for (int64_t i = 0; i < n; ++i) y[i] = f(x[i], z[i]);
+        return;
+    }
+#pragma omp parallel for simd
+    for (int64_t i = 0; i < n; ++i) y[i] = f(x[i], z[i]);
+}
+}  // namespace
+
+API int hetu_cpu_unary(const float* x, float* y, int64_t n, int op, float c) {
+    switch (op) {
+        case U_RELU: map1(x, y, n, [](float v) { return v > 0.f ? v : 0.f; }); break;
+        case U_SIGMOID: map1(x, y, n, [](float v) { return 1.f / (1.f + std::exp(-v)); }); break;
+        case U_TANH: map1(x, y, n, [](float v) { return std::tanh(v); }); break;
+        case U_GELU: map1(x, y, n, [](float v) { return 0.5f * v * (1.f + std::erf(v * 0.70710678118f)); }); break;
+        case U_SQRT: map1(x, y, n, [](float v) { return std::sqrt(v); }); break;
+        case U_RSQRT: map1(x, y, n, [](float v) { return 1.f / std::sqrt(v); }); break;
+        case U_NEG: map1(x, y, n, [](float v) { return -v; }); break;
+        case U_EXP: map1(x, y, n, [](float v) { return std::exp(v); }); break;
+        case U_LOG: map1(x, y, n, [](float v) { return std::log(v); }); break;
+        case U_ABS: map1(x, y, n, [](float v) { return std::fabs(v); }); break;
+        case U_ADDC: map1(x, y, n, [c](float v) { return v + c; }); break;
+        case U_MULC: map1(x, y, n, [c](float v) { return v * c; }); break;
+        default: map1(x, y, n, [c](float v) { return c / v; }); break;
     }
     return 0;
 }
 
 // y = x (op) z ; for the *_GRAD codes x is the forward input (or output for sigmoid/tanh) and z the adjoint
 API int hetu_cpu_binary(const float* x, const float* z, float* y, int64_t n, int op) {
-#pragma omp parallel for simd
-    for (int64_t i = 0; i < n; ++i) {
-        float a = x[i], b = z[i], r;
-        switch (op) {
-            case B_ADD: r = a + b; break;
-            case B_SUB: r = a - b; break;
-            case B_MUL: r = a * b; break;
-            case B_DIV: r = a / b; break;
-            case B_RELU_GRAD: r = a > 0.f ? b : 0.f; break;
-            case B_SIGMOID_GRAD: r = b * a * (1.f - a); break;
-            case B_TANH_GRAD: r = b * (1.f - a * a); break;
-            default: {
+    switch (op) {
+        case B_ADD: map2(x, z, y, n, [](float a, float b) { return a + b; }); break;
+        case B_SUB: map2(x, z, y, n, [](float a, float b) { return a - b; }); break;
+        case B_MUL: map2(x, z, y, n, [](float a, float b) { return a * b; }); break;
+        case B_DIV: map2(x, z, y, n, [](float a, float b) { return a / b; }); break;
+        case B_RELU_GRAD: map2(x, z, y, n, [](float a, float b) { return a > 0.f ? b : 0.f; }); break;
+        case B_SIGMOID_GRAD: map2(x, z, y, n, [](float a, float b) { return b * a * (1.f - a); }); break;
+        case B_TANH_GRAD: map2(x, z, y, n, [](float a, float b) { return b * (1.f - a * a); }); break;
+        default:
+            map2(x, z, y, n, [](float a, float b) {
                 float cdf = 0.5f * (1.f + std::erf(a * 0.70710678118f));
                 float pdf = 0.3989422804f * std::exp(-0.5f * a * a);
-                r = b * (cdf + a * pdf);
-            }
-        }
-        y[i] = r;
+                return b * (cdf + a * pdf);
+            });
     }
     return 0;
 }
 
 API int hetu_cpu_array_set(float* x, int64_t n, float v) {
-#pragma omp parallel for simd
-    for (int64_t i = 0; i < n; ++i) x[i] = v;
+    for_n(n, [=](int64_t i) { x[i] = v; });
     return 0;
 }
 
@@ -313,7 +377,7 @@ API int hetu_cpu_reshape(const float* x, float* y, int64_t n) {
 
 // bias-style broadcast of x[cols] (or x[rows/rep, cols]) over the leading dim (BroadcastTo.cpp)
 API int hetu_cpu_broadcast_to(const float* x, float* y, int64_t in_n, int64_t out_n) {
-#pragma omp parallel for
+#pragma omp parallel for if (out_n >= kParallelMin)
     for (int64_t i = 0; i < out_n; ++i) y[i] = x[i % in_n];
     return 0;
 }
@@ -387,7 +451,7 @@ API int hetu_cpu_pad_grad(const float* gy, float* gx, int64_t nc, int H, int W, 
 // ------------------------------------------------------------------------------------------------
 // softmax family (Softmax.cpp, SoftmaxCrossEntropy.cpp)
 API int hetu_cpu_softmax(const float* x, float* y, int64_t rows, int64_t cols) {
-#pragma omp parallel for
+#pragma omp parallel for if (rows * cols >= kParallelMin)
     for (int64_t r = 0; r < rows; ++r) {
         const float* xr = x + r * cols;
         float* yr = y + r * cols;
@@ -402,7 +466,7 @@ API int hetu_cpu_softmax(const float* x, float* y, int64_t rows, int64_t cols) {
 }
 
 API int hetu_cpu_softmax_cross_entropy(const float* x, const float* label, float* loss, int64_t rows, int64_t cols) {
-#pragma omp parallel for
+#pragma omp parallel for if (rows * cols >= kParallelMin)
     for (int64_t r = 0; r < rows; ++r) {
         const float* xr = x + r * cols;
         const float* lr = label + r * cols;
@@ -419,7 +483,7 @@ API int hetu_cpu_softmax_cross_entropy(const float* x, const float* label, float
 
 API int hetu_cpu_softmax_cross_entropy_grad(const float* x, const float* label, const float* g, float* gx,
                                             int64_t rows, int64_t cols) {
-#pragma omp parallel for
+#pragma omp parallel for if (rows * cols >= kParallelMin)
     for (int64_t r = 0; r < rows; ++r) {
         const float* xr = x + r * cols;
         const float* lr = label + r * cols;
@@ -617,11 +681,10 @@ static inline uint32_t mix32(uint64_t z) {
 
 API int hetu_cpu_dropout(const float* x, float* y, int64_t n, float keep_prob, uint64_t seed) {
     float inv = 1.f / keep_prob;
-#pragma omp parallel for
-    for (int64_t i = 0; i < n; ++i) {
+    for_n(n, [=](int64_t i) {
         float u = mix32(seed * 0x100000001B3ull + (uint64_t)i) * (1.f / 4294967296.f);
         y[i] = u < keep_prob ? x[i] * inv : 0.f;
-    }
+    });
     return 0;
 }
 
@@ -639,8 +702,7 @@ API int hetu_cpu_embedding_lookup(const float* table, const int64_t* ids, float*
 }
 
 API int hetu_cpu_sgd_update(float* p, const float* g, int64_t n, float lr, float l2) {
-#pragma omp parallel for simd
-    for (int64_t i = 0; i < n; ++i) p[i] -= lr * (g[i] + l2 * p[i]);
+    for_n(n, [=](int64_t i) { p[i] -= lr * (g[i] + l2 * p[i]); });
     return 0;
 }
 
@@ -658,38 +720,35 @@ API int hetu_cpu_sgd_sparse_update(float* p, const int64_t* ids, const float* g,
 
 API int hetu_cpu_momentum_update(float* p, const float* g, float* vel, int64_t n, float lr, float momentum,
                                  int nesterov, float l2) {
-#pragma omp parallel for simd
-    for (int64_t i = 0; i < n; ++i) {
+    for_n(n, [=](int64_t i) {
         float gi = g[i] + l2 * p[i];
         float v = momentum * vel[i] - lr * gi;
         vel[i] = v;
         p[i] += nesterov ? momentum * v - lr * gi : v;
-    }
+    });
     return 0;
 }
 
 API int hetu_cpu_adagrad_update(float* p, const float* g, float* acc, int64_t n, float lr, float eps, float l2) {
-#pragma omp parallel for simd
-    for (int64_t i = 0; i < n; ++i) {
+    for_n(n, [=](int64_t i) {
         float gi = g[i] + l2 * p[i];
         acc[i] += gi * gi;
         p[i] -= lr * gi / (std::sqrt(acc[i]) + eps);
-    }
+    });
     return 0;
 }
 
 API int hetu_cpu_adam_update(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
                              float beta2, float eps, int64_t step, float l2, int amsgrad, float* vmax) {
     float c1 = 1.f - std::pow(beta1, (float)step), c2 = 1.f - std::pow(beta2, (float)step);
-#pragma omp parallel for simd
-    for (int64_t i = 0; i < n; ++i) {
+    for_n(n, [=](int64_t i) {
         float gi = g[i] + l2 * p[i];
         m[i] = beta1 * m[i] + (1.f - beta1) * gi;
         v[i] = beta2 * v[i] + (1.f - beta2) * gi * gi;
         float vh = v[i];
         if (amsgrad) { vmax[i] = std::max(vmax[i], vh); vh = vmax[i]; }
         p[i] -= lr * (m[i] / c1) / (std::sqrt(vh / c2) + eps);
-    }
+    });
     return 0;
 }
 
