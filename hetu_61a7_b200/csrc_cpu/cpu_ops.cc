@@ -71,6 +71,29 @@ void kern_avx512(int kc, const float* __restrict a, const float* __restrict b, i
     }
 }
 
+// same panel layout, at most 16 valid columns: half the FMAs (the 10-class output layer and its gradients)
+__attribute__((target("avx512f"), noinline))
+void kern_avx512_n16(int kc, const float* __restrict a, const float* __restrict b, int ldbk, float* __restrict c, int ldc, int mr,
+                     int nr, float alpha, float beta) {
+    constexpr int MR = 12;
+    __m512 acc[MR];
+    for (int i = 0; i < MR; ++i) acc[i] = _mm512_setzero_ps();
+    for (int p = 0; p < kc; ++p) {
+        __m512 b0 = _mm512_loadu_ps(b + (size_t)p * ldbk);
+        const float* ap = a + p * MR;
+#pragma GCC unroll 12
+        for (int i = 0; i < MR; ++i) acc[i] = _mm512_fmadd_ps(_mm512_set1_ps(ap[i]), b0, acc[i]);
+    }
+    __m512 va = _mm512_set1_ps(alpha), vb = _mm512_set1_ps(beta);
+    __mmask16 m0 = nr >= 16 ? (__mmask16)0xffff : (__mmask16)((1u << nr) - 1);
+    for (int i = 0; i < mr; ++i) {
+        float* cr = c + (size_t)i * ldc;
+        __m512 r0 = _mm512_mul_ps(va, acc[i]);
+        if (beta != 0.f) r0 = _mm512_fmadd_ps(vb, _mm512_maskz_loadu_ps(m0, cr), r0);
+        _mm512_mask_storeu_ps(cr, m0, r0);
+    }
+}
+
 __attribute__((target("avx2,fma"), noinline))
 void kern_avx2(int kc, const float* __restrict a, const float* __restrict b, int ldbk, float* __restrict c, int ldc, int mr,
                int nr, float alpha, float beta) {
@@ -264,9 +287,10 @@ API int hetu_cpu_matmul(const float* A, const float* B, float* C, int M, int N, 
                             bptr = B + (size_t)pc * ldb + col;
                             ldbk = ldb;
                         }
+                        const auto fn = (NR == 32 && nr <= 16) ? kern_avx512_n16 : kr.fn;
                         for (int ip = ip0; ip < ip1; ++ip) {
                             const int row = ip * MR;
-                            kr.fn(kc, ap_base + (size_t)ip * K * MR + (size_t)pc * MR, bptr, ldbk, C + (size_t)row * N + col, N,
+                            fn(kc, ap_base + (size_t)ip * K * MR + (size_t)pc * MR, bptr, ldbk, C + (size_t)row * N + col, N,
                                   std::min(MR, M - row), nr, alpha, b_eff);
                         }
                     }
