@@ -685,6 +685,12 @@ class SubExecutor(object):
         if self.device.type == 'cuda' and L.cuda_lib() is not None:
             from ..ops.nn import step_counter
             L.call('increment_i64', L.p(step_counter(self.device)), L.stream_ptr(self.device))
+        plan = getattr(self, '_node_plan', None)
+        if plan is None or len(plan) != len(self.topo_order) or self._node_plan_of is not self.topo_order:
+            self._node_plan_of = self.topo_order
+            # per node: (device, is optimizer, wants the inference flag) - fixed for the life of the executor
+            plan = self._node_plan = [(self._node_device(n), isinstance(n, OptimizerOp), bool(getattr(n, 'takes_inference', False)))
+                                      for n in self.topo_order]
         for idx, node in enumerate(self.topo_order):
             if node in vals:
                 continue
@@ -698,12 +704,12 @@ class SubExecutor(object):
                 vals[node] = v
                 continue
             ins = [vals[i] if i is not None else None for i in node.inputs]
-            dev = self._node_device(node)
-            for j, v in enumerate(ins):
-                if isinstance(v, torch.Tensor) and v.device != dev and not isinstance(
-                        node, OptimizerOp) and v.device.type != 'meta':
-                    ins[j] = v.to(dev, non_blocking=True)
-            if getattr(node, 'takes_inference', False):
+            dev, is_opt, takes_inference = plan[idx]
+            if not is_opt:
+                for j, v in enumerate(ins):
+                    if isinstance(v, torch.Tensor) and v.device != dev and v.device.type != 'meta':
+                        ins[j] = v.to(dev, non_blocking=True)
+            if takes_inference:
                 out = node.compute(ins, None, cfg.comp_stream, inference=inference)
             else:
                 out = node.compute(ins, None, cfg.comp_stream)

@@ -106,11 +106,9 @@ class Op(object, metaclass=OpMeta):
 
     __repr__ = __str__
 
-    def __hash__(self):
-        return id(self)
-
-    def __eq__(self, other):
-        return self is other
+    # identity semantics, taken from object so that the executor's per-node dict lookups stay in C
+    __hash__ = object.__hash__
+    __eq__ = object.__eq__
 
     def __deepcopy__(self, memo):
         if id(self) not in memo:
