@@ -91,13 +91,30 @@ class ClockSampler(object):
 
 
 def reference_arm(args):
-    """The reference cannot be installed here: /root/reference has no setup.py / pyproject.toml
-    (pip: "Neither 'setup.py' nor 'pyproject.toml' found") and its CMake build needs MPI, ZeroMQ,
-    protobuf and oneDNN 1.x, none of which exist in this image (DESIGN.md, section reference arm)."""
-    print(json.dumps({'impl': 'reference', 'unavailable':
-                      "pip install /root/reference fails: not a Python project (no setup.py/pyproject.toml); "
-                      "CMake build needs MPI+ZeroMQ+protobuf+oneDNN which are absent offline"}))
-    return 0
+    """Replace this process by baseline/ref_arm.py: the unmodified reference (copy of /root/reference under
+    baseline/_ref, built by baseline/build_reference.sh) driven through its own API.  The new process has neither
+    this repository's root nor its packages on sys.path, so nothing of hetu_61a7_b200 / libhetu_*.so is loaded."""
+    ref = os.path.join(ROOT, 'baseline', '_ref')
+    lib = os.path.join(ref, 'build', 'lib', 'libc_runtime_api.so')
+    if not os.path.exists(lib) and int(os.environ.get('LOCAL_RANK', '0')) == 0:
+        if os.path.isdir(os.path.join(ref, 'src')) or os.path.isdir('/root/reference/src'):
+            subprocess.run(['bash', os.path.join(ROOT, 'baseline', 'build_reference.sh')],
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    t0 = time.time()
+    while not os.path.exists(lib) and int(os.environ.get('LOCAL_RANK', '0')) != 0 and time.time() - t0 < 900:
+        time.sleep(1.0)
+    if not os.path.exists(lib):
+        if int(os.environ.get('RANK', '0')) == 0:
+            print(json.dumps({'impl': 'reference', 'unavailable': 'baseline/_ref is not present / did not build on '
+                              'this machine (baseline/build_reference.sh needs /root/reference or baseline/_ref/src)'}))
+        return 0
+    env = dict(os.environ)
+    env.pop('PYTHONPATH', None)
+    argv = [sys.executable, os.path.join(ROOT, 'baseline', 'ref_arm.py'), '--gpus', str(args.gpus),
+            '--steps', str(args.steps), '--warmup', str(args.warmup), '--workload', args.workload,
+            '--batch', str(args.batch), '--moe-steps', str(args.moe_steps)]
+    sys.stdout.flush()
+    os.execve(sys.executable, argv, env)
 
 
 def timed(fn, steps, torch, device, comm):
