@@ -7,7 +7,7 @@ baseline/_ref/python/hetu, its native code is baseline/_ref/build/lib/*.so.
 
 Workloads (the configs BASELINE.json names):
   wdl : examples/ctr/models/wdl_criteo.py driven like examples/ctr/run_hetu.py:120-135
-        (N = 1: ht.Executor(eval_nodes, ctx=ht.gpu(0)); N > 1: dist_strategy=ht.dist.DataParallel('AllReduce'))
+        (N = 1: ht.Executor(eval_nodes, ctx=ht.gpu(0)); N > 1: ctx=ht.gpu(local_rank), comm_mode='AllReduce')
   moe : examples/moe/test_moe_top.py:16-97 (TopKGate + MoELayer, AllToAll over NCCL)
 
 Environment shims (none touches the reference tree): numpy 2.x removed np.int / np.float / np.bool which the
@@ -202,8 +202,11 @@ def bench_wdl(args, ht, np, comm, cuda, world, rank, local_rank):
         ctx = ht.gpu(0) if args.ctx == 'gpu' else ht.cpu(0)
         executor = ht.Executor(eval_nodes, ctx=ctx, seed=123)                       # run_hetu.py:120-122 (--comm None)
     else:
-        strategy = ht.dist.DataParallel(aggregate='AllReduce')
-        executor = ht.Executor(eval_nodes, dist_strategy=strategy, seed=123)        # run_hetu.py:124-126
+        # run_hetu.py:124-126 builds ht.dist.DataParallel(aggregate='AllReduce'), whose constructor reads the
+        # cluster file heturun writes to /tmp/hetu_config.yml; the arm is started by torchrun, so it names the
+        # same thing through the executor's own keywords instead (the form examples/moe/test_moe_top.py uses).
+        comm = ht.wrapped_mpi_nccl_init()
+        executor = ht.Executor(eval_nodes, ctx=ht.gpu(comm.local_rank), comm_mode='AllReduce', seed=123)
     timer = Timer(cuda, executor.config.nccl_comm if world > 1 else None)
     last = {}
 
@@ -234,8 +237,14 @@ def bench_moe(args, ht, np, cuda, world, rank, local_rank, steps):
     device_id = comm.local_rank
     ctx = ht.gpu(device_id % 8) if args.ctx == 'gpu' else ht.cpu(0)
     # examples/moe/test_moe_top.py:16-38, with num_gpus = world
+    # Naming: the reference script calls its experts "expert_<i>".  In this snapshot OptimizerOp.backward_hook
+    # (python/hetu/optimizer.py:149-151) drops the gradient of every parameter whose name contains "expert" from
+    # the optimizer's inputs, and Optimizer.update (optimizer.py:187) then fails `assert params_size == len(grads)`
+    # on the first step - the script cannot train as written.  The arm therefore only picks another name; the
+    # reference code itself stays untouched.  Consequence at N > 1: the expert weights take the reference's
+    # ordinary AllReduce path (4 x 16.8 MB per step) like every other dense parameter.
     experts = [htl.Expert(embed_dim=dim, ffn_dim=hid, dropout_rate=0.1, activation='relu',
-                          name='expert_%d' % (device_id * nle + i)) for i in range(nle)]
+                          name='ffn_%d' % (device_id * nle + i)) for i in range(nle)]
     gate = htl.TopKGate(embed_dim=dim, num_tokens=bs * ntok, num_experts=nle * world, k=top)
     model = htl.MoELayer(gate=gate, experts=experts, num_tokens=ntok, embed_dim=dim, all2all_size=world, top=top)
     x = ht.Variable(name='x', ctx=ctx, trainable=False)
