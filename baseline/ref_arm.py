@@ -7,7 +7,7 @@ baseline/_ref/python/hetu, its native code is baseline/_ref/build/lib/*.so.
 
 Workloads (the configs BASELINE.json names):
   wdl : examples/ctr/models/wdl_criteo.py driven like examples/ctr/run_hetu.py:120-135
-        (N = 1: ht.Executor(eval_nodes, ctx=ht.gpu(0)); N > 1: ctx=ht.gpu(local_rank), comm_mode='AllReduce')
+        (N = 1: ht.Executor(eval_nodes, ctx=ht.gpu(0)); N > 1: dist_strategy=ht.dist.DataParallel('AllReduce'))
   moe : examples/moe/test_moe_top.py:16-97 (TopKGate + MoELayer, AllToAll over NCCL)
 
 Environment shims (none touches the reference tree): numpy 2.x removed np.int / np.float / np.bool which the
@@ -149,18 +149,17 @@ class Timer(object):
         self.cuda, self.comm = cuda, comm
 
     def barrier(self):
-        if self.comm is not None and self.comm.nrank > 1:
-            import numpy as np
-            buf = (ctypes.c_char * 1)()
-            self.comm.MPI_Broadcast(buf, 1, 0)        # enough of a rendezvous for bracketing (root releases all)
+        self.max_over_ranks(0.0)              # an NCCL all-reduce on the communicator's stream + a stream sync
 
     def max_over_ranks(self, v):
         if self.comm is None or self.comm.nrank == 1:
             return v
         import hetu as ht
         import numpy as np
-        a = ht.array(np.array([v], dtype=np.float32), ctx=ht.gpu(self.comm.device_id.value))
         from hetu.communicator.mpi_nccl_comm import ncclDataType_t, ncclRedOp_t
+        if self.cuda is not None:
+            self.cuda.sync()
+        a = ht.array(np.array([v], dtype=np.float32), ctx=ht.gpu(self.comm.device_id.value))
         self.comm.dlarrayNcclAllReduce(a, a, ncclDataType_t.ncclFloat32, ncclRedOp_t.ncclMax)
         self.comm.stream.sync()
         return float(a.asnumpy()[0])
@@ -202,11 +201,23 @@ def bench_wdl(args, ht, np, comm, cuda, world, rank, local_rank):
         ctx = ht.gpu(0) if args.ctx == 'gpu' else ht.cpu(0)
         executor = ht.Executor(eval_nodes, ctx=ctx, seed=123)                       # run_hetu.py:120-122 (--comm None)
     else:
-        # run_hetu.py:124-126 builds ht.dist.DataParallel(aggregate='AllReduce'), whose constructor reads the
-        # cluster file heturun writes to /tmp/hetu_config.yml; the arm is started by torchrun, so it names the
-        # same thing through the executor's own keywords instead (the form examples/moe/test_moe_top.py uses).
-        comm = ht.wrapped_mpi_nccl_init()
-        executor = ht.Executor(eval_nodes, ctx=ht.gpu(comm.local_rank), comm_mode='AllReduce', seed=123)
+        # run_hetu.py:124-126.  ht.dist.DataParallel reads the cluster description that heturun leaves in
+        # /tmp/hetu_config.yml (python/hetu/distributed_strategies/base.py:14); the arm is started by torchrun, so it
+        # writes the same one-node description there itself.  In this mode the strategy places the table on every
+        # GPU (distributed_strategies/simple.py:16-22) and the sparse gradient is all-gathered.
+        import socket
+        import yaml
+        try:
+            socket.gethostbyname(socket.gethostname())
+        except Exception:
+            socket.gethostname = lambda: 'localhost'          # DistConfig resolves the host name (context.py:260)
+        cfg = {'nodes': [{'host': 'localhost', 'servers': 0, 'workers': world, 'chief': True}]}
+        tmp = '/tmp/hetu_config.yml.%d' % os.getpid()
+        with open(tmp, 'w') as fw:
+            yaml.dump(cfg, fw)
+        os.replace(tmp, '/tmp/hetu_config.yml')
+        strategy = ht.dist.DataParallel(aggregate='AllReduce')
+        executor = ht.Executor(eval_nodes, dist_strategy=strategy, seed=123)
     timer = Timer(cuda, executor.config.nccl_comm if world > 1 else None)
     last = {}
 
@@ -318,8 +329,9 @@ def main():
             'config': {'model': 'Wide&Deep (13 dense + 26 sparse, 33762577 x 128 fp32 table, MLP 13-256-256-256)',
                        'global_batch': w['global_batch'], 'seq_len': None,
                        'parallelism': 'dp%d' % world if world > 1 else 'single',
-                       'embedding': 'host table (ctx=ht.cpu(0) in examples/ctr/models/wdl_criteo.py), '
-                                    'C++ lookup + sparse SGD on the CPU',
+                       'embedding': ('host table (ctx=ht.cpu(0) in examples/ctr/models/wdl_criteo.py), C++ lookup + '
+                                     'sparse SGD on the CPU') if world == 1 else
+                                    'replicated on every GPU by ht.dist.DataParallel(AllReduce), sparse grads all-gathered',
                        'optimizer': 'SGD lr 0.01', 'final_loss': w['loss'],
                        'l2_policy': 'working set (17.3 GB table, random rows) exceeds L2'},
         })

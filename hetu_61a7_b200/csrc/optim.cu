@@ -114,7 +114,8 @@ __global__ void __launch_bounds__(256) lamb_phase2_kernel(TensorList tl, const f
     long long n = tl.n[t];
     float st = (float)(*step_p);
     float b1t = 1.f - powf(h0, st), b2t = 1.f - powf(h1, st);
-    float ratio = sqrtf(scratch[2 * t]) / sqrtf(scratch[2 * t + 1]);
+    float np2 = scratch[2 * t], nu2 = scratch[2 * t + 1];
+    float ratio = (np2 > 0.f && nu2 > 0.f) ? sqrtf(np2) / sqrtf(nu2) : 1.f;   // zero update or zero weights: plain step
     float lr = *lr_p;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         float pv = tl.p[t][i];

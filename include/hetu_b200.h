@@ -150,8 +150,7 @@ int hetu_multi_tensor_opt(int kind, int ntensors, void* const* params, void* con
  * library, at most 96 tensors per call (more is refused with an error).  The array is shared: the
  * call clears the slots it uses, and calls that can overlap on one GPU race - keep them on one
  * stream.  The first call on a device resolves the array's address; make it before any stream
- * capture.  Calls no cudaMalloc/cudaFree.  No counterpart in the reference (its Lamb step
- * allocates cuDNN reduction workspaces per call, src/ops/Optimizers.cu). */
+ * capture.  Calls no cudaMalloc/cudaFree.  This entry point has no counterpart in the reference. */
 int hetu_lamb_step_noalloc(int ntensors, void* const* params, void* const* grads, void* const* s1,
                            void* const* s2, const long long* sizes, const float* lr_p, const void* step_p,
                            float beta1, float beta2, float eps, float weight_decay, float l2reg, cudaStream_t s);

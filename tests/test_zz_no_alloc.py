@@ -39,6 +39,58 @@ def _state(shapes, device, seed):
     return params, m, v
 
 
+REGULAR_MAX = 48          # tensors per launch of the regular entry point
+
+
+def _regular(lib, n, p, g, m, v, sizes, lr, step, hyper, stream, dev):
+    """The regular entry point takes at most 48 tensors per call and a zeroed scratch from the caller."""
+    f = ctypes.c_float
+    for base in range(0, n, REGULAR_MAX):
+        cnt = min(REGULAR_MAX, n - base)
+        scratch = torch.zeros(2 * cnt, device=dev)    # the allocation the regular path needs
+        sl = slice(base, base + cnt)
+        rc = lib.hetu_multi_tensor_opt(
+            ctypes.c_int(OPT_LAMB), ctypes.c_int(cnt), _arr([t.data_ptr() for t in p[sl]]),
+            _arr([t.data_ptr() for t in g[sl]]), _arr([t.data_ptr() for t in m[sl]]),
+            _arr([t.data_ptr() for t in v[sl]]), _arr(list(sizes[sl]), ctypes.c_longlong),
+            ctypes.c_void_p(lr.data_ptr()), ctypes.c_void_p(step.data_ptr()), *[f(h) for h in hyper], f(0.0),
+            ctypes.c_void_p(scratch.data_ptr()), stream)
+        assert rc == 0, lib.hetu_last_error()
+
+
+def test_lamb_noalloc_two_chunks_then_a_smaller_call():
+    """96 tensors = both 48-tensor chunks of the static array, checked against two regular calls; then a
+    17-tensor call right after it, which reuses slots the big call left non-zero."""
+    assert os.path.exists(LIB_PATH), 'build the library first: python __graft_entry__.py'
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.hetu_last_error.restype = ctypes.c_char_p
+    dev = torch.device('cuda', 0)
+    torch.cuda.set_device(dev)
+    base_shapes = [(13, 256), (256, 256), (3584, 1), (7,), (1000, 33), (64, 64, 3), (5,), (300, 17)]
+    hyper = (0.9, 0.999, 1e-7, 0.1)
+    stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    f = ctypes.c_float
+    lr = torch.full((1,), 0.01, device=dev)
+    for shapes in (base_shapes * 12, base_shapes * 2 + [(11, 3)]):
+        n = len(shapes)
+        assert n == MAX_TENSORS or n < REGULAR_MAX
+        pa, ma, va = _state(shapes, dev, 3)
+        pb, mb, vb = [t.clone() for t in pa], [t.clone() for t in ma], [t.clone() for t in va]
+        sizes = [p.numel() for p in pa]
+        step = torch.ones(1, dtype=torch.int64, device=dev)
+        g = torch.Generator(device='cpu').manual_seed(7 + n)
+        grads = [torch.randn(s, generator=g).to(dev) for s in shapes]
+        _regular(lib, n, pa, grads, ma, va, sizes, lr, step, hyper, stream, dev)
+        rc = lib.hetu_lamb_step_noalloc(
+            ctypes.c_int(n), _arr([t.data_ptr() for t in pb]), _arr([t.data_ptr() for t in grads]),
+            _arr([t.data_ptr() for t in mb]), _arr([t.data_ptr() for t in vb]), _arr(sizes, ctypes.c_longlong),
+            ctypes.c_void_p(lr.data_ptr()), ctypes.c_void_p(step.data_ptr()), *[f(h) for h in hyper], f(0.0), stream)
+        assert rc == 0, lib.hetu_last_error()
+        torch.cuda.synchronize(dev)
+        for a, b in zip(pa + ma + va, pb + mb + vb):
+            torch.testing.assert_close(b, a, rtol=2e-4, atol=1e-5)
+
+
 def test_lamb_noalloc_matches_regular_entry_point():
     assert os.path.exists(LIB_PATH), 'build the library first: python __graft_entry__.py'
     lib = ctypes.CDLL(LIB_PATH)
@@ -46,7 +98,7 @@ def test_lamb_noalloc_matches_regular_entry_point():
     dev = torch.device('cuda', 0)
     torch.cuda.set_device(dev)
     shapes = [(13, 256), (256, 256), (3584, 1), (7,), (1000, 33), (64, 64, 3)] * 6 + [(5,), (2048, 17)]
-    assert len(shapes) <= 48
+    assert len(shapes) <= REGULAR_MAX
     n = len(shapes)
     pa, ma, va = _state(shapes, dev, 1)            # driven by the regular entry point
     pb, mb, vb = [t.clone() for t in pa], [t.clone() for t in ma], [t.clone() for t in va]
