@@ -1,0 +1,458 @@
+// Wide&Deep dense tower: forward, loss and backward of one training step in ONE kernel.
+//
+// reference graph: examples/ctr/models/wdl_criteo.py:8-42 - three matmul (+relu) layers on the 13 dense
+// features, concat with the 26 x 128 embedding block, a [3584, 1] head, sigmoid, binary cross entropy, mean;
+// the reference runs it as ~45 separate kernels per step (python/hetu/gpu_ops/executor.py:1000-1056).
+//
+// Design (B200): the batch of 128 samples is exactly one tcgen05 M tile.  One thread-block cluster of 8 CTAs owns
+// the step; CTA c owns output columns [32c, 32c+32) of every 256-wide layer.
+//   * every 128 x 256 x 256 product is one UMMA chain (M=128, N=32 per CTA, kind::tf32, fp32 accumulator in TMEM),
+//     operands brought in by TMA: activations K-major (SWIZZLE_128B), weights in place either MN-major
+//     (forward, W[k][n]) or K-major (backward data, W[j][n] rows), activations MN-major for the weight gradients;
+//   * layers hand their activations to each other through L2 (plain row-major buffers) with one cluster barrier per
+//     layer - no grid-wide synchronisation, no host round trip, no re-launch;
+//   * the head never materialises its input gradient: dL/dy4 is the outer product dz x W4, so the y3 branch needs
+//     only two matrix-vector products (u = h2^T dz, v = W3 w4y) and the embedding branch is applied straight to
+//     the table by wdl_sparse_sgd_rank1_kernel below;
+//   * the per-sample logit is reduced across the cluster through distributed shared memory.
+// Everything the kernel reads lives in this GPU's memory.
+#include "tcgen05.cuh"
+
+namespace {
+constexpr int TB = 128;            // batch rows (one UMMA M tile)
+constexpr int TH = 256;            // hidden width
+constexpr int TCL = 8;             // CTAs per cluster
+constexpr int TSL = TH / TCL;      // 32 output columns per CTA
+constexpr int TTHREADS = 384;      // 12 warps: 0 = TMA + MMA issue, 1 = TMEM owner, 2..5 = epilogue, 6..11 = vector work
+constexpr int TWARPS = TTHREADS / 32;
+constexpr int kAArea = TB * TH * 4;          // 128 KB
+constexpr int kBArea = TSL * TH * 4;         // 32 KB
+constexpr int kKB = TH / 32;                 // 8 k-blocks of 32 fp32 (128 B)
+
+struct TowerParams {
+    const float* x;        // [128, nd]
+    float* y4;             // [128, pitch]: columns [0, emb_cols) filled by the gather, [emb_cols, pitch) written here
+    const float* labels;   // [128]
+    const float* W1;       // [nd, 256]
+    const float* W2;       // [256, 256]
+    const float* W3;       // [256, 256]
+    const float* W4;       // [pitch]
+    float* h1; float* h2; float* dh2;          // [128, 256] work buffers
+    float* loss; float* pred; float* dz;       // [1], [128], [128]
+    float* dW1; float* dW2; float* dW3; float* dW4;
+    int nd, emb_cols, pitch;
+};
+
+struct TowerSmem {
+    uint64_t full[4][kKB];       // one set of TMA barriers per tensor-core phase (each used once, parity 0)
+    uint64_t done[4];
+    uint32_t tmem_ptr;
+    float zpart[TB];
+    float dz[TB];
+    float w4y[TH];
+    float u[TSL], v3[TSL];
+    float red[TWARPS][TSL];
+    float lossw[4];
+    float x[TB * 16];
+    float dh1[TB][TSL + 1];
+};
+
+__device__ __forceinline__ void cluster_sync_all() {
+    __syncwarp();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ float ld_dsmem(const float* local, uint32_t rank) {
+    uint32_t a = smem_u32(local), ra;
+    float v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(rank));
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+    return v;
+}
+
+// idesc: D = f32, A = B = tf32, M = 128, N = 32
+__device__ __forceinline__ uint32_t tower_idesc(int a_mn, int b_mn) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+           ((uint32_t)(TSL >> 3) << 17) | ((uint32_t)(TB >> 4) << 24);
+}
+
+// C[128, 32c..32c+32) = A[128, 256] * Bslice, A K-major through tmA, B either MN-major ([k][n] memory, forward) or
+// K-major ([j][k] memory, backward data).  Called by ONE thread.
+__device__ void tower_gemm_ka(const CUtensorMap* tmA, const CUtensorMap* tmB, bool b_mn, int c, uint8_t* sA, uint8_t* sB,
+                              uint64_t* full, uint64_t* done, uint32_t tmem_d) {
+    asm volatile("fence.proxy.async.global;" ::: "memory");        // activations were written with ordinary stores
+    for (int kb = 0; kb < kKB; ++kb) {
+        mbar_expect_tx(&full[kb], 16384 + 4096);
+        tma_load_3d(sA + kb * 16384, tmA, kb * 32, 0, 0, &full[kb]);                    // box {32 k, 128 rows}
+        if (b_mn) tma_load_3d(sB + kb * 4096, tmB, c * TSL, kb * 32, 0, &full[kb]);      // box {32 n, 32 k}
+        else tma_load_3d(sB + kb * 4096, tmB, kb * 32, c * TSL, 0, &full[kb]);           // box {32 k, 32 rows}
+    }
+    const uint32_t idesc = tower_idesc(0, b_mn ? 1 : 0);
+    for (int kb = 0; kb < kKB; ++kb) {
+        mbar_wait(&full[kb], 0);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(sA + kb * 16384), b_base = smem_u32(sB + kb * 4096);
+#pragma unroll
+        for (int ki = 0; ki < 4; ++ki) {
+            uint64_t a_desc = make_smem_desc(a_base + ki * 32, 16, 1024, 2);
+            uint64_t b_desc = b_mn ? make_smem_desc(b_base + ki * 1024, 4096, 512, 1) : make_smem_desc(b_base + ki * 32, 16, 1024, 2);
+            umma_tf32(tmem_d, a_desc, b_desc, idesc, (kb > 0 || ki > 0) ? 1u : 0u);
+        }
+    }
+    umma_commit(done);
+}
+
+__global__ void __cluster_dims__(TCL, 1, 1) __launch_bounds__(TTHREADS, 1)
+wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_constant__ CUtensorMap tm_h2k,
+                 const __grid_constant__ CUtensorMap tm_dh2k, const __grid_constant__ CUtensorMap tm_W2mn,
+                 const __grid_constant__ CUtensorMap tm_W3mn, const __grid_constant__ CUtensorMap tm_W2k,
+                 const __grid_constant__ CUtensorMap tm_h1mn, const __grid_constant__ CUtensorMap tm_dh2mn, TowerParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + kAArea;
+    TowerSmem& S = *reinterpret_cast<TowerSmem*>(smem + kAArea + kBArea);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int c = (int)cluster_ctarank();
+    const int n0 = c * TSL;
+    const int ecs = p.emb_cols / TCL;                    // embedding columns of the head handled by this CTA
+    const int hcs = p.pitch / TCL;                       // head-gradient columns handled by this CTA
+
+    if (tid == 0) {
+        prefetch_tmap(&tm_h1k); prefetch_tmap(&tm_W2mn);
+        for (int g = 0; g < 4; ++g) {
+            for (int i = 0; i < kKB; ++i) mbar_init(&S.full[g][i], 1);
+            mbar_init(&S.done[g], 1);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(&S.tmem_ptr, 128);
+    // ---- P0: stage x and the y3 part of W4; partial logits of the embedding block ------------------------------
+    for (int i = tid; i < TB * p.nd; i += TTHREADS) S.x[i] = p.x[i];
+    for (int i = tid; i < TH; i += TTHREADS) S.w4y[i] = p.W4[p.emb_cols + i];
+    {
+        const float4* w4 = reinterpret_cast<const float4*>(p.W4 + (size_t)c * ecs);
+        for (int row = warp; row < TB; row += TWARPS) {
+            const float4* yr = reinterpret_cast<const float4*>(p.y4 + (size_t)row * p.pitch + (size_t)c * ecs);
+            float acc = 0.f;
+            for (int j = lane; j < (ecs >> 2); j += 32) {
+                float4 a = yr[j], b = __ldg(w4 + j);
+                acc += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+            }
+            acc = warp_sum(acc);
+            if (lane == 0) S.zpart[row] = acc;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = S.tmem_ptr;
+    // ---- P1: h1 = relu(x W1), K = nd (13): too thin for a tensor-core tile --------------------------------------
+    for (int idx = tid; idx < TB * TSL; idx += TTHREADS) {
+        const int n = idx & (TSL - 1), b = idx >> 5;
+        float acc = 0.f;
+        for (int k = 0; k < p.nd; ++k) acc += S.x[b * p.nd + k] * __ldg(p.W1 + k * TH + n0 + n);
+        p.h1[b * TH + n0 + n] = fmaxf(acc, 0.f);
+    }
+    __threadfence();
+    __syncthreads();
+    cluster_sync_all();                                                             // h1 complete
+    // ---- P2: h2 = relu(h1 W2) ------------------------------------------------------------------------------------
+    if (tid == 0) tower_gemm_ka(&tm_h1k, &tm_W2mn, true, c, sA, sB, S.full[0], &S.done[0], tmem_base);
+    if (warp >= 2 && warp < 6) {
+        const int q = warp & 3, row = q * 32 + lane;
+        mbar_wait(&S.done[0], 0);
+        tc_fence_after();
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), v);
+        float4* dst = reinterpret_cast<float4*>(p.h2 + row * TH + n0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            dst[j] = make_float4(fmaxf(v[4 * j], 0.f), fmaxf(v[4 * j + 1], 0.f), fmaxf(v[4 * j + 2], 0.f), fmaxf(v[4 * j + 3], 0.f));
+        tc_fence_before();
+    }
+    __threadfence();
+    __syncthreads();
+    cluster_sync_all();                                                             // h2 complete
+    // ---- P3: y3 = h2 W3 -> y4[:, emb_cols + n], logit partial of the y3 block -------------------------------------
+    if (tid == 0) { tc_fence_after(); tower_gemm_ka(&tm_h2k, &tm_W3mn, true, c, sA, sB, S.full[1], &S.done[1], tmem_base); }
+    if (warp >= 2 && warp < 6) {
+        const int q = warp & 3, row = q * 32 + lane;
+        mbar_wait(&S.done[1], 0);
+        tc_fence_after();
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), v);
+        float4* dst = reinterpret_cast<float4*>(p.y4 + (size_t)row * p.pitch + p.emb_cols + n0);
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc += v[j] * S.w4y[n0 + j];
+        S.zpart[row] += acc;
+        tc_fence_before();
+    }
+    __threadfence();
+    __syncthreads();
+    cluster_sync_all();                                                             // every CTA's zpart and y3 columns complete
+    // ---- head: logits through distributed shared memory, sigmoid, BCE, dz -----------------------------------------
+    if (tid < TB) {
+        float z = 0.f;
+#pragma unroll
+        for (int r = 0; r < TCL; ++r) z += ld_dsmem(&S.zpart[tid], (uint32_t)r);
+        const float pr = 1.0f / (1.0f + expf(-z));
+        const float y = p.labels[tid];
+        const float g = (1.0f / TB) * (-y / pr + (1.f - y) / (1.f - pr));          // d mean(bce) / d pred
+        const float dzv = g * pr * (1.f - pr);                                      // through the sigmoid
+        S.dz[tid] = dzv;
+        if (c == 0) {
+            p.pred[tid] = pr;
+            p.dz[tid] = dzv;
+            float l = -y * logf(pr) - (1.f - y) * logf(1.f - pr);
+            l = warp_sum(l);
+            if (lane == 0) S.lossw[warp] = l;
+        }
+    }
+    __syncthreads();
+    if (c == 0 && tid == 0) p.loss[0] = (S.lossw[0] + S.lossw[1] + S.lossw[2] + S.lossw[3]) * (1.0f / TB);
+    // ---- P5: u = h2^T dz, v3 = W3 w4y (slice), dW3 = u x w4y, dh2 = relu'(h2) . (dz x v3) -------------------------
+    {
+        float acc = 0.f;
+        for (int b = warp; b < TB; b += TWARPS) acc += __ldcg(p.h2 + b * TH + n0 + lane) * S.dz[b];
+        S.red[warp][lane] = acc;
+        for (int k = warp; k < TSL; k += TWARPS) {
+            const float* wr = p.W3 + (size_t)(n0 + k) * TH;
+            float a2 = 0.f;
+            for (int j = lane; j < TH; j += 32) a2 += __ldg(wr + j) * S.w4y[j];
+            a2 = warp_sum(a2);
+            if (lane == 0) S.v3[k] = a2;
+        }
+    }
+    __syncthreads();
+    if (tid < TSL) {
+        float a = 0.f;
+#pragma unroll
+        for (int w = 0; w < TWARPS; ++w) a += S.red[w][tid];
+        S.u[tid] = a;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < TSL * TH; idx += TTHREADS) {
+        const int n = idx & (TH - 1), k = idx >> 8;
+        p.dW3[(size_t)(n0 + k) * TH + n] = S.u[k] * S.w4y[n];
+    }
+    for (int idx = tid; idx < TB * TSL; idx += TTHREADS) {
+        const int k = idx & (TSL - 1), b = idx >> 5;
+        const float h = __ldcg(p.h2 + b * TH + n0 + k);
+        p.dh2[b * TH + n0 + k] = h > 0.f ? S.dz[b] * S.v3[k] : 0.f;
+    }
+    __threadfence();
+    __syncthreads();
+    cluster_sync_all();                                                             // dh2 complete
+    // ---- P6a: dh1 = (dh2 W2^T) . relu'(h1)   |  vector warps: dW4 = y4^T dz ---------------------------------------
+    if (tid == 0) {
+        tc_fence_after();
+        tower_gemm_ka(&tm_dh2k, &tm_W2k, false, c, sA, sB, S.full[2], &S.done[2], tmem_base);
+        mbar_wait(&S.done[2], 0);                      // operands of P6a consumed: the A / B areas can be refilled
+        // ---- P6b issue: dW2[:, slice] = h1^T dh2[:, slice]; M = 256 as two halves, K = batch = 128 -----------------
+        asm volatile("fence.proxy.async.global;" ::: "memory");
+        for (int h = 0; h < 2; ++h)
+            for (int kb = 0; kb < 4; ++kb) {
+                const int s = h * 4 + kb;
+                mbar_expect_tx(&S.full[3][s], 16384 + (h == 0 ? 4096 : 0));
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    tma_load_3d(sA + s * 16384 + j * 4096, &tm_h1mn, h * 128 + j * 32, kb * 32, 0, &S.full[3][s]);
+                if (h == 0) tma_load_3d(sB + kb * 4096, &tm_dh2mn, n0, kb * 32, 0, &S.full[3][s]);
+            }
+        const uint32_t idesc = tower_idesc(1, 1);
+        for (int h = 0; h < 2; ++h)
+            for (int kb = 0; kb < 4; ++kb) {
+                const int s = h * 4 + kb;
+                mbar_wait(&S.full[3][s], 0);
+                tc_fence_after();
+                const uint32_t a_base = smem_u32(sA + s * 16384), b_base = smem_u32(sB + kb * 4096);
+#pragma unroll
+                for (int ki = 0; ki < 4; ++ki) {
+                    uint64_t a_desc = make_smem_desc(a_base + ki * 1024, 4096, 512, 1);
+                    uint64_t b_desc = make_smem_desc(b_base + ki * 1024, 4096, 512, 1);
+                    umma_tf32(tmem_base + 32 + h * 32, a_desc, b_desc, idesc, (kb > 0 || ki > 0) ? 1u : 0u);
+                }
+            }
+        umma_commit(&S.done[3]);
+    } else if (warp >= 2 && warp < 6) {
+        const int q = warp & 3, row = q * 32 + lane;
+        mbar_wait(&S.done[2], 0);
+        tc_fence_after();
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), v);
+        const float4* hp = reinterpret_cast<const float4*>(p.h1 + row * TH + n0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 h = __ldcg(hp + j);
+            S.dh1[row][4 * j + 0] = h.x > 0.f ? v[4 * j + 0] : 0.f;
+            S.dh1[row][4 * j + 1] = h.y > 0.f ? v[4 * j + 1] : 0.f;
+            S.dh1[row][4 * j + 2] = h.z > 0.f ? v[4 * j + 2] : 0.f;
+            S.dh1[row][4 * j + 3] = h.w > 0.f ? v[4 * j + 3] : 0.f;
+        }
+    } else if (warp >= 6) {
+        const int t6 = tid - 6 * 32;                    // 192 vector threads
+        for (int col = t6; col < hcs; col += 6 * 32) {
+            const float* yp = p.y4 + (size_t)c * hcs + col;
+            float acc = 0.f;
+#pragma unroll 8
+            for (int b = 0; b < TB; ++b) acc += __ldcg(yp + (size_t)b * p.pitch) * S.dz[b];
+            p.dW4[(size_t)c * hcs + col] = acc;
+        }
+    }
+    __syncthreads();
+    // ---- P6b epilogue: dW2 slice   |  vector warps: dW1 = x^T dh1 (slice) -----------------------------------------
+    if (warp >= 2 && warp < 6) {
+        const int q = warp & 3;
+        mbar_wait(&S.done[3], 0);
+        tc_fence_after();
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+            float v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32 + h * 32, v);
+            float4* dst = reinterpret_cast<float4*>(p.dW2 + (size_t)(h * 128 + q * 32 + lane) * TH + n0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+    } else if (warp >= 6) {
+        const int t6 = tid - 6 * 32;
+        for (int idx = t6; idx < p.nd * TSL; idx += 6 * 32) {
+            const int n = idx & (TSL - 1), k = idx >> 5;
+            float acc = 0.f;
+#pragma unroll 8
+            for (int b = 0; b < TB; ++b) acc += S.x[b * p.nd + k] * S.dh1[b][n];
+            p.dW1[k * TH + n0 + n] = acc;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 128);
+}
+}  // namespace
+
+// work: 3 * 128 * 256 floats (h1, h2, dh2).  All pointers are this GPU's memory; y4 is the concat buffer whose
+// first emb_cols columns hold the gathered embedding rows (hetu_gather_rows_pitched).
+HETU_API int hetu_wdl_tower_step(const float* x, float* y4, const float* labels, const float* W1, const float* W2,
+                                 const float* W3, const float* W4, float* work, float* loss, float* pred, float* dz,
+                                 float* dW1, float* dW2, float* dW3, float* dW4, int batch, int nd, int hidden,
+                                 int emb_cols, cudaStream_t s) {
+    if (batch != TB || hidden != TH || nd < 1 || nd > 16 || emb_cols <= 0 || emb_cols % (4 * TCL) != 0) {
+        hetu_set_error("hetu_wdl_tower_step: needs batch 128, hidden 256, 1..16 dense features, emb_cols %% 32 == 0 "
+                       "(got %d, %d, %d, %d)", batch, hidden, nd, emb_cols);
+        return -1;
+    }
+    TowerParams p;
+    p.x = x; p.y4 = y4; p.labels = labels; p.W1 = W1; p.W2 = W2; p.W3 = W3; p.W4 = W4;
+    p.h1 = work; p.h2 = work + TB * TH; p.dh2 = work + 2 * TB * TH;
+    p.loss = loss; p.pred = pred; p.dz = dz; p.dW1 = dW1; p.dW2 = dW2; p.dW3 = dW3; p.dW4 = dW4;
+    p.nd = nd; p.emb_cols = emb_cols; p.pitch = emb_cols + TH;
+    CUtensorMap h1k, h2k, dh2k, W2mn, W3mn, W2k, h1mn, dh2mn;
+    if (make_tmap(&h1k, p.h1, TH, TB, 1, 0, TB, false) || make_tmap(&h2k, p.h2, TH, TB, 1, 0, TB, false) ||
+        make_tmap(&dh2k, p.dh2, TH, TB, 1, 0, TB, false) || make_tmap(&W2mn, W2, TH, TH, 1, 0, 32, true) ||
+        make_tmap(&W3mn, W3, TH, TH, 1, 0, 32, true) || make_tmap(&W2k, W2, TH, TH, 1, 0, 32, false) ||
+        make_tmap(&h1mn, p.h1, TH, TB, 1, 0, 32, true) || make_tmap(&dh2mn, p.dh2, TH, TB, 1, 0, 32, true))
+        return -1;
+    const int smem_bytes = 1024 + kAArea + kBArea + (int)sizeof(TowerSmem);
+    static bool attr_set = false;
+    if (!attr_set) {
+        HETU_CUDA(cudaFuncSetAttribute(wdl_tower_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        attr_set = true;
+    }
+    wdl_tower_kernel<<<TCL, TTHREADS, smem_bytes, s>>>(h1k, h2k, dh2k, W2mn, W3mn, W2k, h1mn, dh2mn, p);
+    HETU_CHECK_LAUNCH("hetu_wdl_tower_step");
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Embedding side of the fused step.  Row r of a sharded table lives on GPU r % nshard at local row r / nshard
+// (parallel/sharded_embedding.py); nshard == 1 is the plain local table.
+namespace {
+constexpr int kWdlMaxShards = 16;
+struct WdlShards { float* base[kWdlMaxShards]; int nshard; };
+
+// lookup + concat: row i = (sample b, field f) goes to out[b * pitch + f * width ...]
+__global__ void __launch_bounds__(256) gather_rows_pitched_kernel(WdlShards tab, const void* __restrict__ idx, int idx_code,
+                                                                  float* __restrict__ out, size_t n, int width, int fields,
+                                                                  int pitch, size_t vocab) {
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const size_t nwarp = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t i = warp; i < n; i += nwarp) {
+        const long long r = load_index(idx, idx_code, i);
+        float* dst = out + (i / fields) * (size_t)pitch + (i % fields) * (size_t)width;
+        const bool ok = r >= 0 && (size_t)r < vocab;
+        const float* src = ok ? tab.base[(int)(r % tab.nshard)] + (size_t)(r / tab.nshard) * width : nullptr;
+        if ((width & 3) == 0) {
+            for (int j = lane; j < (width >> 2); j += 32)
+                reinterpret_cast<float4*>(dst)[j] = ok ? reinterpret_cast<const float4*>(src)[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+            for (int j = lane; j < width; j += 32) dst[j] = ok ? src[j] : 0.f;
+        }
+    }
+}
+
+// SGD on the embedding rows with the head's rank-one gradient: d loss / d row(b, f) = dz[b] * W4[f * width ...].
+// Duplicate ids accumulate through atomics, as the summed IndexedSlices of the unfused path do.
+__global__ void __launch_bounds__(256) wdl_sparse_sgd_rank1_kernel(WdlShards tab, const void* __restrict__ idx, int idx_code,
+                                                                   const float* __restrict__ dz, const float* __restrict__ w4,
+                                                                   const float* __restrict__ lr_p, float scale, size_t n,
+                                                                   int width, int fields, size_t vocab) {
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const size_t nwarp = ((size_t)gridDim.x * blockDim.x) >> 5;
+    const float k = -(*lr_p) * scale;
+    for (size_t i = warp; i < n; i += nwarp) {
+        const long long r = load_index(idx, idx_code, i);
+        if (r < 0 || (size_t)r >= vocab) continue;
+        float* row = tab.base[(int)(r % tab.nshard)] + (size_t)(r / tab.nshard) * width;
+        const float g = k * dz[i / fields];
+        const float* w = w4 + (i % fields) * (size_t)width;
+        if ((width & 3) == 0) {
+            for (int j = lane; j < (width >> 2); j += 32) {
+                const float4 wv = __ldg(reinterpret_cast<const float4*>(w) + j);
+                atomicAdd(reinterpret_cast<float4*>(row) + j, make_float4(g * wv.x, g * wv.y, g * wv.z, g * wv.w));
+            }
+        } else {
+            for (int j = lane; j < width; j += 32) atomicAdd(row + j, g * w[j]);
+        }
+    }
+}
+
+int fill_shards(WdlShards& tab, void* const* bases, int nshard, const char* who) {
+    if (nshard < 1 || nshard > kWdlMaxShards) { hetu_set_error("%s: nshard %d outside [1, %d]", who, nshard, kWdlMaxShards); return -1; }
+    tab.nshard = nshard;
+    for (int i = 0; i < kWdlMaxShards; ++i) tab.base[i] = i < nshard ? (float*)bases[i] : nullptr;
+    return 0;
+}
+}  // namespace
+
+HETU_API int hetu_gather_rows_pitched(void* const* bases, int nshard, const void* idx, int idx_code, float* out, size_t n,
+                                      int width, int fields, int pitch, size_t vocab, cudaStream_t s) {
+    if (n == 0) return 0;
+    WdlShards tab;
+    if (fill_shards(tab, bases, nshard, "hetu_gather_rows_pitched")) return -1;
+    gather_rows_pitched_kernel<<<ew_grid(n * 32, 256, 16), 256, 0, s>>>(tab, idx, idx_code, out, n, width, fields, pitch, vocab);
+    HETU_CHECK_LAUNCH("hetu_gather_rows_pitched");
+    return 0;
+}
+
+HETU_API int hetu_wdl_sparse_sgd_rank1(void* const* bases, int nshard, const void* idx, int idx_code, const float* dz,
+                                       const float* w4, const float* lr_p, float scale, size_t n, int width, int fields,
+                                       size_t vocab, cudaStream_t s) {
+    if (n == 0) return 0;
+    WdlShards tab;
+    if (fill_shards(tab, bases, nshard, "hetu_wdl_sparse_sgd_rank1")) return -1;
+    wdl_sparse_sgd_rank1_kernel<<<ew_grid(n * 32, 256, 16), 256, 0, s>>>(tab, idx, idx_code, dz, w4, lr_p, scale, n, width,
+                                                                        fields, vocab);
+    HETU_CHECK_LAUNCH("hetu_wdl_sparse_sgd_rank1");
+    return 0;
+}

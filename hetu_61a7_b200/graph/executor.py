@@ -404,6 +404,9 @@ class Executor(object):
             return SubExecutor(name, nodes, config)
 
         from .fusion import fuse_matmul_bias, fuse_matmul_relu
+        from .fusion_wdl import fuse_wide_deep
+        # whole-step fusion first: it wants the graph as autodiff left it (csrc/wdl_tower.cu)
+        self.fused_wdl = 0 if (timing is not None or config.pipeline) else fuse_wide_deep(all_eval_nodes)
         keep = set(all_eval_nodes)
         self.fused_biases = fuse_matmul_bias([n for n in find_topo_sort(all_eval_nodes) if n not in keep])
         self.fused_epilogues = fuse_matmul_relu([n for n in find_topo_sort(all_eval_nodes) if n not in keep or

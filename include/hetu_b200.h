@@ -135,6 +135,23 @@ int hetu_sparse_sgd_sharded(void* const* bases /*host array*/, int nshard, const
 int hetu_scatter_add_rows(float* dense, const void* idx, int idx_code, const float* vals, size_t n, int width,
                           size_t vocab, cudaStream_t s);
 
+/* ---- Wide&Deep training step fused (csrc/wdl_tower.cu; graph of examples/ctr/models/wdl_criteo.py:8-42) -----
+ * gather_rows_pitched: lookup + concat, row (b, f) -> out[b * pitch + f * width]; bases = host array of the nshard
+ *   table shards (row r on shard r % nshard, local row r / nshard; nshard == 1: plain table).
+ * wdl_tower_step: ONE cluster kernel (8 CTAs, tcgen05 kind::tf32) for the dense tower forward, the head, sigmoid +
+ *   BCE + mean, and the whole backward pass; y4 [128, emb_cols + 256] holds the gathered rows in its first emb_cols
+ *   columns; work = 3 * 128 * 256 floats; writes loss[1], pred[128], dz[128] and the four weight gradients.
+ * wdl_sparse_sgd_rank1: table rows -= lr * scale * dz[b] * W4[f * width ...] (the head's gradient is rank one). */
+int hetu_gather_rows_pitched(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code, float* out,
+                             size_t n, int width, int fields, int pitch, size_t vocab, cudaStream_t s);
+int hetu_wdl_tower_step(const float* x, float* y4, const float* labels, const float* W1, const float* W2,
+                        const float* W3, const float* W4, float* work, float* loss, float* pred, float* dz,
+                        float* dW1, float* dW2, float* dW3, float* dW4, int batch, int nd, int hidden, int emb_cols,
+                        cudaStream_t s);
+int hetu_wdl_sparse_sgd_rank1(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code,
+                              const float* dz, const float* w4, const float* lr_p, float scale, size_t n, int width,
+                              int fields, size_t vocab, cudaStream_t s);
+
 /* ---- dense optimizers, all tensors in one launch: Optimizers.cu ------------------------
  * kind: 0 SGD 1 Momentum 2 Nesterov 3 AdaGrad 4 Adam 5 AdamW 6 Lamb.  The pointer arrays are
  * HOST arrays of device pointers (<= 48 entries).  Lamb needs `scratch`: 2 floats per tensor of
