@@ -164,23 +164,34 @@ class Timer(object):
         self.comm.stream.sync()
         return float(a.asnumpy()[0])
 
-    def run(self, fn, steps):
+    def run(self, fn, steps, min_seconds=0.5, max_blocks=40):
+        """Same rule as the other arm: blocks of exactly `steps` steps, each bracketed by a barrier and a device
+        synchronize, repeated until >= 3 blocks and >= min_seconds; median block, max over ranks."""
         c = self.cuda
-        self.barrier()
-        if c is None:
-            t0 = time.perf_counter()
-            for i in range(steps):
-                fn(i)
-            return (time.perf_counter() - t0) * 1e3 / steps
-        c.sync()
-        a, b = c.event(), c.event()
-        c.record(a)
-        for i in range(steps):
-            fn(i)
-        c.record(b)
-        c.sync()
-        self.barrier()
-        return self.max_over_ranks(c.elapsed(a, b)) / steps
+        per_step, total = [], 0.0
+        while True:
+            self.barrier()
+            if c is None:
+                t0 = time.perf_counter()
+                for i in range(steps):
+                    fn(i)
+                ms = (time.perf_counter() - t0) * 1e3
+            else:
+                c.sync()
+                a, b = c.event(), c.event()
+                c.record(a)
+                for i in range(steps):
+                    fn(i)
+                c.record(b)
+                c.sync()
+                self.barrier()
+                ms = self.max_over_ranks(c.elapsed(a, b))
+            per_step.append(ms / steps)
+            total += ms
+            if (len(per_step) >= 3 and total >= min_seconds * 1e3) or len(per_step) >= max_blocks:
+                break
+        per_step.sort()
+        return per_step[len(per_step) // 2]
 
 
 def bench_wdl(args, ht, np, comm, cuda, world, rank, local_rank):

@@ -33,7 +33,7 @@ def parse():
     ap.add_argument('--workload', default='both', choices=['wdl', 'moe', 'both'])
     ap.add_argument('--batch', type=int, default=128, help='WDL batch per GPU (reference: 128)')
     ap.add_argument('--vocab', type=int, default=33762577)
-    ap.add_argument('--moe-steps', type=int, default=0, help='0 = max(5, steps // 10)')
+    ap.add_argument('--moe-steps', type=int, default=0, help='0 = same as --steps')
     ap.add_argument('--collectives', default=None, choices=[None, 'symm', 'nccl'])
     return ap.parse_args()
 
@@ -117,19 +117,32 @@ def reference_arm(args):
     os.execve(sys.executable, argv, env)
 
 
-def timed(fn, steps, torch, device, comm):
-    """K calls of fn bracketed by barrier + synchronize, CUDA events, MAX over ranks -> ms/step."""
+def timed(fn, steps, torch, device, comm, min_seconds=0.5, max_blocks=40, finish=None):
+    """Blocks of EXACTLY `steps` calls of fn, each bracketed by barrier + synchronize on both sides and timed with CUDA
+    events, MAX over ranks.  Blocks repeat until at least three have run and `min_seconds` of timed work has
+    accumulated (short steps would otherwise be timed over a few milliseconds only); the median block is reported.
+    -> (ms/step of the median block, {'blocks': n, 'min': .., 'max': ..})"""
     from hetu_61a7_b200.parallel.comm import device_max_ms
-    comm.barrier()
-    torch.cuda.synchronize(device)
-    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s.record()
-    for i in range(steps):
-        fn(i)
-    e.record()
-    torch.cuda.synchronize(device)
-    comm.barrier()
-    return device_max_ms(s.elapsed_time(e)) / steps
+    per_step, total = [], 0.0
+    while True:
+        comm.barrier()
+        torch.cuda.synchronize(device)
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for i in range(steps):
+            fn(i)
+        if finish is not None:
+            finish()
+        e.record()
+        torch.cuda.synchronize(device)
+        comm.barrier()
+        ms = device_max_ms(s.elapsed_time(e))           # identical on every rank: the loop exit is collective
+        per_step.append(ms / steps)
+        total += ms
+        if (len(per_step) >= 3 and total >= min_seconds * 1e3) or len(per_step) >= max_blocks:
+            break
+    srt = sorted(per_step)
+    return srt[len(srt) // 2], {'blocks': len(srt), 'min_ms_per_step': srt[0], 'max_ms_per_step': srt[-1]}
 
 
 def bench_wdl(args, ht, torch, np, comm, device):
@@ -178,25 +191,33 @@ def bench_wdl(args, ht, torch, np, comm, device):
     for i in range(3):
         step_dev(i)
     sampler.mark()
-    ms_dev = timed(step_dev, args.steps, torch, device, comm)
+    ms_dev, spread_dev = timed(step_dev, args.steps, torch, device, comm)
     # --- end to end: numpy batch -> pinned -> H2D, loss D2H every step ---------------------
     h2d = sum(a.nbytes for a in pool[0])
     last = {}
 
     def step_e2e(i):
         out = ex.run('train')                   # batch i: H2D from the pinned dataset, prefetched one step ahead
-        last['loss'] = out[0].asnumpy()
+        fut = out[0].asnumpy_async()            # loss i: D2H queued behind step i, read while step i+1 is queued
+        if last.get('pending') is not None:
+            last['loss'] = last['pending'].get()
+        last['pending'] = fut
+
+    def finish_e2e():
+        if last.get('pending') is not None:
+            last['loss'] = last.pop('pending').get()
 
     for i in range(max(args.warmup, 3)):
         step_e2e(i)
-    ms_e2e = timed(step_e2e, args.steps, torch, device, comm)
+    ms_e2e, spread_e2e = timed(step_e2e, args.steps, torch, device, comm, finish=finish_e2e)
     clocks = sampler.stop()
     launches = getattr(sub, 'graph_launches', 0) * args.steps if sub._graph is not None else 0
     return {
         'ms_dev': ms_dev, 'ms_e2e': ms_e2e, 'clocks': clocks, 'h2d': h2d, 'd2h': 4,
         'global_batch': B * world, 'launches': launches, 'graph': sub._graph is not None,
         'loss': float(np.asarray(last['loss']).reshape(-1)[0]),
-        'launches_per_step': getattr(sub, 'graph_launches', 0),
+        'launches_per_step': getattr(sub, 'graph_launches', 0), 'spread': spread_dev, 'spread_e2e': spread_e2e,
+        'fused_wdl': getattr(ex, 'fused_wdl', 0),
     }
 
 
@@ -234,21 +255,29 @@ def bench_moe(args, ht, torch, np, comm, device, steps):
 
     for i in range(max(3, min(args.warmup, 4))):
         step_dev(i)
-    ms_dev = timed(step_dev, steps, torch, device, comm)
+    ms_dev, spread_dev = timed(step_dev, steps, torch, device, comm)
 
     # (b) end to end: every step's input batch comes from pinned host memory (H2D inside the timed
     #     region, overlapped with the previous step's compute) and the loss is read back every step
     def step(i):
         out = ex.run('train', feed_dict={t: tv})
-        last['loss'] = out[0].asnumpy()
+        fut = out[0].asnumpy_async()
+        if last.get('pending') is not None:
+            last['loss'] = last['pending'].get()
+        last['pending'] = fut
+
+    def finish():
+        if last.get('pending') is not None:
+            last['loss'] = last.pop('pending').get()
 
     for i in range(3):
         step(i)
-    ms = timed(step, steps, torch, device, comm)
+    ms, spread_e2e = timed(step, steps, torch, device, comm, finish=finish)
     sub = ex.subexecutor['train']
     return {'ms_e2e': ms, 'ms_dev': ms_dev, 'tokens': bs * ntok * world, 'h2d': bs * ntok * dim * 4 + tv.nbytes, 'd2h': 4,
             'loss': float(np.asarray(last['loss']).reshape(-1)[0]),
-            'launches_per_step': getattr(sub, 'graph_launches', 0), 'graph': sub._graph is not None}
+            'launches_per_step': getattr(sub, 'graph_launches', 0), 'graph': sub._graph is not None,
+            'spread': spread_dev, 'spread_e2e': spread_e2e}
 
 
 def main():
@@ -288,16 +317,19 @@ def main():
                        'optimizer': 'SGD lr 0.01', 'cuda_graph': w['graph'],
                        'kernel_launches_per_step': w['launches_per_step'],
                        'l2_policy': 'working set (17.3 GB embedding table, random rows) exceeds the 126 MB L2',
-                       'final_loss': w['loss']},
+                       'final_loss': w['loss'], 'fused_step': bool(w['fused_wdl']),
+                       'timing': dict(w['spread'], rule='median of blocks of `steps` steps, >= 3 blocks and >= 0.5 s'),
+                       'e2e_timing': dict(w['spread_e2e'], loss_readback='async D2H to pinned memory every step, '
+                                          'consumed one step later')},
         })
     if args.workload in ('moe', 'both'):
-        steps = args.moe_steps or max(5, args.steps // 10)
+        steps = args.moe_steps or args.steps
         m = bench_moe(args, ht, torch, np, comm, device, steps)
         moe_out = {'metric': 'moe_tokens_per_s', 'value': m['tokens'] / (m['ms_dev'] / 1e3), 'unit': 'tokens/s',
                    'ms_per_step': m['ms_dev'], 'steps': steps,
                    'e2e': {'value': m['tokens'] / (m['ms_e2e'] / 1e3), 'unit': 'tokens/s', 'ms_per_step': m['ms_e2e'],
                            'h2d_bytes_per_step': m['h2d'], 'd2h_bytes_per_step': m['d2h']},
-                   'final_loss': m['loss'], 'cuda_graph': m['graph'],
+                   'final_loss': m['loss'], 'cuda_graph': m['graph'], 'timing': m['spread'], 'e2e_timing': m['spread_e2e'],
                    'kernel_launches_per_step': m['launches_per_step'],
                    'config': {'model': 'MoE layer top-2, 16x1024 tokens/GPU, d=h=2048, 2 experts/GPU',
                               'global_tokens': m['tokens'], 'parallelism': 'ep%d' % world}}

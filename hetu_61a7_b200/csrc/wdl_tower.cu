@@ -41,6 +41,7 @@ struct TowerParams {
     float* loss; float* pred; float* dz;       // [1], [128], [128]
     float* dW1; float* dW2; float* dW3; float* dW4;
     int nd, emb_cols, pitch;
+    unsigned long long* stamps;   // optional phase time stamps (ns), written by CTA 0 / thread 0
 };
 
 struct TowerSmem {
@@ -57,6 +58,13 @@ struct TowerSmem {
     float dh1[TB][TSL + 1];
 };
 
+__device__ __forceinline__ void stamp(const TowerParams& p, int i) {
+    if (p.stamps != nullptr && threadIdx.x == 0 && blockIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.stamps[i] = t;
+    }
+}
 __device__ __forceinline__ void cluster_sync_all() {
     __syncwarp();
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
@@ -124,6 +132,7 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     const int ecs = p.emb_cols / TCL;                    // embedding columns of the head handled by this CTA
     const int hcs = p.pitch / TCL;                       // head-gradient columns handled by this CTA
 
+    stamp(p, 0);
     if (tid == 0) {
         prefetch_tmap(&tm_h1k); prefetch_tmap(&tm_W2mn);
         for (int g = 0; g < 4; ++g) {
@@ -153,6 +162,7 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = S.tmem_ptr;
+    stamp(p, 1);
     // ---- P1: h1 = relu(x W1), K = nd (13): too thin for a tensor-core tile --------------------------------------
     for (int idx = tid; idx < TB * TSL; idx += TTHREADS) {
         const int n = idx & (TSL - 1), b = idx >> 5;
@@ -163,6 +173,7 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     __threadfence();
     __syncthreads();
     cluster_sync_all();                                                             // h1 complete
+    stamp(p, 2);
     // ---- P2: h2 = relu(h1 W2) ------------------------------------------------------------------------------------
     if (tid == 0) tower_gemm_ka(&tm_h1k, &tm_W2mn, true, c, sA, sB, S.full[0], &S.done[0], tmem_base);
     if (warp >= 2 && warp < 6) {
@@ -180,6 +191,7 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     __threadfence();
     __syncthreads();
     cluster_sync_all();                                                             // h2 complete
+    stamp(p, 3);
     // ---- P3: y3 = h2 W3 -> y4[:, emb_cols + n], logit partial of the y3 block -------------------------------------
     if (tid == 0) { tc_fence_after(); tower_gemm_ka(&tm_h2k, &tm_W3mn, true, c, sA, sB, S.full[1], &S.done[1], tmem_base); }
     if (warp >= 2 && warp < 6) {
@@ -200,6 +212,7 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     __threadfence();
     __syncthreads();
     cluster_sync_all();                                                             // every CTA's zpart and y3 columns complete
+    stamp(p, 4);
     // ---- head: logits through distributed shared memory, sigmoid, BCE, dz -----------------------------------------
     if (tid < TB) {
         float z = 0.f;
@@ -220,6 +233,7 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     }
     __syncthreads();
     if (c == 0 && tid == 0) p.loss[0] = (S.lossw[0] + S.lossw[1] + S.lossw[2] + S.lossw[3]) * (1.0f / TB);
+    stamp(p, 5);
     // ---- P5: u = h2^T dz, v3 = W3 w4y (slice), dW3 = u x w4y, dh2 = relu'(h2) . (dz x v3) -------------------------
     {
         float acc = 0.f;
@@ -253,6 +267,7 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     __threadfence();
     __syncthreads();
     cluster_sync_all();                                                             // dh2 complete
+    stamp(p, 6);
     // ---- P6a: dh1 = (dh2 W2^T) . relu'(h1)   |  vector warps: dW4 = y4^T dz ---------------------------------------
     if (tid == 0) {
         tc_fence_after();
@@ -310,6 +325,7 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
         }
     }
     __syncthreads();
+    stamp(p, 7);
     // ---- P6b epilogue: dW2 slice   |  vector warps: dW1 = x^T dh1 (slice) -----------------------------------------
     if (warp >= 2 && warp < 6) {
         const int q = warp & 3;
@@ -335,9 +351,12 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     }
     tc_fence_before();
     __syncthreads();
+    stamp(p, 8);
     if (warp == 1) tmem_dealloc(tmem_base, 128);
 }
 }  // namespace
+
+static unsigned long long* g_tower_stamps = nullptr;
 
 // work: 3 * 128 * 256 floats (h1, h2, dh2).  All pointers are this GPU's memory; y4 is the concat buffer whose
 // first emb_cols columns hold the gathered embedding rows (hetu_gather_rows_pitched).
@@ -355,6 +374,11 @@ HETU_API int hetu_wdl_tower_step(const float* x, float* y4, const float* labels,
     p.h1 = work; p.h2 = work + TB * TH; p.dh2 = work + 2 * TB * TH;
     p.loss = loss; p.pred = pred; p.dz = dz; p.dW1 = dW1; p.dW2 = dW2; p.dW3 = dW3; p.dW4 = dW4;
     p.nd = nd; p.emb_cols = emb_cols; p.pitch = emb_cols + TH;
+    p.stamps = nullptr;
+    if (getenv("HETU_WDL_STAMPS") != nullptr) {          // diagnostics: phase boundaries in managed memory
+        if (g_tower_stamps == nullptr) HETU_CUDA(cudaMallocManaged(&g_tower_stamps, 16 * sizeof(unsigned long long)));
+        p.stamps = g_tower_stamps;
+    }
     CUtensorMap h1k, h2k, dh2k, W2mn, W3mn, W2k, h1mn, dh2mn;
     if (make_tmap(&h1k, p.h1, TH, TB, 1, 0, TB, false) || make_tmap(&h2k, p.h2, TH, TB, 1, 0, TB, false) ||
         make_tmap(&dh2k, p.dh2, TH, TB, 1, 0, TB, false) || make_tmap(&W2mn, W2, TH, TH, 1, 0, 32, true) ||
@@ -454,5 +478,13 @@ HETU_API int hetu_wdl_sparse_sgd_rank1(void* const* bases, int nshard, const voi
     wdl_sparse_sgd_rank1_kernel<<<ew_grid(n * 32, 256, 16), 256, 0, s>>>(tab, idx, idx_code, dz, w4, lr_p, scale, n, width,
                                                                         fields, vocab);
     HETU_CHECK_LAUNCH("hetu_wdl_sparse_sgd_rank1");
+    return 0;
+}
+
+// diagnostics: phase time stamps (ns) of the last hetu_wdl_tower_step launched with HETU_WDL_STAMPS set
+HETU_API int hetu_wdl_tower_stamps(unsigned long long* out9) {
+    if (g_tower_stamps == nullptr) { hetu_set_error("hetu_wdl_tower_stamps: no stamped launch yet"); return -1; }
+    HETU_CUDA(cudaDeviceSynchronize());
+    for (int i = 0; i < 9; ++i) out9[i] = g_tower_stamps[i];
     return 0;
 }

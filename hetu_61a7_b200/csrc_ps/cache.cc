@@ -136,6 +136,15 @@ class Cache {
         }
         return prow.size();
     }
+    // Forget every line, pending local gradients included (the server copy was just replaced, e.g. by a checkpoint
+    // load: rows and un-pushed deltas held here describe the old parameters).
+    void invalidate() {
+        std::unique_lock<std::mutex> l(mu_);
+        lines_.clear();
+        order_.clear();
+        evicted_.clear();
+        permanent_ = 0;
+    }
     size_t size() const { return lines_.size(); }
     Perf perf_;
     bool bypass_ = false;
@@ -298,6 +307,7 @@ HPS_API int64_t hcache_flush(void* h) {
     try { return (int64_t)static_cast<Cache*>(h)->flush(); }
     catch (const std::exception& e) { g_cerr = e.what(); return -1; }
 }
+HPS_API void hcache_invalidate(void* h) { static_cast<Cache*>(h)->invalidate(); }
 HPS_API uint64_t hcache_size(void* h) { return static_cast<Cache*>(h)->size(); }
 HPS_API void hcache_bypass(void* h, int on) { static_cast<Cache*>(h)->bypass_ = on != 0; }
 HPS_API int hcache_count(void* h, int64_t key) { return static_cast<Cache*>(h)->count(key); }

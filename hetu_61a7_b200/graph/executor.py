@@ -469,6 +469,14 @@ class Executor(object):
                 continue
             if hasattr(val, 'export_dense'):
                 val = val.export_dense()
+            if cfg.ps_comm is not None and getattr(node, 'ps_resident', False):
+                # dense parameter kept on the servers: the device replica only mirrors it (and lags under ASP / SSP).
+                # The checkpoint holds the servers' value, in the pickle and as <id>_<shard>.dat like the
+                # reference (executor.py:469-474)
+                state[name] = np.asarray(cfg.ps_comm.Pull(node.id)).reshape(tuple(val.shape)).copy()
+                if self.rank == 0:
+                    cfg.ps_comm.SaveParam(node.id, file_path)
+                continue
             state[name] = val.detach().cpu().numpy()
         # BatchNorm running statistics (not checkpointed upstream - SURVEY 5.4)
         for node in self.topo_order:
@@ -529,6 +537,8 @@ class Executor(object):
 
     def load_dict(self, state_dict, file_path: str = None, consider_splits: bool = False):
         cfg = self.config
+        if cfg.ps_comm is not None:
+            cfg.ps_comm.BarrierWorker()                  # nobody is still pushing into the parameters being replaced
         for name, node in self._named_params().items():
             cur = cfg.placeholder_to_arr_map.get(node)
             if cur is None:
@@ -539,6 +549,18 @@ class Executor(object):
             if name not in state_dict:
                 continue
             value = state_dict[name]
+            if cfg.ps_comm is not None and getattr(node, 'ps_resident', False) and not hasattr(cur, 'import_dense'):
+                # dense parameter owned by the servers: restore THEIR copy (a push is "+="), then every worker
+                # refreshes its replica; copying into the replica alone is undone by the next push-pull
+                want = np.asarray(value, dtype=np.float32).reshape(-1)
+                if self.rank == 0:
+                    have = np.asarray(cfg.ps_comm.Pull(node.id), dtype=np.float32).reshape(-1)
+                    cfg.ps_comm.Push(node.id, want - have)
+                    cfg.ps_comm.Wait(node.id)
+                cfg.ps_comm.BarrierWorker()
+                fresh = np.asarray(cfg.ps_comm.Pull(node.id), dtype=np.float32).reshape(tuple(cur.shape))
+                cur.copy_(to_tensor(fresh.copy()).to(cur.device))
+                continue
             if consider_splits and node.reshaped:
                 value = node.reshape_tensor(np.asarray(value))
             if hasattr(cur, 'import_dense'):
@@ -560,6 +582,14 @@ class Executor(object):
                             t.copy_(v.to(t.device))
         if cfg.ps_comm is not None:
             cfg.ps_comm.BarrierWorker()
+            # rows and un-pushed deltas in the HET caches describe the parameters that were just replaced
+            for sub in self.subexecutor.values():
+                for n in sub.topo_order:
+                    cache = getattr(n, 'cache', None)
+                    if cache is not None and hasattr(cache, 'invalidate'):
+                        cache.invalidate()
+                    if hasattr(n, '_pf'):
+                        n._pf = None                      # prefetched rows of the old table
 
     def recordLoads(self):
         if self.config.ps_comm is not None:

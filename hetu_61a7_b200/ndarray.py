@@ -125,6 +125,41 @@ def to_tensor(value, device=None, dtype=None) -> torch.Tensor:
     return t
 
 
+_PINNED_RING = {}
+
+
+def _pinned_copy(t):
+    """Copies ``t`` into the next slot of a small ring of pinned host buffers (one ring per shape / dtype / device);
+    eight copies may be in flight before a slot is reused."""
+    import torch
+    key = (tuple(t.shape), t.dtype, t.device.index)
+    ring = _PINNED_RING.get(key)
+    if ring is None:
+        ring = _PINNED_RING[key] = {'bufs': [torch.empty(tuple(t.shape), dtype=t.dtype).pin_memory() for _ in range(8)],
+                                    'events': [torch.cuda.Event() for _ in range(8)], 'turn': 0}
+    i = ring['turn'] % 8
+    ring['turn'] += 1
+    buf, ev = ring['bufs'][i], ring['events'][i]
+    buf.copy_(t, non_blocking=True)
+    ev.record(torch.cuda.current_stream(t.device))
+    return buf, ev
+
+
+class HostFuture(object):
+    """Result of ``NDArray.asnumpy_async``: ``get()`` returns the numpy value once its copy has landed."""
+
+    def __init__(self, host_tensor, event):
+        self._t, self._ev = host_tensor, event
+
+    def ready(self) -> bool:
+        return self._ev is None or self._ev.query()
+
+    def get(self) -> np.ndarray:
+        if self._ev is not None:
+            self._ev.synchronize()
+        return self._t.numpy().copy()
+
+
 class NDArray(object):
     """Thin handle over a torch tensor.  reference: ndarray.py:140-403."""
 
@@ -187,6 +222,17 @@ class NDArray(object):
 
     def asnumpy(self) -> np.ndarray:
         return self.tensor.detach().cpu().numpy()
+
+    def asnumpy_async(self) -> 'HostFuture':
+        """Device -> host copy that does not stall the host: the copy into a pinned staging buffer is queued on the
+        current stream behind the work that produces this array, and the returned handle's ``get()`` waits for
+        that copy only.  A training loop reads step i's loss while step i+1 is already queued, so the host never
+        idles on the device (the reference's ``asnumpy`` is a synchronous cudaMemcpy, python/hetu/ndarray.py:265-279).
+        """
+        t = self.tensor.detach()
+        if t.device.type != 'cuda':
+            return HostFuture(t.cpu().clone(), None)
+        return HostFuture(*_pinned_copy(t))
 
     def copyto(self, target):
         if isinstance(target, DLContext):

@@ -122,6 +122,12 @@ class CacheSparseTable(object):
             self._chk(-1)
         return n
 
+    def invalidate(self) -> None:
+        """Drop every cached row and every un-pushed local update (after the server copy was replaced, e.g.
+        ``Executor.load``); the next lookup pulls fresh rows."""
+        self.pool.submit(lambda: None).result()            # queued calls on this table finish first
+        self.lib.hcache_invalidate(self.handle)
+
     def bypass(self):
         self.lib.hcache_bypass(self.handle, 1)
 

@@ -22,6 +22,18 @@ def test_heturun_ps_modes(mode, policy, extra):
         assert 'ckpt_%s.bin' % mode in files and any(f.endswith('.dat') for f in files), files
 
 
+@pytest.mark.parametrize('mode,policy', [('PS', 'none'), ('Hybrid', 'lfuopt')])
+def test_checkpoint_round_trip_in_ps_modes(mode, policy):
+    """save -> drift -> load -> the next step reproduces the step taken right after the save (servers' copies of dense
+    and embedding parameters restored, replicas refreshed, HET cache dropped)."""
+    with tempfile.TemporaryDirectory() as d:
+        env = dict(os.environ, HETU_CONFIG_PATH=os.path.join(d, 'hetu_config.yml'), OMP_NUM_THREADS='2')
+        cmd = [os.path.join(ROOT, 'bin', 'heturun'), '-s', '1', '-w', '2', sys.executable,
+               os.path.join(ROOT, 'tests', 'ps_ckpt_worker.py'), mode, policy, d]
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+        assert r.returncode == 0 and r.stdout.count('OK') == 2, r.stdout[-2000:] + r.stderr[-3000:]
+
+
 def test_heturun_detects_a_dead_worker_and_restarts(tmp_path):
     """A worker that exits with an error takes the group down instead of leaving the others hanging in a
     collective; with --max-restarts the group is relaunched and resumes from its checkpoint."""
