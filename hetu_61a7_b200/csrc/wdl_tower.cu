@@ -28,6 +28,7 @@ constexpr int TWARPS = TTHREADS / 32;
 constexpr int kAArea = TB * TH * 4;          // 128 KB
 constexpr int kBArea = TSL * TH * 4;         // 32 KB
 constexpr int kKB = TH / 32;                 // 8 k-blocks of 32 fp32 (128 B)
+constexpr int kMaxSlice4 = 160;              // float4 columns of the head input per CTA: pitch <= 5120
 
 struct TowerParams {
     const float* x;        // [128, nd]
@@ -40,7 +41,8 @@ struct TowerParams {
     float* h1; float* h2; float* dh2;          // [128, 256] work buffers
     float* loss; float* pred; float* dz;       // [1], [128], [128]
     float* dW1; float* dW2; float* dW3; float* dW4;
-    int nd, emb_cols, pitch;
+    const float* zpf;      // [128, fields]: per-(sample, field) partial logits written by the gather kernel
+    int nd, emb_cols, pitch, width;
     unsigned long long* stamps;   // optional phase time stamps (ns), written by CTA 0 / thread 0
 };
 
@@ -55,7 +57,10 @@ struct TowerSmem {
     float red[TWARPS][TSL];
     float lossw[4];
     float x[TB * 16];
+    float w1[16 * TSL];          // this CTA's 32 columns of W1
+    float h2s[TB][TSL + 1];      // this CTA's 32 columns of h2 (kept for u = h2^T dz and the relu mask of dh2)
     float dh1[TB][TSL + 1];
+    float4 colsum[2][kMaxSlice4];
 };
 
 __device__ __forceinline__ void stamp(const TowerParams& p, int i) {
@@ -82,6 +87,18 @@ __device__ __forceinline__ float ld_dsmem(const float* local, uint32_t rank) {
     asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
     return v;
 }
+// TMA tile load delivered to the same shared-memory offset of every CTA in `mask`; each destination's mbarrier (same
+// offset) receives the byte count.  Only used on tensor maps over this GPU's own work buffers (h1, h2, dh2): TMA
+// multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory
+// hung the GPU.
+__device__ __forceinline__ void tma_load_3d_mc(void* dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar,
+                                               uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
+        "[%0], [%1, {%3, %4, %5}], [%2], %6;"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "h"(mask)
+        : "memory");
+}
 
 // idesc: D = f32, A = B = tf32, M = 128, N = 32
 __device__ __forceinline__ uint32_t tower_idesc(int a_mn, int b_mn) {
@@ -90,13 +107,15 @@ __device__ __forceinline__ uint32_t tower_idesc(int a_mn, int b_mn) {
 }
 
 // C[128, 32c..32c+32) = A[128, 256] * Bslice, A K-major through tmA, B either MN-major ([k][n] memory, forward) or
-// K-major ([j][k] memory, backward data).  Called by ONE thread.
+// K-major ([j][k] memory, backward data).  Called by ONE thread of every CTA of the cluster, all CTAs past the same
+// cluster barrier: CTA c fetches k-block c of A once and multicasts it to the whole cluster (each CTA needs all of A
+// but reads only 1/8 of it from L2); B slices are private.
 __device__ void tower_gemm_ka(const CUtensorMap* tmA, const CUtensorMap* tmB, bool b_mn, int c, uint8_t* sA, uint8_t* sB,
                               uint64_t* full, uint64_t* done, uint32_t tmem_d) {
     asm volatile("fence.proxy.async.global;" ::: "memory");        // activations were written with ordinary stores
+    for (int kb = 0; kb < kKB; ++kb) mbar_expect_tx(&full[kb], 16384 + 4096);
+    tma_load_3d_mc(sA + c * 16384, tmA, c * 32, 0, 0, &full[c], (uint16_t)0xFF);           // box {32 k, 128 rows}
     for (int kb = 0; kb < kKB; ++kb) {
-        mbar_expect_tx(&full[kb], 16384 + 4096);
-        tma_load_3d(sA + kb * 16384, tmA, kb * 32, 0, 0, &full[kb]);                    // box {32 k, 128 rows}
         if (b_mn) tma_load_3d(sB + kb * 4096, tmB, c * TSL, kb * 32, 0, &full[kb]);      // box {32 n, 32 k}
         else tma_load_3d(sB + kb * 4096, tmB, kb * 32, c * TSL, 0, &full[kb]);           // box {32 k, 32 rows}
     }
@@ -129,8 +148,8 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int c = (int)cluster_ctarank();
     const int n0 = c * TSL;
-    const int ecs = p.emb_cols / TCL;                    // embedding columns of the head handled by this CTA
-    const int hcs = p.pitch / TCL;                       // head-gradient columns handled by this CTA
+    const int hcs4 = p.pitch / (4 * TCL);                // float4 columns of the head gradient handled by this CTA
+    const int fields = p.emb_cols / p.width;
 
     stamp(p, 0);
     if (tid == 0) {
@@ -142,21 +161,17 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(&S.tmem_ptr, 128);
-    // ---- P0: stage x and the y3 part of W4; partial logits of the embedding block ------------------------------
+    // ---- P0: stage x, this CTA's W1 columns and the y3 part of W4; logits of the embedding block (CTA 0) ----------
     for (int i = tid; i < TB * p.nd; i += TTHREADS) S.x[i] = p.x[i];
-    for (int i = tid; i < TH; i += TTHREADS) S.w4y[i] = p.W4[p.emb_cols + i];
-    {
-        const float4* w4 = reinterpret_cast<const float4*>(p.W4 + (size_t)c * ecs);
-        for (int row = warp; row < TB; row += TWARPS) {
-            const float4* yr = reinterpret_cast<const float4*>(p.y4 + (size_t)row * p.pitch + (size_t)c * ecs);
-            float acc = 0.f;
-            for (int j = lane; j < (ecs >> 2); j += 32) {
-                float4 a = yr[j], b = __ldg(w4 + j);
-                acc += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
-            }
-            acc = warp_sum(acc);
-            if (lane == 0) S.zpart[row] = acc;
+    for (int i = tid; i < p.nd * TSL; i += TTHREADS) S.w1[i] = __ldg(p.W1 + (i >> 5) * TH + n0 + (i & 31));
+    for (int i = tid; i < TH; i += TTHREADS) S.w4y[i] = __ldg(p.W4 + p.emb_cols + i);
+    if (tid < TB) {
+        float z = 0.f;
+        if (c == 0) {                                    // per-(sample, field) partial dots left by the gather kernel
+            const float* zp = p.zpf + (size_t)tid * fields;
+            for (int f = 0; f < fields; ++f) z += zp[f];
         }
+        S.zpart[tid] = z;
     }
     tc_fence_before();
     __syncthreads();
@@ -167,7 +182,7 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     for (int idx = tid; idx < TB * TSL; idx += TTHREADS) {
         const int n = idx & (TSL - 1), b = idx >> 5;
         float acc = 0.f;
-        for (int k = 0; k < p.nd; ++k) acc += S.x[b * p.nd + k] * __ldg(p.W1 + k * TH + n0 + n);
+        for (int k = 0; k < p.nd; ++k) acc += S.x[b * p.nd + k] * S.w1[k * TSL + n];
         p.h1[b * TH + n0 + n] = fmaxf(acc, 0.f);
     }
     __threadfence();
@@ -184,8 +199,9 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), v);
         float4* dst = reinterpret_cast<float4*>(p.h2 + row * TH + n0);
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-            dst[j] = make_float4(fmaxf(v[4 * j], 0.f), fmaxf(v[4 * j + 1], 0.f), fmaxf(v[4 * j + 2], 0.f), fmaxf(v[4 * j + 3], 0.f));
+        for (int j = 0; j < 32; ++j) { v[j] = fmaxf(v[j], 0.f); S.h2s[row][j] = v[j]; }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         tc_fence_before();
     }
     __threadfence();
@@ -208,6 +224,16 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
         for (int j = 0; j < 32; ++j) acc += v[j] * S.w4y[n0 + j];
         S.zpart[row] += acc;
         tc_fence_before();
+    } else if (warp >= 6) {
+        // v3 = W3 w4y for this CTA's 32 rows of W3: independent of the activations, done while the tensor core works
+        for (int k = warp - 6; k < TSL; k += 6) {
+            const float* wr = p.W3 + (size_t)(n0 + k) * TH;
+            float a2 = 0.f;
+#pragma unroll
+            for (int j = 0; j < TH / 32; ++j) a2 += __ldg(wr + lane + 32 * j) * S.w4y[lane + 32 * j];
+            a2 = warp_sum(a2);
+            if (lane == 0) S.v3[k] = a2;
+        }
     }
     __threadfence();
     __syncthreads();
@@ -234,41 +260,27 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     __syncthreads();
     if (c == 0 && tid == 0) p.loss[0] = (S.lossw[0] + S.lossw[1] + S.lossw[2] + S.lossw[3]) * (1.0f / TB);
     stamp(p, 5);
-    // ---- P5: u = h2^T dz, v3 = W3 w4y (slice), dW3 = u x w4y, dh2 = relu'(h2) . (dz x v3) -------------------------
+    // ---- P5: u = h2^T dz (slice, from shared memory), dW3 = u x w4y, dh2 = relu'(h2) . (dz x v3) -------------------
     {
         float acc = 0.f;
-        for (int b = warp; b < TB; b += TWARPS) acc += __ldcg(p.h2 + b * TH + n0 + lane) * S.dz[b];
+        for (int b = warp; b < TB; b += TWARPS) acc += S.h2s[b][lane] * S.dz[b];
         S.red[warp][lane] = acc;
-        for (int k = warp; k < TSL; k += TWARPS) {
-            const float* wr = p.W3 + (size_t)(n0 + k) * TH;
-            float a2 = 0.f;
-            for (int j = lane; j < TH; j += 32) a2 += __ldg(wr + j) * S.w4y[j];
-            a2 = warp_sum(a2);
-            if (lane == 0) S.v3[k] = a2;
-        }
     }
+    for (int idx = tid; idx < TB * TSL; idx += TTHREADS) {
+        const int k = idx & (TSL - 1), b = idx >> 5;
+        p.dh2[b * TH + n0 + k] = S.h2s[b][k] > 0.f ? S.dz[b] * S.v3[k] : 0.f;
+    }
+    __threadfence();
     __syncthreads();
+    cluster_sync_all();                                                             // dh2 complete
+    stamp(p, 6);
     if (tid < TSL) {
         float a = 0.f;
 #pragma unroll
         for (int w = 0; w < TWARPS; ++w) a += S.red[w][tid];
         S.u[tid] = a;
     }
-    __syncthreads();
-    for (int idx = tid; idx < TSL * TH; idx += TTHREADS) {
-        const int n = idx & (TH - 1), k = idx >> 8;
-        p.dW3[(size_t)(n0 + k) * TH + n] = S.u[k] * S.w4y[n];
-    }
-    for (int idx = tid; idx < TB * TSL; idx += TTHREADS) {
-        const int k = idx & (TSL - 1), b = idx >> 5;
-        const float h = __ldcg(p.h2 + b * TH + n0 + k);
-        p.dh2[b * TH + n0 + k] = h > 0.f ? S.dz[b] * S.v3[k] : 0.f;
-    }
-    __threadfence();
-    __syncthreads();
-    cluster_sync_all();                                                             // dh2 complete
-    stamp(p, 6);
-    // ---- P6a: dh1 = (dh2 W2^T) . relu'(h1)   |  vector warps: dW4 = y4^T dz ---------------------------------------
+    // ---- P6a: dh1 = (dh2 W2^T) . relu'(h1)   |  vector warps: dW4 = y4^T dz, dW3 --------------------------------
     if (tid == 0) {
         tc_fence_after();
         tower_gemm_ka(&tm_dh2k, &tm_W2k, false, c, sA, sB, S.full[2], &S.done[2], tmem_base);
@@ -301,32 +313,46 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
         umma_commit(&S.done[3]);
     } else if (warp >= 2 && warp < 6) {
         const int q = warp & 3, row = q * 32 + lane;
+        const float4* hp = reinterpret_cast<const float4*>(p.h1 + row * TH + n0);
+        float4 h[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) h[j] = __ldcg(hp + j);                         // relu mask of h1, loaded under the MMA
         mbar_wait(&S.done[2], 0);
         tc_fence_after();
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), v);
-        const float4* hp = reinterpret_cast<const float4*>(p.h1 + row * TH + n0);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const float4 h = __ldcg(hp + j);
-            S.dh1[row][4 * j + 0] = h.x > 0.f ? v[4 * j + 0] : 0.f;
-            S.dh1[row][4 * j + 1] = h.y > 0.f ? v[4 * j + 1] : 0.f;
-            S.dh1[row][4 * j + 2] = h.z > 0.f ? v[4 * j + 2] : 0.f;
-            S.dh1[row][4 * j + 3] = h.w > 0.f ? v[4 * j + 3] : 0.f;
+            S.dh1[row][4 * j + 0] = h[j].x > 0.f ? v[4 * j + 0] : 0.f;
+            S.dh1[row][4 * j + 1] = h[j].y > 0.f ? v[4 * j + 1] : 0.f;
+            S.dh1[row][4 * j + 2] = h[j].z > 0.f ? v[4 * j + 2] : 0.f;
+            S.dh1[row][4 * j + 3] = h[j].w > 0.f ? v[4 * j + 3] : 0.f;
         }
     } else if (warp >= 6) {
-        const int t6 = tid - 6 * 32;                    // 192 vector threads
-        for (int col = t6; col < hcs; col += 6 * 32) {
-            const float* yp = p.y4 + (size_t)c * hcs + col;
-            float acc = 0.f;
-#pragma unroll 8
-            for (int b = 0; b < TB; ++b) acc += __ldcg(yp + (size_t)b * p.pitch) * S.dz[b];
-            p.dW4[(size_t)c * hcs + col] = acc;
+        // dW4 slice: (float4 column, batch half) items, 16 independent loads in flight per thread
+        const int t6 = tid - 6 * 32;
+        for (int item = t6; item < 2 * hcs4; item += 6 * 32) {
+            const int c4 = item % hcs4, half = item / hcs4;
+            const float4* yp = reinterpret_cast<const float4*>(p.y4 + (size_t)(half * 64) * p.pitch) + (size_t)c * hcs4 + c4;
+            const size_t rstride = (size_t)p.pitch >> 2;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+            for (int b0 = 0; b0 < 64; b0 += 16) {
+                float4 t[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) t[j] = __ldcg(yp + (size_t)(b0 + j) * rstride);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float d = S.dz[half * 64 + b0 + j];
+                    acc.x += t[j].x * d; acc.y += t[j].y * d; acc.z += t[j].z * d; acc.w += t[j].w * d;
+                }
+            }
+            S.colsum[half][c4] = acc;
         }
     }
     __syncthreads();
     stamp(p, 7);
-    // ---- P6b epilogue: dW2 slice   |  vector warps: dW1 = x^T dh1 (slice) -----------------------------------------
+    // ---- P6b epilogue: dW2 slice   |  vector warps: dW4 store, dW3 = u x w4y, dW1 = x^T dh1 (slice) ----------------
     if (warp >= 2 && warp < 6) {
         const int q = warp & 3;
         mbar_wait(&S.done[3], 0);
@@ -341,6 +367,16 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
         }
     } else if (warp >= 6) {
         const int t6 = tid - 6 * 32;
+        for (int c4 = t6; c4 < hcs4; c4 += 6 * 32) {
+            const float4 a = S.colsum[0][c4], b = S.colsum[1][c4];
+            reinterpret_cast<float4*>(p.dW4)[(size_t)c * hcs4 + c4] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+        }
+        for (int idx = t6; idx < TSL * (TH / 4); idx += 6 * 32) {
+            const int n4 = idx & (TH / 4 - 1), k = idx >> 6;
+            const float uk = S.u[k];
+            reinterpret_cast<float4*>(p.dW3 + (size_t)(n0 + k) * TH)[n4] =
+                make_float4(uk * S.w4y[4 * n4], uk * S.w4y[4 * n4 + 1], uk * S.w4y[4 * n4 + 2], uk * S.w4y[4 * n4 + 3]);
+        }
         for (int idx = t6; idx < p.nd * TSL; idx += 6 * 32) {
             const int n = idx & (TSL - 1), k = idx >> 5;
             float acc = 0.f;
@@ -360,23 +396,25 @@ static unsigned long long* g_tower_stamps = nullptr;
 
 // work: 3 * 128 * 256 floats (h1, h2, dh2).  All pointers are this GPU's memory; y4 is the concat buffer whose
 // first emb_cols columns hold the gathered embedding rows (hetu_gather_rows_pitched).
-HETU_API int hetu_wdl_tower_step(const float* x, float* y4, const float* labels, const float* W1, const float* W2,
-                                 const float* W3, const float* W4, float* work, float* loss, float* pred, float* dz,
-                                 float* dW1, float* dW2, float* dW3, float* dW4, int batch, int nd, int hidden,
-                                 int emb_cols, cudaStream_t s) {
-    if (batch != TB || hidden != TH || nd < 1 || nd > 16 || emb_cols <= 0 || emb_cols % (4 * TCL) != 0) {
-        hetu_set_error("hetu_wdl_tower_step: needs batch 128, hidden 256, 1..16 dense features, emb_cols %% 32 == 0 "
-                       "(got %d, %d, %d, %d)", batch, hidden, nd, emb_cols);
+HETU_API int hetu_wdl_tower_step(const float* x, float* y4, const float* zpf, const float* labels, const float* W1,
+                                 const float* W2, const float* W3, const float* W4, float* work, float* loss, float* pred,
+                                 float* dz, float* dW1, float* dW2, float* dW3, float* dW4, int batch, int nd, int hidden,
+                                 int emb_cols, int width, cudaStream_t s) {
+    if (batch != TB || hidden != TH || nd < 1 || nd > 16 || emb_cols <= 0 || emb_cols % (4 * TCL) != 0 || width <= 0 ||
+        emb_cols % width != 0 || (emb_cols + TH) / (4 * TCL) > kMaxSlice4) {
+        hetu_set_error("hetu_wdl_tower_step: needs batch 128, hidden 256, 1..16 dense features, emb_cols %% 32 == 0, "
+                       "emb_cols + 256 <= %d (got %d, %d, %d, %d, width %d)", kMaxSlice4 * 4 * TCL, batch, hidden, nd,
+                       emb_cols, width);
         return -1;
     }
     TowerParams p;
-    p.x = x; p.y4 = y4; p.labels = labels; p.W1 = W1; p.W2 = W2; p.W3 = W3; p.W4 = W4;
+    p.x = x; p.y4 = y4; p.zpf = zpf; p.width = width; p.labels = labels; p.W1 = W1; p.W2 = W2; p.W3 = W3; p.W4 = W4;
     p.h1 = work; p.h2 = work + TB * TH; p.dh2 = work + 2 * TB * TH;
     p.loss = loss; p.pred = pred; p.dz = dz; p.dW1 = dW1; p.dW2 = dW2; p.dW3 = dW3; p.dW4 = dW4;
     p.nd = nd; p.emb_cols = emb_cols; p.pitch = emb_cols + TH;
     p.stamps = nullptr;
-    if (getenv("HETU_WDL_STAMPS") != nullptr) {          // diagnostics: phase boundaries in managed memory
-        if (g_tower_stamps == nullptr) HETU_CUDA(cudaMallocManaged(&g_tower_stamps, 16 * sizeof(unsigned long long)));
+    if (getenv("HETU_WDL_STAMPS") != nullptr) {          // diagnostics: phase boundaries
+        if (g_tower_stamps == nullptr) HETU_CUDA(cudaMalloc(&g_tower_stamps, 16 * sizeof(unsigned long long)));
         p.stamps = g_tower_stamps;
     }
     CUtensorMap h1k, h2k, dh2k, W2mn, W3mn, W2k, h1mn, dh2mn;
@@ -403,23 +441,42 @@ namespace {
 constexpr int kWdlMaxShards = 16;
 struct WdlShards { float* base[kWdlMaxShards]; int nshard; };
 
-// lookup + concat: row i = (sample b, field f) goes to out[b * pitch + f * width ...]
+// lookup + concat: row i = (sample b, field f) goes to out[b * pitch + f * width ...].  With w4 / zpf given the warp
+// also leaves the row's share of the head logit, zpf[i] = <row, w4[f * width ...]>, so the tower kernel never re-reads
+// the embedding block for its forward pass.
 __global__ void __launch_bounds__(256) gather_rows_pitched_kernel(WdlShards tab, const void* __restrict__ idx, int idx_code,
                                                                   float* __restrict__ out, size_t n, int width, int fields,
-                                                                  int pitch, size_t vocab) {
+                                                                  int pitch, size_t vocab, const float* __restrict__ w4,
+                                                                  float* __restrict__ zpf) {
     size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     const size_t nwarp = ((size_t)gridDim.x * blockDim.x) >> 5;
     for (size_t i = warp; i < n; i += nwarp) {
         const long long r = load_index(idx, idx_code, i);
-        float* dst = out + (i / fields) * (size_t)pitch + (i % fields) * (size_t)width;
+        const int f = (int)(i % fields);
+        float* dst = out + (i / fields) * (size_t)pitch + f * (size_t)width;
         const bool ok = r >= 0 && (size_t)r < vocab;
         const float* src = ok ? tab.base[(int)(r % tab.nshard)] + (size_t)(r / tab.nshard) * width : nullptr;
+        float dot = 0.f;
         if ((width & 3) == 0) {
-            for (int j = lane; j < (width >> 2); j += 32)
-                reinterpret_cast<float4*>(dst)[j] = ok ? reinterpret_cast<const float4*>(src)[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int j = lane; j < (width >> 2); j += 32) {
+                const float4 v = ok ? reinterpret_cast<const float4*>(src)[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+                reinterpret_cast<float4*>(dst)[j] = v;
+                if (w4 != nullptr) {
+                    const float4 w = __ldg(reinterpret_cast<const float4*>(w4 + f * (size_t)width) + j);
+                    dot += v.x * w.x + v.y * w.y + v.z * w.z + v.w * w.w;
+                }
+            }
         } else {
-            for (int j = lane; j < width; j += 32) dst[j] = ok ? src[j] : 0.f;
+            for (int j = lane; j < width; j += 32) {
+                const float v = ok ? src[j] : 0.f;
+                dst[j] = v;
+                if (w4 != nullptr) dot += v * __ldg(w4 + f * (size_t)width + j);
+            }
+        }
+        if (zpf != nullptr) {
+            dot = warp_sum(dot);
+            if (lane == 0) zpf[i] = dot;
         }
     }
 }
@@ -460,11 +517,13 @@ int fill_shards(WdlShards& tab, void* const* bases, int nshard, const char* who)
 }  // namespace
 
 HETU_API int hetu_gather_rows_pitched(void* const* bases, int nshard, const void* idx, int idx_code, float* out, size_t n,
-                                      int width, int fields, int pitch, size_t vocab, cudaStream_t s) {
+                                      int width, int fields, int pitch, size_t vocab, const float* w4, float* zpf,
+                                      cudaStream_t s) {
     if (n == 0) return 0;
     WdlShards tab;
     if (fill_shards(tab, bases, nshard, "hetu_gather_rows_pitched")) return -1;
-    gather_rows_pitched_kernel<<<ew_grid(n * 32, 256, 16), 256, 0, s>>>(tab, idx, idx_code, out, n, width, fields, pitch, vocab);
+    gather_rows_pitched_kernel<<<ew_grid(n * 32, 256, 16), 256, 0, s>>>(tab, idx, idx_code, out, n, width, fields, pitch, vocab,
+                                                                       w4, zpf);
     HETU_CHECK_LAUNCH("hetu_gather_rows_pitched");
     return 0;
 }
@@ -485,6 +544,6 @@ HETU_API int hetu_wdl_sparse_sgd_rank1(void* const* bases, int nshard, const voi
 HETU_API int hetu_wdl_tower_stamps(unsigned long long* out9) {
     if (g_tower_stamps == nullptr) { hetu_set_error("hetu_wdl_tower_stamps: no stamped launch yet"); return -1; }
     HETU_CUDA(cudaDeviceSynchronize());
-    for (int i = 0; i < 9; ++i) out9[i] = g_tower_stamps[i];
+    HETU_CUDA(cudaMemcpy(out9, g_tower_stamps, 9 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     return 0;
 }

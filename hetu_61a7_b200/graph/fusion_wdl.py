@@ -162,6 +162,7 @@ def _make_op_class():
                 f = dict(dtype=torch.float32, device=dev)
                 self._bufs = dict(y4=torch.empty((B, pitch), **f), work=torch.empty(3 * B * hid, **f),
                                   loss=torch.empty(1, **f), pred=torch.empty((B, 1), **f), dz=torch.empty(B, **f),
+                                  zpf=torch.empty((B, m['fields']), **f),
                                   dW1=torch.empty((m['nd'], hid), **f), dW2=torch.empty((hid, hid), **f),
                                   dW3=torch.empty((hid, hid), **f), dW4=torch.empty((pitch, 1), **f))
             b = self._bufs
@@ -173,10 +174,10 @@ def _make_op_class():
             n = ids.numel()
             st = L.stream_ptr(dev)
             L.call('gather_rows_pitched', bases, L.c_int(nshard), L.p(ids), L.c_int(_IDX_CODE[ids.dtype]), L.p(b['y4']),
-                   L.c_sz(n), L.c_int(m['width']), L.c_int(m['fields']), L.c_int(pitch), L.c_sz(vocab), st)
-            L.call('wdl_tower_step', L.p(x), L.p(b['y4']), L.p(labels), L.p(W1), L.p(W2), L.p(W3), L.p(W4), L.p(b['work']),
+                   L.c_sz(n), L.c_int(m['width']), L.c_int(m['fields']), L.c_int(pitch), L.c_sz(vocab), L.p(W4), L.p(b['zpf']), st)
+            L.call('wdl_tower_step', L.p(x), L.p(b['y4']), L.p(b['zpf']), L.p(labels), L.p(W1), L.p(W2), L.p(W3), L.p(W4), L.p(b['work']),
                    L.p(b['loss']), L.p(b['pred']), L.p(b['dz']), L.p(b['dW1']), L.p(b['dW2']), L.p(b['dW3']), L.p(b['dW4']),
-                   L.c_int(B), L.c_int(m['nd']), L.c_int(hid), L.c_int(m['emb_cols']), st)
+                   L.c_int(B), L.c_int(m['nd']), L.c_int(hid), L.c_int(m['emb_cols']), L.c_int(m['width']), st)
             self.fused_launches += 2
             self.last = dict(ids=ids, dz=b['dz'], grads=(b['dW1'], b['dW2'], b['dW3'], b['dW4']), W4=W4, E=E,
                              bases=bases, nshard=nshard, vocab=vocab, torch_path=False)

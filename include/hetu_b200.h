@@ -143,11 +143,14 @@ int hetu_scatter_add_rows(float* dense, const void* idx, int idx_code, const flo
  *   columns; work = 3 * 128 * 256 floats; writes loss[1], pred[128], dz[128] and the four weight gradients.
  * wdl_sparse_sgd_rank1: table rows -= lr * scale * dz[b] * W4[f * width ...] (the head's gradient is rank one). */
 int hetu_gather_rows_pitched(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code, float* out,
-                             size_t n, int width, int fields, int pitch, size_t vocab, cudaStream_t s);
-int hetu_wdl_tower_step(const float* x, float* y4, const float* labels, const float* W1, const float* W2,
-                        const float* W3, const float* W4, float* work, float* loss, float* pred, float* dz,
-                        float* dW1, float* dW2, float* dW3, float* dW4, int batch, int nd, int hidden, int emb_cols,
-                        cudaStream_t s);
+                             size_t n, int width, int fields, int pitch, size_t vocab,
+                             const float* w4 /*optional*/, float* zpf /*optional [n]: <row, w4 block of its field>*/,
+                             cudaStream_t s);
+int hetu_wdl_tower_step(const float* x, float* y4, const float* zpf /*[128, fields] from the gather*/,
+                        const float* labels, const float* W1, const float* W2, const float* W3, const float* W4,
+                        float* work, float* loss, float* pred, float* dz, float* dW1, float* dW2, float* dW3,
+                        float* dW4, int batch, int nd, int hidden, int emb_cols, int width, cudaStream_t s);
+int hetu_wdl_tower_stamps(unsigned long long* out9);   /* diagnostics, see benchmarks/wdl_tower_phases.py */
 int hetu_wdl_sparse_sgd_rank1(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code,
                               const float* dz, const float* w4, const float* lr_p, float scale, size_t n, int width,
                               int fields, size_t vocab, cudaStream_t s);
