@@ -7,7 +7,7 @@ baseline/_ref/python/hetu, its native code is baseline/_ref/build/lib/*.so.
 
 Workloads (the configs BASELINE.json names):
   wdl : examples/ctr/models/wdl_criteo.py driven like examples/ctr/run_hetu.py:120-135
-        (N = 1: ht.Executor(eval_nodes, ctx=ht.gpu(0)); N > 1: dist_strategy=ht.dist.DataParallel('AllReduce'))
+        (N = 1: ht.Executor(eval_nodes, ctx=ht.gpu(0)); N > 1: same graph stated in the arm, table on the GPUs, comm_mode='AllReduce' - see bench_wdl)
   moe : examples/moe/test_moe_top.py:16-97 (TopKGate + MoELayer, AllToAll over NCCL)
 
 Environment shims (none touches the reference tree): numpy 2.x removed np.int / np.float / np.bool which the
@@ -206,29 +206,44 @@ def bench_wdl(args, ht, np, comm, cuda, world, rank, local_rank):
     dense_input = ht.dataloader_op([[dense, B, 'train']])
     sparse_input = ht.dataloader_op([[sparse, B, 'train']])
     y_ = ht.dataloader_op([[labels, B, 'train']])
-    loss, prediction, y_, train_op = wdl_criteo(dense_input, sparse_input, y_)
+    if world == 1:
+        loss, prediction, y_, train_op = wdl_criteo(dense_input, sparse_input, y_)
+    else:
+        from hetu import init
+
+        def wdl_criteo_gpu_table(dense_input, sparse_input, y_):
+            feature_dimension, embedding_size, learning_rate = 33762577, 128, 0.01
+            Embedding = init.random_normal([feature_dimension, embedding_size], stddev=0.01, name="snd_order_embedding")
+            sparse = ht.embedding_lookup_op(Embedding, sparse_input)
+            sparse = ht.array_reshape_op(sparse, (-1, 26 * embedding_size))
+            W1 = init.random_normal([13, 256], stddev=0.01, name="W1")
+            W2 = init.random_normal([256, 256], stddev=0.01, name="W2")
+            W3 = init.random_normal([256, 256], stddev=0.01, name="W3")
+            W4 = init.random_normal([256 + 26 * embedding_size, 1], stddev=0.01, name="W4")
+            relu1 = ht.relu_op(ht.matmul_op(dense_input, W1))
+            relu2 = ht.relu_op(ht.matmul_op(relu1, W2))
+            y3 = ht.matmul_op(relu2, W3)
+            y = ht.sigmoid_op(ht.matmul_op(ht.concat_op(sparse, y3, axis=1), W4))
+            loss = ht.reduce_mean_op(ht.binarycrossentropy_op(y, y_), [0])
+            train_op = ht.optim.SGDOptimizer(learning_rate=learning_rate).minimize(loss)
+            return loss, y, y_, train_op
+        loss, prediction, y_, train_op = wdl_criteo_gpu_table(dense_input, sparse_input, y_)
     eval_nodes = {'train': [loss, prediction, y_, train_op]}
     if world == 1:
         ctx = ht.gpu(0) if args.ctx == 'gpu' else ht.cpu(0)
         executor = ht.Executor(eval_nodes, ctx=ctx, seed=123)                       # run_hetu.py:120-122 (--comm None)
     else:
-        # run_hetu.py:124-126.  ht.dist.DataParallel reads the cluster description that heturun leaves in
-        # /tmp/hetu_config.yml (python/hetu/distributed_strategies/base.py:14); the arm is started by torchrun, so it
-        # writes the same one-node description there itself.  In this mode the strategy places the table on every
-        # GPU (distributed_strategies/simple.py:16-22) and the sparse gradient is all-gathered.
-        import socket
-        import yaml
-        try:
-            socket.gethostbyname(socket.gethostname())
-        except Exception:
-            socket.gethostname = lambda: 'localhost'          # DistConfig resolves the host name (context.py:260)
-        cfg = {'nodes': [{'host': 'localhost', 'servers': 0, 'workers': world, 'chief': True}]}
-        tmp = '/tmp/hetu_config.yml.%d' % os.getpid()
-        with open(tmp, 'w') as fw:
-            yaml.dump(cfg, fw)
-        os.replace(tmp, '/tmp/hetu_config.yml')
-        strategy = ht.dist.DataParallel(aggregate='AllReduce')
-        executor = ht.Executor(eval_nodes, dist_strategy=strategy, seed=123)
+        # N > 1.  The reference ships multi-worker W&D only in PS / Hybrid mode (examples/ctr/tests/{ps,hybrid}_wdl_criteo.sh),
+        # which needs ps-lite (ZeroMQ + protobuf: neither can be had offline).  Its AllReduce mode does not run with the
+        # stock model file: wdl_criteo.py pins the table with ctx=ht.cpu(0), the gradient node inherits that as a
+        # DeviceGroup and OptimizerOp.backward_hook -> AllReduceCommunicateOp.__init__ fails in is_gpu_ctx
+        # ("'DeviceGroup' object has no attribute 'device_type'", python/hetu/gpu_ops/AllReduceCommunicate.py:10) before
+        # forward_hook would have resolved it.  So for N > 1 the arm states the same graph (wdl_criteo.py:8-42) itself,
+        # without the two ctx=ht.cpu(0) arguments: table replicated on every GPU, sparse gradients all-gathered by the
+        # reference's AllReduceCommunicateOp, everything else as in the model file.  Kernels, executor, NCCL path: the
+        # reference's own.
+        comm = ht.wrapped_mpi_nccl_init()
+        executor = ht.Executor(eval_nodes, ctx=ht.gpu(comm.local_rank), comm_mode='AllReduce', seed=123)
     timer = Timer(cuda, executor.config.nccl_comm if world > 1 else None)
     last = {}
 
@@ -342,7 +357,8 @@ def main():
                        'parallelism': 'dp%d' % world if world > 1 else 'single',
                        'embedding': ('host table (ctx=ht.cpu(0) in examples/ctr/models/wdl_criteo.py), C++ lookup + '
                                      'sparse SGD on the CPU') if world == 1 else
-                                    'replicated on every GPU by ht.dist.DataParallel(AllReduce), sparse grads all-gathered',
+                                    'replicated on every GPU (graph of wdl_criteo.py without its ctx=ht.cpu(0) pin, which crashes the '
+                                    'reference in AllReduce mode), sparse grads all-gathered over NCCL',
                        'optimizer': 'SGD lr 0.01', 'final_loss': w['loss'],
                        'l2_policy': 'working set (17.3 GB table, random rows) exceeds L2'},
         })

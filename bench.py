@@ -35,6 +35,7 @@ def parse():
     ap.add_argument('--vocab', type=int, default=33762577)
     ap.add_argument('--moe-steps', type=int, default=0, help='0 = same as --steps')
     ap.add_argument('--collectives', default=None, choices=[None, 'symm', 'nccl'])
+    ap.add_argument('--profile', default=None, help='write a per-kernel time table of 50 W&D steps (torch.profiler) here')
     return ap.parse_args()
 
 
@@ -192,6 +193,18 @@ def bench_wdl(args, ht, torch, np, comm, device):
         step_dev(i)
     sampler.mark()
     ms_dev, spread_dev = timed(step_dev, args.steps, torch, device, comm)
+    if args.profile:                                # diagnostics only: kernel durations inside the replayed graph
+        from torch.profiler import profile, ProfilerActivity
+        comm.barrier()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for i in range(50):
+                step_dev(i)
+            torch.cuda.synchronize(device)
+        if rank == 0:
+            with open(args.profile, 'w') as fw:
+                fw.write('W&D step, %d GPU(s), 50 steps, torch.profiler (CUPTI) kernel times\n' % world)
+                fw.write(prof.key_averages().table(sort_by='cuda_time_total', row_limit=25, max_name_column_width=90))
+        comm.barrier()
     # --- end to end: numpy batch -> pinned -> H2D, loss D2H every step ---------------------
     h2d = sum(a.nbytes for a in pool[0])
     last = {}
