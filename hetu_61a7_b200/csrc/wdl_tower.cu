@@ -43,6 +43,24 @@ struct TowerParams {
     float* dW1; float* dW2; float* dW3; float* dW4;
     const float* zpf;      // [128, fields]: per-(sample, field) partial logits written by the gather kernel
     int nd, emb_cols, pitch, width;
+    // data-parallel all-reduce + SGD inside the kernel (apply_sgd != 0).  Gradient slices are PUSHED, as they are
+    // produced, into block [slot][rank] of every rank's arena (peer st.global over NVLink; world == 1: the local
+    // buffer); one release flag per (source, destination) closes the step's pushes; after the flags of all sources
+    // have arrived every rank sums the `world` blocks in rank order and applies the identical update.  Two slots
+    // alternate by step parity, so no barrier is needed: a rank overwrites a slot only after it has seen every
+    // peer's flag of the step in between.
+    int apply_sgd, world, rank, total, o2, o3, o4;
+    float* arena[8];       // [2][world][total] floats on every rank
+    unsigned* flags[8];    // flags[dst][src] = number of complete steps pushed by src
+    unsigned* epoch;       // this rank's completed-step counter (device memory: graph replays keep counting)
+    const float* lr;
+    long long* opt_step;
+    // programmatic dependent launch: the kernel may start while the gather that feeds it is still running (pdl != 0:
+    // griddepcontrol.wait before the first use of zpf / y4's embedding block) and releases the sparse SGD kernel as
+    // soon as dz is out (dz_flag counts published dz vectors)
+    int pdl;
+    unsigned* dz_flag;
+    int stamp_cta;
     unsigned long long* stamps;   // optional phase time stamps (ns), written by CTA 0 / thread 0
 };
 
@@ -56,7 +74,7 @@ struct TowerSmem {
     float u[TSL], v3[TSL];
     float red[TWARPS][TSL];
     float lossw[4];
-    float x[TB * 16];
+    alignas(16) float x[TB * 16];   // rows padded to 16 floats
     float w1[16 * TSL];          // this CTA's 32 columns of W1
     float h2s[TB][TSL + 1];      // this CTA's 32 columns of h2 (kept for u = h2^T dz and the relu mask of dh2)
     float dh1[TB][TSL + 1];
@@ -64,7 +82,7 @@ struct TowerSmem {
 };
 
 __device__ __forceinline__ void stamp(const TowerParams& p, int i) {
-    if (p.stamps != nullptr && threadIdx.x == 0 && blockIdx.x == 0) {
+    if (p.stamps != nullptr && threadIdx.x == 0 && (int)blockIdx.x == p.stamp_cta) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         p.stamps[i] = t;
@@ -86,6 +104,30 @@ __device__ __forceinline__ float ld_dsmem(const float* local, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(rank));
     asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
     return v;
+}
+// Where a gradient slice goes: (a) apply_sgd == 0: the caller's gradient buffer; (b) one GPU: straight into the weights
+// (w -= lr * g), every slice is applied by the CTA that produced it once no CTA reads the old weights any more;
+// (c) data parallel: block [slot][rank] of every rank's arena (peer stores), summed and applied in the kernel's tail.
+// `old` = the weights at `prm`, loaded by the caller ahead of time (only read when the update is applied in place): a
+// load-modify-store per slice would serialise one L2 round trip per store.
+__device__ __forceinline__ bool inplace(const TowerParams& p) { return p.apply_sgd && p.world == 1; }
+__device__ __forceinline__ void grad_store4(const TowerParams& p, unsigned slot, float* own, const float* prm, int off,
+                                            float4 v, float lr, float4 old) {
+    if (!p.apply_sgd) { *reinterpret_cast<float4*>(own) = v; return; }
+    if (p.world == 1) {
+        old.x -= lr * v.x; old.y -= lr * v.y; old.z -= lr * v.z; old.w -= lr * v.w;
+        *reinterpret_cast<float4*>(const_cast<float*>(prm)) = old;
+        return;
+    }
+    const size_t at = ((size_t)slot * p.world + p.rank) * p.total + off;
+    for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.arena[r] + at) = v;
+}
+__device__ __forceinline__ void grad_store1(const TowerParams& p, unsigned slot, float* own, const float* prm, int off,
+                                            float v, float lr, float old) {
+    if (!p.apply_sgd) { *own = v; return; }
+    if (p.world == 1) { *const_cast<float*>(prm) = old - lr * v; return; }
+    const size_t at = ((size_t)slot * p.world + p.rank) * p.total + off;
+    for (int r = 0; r < p.world; ++r) p.arena[r][at] = v;
 }
 // TMA tile load delivered to the same shared-memory offset of every CTA in `mask`; each destination's mbarrier (same
 // offset) receives the byte count.  Only used on tensor maps over this GPU's own work buffers (h1, h2, dh2): TMA
@@ -150,6 +192,9 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     const int n0 = c * TSL;
     const int hcs4 = p.pitch / (4 * TCL);                // float4 columns of the head gradient handled by this CTA
     const int fields = p.emb_cols / p.width;
+    const unsigned epoch0 = p.apply_sgd ? *reinterpret_cast<volatile unsigned*>(p.epoch) : 0u;
+    const unsigned slot = epoch0 & 1u;
+    const float lr_now = p.apply_sgd ? *p.lr : 0.f;
 
     stamp(p, 0);
     if (tid == 0) {
@@ -162,32 +207,34 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     }
     if (warp == 1) tmem_alloc(&S.tmem_ptr, 128);
     // ---- P0: stage x, this CTA's W1 columns and the y3 part of W4; logits of the embedding block (CTA 0) ----------
-    for (int i = tid; i < TB * p.nd; i += TTHREADS) S.x[i] = p.x[i];
+    for (int i = tid; i < TB * 16; i += TTHREADS) S.x[i] = (i & 15) < p.nd ? p.x[(i >> 4) * p.nd + (i & 15)] : 0.f;   // rows padded to 16
     for (int i = tid; i < p.nd * TSL; i += TTHREADS) S.w1[i] = __ldg(p.W1 + (i >> 5) * TH + n0 + (i & 31));
     for (int i = tid; i < TH; i += TTHREADS) S.w4y[i] = __ldg(p.W4 + p.emb_cols + i);
-    if (tid < TB) {
-        float z = 0.f;
-        if (c == 0) {                                    // per-(sample, field) partial dots left by the gather kernel
-            const float* zp = p.zpf + (size_t)tid * fields;
-            for (int f = 0; f < fields; ++f) z += zp[f];
-        }
-        S.zpart[tid] = z;
-    }
+    if (tid < TB) S.zpart[tid] = 0.f;
+    const unsigned dz_seq = (p.dz_flag != nullptr) ? *reinterpret_cast<volatile unsigned*>(p.dz_flag) : 0u;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = S.tmem_ptr;
     stamp(p, 1);
     // ---- P1: h1 = relu(x W1), K = nd (13): too thin for a tensor-core tile --------------------------------------
-    for (int idx = tid; idx < TB * TSL; idx += TTHREADS) {
-        const int n = idx & (TSL - 1), b = idx >> 5;
-        float acc = 0.f;
-        for (int k = 0; k < p.nd; ++k) acc += S.x[b * p.nd + k] * S.w1[k * TSL + n];
-        p.h1[b * TH + n0 + n] = fmaxf(acc, 0.f);
+    {
+        float w1r[16];                                   // this lane's column of W1 (zero beyond nd)
+#pragma unroll
+        for (int k = 0; k < 16; ++k) w1r[k] = k < p.nd ? S.w1[k * TSL + lane] : 0.f;
+        for (int b = warp; b < TB; b += TWARPS) {
+            const float4* xr = reinterpret_cast<const float4*>(&S.x[b * 16]);
+            float acc = 0.f;
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4) {
+                const float4 xv = xr[k4];
+                acc += xv.x * w1r[4 * k4] + xv.y * w1r[4 * k4 + 1] + xv.z * w1r[4 * k4 + 2] + xv.w * w1r[4 * k4 + 3];
+            }
+            p.h1[b * TH + n0 + lane] = fmaxf(acc, 0.f);
+        }
     }
-    __threadfence();
     __syncthreads();
-    cluster_sync_all();                                                             // h1 complete
+    cluster_sync_all();                 // arrive.release / wait.acquire: this thread's stores are visible cluster-wide                                                             // h1 complete
     stamp(p, 2);
     // ---- P2: h2 = relu(h1 W2) ------------------------------------------------------------------------------------
     if (tid == 0) tower_gemm_ka(&tm_h1k, &tm_W2mn, true, c, sA, sB, S.full[0], &S.done[0], tmem_base);
@@ -204,9 +251,8 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
         for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         tc_fence_before();
     }
-    __threadfence();
     __syncthreads();
-    cluster_sync_all();                                                             // h2 complete
+    cluster_sync_all();                 // arrive.release / wait.acquire: this thread's stores are visible cluster-wide                                                             // h2 complete
     stamp(p, 3);
     // ---- P3: y3 = h2 W3 -> y4[:, emb_cols + n], logit partial of the y3 block -------------------------------------
     if (tid == 0) { tc_fence_after(); tower_gemm_ka(&tm_h2k, &tm_W3mn, true, c, sA, sB, S.full[1], &S.done[1], tmem_base); }
@@ -235,13 +281,15 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
             if (lane == 0) S.v3[k] = a2;
         }
     }
-    __threadfence();
     __syncthreads();
-    cluster_sync_all();                                                             // every CTA's zpart and y3 columns complete
+    cluster_sync_all();                 // arrive.release / wait.acquire: this thread's stores are visible cluster-wide                                                             // every CTA's zpart and y3 columns complete
     stamp(p, 4);
     // ---- head: logits through distributed shared memory, sigmoid, BCE, dz -----------------------------------------
+    if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");      // the gather's rows and partial logits are complete
     if (tid < TB) {
         float z = 0.f;
+        const float* zp = p.zpf + (size_t)tid * fields;                 // per-(sample, field) dots left by the gather kernel
+        for (int f = 0; f < fields; ++f) z += __ldcg(zp + f);
 #pragma unroll
         for (int r = 0; r < TCL; ++r) z += ld_dsmem(&S.zpart[tid], (uint32_t)r);
         const float pr = 1.0f / (1.0f + expf(-z));
@@ -257,8 +305,14 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
             if (lane == 0) S.lossw[warp] = l;
         }
     }
+    if (c == 0 && p.dz_flag != nullptr) __threadfence();
     __syncthreads();
-    if (c == 0 && tid == 0) p.loss[0] = (S.lossw[0] + S.lossw[1] + S.lossw[2] + S.lossw[3]) * (1.0f / TB);
+    if (c == 0 && tid == 0) {
+        p.loss[0] = (S.lossw[0] + S.lossw[1] + S.lossw[2] + S.lossw[3]) * (1.0f / TB);
+        if (p.dz_flag != nullptr)                           // dz is out: the sparse SGD kernel may go ahead
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.dz_flag), "r"(dz_seq + 1u) : "memory");
+    }
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     stamp(p, 5);
     // ---- P5: u = h2^T dz (slice, from shared memory), dW3 = u x w4y, dh2 = relu'(h2) . (dz x v3) -------------------
     {
@@ -270,16 +324,9 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
         const int k = idx & (TSL - 1), b = idx >> 5;
         p.dh2[b * TH + n0 + k] = S.h2s[b][k] > 0.f ? S.dz[b] * S.v3[k] : 0.f;
     }
-    __threadfence();
     __syncthreads();
-    cluster_sync_all();                                                             // dh2 complete
+    cluster_sync_all();                 // arrive.release / wait.acquire: this thread's stores are visible cluster-wide                                                             // dh2 complete
     stamp(p, 6);
-    if (tid < TSL) {
-        float a = 0.f;
-#pragma unroll
-        for (int w = 0; w < TWARPS; ++w) a += S.red[w][tid];
-        S.u[tid] = a;
-    }
     // ---- P6a: dh1 = (dh2 W2^T) . relu'(h1)   |  vector warps: dW4 = y4^T dz, dW3 --------------------------------
     if (tid == 0) {
         tc_fence_after();
@@ -331,6 +378,12 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     } else if (warp >= 6) {
         // dW4 slice: (float4 column, batch half) items, 16 independent loads in flight per thread
         const int t6 = tid - 6 * 32;
+        if (warp == 6) {                                 // u = h2^T dz for this CTA's slice (partials from P5)
+            float a = 0.f;
+#pragma unroll
+            for (int w = 0; w < TWARPS; ++w) a += S.red[w][lane];
+            S.u[lane] = a;
+        }
         for (int item = t6; item < 2 * hcs4; item += 6 * 32) {
             const int c4 = item % hcs4, half = item / hcs4;
             const float4* yp = reinterpret_cast<const float4*>(p.y4 + (size_t)(half * 64) * p.pitch) + (size_t)c * hcs4 + c4;
@@ -349,57 +402,198 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
             }
             S.colsum[half][c4] = acc;
         }
+        asm volatile("bar.sync 1, 192;" ::: "memory");          // the six vector warps only: both batch halves are in
+        for (int c4 = t6; c4 < hcs4; c4 += 6 * 32) {
+            const float4 a = S.colsum[0][c4], b = S.colsum[1][c4];
+            const int off = 4 * (c * hcs4 + c4);
+            float4 old = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (inplace(p)) old = *reinterpret_cast<const float4*>(p.W4 + off);
+            grad_store4(p, slot, p.dW4 + off, p.W4 + off, p.o4 + off, make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w), lr_now, old);
+        }
+        for (int base = t6; base < TSL * (TH / 4); base += 4 * 6 * 32) {
+            float4 old[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int idx = base + u * 6 * 32;
+                if (inplace(p) && idx < TSL * (TH / 4))
+                    old[u] = *reinterpret_cast<const float4*>(p.W3 + (n0 + (idx >> 6)) * TH + 4 * (idx & (TH / 4 - 1)));
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int idx = base + u * 6 * 32;
+                if (idx >= TSL * (TH / 4)) break;
+                const int n4 = idx & (TH / 4 - 1), k = idx >> 6;
+                const float uk = S.u[k];
+                const int off = (n0 + k) * TH + 4 * n4;
+                grad_store4(p, slot, p.dW3 + off, p.W3 + off, p.o3 + off,
+                            make_float4(uk * S.w4y[4 * n4], uk * S.w4y[4 * n4 + 1], uk * S.w4y[4 * n4 + 2], uk * S.w4y[4 * n4 + 3]),
+                            lr_now, old[u]);
+            }
+        }
     }
     __syncthreads();
+    if (p.apply_sgd && p.world == 1) cluster_sync_all();   // every CTA's dh1 product has consumed the old W2
     stamp(p, 7);
     // ---- P6b epilogue: dW2 slice   |  vector warps: dW4 store, dW3 = u x w4y, dW1 = x^T dh1 (slice) ----------------
     if (warp >= 2 && warp < 6) {
         const int q = warp & 3;
         mbar_wait(&S.done[3], 0);
         tc_fence_after();
+        if (p.stamps != nullptr && warp == 2 && lane == 0 && c == p.stamp_cta) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            p.stamps[9] = t;
+        }
 #pragma unroll 1
         for (int h = 0; h < 2; ++h) {
+            const int off = (h * 128 + q * 32 + lane) * TH + n0;
+            float4 old[8];
+            if (inplace(p)) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) old[j] = *reinterpret_cast<const float4*>(p.W2 + off + 4 * j);
+            }
             float v[32];
             tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32 + h * 32, v);
-            float4* dst = reinterpret_cast<float4*>(p.dW2 + (size_t)(h * 128 + q * 32 + lane) * TH + n0);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            for (int j = 0; j < 8; ++j)
+                grad_store4(p, slot, p.dW2 + off + 4 * j, p.W2 + off + 4 * j, p.o2 + off + 4 * j,
+                            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]), lr_now, old[j]);
         }
     } else if (warp >= 6) {
-        const int t6 = tid - 6 * 32;
-        for (int c4 = t6; c4 < hcs4; c4 += 6 * 32) {
-            const float4 a = S.colsum[0][c4], b = S.colsum[1][c4];
-            reinterpret_cast<float4*>(p.dW4)[(size_t)c * hcs4 + c4] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+        // dW1[k, n0 + lane] = sum_b x[b, k] dh1[b, lane].  Shared-memory bandwidth sets the pace, so every load of
+        // dh1 feeds all 16 (padded) k at once: warp w covers rows w, w + 6, ..., the six partial sums meet in the
+        // (now idle) h2 slice buffer.
+        {
+            float acc[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) acc[k] = 0.f;
+            for (int b = warp - 6; b < TB; b += 6) {
+                const float d = S.dh1[b][lane];
+                const float4* xr = reinterpret_cast<const float4*>(&S.x[b * 16]);
+#pragma unroll
+                for (int k4 = 0; k4 < 4; ++k4) {
+                    const float4 xv = xr[k4];
+                    acc[4 * k4] += xv.x * d; acc[4 * k4 + 1] += xv.y * d; acc[4 * k4 + 2] += xv.z * d; acc[4 * k4 + 3] += xv.w * d;
+                }
+            }
+            float* part = &S.h2s[0][0];                  // [6][16][32]
+#pragma unroll
+            for (int k = 0; k < 16; ++k) part[((warp - 6) * 16 + k) * TSL + lane] = acc[k];
+            asm volatile("bar.sync 1, 192;" ::: "memory");
+            for (int idx = tid - 6 * 32; idx < p.nd * TSL; idx += 6 * 32) {
+                const int n = idx & (TSL - 1), k = idx >> 5;
+                const float old = inplace(p) ? p.W1[k * TH + n0 + n] : 0.f;
+                float g = 0.f;
+#pragma unroll
+                for (int w = 0; w < 6; ++w) g += part[(w * 16 + k) * TSL + n];
+                grad_store1(p, slot, p.dW1 + k * TH + n0 + n, p.W1 + k * TH + n0 + n, k * TH + n0 + n, g, lr_now, old);
+            }
         }
-        for (int idx = t6; idx < TSL * (TH / 4); idx += 6 * 32) {
-            const int n4 = idx & (TH / 4 - 1), k = idx >> 6;
-            const float uk = S.u[k];
-            reinterpret_cast<float4*>(p.dW3 + (size_t)(n0 + k) * TH)[n4] =
-                make_float4(uk * S.w4y[4 * n4], uk * S.w4y[4 * n4 + 1], uk * S.w4y[4 * n4 + 2], uk * S.w4y[4 * n4 + 3]);
-        }
-        for (int idx = t6; idx < p.nd * TSL; idx += 6 * 32) {
-            const int n = idx & (TSL - 1), k = idx >> 5;
-            float acc = 0.f;
-#pragma unroll 8
-            for (int b = 0; b < TB; ++b) acc += S.x[b * p.nd + k] * S.dh1[b][n];
-            p.dW1[k * TH + n0 + n] = acc;
+        if (p.stamps != nullptr && warp == 6 && lane == 0 && c == p.stamp_cta) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            p.stamps[15] = t;
         }
     }
     tc_fence_before();
     __syncthreads();
     stamp(p, 8);
-    if (warp == 1) tmem_dealloc(tmem_base, 128);
+    if (warp == 1) {
+        tmem_dealloc(tmem_base, 128);
+        if (p.stamps != nullptr && lane == 0 && c == p.stamp_cta) {       // diagnostics: after the TMEM release
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            p.stamps[14] = t;
+        }
+    }
+    if (!p.apply_sgd) return;
+    if (p.world == 1) {                                  // the weights were updated where the gradients were produced
+        if (c == 0 && tid == 0 && p.opt_step != nullptr) *p.opt_step += 1;
+        return;
+    }
+    // ---- all-reduce + SGD: every gradient slice of this step has been pushed ---------------------------------------
+    __syncthreads();
+    if (tid == 0) __threadfence_system();                // this CTA's pushes (ordered before by the barrier) reach the peers
+    cluster_sync_all();
+    const unsigned target = epoch0 + 1u;
+    if (p.world > 1) {
+        if (tid < p.world && tid != p.rank) {
+            if (c == 0) {
+                __threadfence_system();
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.flags[tid] + p.rank), "r"(target) : "memory");
+            }
+            const unsigned* f = p.flags[p.rank] + tid;
+            unsigned v;
+            do { asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory"); } while ((int)(v - target) < 0);
+        }
+        __syncthreads();
+    }
+    {
+        const float lr = *p.lr;
+        const float* mine = p.arena[p.rank] + (size_t)slot * p.world * p.total;
+        float* prm[4] = {const_cast<float*>(p.W1), const_cast<float*>(p.W2), const_cast<float*>(p.W3), const_cast<float*>(p.W4)};
+        const int off[5] = {0, p.o2, p.o3, p.o4, p.total};
+        const int len[4] = {p.nd * TH, TH * TH, TH * TH, p.pitch};
+        // 4 float4 per thread and pass, every load of a pass issued before the first use: the loop is latency bound
+        // (8 SMs, L2-resident data), so independent loads in flight are what sets its time
+#pragma unroll
+        for (int sgm = 0; sgm < 4; ++sgm) {
+            float4* w4p = reinterpret_cast<float4*>(prm[sgm]);
+            const int n4 = len[sgm] >> 2;
+            const float4* g0 = reinterpret_cast<const float4*>(mine + off[sgm]);
+            const size_t rs = (size_t)p.total >> 2;                     // float4 stride between source blocks
+            for (int base = c * TTHREADS + tid; base < n4; base += 4 * TCL * TTHREADS) {
+                float4 w[4], g[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int i = base + u * TCL * TTHREADS;
+                    if (i < n4) { w[u] = w4p[i]; g[u] = __ldcg(g0 + i); }
+                }
+                for (int r = 1; r < p.world; ++r) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int i = base + u * TCL * TTHREADS;
+                        if (i < n4) {
+                            const float4 t = __ldcg(g0 + (size_t)r * rs + i);
+                            g[u].x += t.x; g[u].y += t.y; g[u].z += t.z; g[u].w += t.w;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int i = base + u * TCL * TTHREADS;
+                    if (i < n4) {
+                        w[u].x -= lr * g[u].x; w[u].y -= lr * g[u].y; w[u].z -= lr * g[u].z; w[u].w -= lr * g[u].w;
+                        w4p[i] = w[u];
+                    }
+                }
+            }
+        }
+    }
+    if (c == 0 && tid == 0) {
+        *p.epoch = target;
+        if (p.opt_step != nullptr) *p.opt_step += 1;
+    }
+    stamp(p, 9);
 }
 }  // namespace
 
 static unsigned long long* g_tower_stamps = nullptr;
+static void ensure_stamps() {
+    if (g_tower_stamps == nullptr && getenv("HETU_WDL_STAMPS") != nullptr) {
+        cudaMalloc(&g_tower_stamps, 16 * sizeof(unsigned long long));
+        const unsigned long long init[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, ~0ull, 0, ~0ull, 0, 0, 0};
+        cudaMemcpy(g_tower_stamps, init, sizeof(init), cudaMemcpyHostToDevice);
+    }
+}
 
 // work: 3 * 128 * 256 floats (h1, h2, dh2).  All pointers are this GPU's memory; y4 is the concat buffer whose
 // first emb_cols columns hold the gathered embedding rows (hetu_gather_rows_pitched).
 HETU_API int hetu_wdl_tower_step(const float* x, float* y4, const float* zpf, const float* labels, const float* W1,
                                  const float* W2, const float* W3, const float* W4, float* work, float* loss, float* pred,
                                  float* dz, float* dW1, float* dW2, float* dW3, float* dW4, int batch, int nd, int hidden,
-                                 int emb_cols, int width, cudaStream_t s) {
+                                 int emb_cols, int width, void* const* arenas, void* const* flags, int world, int rank,
+                                 void* epoch, const float* lr, void* opt_step, int pdl, void* dz_flag, cudaStream_t s) {
     if (batch != TB || hidden != TH || nd < 1 || nd > 16 || emb_cols <= 0 || emb_cols % (4 * TCL) != 0 || width <= 0 ||
         emb_cols % width != 0 || (emb_cols + TH) / (4 * TCL) > kMaxSlice4) {
         hetu_set_error("hetu_wdl_tower_step: needs batch 128, hidden 256, 1..16 dense features, emb_cols %% 32 == 0, "
@@ -412,9 +606,27 @@ HETU_API int hetu_wdl_tower_step(const float* x, float* y4, const float* zpf, co
     p.h1 = work; p.h2 = work + TB * TH; p.dh2 = work + 2 * TB * TH;
     p.loss = loss; p.pred = pred; p.dz = dz; p.dW1 = dW1; p.dW2 = dW2; p.dW3 = dW3; p.dW4 = dW4;
     p.nd = nd; p.emb_cols = emb_cols; p.pitch = emb_cols + TH;
-    p.stamps = nullptr;
+    p.o2 = nd * TH; p.o3 = p.o2 + TH * TH; p.o4 = p.o3 + TH * TH; p.total = p.o4 + p.pitch;
+    p.apply_sgd = arenas != nullptr ? 1 : 0;
+    p.world = 1; p.rank = 0; p.epoch = (unsigned*)epoch; p.lr = lr; p.opt_step = (long long*)opt_step;
+    for (int i = 0; i < 8; ++i) { p.arena[i] = nullptr; p.flags[i] = nullptr; }
+    if (p.apply_sgd) {
+        if (world < 1 || world > 8 || rank < 0 || rank >= world || epoch == nullptr || lr == nullptr ||
+            (world > 1 && flags == nullptr)) {
+            hetu_set_error("hetu_wdl_tower_step: in-kernel SGD needs 1 <= world <= 8, 0 <= rank < world, an epoch counter, "
+                           "lr and (world > 1) the flag table (got world %d rank %d)", world, rank);
+            return -1;
+        }
+        p.world = world; p.rank = rank;
+        for (int i = 0; i < world; ++i) {
+            p.arena[i] = (float*)arenas[i];
+            p.flags[i] = world > 1 ? (unsigned*)flags[i] : nullptr;
+        }
+    }
+    p.pdl = pdl ? 1 : 0; p.dz_flag = (unsigned*)dz_flag;
+    p.stamps = nullptr; p.stamp_cta = getenv("HETU_WDL_STAMP_CTA") ? atoi(getenv("HETU_WDL_STAMP_CTA")) : 0;
     if (getenv("HETU_WDL_STAMPS") != nullptr) {          // diagnostics: phase boundaries
-        if (g_tower_stamps == nullptr) HETU_CUDA(cudaMalloc(&g_tower_stamps, 16 * sizeof(unsigned long long)));
+        ensure_stamps();
         p.stamps = g_tower_stamps;
     }
     CUtensorMap h1k, h2k, dh2k, W2mn, W3mn, W2k, h1mn, dh2mn;
@@ -429,7 +641,13 @@ HETU_API int hetu_wdl_tower_step(const float* x, float* y4, const float* zpf, co
         HETU_CUDA(cudaFuncSetAttribute(wdl_tower_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
         attr_set = true;
     }
-    wdl_tower_kernel<<<TCL, TTHREADS, smem_bytes, s>>>(h1k, h2k, dh2k, W2mn, W3mn, W2k, h1mn, dh2mn, p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(TCL); cfg.blockDim = dim3(TTHREADS); cfg.dynamicSmemBytes = smem_bytes; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    HETU_CUDA(cudaLaunchKernelEx(&cfg, wdl_tower_kernel, h1k, h2k, dh2k, W2mn, W3mn, W2k, h1mn, dh2mn, p));
     HETU_CHECK_LAUNCH("hetu_wdl_tower_step");
     return 0;
 }
@@ -447,7 +665,22 @@ struct WdlShards { float* base[kWdlMaxShards]; int nshard; };
 __global__ void __launch_bounds__(256) gather_rows_pitched_kernel(WdlShards tab, const void* __restrict__ idx, int idx_code,
                                                                   float* __restrict__ out, size_t n, int width, int fields,
                                                                   int pitch, size_t vocab, const float* __restrict__ w4,
-                                                                  float* __restrict__ zpf) {
+                                                                  float* __restrict__ zpf, float* __restrict__ w4_snap,
+                                                                  const unsigned* __restrict__ dz_flag,
+                                                                  unsigned* __restrict__ dz_expect,
+                                                                  unsigned long long* stamps) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");     // the tower kernel's first layers do not need us
+    if (stamps != nullptr && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicMin(stamps + 10, t);
+    }
+    if (dz_expect != nullptr && blockIdx.x == 0 && threadIdx.x == 0)    // what dz_flag will read once this step's dz is out
+        *dz_expect = *reinterpret_cast<const volatile unsigned*>(dz_flag) + 1u;
+    if (w4_snap != nullptr) {       // the head weights as of this step's forward pass (the tower kernel updates W4)
+        const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+        if (gid < (size_t)fields * width) w4_snap[gid] = w4[gid];
+    }
     size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     const size_t nwarp = ((size_t)gridDim.x * blockDim.x) >> 5;
@@ -479,6 +712,11 @@ __global__ void __launch_bounds__(256) gather_rows_pitched_kernel(WdlShards tab,
             if (lane == 0) zpf[i] = dot;
         }
     }
+    if (stamps != nullptr && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicMax(stamps + 11, t);
+    }
 }
 
 // SGD on the embedding rows with the head's rank-one gradient: d loss / d row(b, f) = dz[b] * W4[f * width ...].
@@ -486,7 +724,25 @@ __global__ void __launch_bounds__(256) gather_rows_pitched_kernel(WdlShards tab,
 __global__ void __launch_bounds__(256) wdl_sparse_sgd_rank1_kernel(WdlShards tab, const void* __restrict__ idx, int idx_code,
                                                                    const float* __restrict__ dz, const float* __restrict__ w4,
                                                                    const float* __restrict__ lr_p, float scale, size_t n,
-                                                                   int width, int fields, size_t vocab) {
+                                                                   int width, int fields, size_t vocab,
+                                                                   const unsigned* __restrict__ dz_flag,
+                                                                   const unsigned* __restrict__ dz_expect,
+                                                                   unsigned long long* stamps) {
+    if (stamps != nullptr && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicMin(stamps + 12, t);
+    }
+    if (dz_flag != nullptr) {
+        // launched programmatically behind the tower kernel, which is still running its backward pass: go once it
+        // has published this step's dz.  (The tower kernel is resident before this grid can be scheduled.)
+        if (threadIdx.x == 0) {
+            const unsigned want = *reinterpret_cast<const volatile unsigned*>(dz_expect);
+            unsigned v;
+            do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(dz_flag) : "memory"); } while ((int)(v - want) < 0);
+        }
+        __syncthreads();
+    }
     size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     const size_t nwarp = ((size_t)gridDim.x * blockDim.x) >> 5;
@@ -506,6 +762,13 @@ __global__ void __launch_bounds__(256) wdl_sparse_sgd_rank1_kernel(WdlShards tab
             for (int j = lane; j < width; j += 32) atomicAdd(row + j, g * w[j]);
         }
     }
+    if (stamps != nullptr && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicMax(stamps + 13, t);
+    }
+    // completion of this grid must imply completion of the tower kernel for whatever is queued behind it
+    if (dz_flag != nullptr) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 int fill_shards(WdlShards& tab, void* const* bases, int nshard, const char* who) {
@@ -518,32 +781,60 @@ int fill_shards(WdlShards& tab, void* const* bases, int nshard, const char* who)
 
 HETU_API int hetu_gather_rows_pitched(void* const* bases, int nshard, const void* idx, int idx_code, float* out, size_t n,
                                       int width, int fields, int pitch, size_t vocab, const float* w4, float* zpf,
-                                      cudaStream_t s) {
+                                      float* w4_snap, const void* dz_flag, void* dz_expect, cudaStream_t s) {
     if (n == 0) return 0;
     WdlShards tab;
+    ensure_stamps();
     if (fill_shards(tab, bases, nshard, "hetu_gather_rows_pitched")) return -1;
+    static bool carve_set = false;
+    if (!carve_set) {
+        // the tower kernel that follows needs the SMs configured for maximal shared memory; a kernel in between that
+        // prefers L1 makes the SMs it ran on re-partition twice per step
+        if (getenv("HETU_WDL_NO_CARVEOUT") == nullptr) {
+            HETU_CUDA(cudaFuncSetAttribute(gather_rows_pitched_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                           cudaSharedmemCarveoutMaxShared));
+            HETU_CUDA(cudaFuncSetAttribute(wdl_sparse_sgd_rank1_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                           cudaSharedmemCarveoutMaxShared));
+        }
+        carve_set = true;
+    }
+    if (w4_snap != nullptr && (size_t)fields * width > (size_t)ew_grid(n * 32, 256, 16) * 256) {
+        hetu_set_error("hetu_gather_rows_pitched: grid too small to snapshot %d head weights", fields * width);
+        return -1;
+    }
     gather_rows_pitched_kernel<<<ew_grid(n * 32, 256, 16), 256, 0, s>>>(tab, idx, idx_code, out, n, width, fields, pitch, vocab,
-                                                                       w4, zpf);
+                                                                       w4, zpf, w4_snap, (const unsigned*)dz_flag,
+                                                                       (unsigned*)dz_expect,
+                                                                       getenv("HETU_WDL_STAMPS") != nullptr ? g_tower_stamps : nullptr);
     HETU_CHECK_LAUNCH("hetu_gather_rows_pitched");
     return 0;
 }
 
 HETU_API int hetu_wdl_sparse_sgd_rank1(void* const* bases, int nshard, const void* idx, int idx_code, const float* dz,
                                        const float* w4, const float* lr_p, float scale, size_t n, int width, int fields,
-                                       size_t vocab, cudaStream_t s) {
+                                       size_t vocab, const void* dz_flag, const void* dz_expect, cudaStream_t s) {
     if (n == 0) return 0;
     WdlShards tab;
     if (fill_shards(tab, bases, nshard, "hetu_wdl_sparse_sgd_rank1")) return -1;
-    wdl_sparse_sgd_rank1_kernel<<<ew_grid(n * 32, 256, 16), 256, 0, s>>>(tab, idx, idx_code, dz, w4, lr_p, scale, n, width,
-                                                                        fields, vocab);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ew_grid(n * 32, 256, 16)); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = dz_flag != nullptr ? 1 : 0;
+    HETU_CUDA(cudaLaunchKernelEx(&cfg, wdl_sparse_sgd_rank1_kernel, tab, idx, idx_code, dz, w4, lr_p, scale, n, width, fields,
+                                 vocab, (const unsigned*)dz_flag, (const unsigned*)dz_expect,
+                                 getenv("HETU_WDL_STAMPS") != nullptr ? g_tower_stamps : nullptr));
     HETU_CHECK_LAUNCH("hetu_wdl_sparse_sgd_rank1");
     return 0;
 }
 
 // diagnostics: phase time stamps (ns) of the last hetu_wdl_tower_step launched with HETU_WDL_STAMPS set
-HETU_API int hetu_wdl_tower_stamps(unsigned long long* out9) {
+HETU_API int hetu_wdl_tower_stamps(unsigned long long* out9 /* 15 values; [10..13] = gather start/end, sparse start/end, [14] = last CTA after its TMEM release */) {
     if (g_tower_stamps == nullptr) { hetu_set_error("hetu_wdl_tower_stamps: no stamped launch yet"); return -1; }
     HETU_CUDA(cudaDeviceSynchronize());
-    HETU_CUDA(cudaMemcpy(out9, g_tower_stamps, 9 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    HETU_CUDA(cudaMemcpy(out9, g_tower_stamps, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    const unsigned long long reset[4] = {~0ull, 0ull, ~0ull, 0ull};
+    HETU_CUDA(cudaMemcpy(g_tower_stamps + 10, reset, sizeof(reset), cudaMemcpyHostToDevice));
     return 0;
 }

@@ -715,7 +715,10 @@ class SubExecutor(object):
     def _compute_all(self, vals: Dict[Op, object], release: bool) -> None:
         cfg = self.config
         inference = self.inference
-        if self.device.type == 'cuda' and L.cuda_lib() is not None:
+        if getattr(self, '_uses_step_counter', None) is None:
+            # the per-device step counter feeds the dropout masks; graphs without such an op skip the bump kernel
+            self._uses_step_counter = any(getattr(n, 'uses_step_counter', False) for n in self.topo_order)
+        if self._uses_step_counter and self.device.type == 'cuda' and L.cuda_lib() is not None:
             from ..ops.nn import step_counter
             L.call('increment_i64', L.p(step_counter(self.device)), L.stream_ptr(self.device))
         plan = getattr(self, '_node_plan', None)

@@ -114,6 +114,7 @@ def _make_op_class():
             super().__init__(_WdlTowerStepOp, [m['x'], m['ids'], m['labels'], m['E'], m['W1'], m['W2'], m['W3'], m['W4']], ctx)
             self.m = m
             self._bufs = None
+            self._dp = None
             self.last = None
             self.fused_launches = 0
 
@@ -173,15 +174,68 @@ def _make_op_class():
             x, ids, labels = x.contiguous(), ids.contiguous(), labels.contiguous()
             n = ids.numel()
             st = L.stream_ptr(dev)
+            dp = self._dp_state(dev, pitch)
+            # programmatic dependent launches: gather || first tower layers, sparse SGD || tower backward.  Not under
+            # BSP, where cross-GPU barrier kernels sit between the tower and the table update.
+            pdl = os.environ.get('HETU_WDL_PDL', '1') == '1' and getattr(E, 'bsp', -1) != 0
+            if pdl and 'dz_flag' not in b:
+                b['dz_flag'] = torch.zeros(1, dtype=torch.int32, device=dev)
+                b['dz_expect'] = torch.zeros(1, dtype=torch.int32, device=dev)
             L.call('gather_rows_pitched', bases, L.c_int(nshard), L.p(ids), L.c_int(_IDX_CODE[ids.dtype]), L.p(b['y4']),
-                   L.c_sz(n), L.c_int(m['width']), L.c_int(m['fields']), L.c_int(pitch), L.c_sz(vocab), L.p(W4), L.p(b['zpf']), st)
-            L.call('wdl_tower_step', L.p(x), L.p(b['y4']), L.p(b['zpf']), L.p(labels), L.p(W1), L.p(W2), L.p(W3), L.p(W4), L.p(b['work']),
-                   L.p(b['loss']), L.p(b['pred']), L.p(b['dz']), L.p(b['dW1']), L.p(b['dW2']), L.p(b['dW3']), L.p(b['dW4']),
-                   L.c_int(B), L.c_int(m['nd']), L.c_int(hid), L.c_int(m['emb_cols']), L.c_int(m['width']), st)
+                   L.c_sz(n), L.c_int(m['width']), L.c_int(m['fields']), L.c_int(pitch), L.c_sz(vocab), L.p(W4),
+                   L.p(b['zpf']), L.p(b['w4_snap'] if dp is not None else None),
+                   L.p(b['dz_flag'] if pdl else None), L.p(b['dz_expect'] if pdl else None), st)
+            if dp is None:
+                tail = (None, None, L.c_int(1), L.c_int(0), L.p(None), L.p(None), L.p(None))
+            else:
+                tail = (dp['arenas'], dp['flags'], L.c_int(dp['world']), L.c_int(dp['rank']), L.p(dp['epoch']),
+                        L.p(dp['opt'].lr_t), L.p(dp['opt'].step_t))
+            L.call('wdl_tower_step', L.p(x), L.p(b['y4']), L.p(b['zpf']), L.p(labels), L.p(W1), L.p(W2), L.p(W3), L.p(W4),
+                   L.p(b['work']), L.p(b['loss']), L.p(b['pred']), L.p(b['dz']), L.p(b['dW1']), L.p(b['dW2']),
+                   L.p(b['dW3']), L.p(b['dW4']), L.c_int(B), L.c_int(m['nd']), L.c_int(hid), L.c_int(m['emb_cols']),
+                   L.c_int(m['width']), *tail, L.c_int(1 if pdl else 0), L.p(b['dz_flag'] if pdl else None), st)
             self.fused_launches += 2
-            self.last = dict(ids=ids, dz=b['dz'], grads=(b['dW1'], b['dW2'], b['dW3'], b['dW4']), W4=W4, E=E,
-                             bases=bases, nshard=nshard, vocab=vocab, torch_path=False)
+            self.last = dict(ids=ids, dz=b['dz'], grads=(b['dW1'], b['dW2'], b['dW3'], b['dW4']),
+                             W4=b['w4_snap'] if dp is not None else W4, E=E, bases=bases, nshard=nshard, vocab=vocab,
+                             torch_path=False, dense_done=dp is not None,
+                             dz_flag=b['dz_flag'] if pdl else None, dz_expect=b['dz_expect'] if pdl else None)
             return (b['loss'], b['pred'])
+
+        def _dp_state(self, dev, pitch):
+            """In-kernel all-reduce + SGD (csrc/wdl_tower.cu): arena / flags / epoch, built on the first step.
+            None when the dense update stays outside the kernel (no optimizer attached: kernel tests)."""
+            if self._dp is not None:
+                return self._dp or None
+            opt_node = getattr(self, 'opt_node', None)
+            if opt_node is None or os.environ.get('HETU_WDL_INKERNEL_SGD', '1') != '1':
+                self._dp = False
+                return None
+            m = self.m
+            opt = opt_node.optimizer
+            total = m['nd'] * TOWER_HIDDEN + 2 * TOWER_HIDDEN * TOWER_HIDDEN + pitch
+            self._bufs['w4_snap'] = torch.empty(m['emb_cols'], dtype=torch.float32, device=dev)
+            if opt.step_t is None or opt.step_t.device != dev:
+                opt.step_t = torch.zeros(1, dtype=torch.int64, device=dev) if opt.step_t is None else opt.step_t.to(dev)
+                opt.lr_t = opt.lr_t.to(dev)
+            fdp = opt_node.fused_dp
+            if fdp is None:
+                arena = torch.empty(2 * total, dtype=torch.float32, device=dev)
+                self._dp = dict(world=1, rank=0, arenas=(ctypes.c_void_p * 1)(arena.data_ptr()), flags=None,
+                                epoch=torch.zeros(1, dtype=torch.int32, device=dev), opt=opt, keep=arena)
+                return self._dp
+            eng = fdp.engine
+            pos = {id(p): i for i, p in enumerate(opt.params)}
+            if eng.world > 8 or sorted(fdp.ids) != sorted(pos[id(m[k])] for k in ('W1', 'W2', 'W3', 'W4')):
+                self._dp = False
+                return None
+            arena = eng.buffer(('wdl_arena', id(self)), 2 * eng.world * total * 4)
+            flags = eng.buffer(('wdl_flags', id(self)), 256)
+            flags.tensor(dtype=torch.int32, numel=64).zero_()
+            torch.cuda.synchronize(dev)
+            eng.comm.barrier()
+            self._dp = dict(world=eng.world, rank=eng.rank, arenas=arena.ptrs, flags=flags.ptrs,
+                            epoch=torch.zeros(1, dtype=torch.int32, device=dev), opt=opt, keep=(arena, flags))
+            return self._dp
 
         # ---- the optimizer node's new compute -------------------------------------------------------------------
         def apply_update(self, opt_node):
@@ -190,8 +244,9 @@ def _make_op_class():
             E = last['E']
             pos = {id(p): i for i, p in enumerate(opt.params)}
             grads = [None] * len(opt.params)
-            for name, g in zip(('W1', 'W2', 'W3', 'W4'), last['grads']):
-                grads[pos[id(m[name])]] = g
+            if not last.get('dense_done'):
+                for name, g in zip(('W1', 'W2', 'W3', 'W4'), last['grads']):
+                    grads[pos[id(m[name])]] = g
             bsp = getattr(E, 'bsp', -1) == 0 and hasattr(E, 'engine') and not last['torch_path']
             if bsp:
                 E.engine.barrier()
@@ -206,9 +261,11 @@ def _make_op_class():
                 L.call('wdl_sparse_sgd_rank1', last['bases'], L.c_int(last['nshard']), L.p(ids),
                        L.c_int(_IDX_CODE[ids.dtype]), L.p(last['dz']), L.p(last['W4']), L.p(opt.lr_t), L.c_f32(1.0),
                        L.c_sz(ids.numel()), L.c_int(m['width']), L.c_int(m['fields']), L.c_sz(last['vocab']),
-                       L.stream_ptr(ids.device))
+                       L.p(last.get('dz_flag')), L.p(last.get('dz_expect')), L.stream_ptr(ids.device))
             if bsp:
                 E.engine.barrier()
+            if last.get('dense_done'):
+                return                                    # all-reduce, SGD and the step counter: done inside the tower kernel
             if opt_node.fused_dp is not None:
                 opt_node.fused_dp.step(opt, grads)
             else:
@@ -254,5 +311,6 @@ def fuse_wide_deep(eval_nodes) -> int:
         opt_node.compute = (lambda input_vals, output_val=None, stream_handle=None, new_tensors_map=None,
                             _n=node, _o=opt_node: _n.apply_update(_o))
         opt_node.wdl_fused = node
+        node.opt_node = opt_node
         fused += 1
     return fused

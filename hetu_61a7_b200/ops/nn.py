@@ -576,6 +576,7 @@ def step_counter(device) -> torch.Tensor:
 
 class DropoutOp(Op):
     takes_inference = True
+    uses_step_counter = True
 
     def __init__(self, node_in, keep_prob, recompute=True, inplace=False, ctx=None):
         super().__init__(DropoutOp, [node_in], ctx)

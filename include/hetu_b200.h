@@ -145,15 +145,28 @@ int hetu_scatter_add_rows(float* dense, const void* idx, int idx_code, const flo
 int hetu_gather_rows_pitched(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code, float* out,
                              size_t n, int width, int fields, int pitch, size_t vocab,
                              const float* w4 /*optional*/, float* zpf /*optional [n]: <row, w4 block of its field>*/,
-                             cudaStream_t s);
+                             float* w4_snap /*optional: copy of w4[0 .. fields * width)*/,
+                             const void* dz_flag /*optional*/, void* dz_expect /*optional: *dz_flag + 1*/, cudaStream_t s);
 int hetu_wdl_tower_step(const float* x, float* y4, const float* zpf /*[128, fields] from the gather*/,
                         const float* labels, const float* W1, const float* W2, const float* W3, const float* W4,
                         float* work, float* loss, float* pred, float* dz, float* dW1, float* dW2, float* dW3,
-                        float* dW4, int batch, int nd, int hidden, int emb_cols, int width, cudaStream_t s);
+                        float* dW4, int batch, int nd, int hidden, int emb_cols, int width,
+                        /* arenas != NULL: data-parallel all-reduce + SGD inside the kernel.  arenas[r] = rank r's
+                         * [2][world][total] float arena (peer-mapped; total = nd*256 + 2*65536 + emb_cols + 256),
+                         * flags[r] = rank r's unsigned[world] flag row (zeroed once), epoch = this rank's device
+                         * counter (zeroed once), lr / opt_step = device scalars.  The gradient slices are pushed to
+                         * all ranks as the backward pass produces them; W1..W4 are updated in place. */
+                        void* const* arenas /*host array or NULL*/, void* const* flags /*host array*/, int world,
+                        int rank, void* epoch, const float* lr, void* opt_step,
+                        /* pdl != 0: launched as a programmatic dependent of the gather (the first layers overlap
+                         * it); dz_flag (optional, device unsigned, zeroed once) is bumped when dz is out, which is
+                         * what hetu_wdl_sparse_sgd_rank1 waits for when it is given the same flag */
+                        int pdl, void* dz_flag, cudaStream_t s);
 int hetu_wdl_tower_stamps(unsigned long long* out9);   /* diagnostics, see benchmarks/wdl_tower_phases.py */
 int hetu_wdl_sparse_sgd_rank1(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code,
                               const float* dz, const float* w4, const float* lr_p, float scale, size_t n, int width,
-                              int fields, size_t vocab, cudaStream_t s);
+                              int fields, size_t vocab, const void* dz_flag /*optional*/,
+                              const void* dz_expect /*optional*/, cudaStream_t s);
 
 /* ---- dense optimizers, all tensors in one launch: Optimizers.cu ------------------------
  * kind: 0 SGD 1 Momentum 2 Nesterov 3 AdaGrad 4 Adam 5 AdamW 6 Lamb.  The pointer arrays are

@@ -151,5 +151,43 @@ if gpu:
     log('moe losses fused', losses['1'], 'nccl', losses['0'])
     assert np.allclose(losses['1'], losses['0'], rtol=2e-3, atol=1e-4), losses
 
+# ------------------------------------- Wide&Deep: fused step (in-kernel push all-reduce + SGD) vs node-by-node
+if gpu:
+    from hetu_61a7_b200.models import ctr
+    res = {}
+    for fuse in ('1', '0'):
+        os.environ['HETU_FUSE_WDL'] = fuse
+        B, vocab = 128, 40000
+        pool = [ht.data.criteo_synthetic(B, vocab=vocab, seed=100 * rank + i) for i in range(4)]
+        dense = ht.dataloader_op([ht.Dataloader(np.concatenate([p_[0] for p_ in pool]), B, 'train')])
+        sparse = ht.dataloader_op([ht.Dataloader(np.concatenate([p_[1] for p_ in pool]), B, 'train', dtype=np.int64)])
+        y_ = ht.dataloader_op([ht.Dataloader(np.concatenate([p_[2] for p_ in pool]), B, 'train')])
+        wl, wp, _, wt = ctr.wdl_criteo(dense, sparse, y_, feature_dimension=vocab, learning_rate=0.5, ctx=ctx)
+        ex = ht.Executor({'train': [wl, wp, wt]}, ctx=ctx, comm_mode='Hybrid', seed=123, bsp=0, shard_dataloaders=False)
+        assert ex.fused_wdl == int(fuse), (ex.fused_wdl, fuse)
+        named = ex._named_params()
+        if fuse == '1':
+            snap = {n: (ex.config.placeholder_to_arr_map[p_].export_dense().numpy().copy()
+                        if hasattr(ex.config.placeholder_to_arr_map[p_], 'export_dense')
+                        else ex.config.placeholder_to_arr_map[p_].detach().cpu().numpy().copy()) for n, p_ in named.items()}
+        else:
+            ex.load_dict(snap)
+        ls = [float(ex.run('train')[0].asnumpy().reshape(-1)[0]) for _ in range(8)]
+        torch.cuda.synchronize()
+        comm.barrier()
+        dense_params = {n: ex.config.placeholder_to_arr_map[p_].detach().cpu().clone() for n, p_ in named.items()
+                        if not hasattr(ex.config.placeholder_to_arr_map[p_], 'export_dense')}
+        res[fuse] = (ls, dense_params)
+    log('wdl losses fused', res['1'][0], 'unfused', res['0'][0])
+    assert np.allclose(res['1'][0], res['0'][0], rtol=3e-3), res
+    for n in res['0'][1]:
+        a, b = res['1'][1][n], res['0'][1][n]
+        assert (a - b).abs().max().item() <= 3e-2 * b.abs().max().item() + 1e-5, n
+        r0 = a.to(dev).clone()
+        comm.broadcast(r0, 0)                       # every rank sums the pushed blocks in rank order: replicas stay bit-identical
+        assert torch.equal(r0.cpu(), a), 'replicas of %s diverged' % n
+    log('ok wdl fused step == node-by-node step on %d GPUs' % nrank)
+    os.environ['HETU_FUSE_WDL'] = '1'
+
 comm.barrier()
 log('ALL DIST CHECKS PASSED (mode %s, %d ranks)' % (mode, nrank))

@@ -96,7 +96,7 @@ def test_tower_kernel_matches_fp32_torch_step():
              W1=None, W2=None, W3=None, W4=None)
     cls = fw._make_op_class()
     op = cls.__new__(cls)
-    op.m, op._bufs, op.last, op.fused_launches = m, None, None, 0
+    op.m, op._bufs, op._dp, op.last, op.fused_launches = m, None, None, None, 0
     x = torch.rand(B, nd, generator=g)
     ids = torch.randint(0, vocab, (B, fields), generator=g)
     ids[5] = ids[4]                                    # duplicate rows
