@@ -654,6 +654,7 @@ class SubExecutor(object):
                          and all(getattr(n, 'graph_safe', True) for n in self.topo_order))
         self._graph = None
         self._graph_key = None
+        self._packed = None
         self._static_in: Dict[Op, torch.Tensor] = {}
         self._stage: Dict[Op, torch.Tensor] = {}
         self._static_out: Dict[Op, object] = {}
@@ -870,7 +871,8 @@ class SubExecutor(object):
         return vals
 
     def _graph_signature(self, feeds):
-        return tuple((id(n), tuple(t.shape), str(t.dtype)) for n, t in feeds.items())
+        # where the feeds live is part of the plan: host feeds get a packed staging buffer, device feeds are read in place
+        return tuple((id(n), tuple(t.shape), str(t.dtype), t.device.type) for n, t in feeds.items())
 
     def _run_graph(self, feeds):
         key = self._graph_signature(feeds)
@@ -886,10 +888,33 @@ class SubExecutor(object):
             self._capture(feeds, key)
         # stage inputs: straight into the graph's static buffers on the compute stream (a pinned
         # source makes this a true async H2D; no intermediate host copy, no memcpy node in the graph)
-        for node, t in feeds.items():
-            st = self._static_in[node]
-            if st.data_ptr() != t.data_ptr():
-                st.copy_(t, non_blocking=True)
+        pk = self._packed
+        if pk is not None and all(t.device.type == 'cpu' for t in feeds.values()):
+            # several small host feeds: one staging slot, ONE host->device copy for the whole step
+            slot = pk['turn'] % len(pk['host'])
+            pk['turn'] += 1
+            ev = pk['events'][slot]
+            if ev is not None:
+                ev.synchronize()                         # the copy that last used this slot has left the host
+            host = pk['host'][slot]
+            views, dst = pk['views'], pk['host_np'][slot]
+            for node, t in feeds.items():
+                off, nbytes = pk['layout'][node]
+                src = views.get(t.data_ptr())            # dataloader batches recur (pinned ring slots): byte views are cached
+                if src is None or src.size != nbytes:
+                    src = t.contiguous().numpy().reshape(-1).view(np.uint8)
+                    if t.is_contiguous() and len(views) < 64:
+                        views[t.data_ptr()] = src
+                np.copyto(dst[off:off + nbytes], src)
+            pk['dev'].copy_(host, non_blocking=True)
+            if ev is None:
+                ev = pk['events'][slot] = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+        else:
+            for node, t in feeds.items():
+                st = self._static_in[node]
+                if st.data_ptr() != t.data_ptr():
+                    st.copy_(t, non_blocking=True)
         self._mark_feeds_consumed()
         self._graph.replay()
         return self._static_out
@@ -898,7 +923,28 @@ class SubExecutor(object):
         dev = self.device
         torch.cuda.synchronize(dev)
         self._static_in, self._stage = {}, {}
+        self._packed = None
         pf_ptrs = getattr(self, '_pf_ptrs', set())
+        host_feeds = [(n, t) for n, t in feeds.items() if t.device.type == 'cpu']
+        if (len(host_feeds) == len(feeds) and len(feeds) > 1 and all(t.is_contiguous() for _, t in host_feeds)
+                and sum(t.numel() * t.element_size() for _, t in host_feeds) < (1 << 20)
+                and os.environ.get('HETU_PACK_FEEDS', '1') == '1'):
+            # all inputs are small host arrays (a CTR batch: a few KB each): give them one device buffer and one
+            # pinned staging ring, so that a step costs one cudaMemcpyAsync instead of one per input
+            layout, total = {}, 0
+            for n, t in host_feeds:
+                nbytes = t.numel() * t.element_size()
+                layout[n] = (total, nbytes)
+                total += (nbytes + 255) // 256 * 256
+            dev_buf = torch.empty(total, dtype=torch.uint8, device=dev)
+            hosts = [torch.empty(total, dtype=torch.uint8).pin_memory() for _ in range(4)]
+            self._packed = {'layout': layout, 'dev': dev_buf, 'host': hosts, 'host_np': [h.numpy() for h in hosts],
+                            'events': [None] * 4, 'turn': 0, 'views': {}}
+            for n, t in host_feeds:
+                off, nbytes = layout[n]
+                self._static_in[n] = dev_buf[off:off + nbytes].view(t.dtype).view(tuple(t.shape))
+                self._static_in[n].copy_(t, non_blocking=True)
+            feeds = {}
         for node, t in feeds.items():
             if t.device.type == 'cpu' or t.data_ptr() in pf_ptrs or t.device != dev:
                 self._static_in[node] = torch.empty(tuple(t.shape), dtype=t.dtype, device=dev)
