@@ -205,6 +205,14 @@ def bench_wdl(args, ht, torch, np, comm, device):
                 fw.write('W&D step, %d GPU(s), 50 steps, torch.profiler (CUPTI) kernel times\n' % world)
                 fw.write(prof.key_averages().table(sort_by='cuda_time_total', row_limit=25, max_name_column_width=90))
         comm.barrier()
+    if os.environ.get('HETU_WDL_STAMPS'):           # diagnostics: phase time stamps of the last fused tower launch
+        import ctypes
+        out = (ctypes.c_ulonglong * 16)()
+        _lib.call('wdl_tower_stamps', out)
+        names = ['P0', 'P1', 'P2', 'P3', 'head', 'P5', 'P6a', 'P6b', 'tail']
+        row = ' '.join('%s %.2f' % (n, (out[i + 1] - out[i]) / 1e3) for i, n in enumerate(names) if out[i + 1] and out[i])
+        rel = ' '.join('%s %.2f' % (n, (out[k] - out[0]) / 1e3) for n, k in (('gather0', 10), ('gather1', 11), ('sparse0', 12), ('sparse1', 13)))
+        print('[rank %d] tower phases (us): %s | relative to tower start: %s' % (rank, row, rel), flush=True)
     # --- end to end: numpy batch -> pinned -> H2D, loss D2H every step ---------------------
     h2d = sum(a.nbytes for a in pool[0])
     last = {}

@@ -51,6 +51,8 @@ struct TowerParams {
     // peer's flag of the step in between.
     int apply_sgd, world, rank, total, o2, o3, o4;
     float* arena[8];       // [2][world][total] floats on every rank
+    float* arena_mc;       // NVLS multicast mapping of the arenas (or null): one multimem.st reaches every rank
+    unsigned* flags_mc;    // the same for the flag rows
     unsigned* flags[8];    // flags[dst][src] = number of complete steps pushed by src
     unsigned* epoch;       // this rank's completed-step counter (device memory: graph replays keep counting)
     const float* lr;
@@ -120,6 +122,11 @@ __device__ __forceinline__ void grad_store4(const TowerParams& p, unsigned slot,
         return;
     }
     const size_t at = ((size_t)slot * p.world + p.rank) * p.total + off;
+    if (p.arena_mc != nullptr) {       // the switch replicates the store into every rank's arena
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p.arena_mc + at), "f"(v.x), "f"(v.y),
+                     "f"(v.z), "f"(v.w) : "memory");
+        return;
+    }
     for (int r = 0; r < p.world; ++r) *reinterpret_cast<float4*>(p.arena[r] + at) = v;
 }
 __device__ __forceinline__ void grad_store1(const TowerParams& p, unsigned slot, float* own, const float* prm, int off,
@@ -127,6 +134,10 @@ __device__ __forceinline__ void grad_store1(const TowerParams& p, unsigned slot,
     if (!p.apply_sgd) { *own = v; return; }
     if (p.world == 1) { *const_cast<float*>(prm) = old - lr * v; return; }
     const size_t at = ((size_t)slot * p.world + p.rank) * p.total + off;
+    if (p.arena_mc != nullptr) {
+        asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p.arena_mc + at), "f"(v) : "memory");
+        return;
+    }
     for (int r = 0; r < p.world; ++r) p.arena[r][at] = v;
 }
 // TMA tile load delivered to the same shared-memory offset of every CTA in `mask`; each destination's mbarrier (same
@@ -517,8 +528,12 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     cluster_sync_all();
     const unsigned target = epoch0 + 1u;
     if (p.world > 1) {
+        if (p.flags_mc != nullptr && c == 0 && tid == 0) {     // one multicast store raises this rank's flag everywhere
+            __threadfence_system();
+            asm volatile("multimem.st.release.sys.global.u32 [%0], %1;" ::"l"(p.flags_mc + p.rank), "r"(target) : "memory");
+        }
         if (tid < p.world && tid != p.rank) {
-            if (c == 0) {
+            if (c == 0 && p.flags_mc == nullptr) {
                 __threadfence_system();
                 asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.flags[tid] + p.rank), "r"(target) : "memory");
             }
@@ -593,7 +608,8 @@ HETU_API int hetu_wdl_tower_step(const float* x, float* y4, const float* zpf, co
                                  const float* W2, const float* W3, const float* W4, float* work, float* loss, float* pred,
                                  float* dz, float* dW1, float* dW2, float* dW3, float* dW4, int batch, int nd, int hidden,
                                  int emb_cols, int width, void* const* arenas, void* const* flags, int world, int rank,
-                                 void* epoch, const float* lr, void* opt_step, int pdl, void* dz_flag, cudaStream_t s) {
+                                 void* epoch, const float* lr, void* opt_step, int pdl, void* dz_flag, void* arena_mc, void* flags_mc,
+                                 cudaStream_t s) {
     if (batch != TB || hidden != TH || nd < 1 || nd > 16 || emb_cols <= 0 || emb_cols % (4 * TCL) != 0 || width <= 0 ||
         emb_cols % width != 0 || (emb_cols + TH) / (4 * TCL) > kMaxSlice4) {
         hetu_set_error("hetu_wdl_tower_step: needs batch 128, hidden 256, 1..16 dense features, emb_cols %% 32 == 0, "
@@ -610,6 +626,8 @@ HETU_API int hetu_wdl_tower_step(const float* x, float* y4, const float* zpf, co
     p.apply_sgd = arenas != nullptr ? 1 : 0;
     p.world = 1; p.rank = 0; p.epoch = (unsigned*)epoch; p.lr = lr; p.opt_step = (long long*)opt_step;
     for (int i = 0; i < 8; ++i) { p.arena[i] = nullptr; p.flags[i] = nullptr; }
+    p.arena_mc = (world > 1) ? (float*)arena_mc : nullptr;
+    p.flags_mc = (world > 1) ? (unsigned*)flags_mc : nullptr;
     if (p.apply_sgd) {
         if (world < 1 || world > 8 || rank < 0 || rank >= world || epoch == nullptr || lr == nullptr ||
             (world > 1 && flags == nullptr)) {

@@ -193,7 +193,8 @@ def _make_op_class():
             L.call('wdl_tower_step', L.p(x), L.p(b['y4']), L.p(b['zpf']), L.p(labels), L.p(W1), L.p(W2), L.p(W3), L.p(W4),
                    L.p(b['work']), L.p(b['loss']), L.p(b['pred']), L.p(b['dz']), L.p(b['dW1']), L.p(b['dW2']),
                    L.p(b['dW3']), L.p(b['dW4']), L.c_int(B), L.c_int(m['nd']), L.c_int(hid), L.c_int(m['emb_cols']),
-                   L.c_int(m['width']), *tail, L.c_int(1 if pdl else 0), L.p(b['dz_flag'] if pdl else None), st)
+                   L.c_int(m['width']), *tail, L.c_int(1 if pdl else 0), L.p(b['dz_flag'] if pdl else None),
+                   ctypes.c_void_p((dp or {}).get('arena_mc', 0) or 0), ctypes.c_void_p((dp or {}).get('flags_mc', 0) or 0), st)
             self.fused_launches += 2
             self.last = dict(ids=ids, dz=b['dz'], grads=(b['dW1'], b['dW2'], b['dW3'], b['dW4']),
                              W4=b['w4_snap'] if dp is not None else W4, E=E, bases=bases, nshard=nshard, vocab=vocab,
@@ -228,7 +229,14 @@ def _make_op_class():
             if eng.world > 8 or sorted(fdp.ids) != sorted(pos[id(m[k])] for k in ('W1', 'W2', 'W3', 'W4')):
                 self._dp = False
                 return None
-            arena = eng.buffer(('wdl_arena', id(self)), 2 * eng.world * total * 4)
+            arena_bytes = 2 * eng.world * total * 4
+            mc = eng.mc_buffer(('wdl_arena', id(self)), arena_bytes + 256)       # arena + flag row, NVLS multicast mapped
+            if mc is not None:
+                self._dp = dict(world=eng.world, rank=eng.rank, arenas=mc.ptrs, flags=mc.peer_ptrs(arena_bytes),
+                                arena_mc=mc.mc_ptr, flags_mc=mc.mc_ptr + arena_bytes,
+                                epoch=torch.zeros(1, dtype=torch.int32, device=dev), opt=opt, keep=mc)
+                return self._dp
+            arena = eng.buffer(('wdl_arena', id(self)), arena_bytes)
             flags = eng.buffer(('wdl_flags', id(self)), 256)
             flags.tensor(dtype=torch.int32, numel=64).zero_()
             torch.cuda.synchronize(dev)

@@ -66,6 +66,38 @@ class SymmBuffer(object):
         return _PTRS16(*([a + offset_bytes for a in self.addrs] + [0] * (16 - len(self.addrs))))
 
 
+class MulticastBuffer(object):
+    """Symmetric buffer that also has an NVLS multicast mapping: a store to ``mc_ptr + off`` lands at offset ``off``
+    of EVERY rank's copy (the NVSwitch replicates it), a ``multimem.ld_reduce`` there returns the sum over the ranks.
+    The allocation (cuMemCreate + cuMulticastCreate / BindMem and the exchange of the handles between the
+    processes) is torch's symmetric-memory allocator - plumbing only; the kernels that use the mapping are ours
+    (csrc/wdl_tower.cu, csrc/collectives.cu).  ``mc_ptr`` is 0 where the fabric has no multicast support."""
+
+    def __init__(self, engine: 'SymmEngine', nbytes: int):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as sm
+        self.engine = engine
+        self.nbytes = int((nbytes + 255) // 256 * 256)
+        group = engine.comm.group if engine.comm.group is not None else dist.group.WORLD
+        self._t = sm.empty(self.nbytes // 4, dtype=torch.float32, device=engine.device)
+        self._h = sm.rendezvous(self._t, group.group_name)
+        self.addrs = [int(p_) for p_ in self._h.buffer_ptrs]
+        self.local_ptr = self.addrs[engine.rank]
+        self.mc_ptr = int(getattr(self._h, 'multicast_ptr', 0) or 0)
+        self.ptrs = _PTRS16(*(self.addrs + [0] * (16 - len(self.addrs))))
+        self._t.zero_()
+        torch.cuda.synchronize(engine.device)
+        engine.comm.barrier()
+
+    def tensor(self, dtype=torch.float32, offset_bytes: int = 0, numel: Optional[int] = None) -> torch.Tensor:
+        v = self._t.view(torch.uint8)[offset_bytes:]
+        t = v.view(dtype)
+        return t if numel is None else t[:numel]
+
+    def peer_ptrs(self, offset_bytes: int = 0):
+        return _PTRS16(*([a + offset_bytes for a in self.addrs] + [0] * (16 - len(self.addrs))))
+
+
 class _ArenaView(object):
     """A sub-range of the arena with the SymmBuffer interface (tensor / ptrs / peer_ptrs)."""
 
@@ -139,6 +171,26 @@ class SymmEngine(object):
 
     def next_slot(self, key, nbytes: int) -> int:
         return 0
+
+    def mc_buffer(self, key, nbytes: int) -> Optional[MulticastBuffer]:
+        """Zeroed symmetric buffer with an NVLS multicast mapping, or None where that is not available
+        (``HETU_NVLS=0`` switches it off)."""
+        if os.environ.get('HETU_NVLS', '1') != '1' or getattr(self, '_mc_broken', False):
+            return None
+        k = ('mc', key, int(nbytes))
+        if k not in self._bufs:
+            try:
+                buf = MulticastBuffer(self, int(nbytes))
+            except Exception as exc:                      # old driver / no NVSwitch multicast: peer pointers remain
+                import warnings
+                warnings.warn('NVLS multicast buffers unavailable (%s); using peer stores' % exc)
+                self._mc_broken = True
+                return None
+            if not buf.mc_ptr:
+                self._mc_broken = True
+                return None
+            self._bufs[k] = buf
+        return self._bufs[k]
 
     def _stream(self):
         return L.stream_ptr(self.device)

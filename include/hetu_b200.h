@@ -161,7 +161,10 @@ int hetu_wdl_tower_step(const float* x, float* y4, const float* zpf /*[128, fiel
                         /* pdl != 0: launched as a programmatic dependent of the gather (the first layers overlap
                          * it); dz_flag (optional, device unsigned, zeroed once) is bumped when dz is out, which is
                          * what hetu_wdl_sparse_sgd_rank1 waits for when it is given the same flag */
-                        int pdl, void* dz_flag, cudaStream_t s);
+                        int pdl, void* dz_flag,
+                        /* NVLS multicast mappings of the arenas / flag rows (or NULL: plain peer stores): the pushes
+                         * become multimem.st, one store per value instead of one per rank */
+                        void* arena_mc, void* flags_mc, cudaStream_t s);
 int hetu_wdl_tower_stamps(unsigned long long* out9);   /* diagnostics, see benchmarks/wdl_tower_phases.py */
 int hetu_wdl_sparse_sgd_rank1(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code,
                               const float* dz, const float* w4, const float* lr_p, float scale, size_t n, int width,
