@@ -455,20 +455,32 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
             p.stamps[9] = t;
         }
+        // TMEM lane = row of dW2, so a thread holds 32 columns of ONE row: rows go through a warp-private tile in the
+        // (now idle) A area and leave as 128-byte row segments, four rows per store instruction - over NVLink a
+        // 16-byte store per lane would be one packet each
+        float* tile = reinterpret_cast<float*>(sA) + (warp - 2) * (32 * 36);
+        const int sub_row = lane >> 3, c4 = (lane & 7) * 4;
 #pragma unroll 1
         for (int h = 0; h < 2; ++h) {
-            const int off = (h * 128 + q * 32 + lane) * TH + n0;
-            float4 old[8];
-            if (inplace(p)) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) old[j] = *reinterpret_cast<const float4*>(p.W2 + off + 4 * j);
-            }
             float v[32];
             tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 32 + h * 32, v);
 #pragma unroll
             for (int j = 0; j < 8; ++j)
-                grad_store4(p, slot, p.dW2 + off + 4 * j, p.W2 + off + 4 * j, p.o2 + off + 4 * j,
-                            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]), lr_now, old[j]);
+                *reinterpret_cast<float4*>(&tile[lane * 36 + 4 * j]) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            __syncwarp();
+            float4 old[8];
+            if (inplace(p)) {
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+                    old[r] = *reinterpret_cast<const float4*>(p.W2 + (h * 128 + q * 32 + 4 * r + sub_row) * TH + n0 + c4);
+            }
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const int off = (h * 128 + q * 32 + 4 * r + sub_row) * TH + n0 + c4;
+                const float4 g = *reinterpret_cast<const float4*>(&tile[(4 * r + sub_row) * 36 + c4]);
+                grad_store4(p, slot, p.dW2 + off, p.W2 + off, p.o2 + off, g, lr_now, old[r]);
+            }
+            __syncwarp();
         }
     } else if (warp >= 6) {
         // dW1[k, n0 + lane] = sum_b x[b, k] dh1[b, lane].  Shared-memory bandwidth sets the pace, so every load of
@@ -527,71 +539,74 @@ wdl_tower_kernel(const __grid_constant__ CUtensorMap tm_h1k, const __grid_consta
     if (tid == 0) __threadfence_system();                // this CTA's pushes (ordered before by the barrier) reach the peers
     cluster_sync_all();
     const unsigned target = epoch0 + 1u;
-    if (p.world > 1) {
-        if (p.flags_mc != nullptr && c == 0 && tid == 0) {     // one multicast store raises this rank's flag everywhere
-            __threadfence_system();
-            asm volatile("multimem.st.release.sys.global.u32 [%0], %1;" ::"l"(p.flags_mc + p.rank), "r"(target) : "memory");
-        }
-        if (tid < p.world && tid != p.rank) {
-            if (c == 0 && p.flags_mc == nullptr) {
-                __threadfence_system();
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.flags[tid] + p.rank), "r"(target) : "memory");
-            }
-            const unsigned* f = p.flags[p.rank] + tid;
-            unsigned v;
-            do { asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory"); } while ((int)(v - target) < 0);
-        }
-        __syncthreads();
-    }
-    {
-        const float lr = *p.lr;
-        const float* mine = p.arena[p.rank] + (size_t)slot * p.world * p.total;
-        float* prm[4] = {const_cast<float*>(p.W1), const_cast<float*>(p.W2), const_cast<float*>(p.W3), const_cast<float*>(p.W4)};
-        const int off[5] = {0, p.o2, p.o3, p.o4, p.total};
-        const int len[4] = {p.nd * TH, TH * TH, TH * TH, p.pitch};
-        // 4 float4 per thread and pass, every load of a pass issued before the first use: the loop is latency bound
-        // (8 SMs, L2-resident data), so independent loads in flight are what sets its time
-#pragma unroll
-        for (int sgm = 0; sgm < 4; ++sgm) {
-            float4* w4p = reinterpret_cast<float4*>(prm[sgm]);
-            const int n4 = len[sgm] >> 2;
-            const float4* g0 = reinterpret_cast<const float4*>(mine + off[sgm]);
-            const size_t rs = (size_t)p.total >> 2;                     // float4 stride between source blocks
-            for (int base = c * TTHREADS + tid; base < n4; base += 4 * TCL * TTHREADS) {
-                float4 w[4], g[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int i = base + u * TCL * TTHREADS;
-                    if (i < n4) { w[u] = w4p[i]; g[u] = __ldcg(g0 + i); }
-                }
-                for (int r = 1; r < p.world; ++r) {
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int i = base + u * TCL * TTHREADS;
-                        if (i < n4) {
-                            const float4 t = __ldcg(g0 + (size_t)r * rs + i);
-                            g[u].x += t.x; g[u].y += t.y; g[u].z += t.z; g[u].w += t.w;
-                        }
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int i = base + u * TCL * TTHREADS;
-                    if (i < n4) {
-                        w[u].x -= lr * g[u].x; w[u].y -= lr * g[u].y; w[u].z -= lr * g[u].z; w[u].w -= lr * g[u].w;
-                        w4p[i] = w[u];
-                    }
-                }
-            }
-        }
-    }
     if (c == 0 && tid == 0) {
-        *p.epoch = target;
+        __threadfence_system();
+        if (p.flags_mc != nullptr) {                     // one multicast store raises this rank's flag on every rank
+            asm volatile("multimem.st.release.sys.global.u32 [%0], %1;" ::"l"(p.flags_mc + p.rank), "r"(target) : "memory");
+        } else {
+            for (int r = 0; r < p.world; ++r)
+                if (r != p.rank)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.flags[r] + p.rank), "r"(target) : "memory");
+        }
+        *p.epoch = target;                               // hetu_wdl_dp_apply (next in the stream) reduces this step's slot
         if (p.opt_step != nullptr) *p.opt_step += 1;
     }
     stamp(p, 9);
 }
+// Second half of the data-parallel step: every rank's gradient blocks are (being) pushed into this rank's arena by the
+// tower kernels; once the flags of all sources show this step, sum the blocks in rank order (bit-identical replicas)
+// and apply SGD.  A full-width grid: the 8 SMs of the tower cluster would need ~6 us just to read world x 0.55 MB.
+struct DpApplyParams {
+    const float* arena;        // this rank's [2][world][total]
+    const unsigned* flags;     // this rank's flag row [world]
+    const unsigned* epoch;     // set by the tower kernel of this step
+    const float* lr;
+    float* prm[4];
+    int off[5];
+    int world, rank, total;
+};
+__global__ void __launch_bounds__(256) wdl_dp_apply_kernel(DpApplyParams p) {
+    const unsigned target = *reinterpret_cast<const volatile unsigned*>(p.epoch);
+    const unsigned slot = (target - 1u) & 1u;
+    if ((int)threadIdx.x < p.world && (int)threadIdx.x != p.rank) {
+        const unsigned* f = p.flags + threadIdx.x;
+        unsigned v;
+        do { asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory"); } while ((int)(v - target) < 0);
+    }
+    __syncthreads();
+    const float lr = *p.lr;
+    const float4* blk = reinterpret_cast<const float4*>(p.arena + (size_t)slot * p.world * p.total);
+    const size_t rs = (size_t)p.total >> 2;
+    const int n4 = p.total >> 2;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
+        int sg = 0;
+        while (sg < 3 && 4 * i >= p.off[sg + 1]) ++sg;
+        float4* w = reinterpret_cast<float4*>(p.prm[sg] + (4 * i - p.off[sg]));
+        float4 wv = *w;
+        float4 g = __ldcg(blk + i);
+        for (int r = 1; r < p.world; ++r) {
+            const float4 t = __ldcg(blk + (size_t)r * rs + i);
+            g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+        }
+        wv.x -= lr * g.x; wv.y -= lr * g.y; wv.z -= lr * g.z; wv.w -= lr * g.w;
+        *w = wv;
+    }
+}
 }  // namespace
+
+HETU_API int hetu_wdl_dp_apply(const float* arena_local, const void* flags_local, const void* epoch, const float* lr,
+                               float* W1, float* W2, float* W3, float* W4, int nd, int emb_cols, int world, int rank,
+                               cudaStream_t s) {
+    DpApplyParams p;
+    p.arena = arena_local; p.flags = (const unsigned*)flags_local; p.epoch = (const unsigned*)epoch; p.lr = lr;
+    p.prm[0] = W1; p.prm[1] = W2; p.prm[2] = W3; p.prm[3] = W4;
+    p.off[0] = 0; p.off[1] = nd * TH; p.off[2] = p.off[1] + TH * TH; p.off[3] = p.off[2] + TH * TH;
+    p.off[4] = p.off[3] + emb_cols + TH;
+    p.total = p.off[4]; p.world = world; p.rank = rank;
+    wdl_dp_apply_kernel<<<kNumSMs, 256, 0, s>>>(p);
+    HETU_CHECK_LAUNCH("hetu_wdl_dp_apply");
+    return 0;
+}
 
 static unsigned long long* g_tower_stamps = nullptr;
 static void ensure_stamps() {

@@ -198,7 +198,7 @@ def _make_op_class():
             self.fused_launches += 2
             self.last = dict(ids=ids, dz=b['dz'], grads=(b['dW1'], b['dW2'], b['dW3'], b['dW4']),
                              W4=b['w4_snap'] if dp is not None else W4, E=E, bases=bases, nshard=nshard, vocab=vocab,
-                             torch_path=False, dense_done=dp is not None,
+                             torch_path=False, dense_done=dp is not None, weights=(W1, W2, W3, W4),
                              dz_flag=b['dz_flag'] if pdl else None, dz_expect=b['dz_expect'] if pdl else None)
             return (b['loss'], b['pred'])
 
@@ -234,6 +234,7 @@ def _make_op_class():
             if mc is not None:
                 self._dp = dict(world=eng.world, rank=eng.rank, arenas=mc.ptrs, flags=mc.peer_ptrs(arena_bytes),
                                 arena_mc=mc.mc_ptr, flags_mc=mc.mc_ptr + arena_bytes,
+                                arena_local=mc.local_ptr, flags_local=mc.local_ptr + arena_bytes,
                                 epoch=torch.zeros(1, dtype=torch.int32, device=dev), opt=opt, keep=mc)
                 return self._dp
             arena = eng.buffer(('wdl_arena', id(self)), arena_bytes)
@@ -242,6 +243,7 @@ def _make_op_class():
             torch.cuda.synchronize(dev)
             eng.comm.barrier()
             self._dp = dict(world=eng.world, rank=eng.rank, arenas=arena.ptrs, flags=flags.ptrs,
+                            arena_local=arena.local_ptr, flags_local=flags.local_ptr,
                             epoch=torch.zeros(1, dtype=torch.int32, device=dev), opt=opt, keep=(arena, flags))
             return self._dp
 
@@ -273,7 +275,16 @@ def _make_op_class():
             if bsp:
                 E.engine.barrier()
             if last.get('dense_done'):
-                return                                    # all-reduce, SGD and the step counter: done inside the tower kernel
+                dp = self._dp
+                if dp and dp['world'] > 1:
+                    # the tower kernel has pushed its gradient blocks to every rank (multimem.st) and raised its flag;
+                    # sum the blocks that arrived here and apply SGD
+                    W = last['weights']
+                    L.call('wdl_dp_apply', ctypes.c_void_p(dp['arena_local']), ctypes.c_void_p(dp['flags_local']),
+                           L.p(dp['epoch']), L.p(opt.lr_t), L.p(W[0]), L.p(W[1]), L.p(W[2]), L.p(W[3]),
+                           L.c_int(m['nd']), L.c_int(m['emb_cols']), L.c_int(dp['world']), L.c_int(dp['rank']),
+                           L.stream_ptr(W[0].device))
+                return                                    # one GPU: SGD and the step counter were done inside the tower kernel
             if opt_node.fused_dp is not None:
                 opt_node.fused_dp.step(opt, grads)
             else:

@@ -165,6 +165,10 @@ int hetu_wdl_tower_step(const float* x, float* y4, const float* zpf /*[128, fiel
                         /* NVLS multicast mappings of the arenas / flag rows (or NULL: plain peer stores): the pushes
                          * become multimem.st, one store per value instead of one per rank */
                         void* arena_mc, void* flags_mc, cudaStream_t s);
+/* data-parallel W&D: after hetu_wdl_tower_step has pushed this step's gradient blocks, wait for every source's flag,
+ * sum the blocks of this rank's arena in rank order and apply SGD to W1..W4 (full-width grid) */
+int hetu_wdl_dp_apply(const float* arena_local, const void* flags_local, const void* epoch, const float* lr, float* W1,
+                      float* W2, float* W3, float* W4, int nd, int emb_cols, int world, int rank, cudaStream_t s);
 int hetu_wdl_tower_stamps(unsigned long long* out9);   /* diagnostics, see benchmarks/wdl_tower_phases.py */
 int hetu_wdl_sparse_sgd_rank1(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code,
                               const float* dz, const float* w4, const float* lr_p, float scale, size_t n, int width,
