@@ -79,11 +79,18 @@ inline bool recv_msg(int fd, Message* m) {
     if (magic != kMagic) return false;
     memcpy(&m->type, hdr + 4, 4); memcpy(&m->key, hdr + 8, 8);
     memcpy(&m->arg0, hdr + 16, 8); memcpy(&m->arg1, hdr + 24, 8); memcpy(&m->sig, hdr + 32, 8); memcpy(&na, hdr + 40, 4);
+    // a peer is not trusted with our memory: bounded array count and sizes (HETU_PS_MAX_ARRAY_MB, default 16 GiB)
+    static const uint64_t max_bytes = [] {
+        const char* e = getenv("HETU_PS_MAX_ARRAY_MB");
+        return (uint64_t)(e ? strtoull(e, nullptr, 10) : 16384ull) << 20;
+    }();
+    if (na > 16) return false;
     m->arrays.clear();
     m->arrays.resize(na);
     for (uint32_t i = 0; i < na; ++i) {
         uint64_t nb;
         if (!read_all(fd, &nb, 8)) return false;
+        if (nb > max_bytes) return false;
         m->arrays[i].resize(nb);
         if (nb && !read_all(fd, m->arrays[i].data(), nb)) return false;
     }
@@ -101,7 +108,16 @@ inline int listen_on(int port, int* bound_port = nullptr) {
     setsockopt(fd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof(one));
     sockaddr_in addr{};
     addr.sin_family = AF_INET;
+    // Listen where the job lives: HETU_PS_BIND names the interface address; a job whose scheduler is on the loopback
+    // address (single-node runs, the tests) is not reachable from outside at all; otherwise every interface.
     addr.sin_addr.s_addr = htonl(INADDR_ANY);
+    const char* bind_to = getenv("HETU_PS_BIND");
+    const char* root = getenv("DMLC_PS_ROOT_URI");
+    if (bind_to != nullptr && bind_to[0]) {
+        if (inet_pton(AF_INET, bind_to, &addr.sin_addr) != 1) { ::close(fd); throw std::runtime_error(std::string("HETU_PS_BIND: bad address ") + bind_to); }
+    } else if (root != nullptr && (strcmp(root, "127.0.0.1") == 0 || strcmp(root, "localhost") == 0)) {
+        addr.sin_addr.s_addr = htonl(INADDR_LOOPBACK);
+    }
     addr.sin_port = htons((uint16_t)port);
     if (::bind(fd, (sockaddr*)&addr, sizeof(addr)) != 0) { ::close(fd); throw std::runtime_error(std::string("bind: ") + strerror(errno)); }
     if (::listen(fd, 256) != 0) { ::close(fd); throw std::runtime_error("listen failed"); }

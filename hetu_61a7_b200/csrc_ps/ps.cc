@@ -126,9 +126,20 @@ class Server {
         if (it == params_.end()) throw std::runtime_error("parameter " + std::to_string(key) + " not initialised on server");
         return it->second;
     }
+    // every handler checks what it is about to index: a malformed or mismatching request gets kError, not a wild read
+    static void need(const Message& req, size_t i, size_t min_bytes, const char* what) {
+        if (req.arrays.size() <= i || req.arrays[i].size() < min_bytes)
+            throw std::runtime_error(std::string("malformed request: ") + what);
+    }
     // arrays: [0] = {type, len, width, init_type, opt_type} as int64, [1] = {a, b} double, [2] = seed u64
     void param_init(const Message& req) {
+        need(req, 0, 5 * sizeof(int64_t), "ParamInit header");
+        need(req, 1, 2 * sizeof(double), "ParamInit range");
+        need(req, 2, sizeof(uint64_t), "ParamInit seed");
         const int64_t* h = req.data<int64_t>(0);
+        if (h[0] < 0 || h[0] > 2 || h[1] < 0 || h[2] < 0 || (h[0] != 0 && h[2] == 0) ||
+            (double)h[1] * (double)(h[0] == 0 ? 1 : h[2]) > 1e12)
+            throw std::runtime_error("malformed request: ParamInit shape");
         const double* ab = req.data<double>(1);
         uint64_t seed = *req.data<uint64_t>(2);
         auto p = std::make_shared<Param>();
@@ -171,6 +182,7 @@ class Server {
     void dense_push(const Message& req) {
         auto p = get(req.key);
         std::unique_lock<std::shared_mutex> l(p->mu);
+        need(req, 0, 0, "dense push data");
         const float* g = req.data<float>(0);
         size_t n = std::min(p->data.size(), req.count<float>(0));
         p->apply(0, g, n, 0);
@@ -178,6 +190,7 @@ class Server {
     void sparse_pull(const Message& req, size_t off_idx, Message* rsp) {
         auto p = get(req.key);
         std::shared_lock<std::shared_mutex> l(p->mu);
+        need(req, off_idx, 0, "sparse pull rows");
         const int64_t* rows = req.data<int64_t>(off_idx);
         size_t n = req.count<int64_t>(off_idx), w = p->width;
         std::vector<float> out(n * w);
@@ -190,9 +203,13 @@ class Server {
     void sparse_push(const Message& req, size_t off_idx, size_t data_idx) {
         auto p = get(req.key);
         std::unique_lock<std::shared_mutex> l(p->mu);
+        need(req, off_idx, 0, "sparse push rows");
+        need(req, data_idx, 0, "sparse push data");
         const int64_t* rows = req.data<int64_t>(off_idx);
         const float* g = req.data<float>(data_idx);
         size_t n = req.count<int64_t>(off_idx), w = p->width;
+        if (req.count<float>(data_idx) != n * w) throw std::runtime_error("malformed request: sparse push carries " +
+            std::to_string(req.count<float>(data_idx)) + " floats for " + std::to_string(n) + " rows of width " + std::to_string(w));
         for (size_t i = 0; i < n; ++i) {
             int64_t r = rows[i];
             if (r < 0 || (size_t)r >= p->len) continue;
@@ -203,9 +220,12 @@ class Server {
     void sync_embedding(const Message& req, size_t base, Message* rsp) {
         auto p = get(req.key);
         std::shared_lock<std::shared_mutex> l(p->mu);
+        need(req, base, 0, "sync rows");
+        need(req, base + 1, 0, "sync versions");
         const int64_t* rows = req.data<int64_t>(base);
         const int64_t* cver = req.data<int64_t>(base + 1);
         size_t n = req.count<int64_t>(base), w = p->width;
+        if (req.count<int64_t>(base + 1) != n) throw std::runtime_error("malformed request: sync rows / versions differ in length");
         int64_t bound = req.arg0;
         std::vector<int64_t> idx, ver;
         std::vector<float> data;
@@ -227,10 +247,15 @@ class Server {
     void push_embedding(const Message& req, size_t base) {
         auto p = get(req.key);
         std::unique_lock<std::shared_mutex> l(p->mu);
+        need(req, base, 0, "push rows");
+        need(req, base + 1, 0, "push data");
+        need(req, base + 2, 0, "push update counts");
         const int64_t* rows = req.data<int64_t>(base);
         const float* g = req.data<float>(base + 1);
         const int64_t* upd = req.data<int64_t>(base + 2);
         size_t n = req.count<int64_t>(base), w = p->width;
+        if (req.count<float>(base + 1) != n * w || req.count<int64_t>(base + 2) != n)
+            throw std::runtime_error("malformed request: embedding push arrays do not match " + std::to_string(n) + " rows of width " + std::to_string(w));
         for (size_t i = 0; i < n; ++i) {
             int64_t r = rows[i];
             if (r < 0 || (size_t)r >= p->len) continue;
@@ -239,8 +264,17 @@ class Server {
             for (size_t j = 0; j < w; ++j) dst[j] += g[i * w + j];
         }
     }
+    // Checkpoint files go under the directory the request names - which must not climb (".."), and, when the operator
+    // sets HETU_PS_CKPT_ROOT, must lie under that root.
     std::string path_of(const Message& req) const {
-        return req.str(0) + "/" + std::to_string(req.key) + "_" + std::to_string(id_.load()) + ".dat";
+        need(req, 0, 1, "checkpoint directory");
+        const std::string dir = req.str(0);
+        if (dir.find("..") != std::string::npos || dir.find('\0') != std::string::npos)
+            throw std::runtime_error("checkpoint directory may not contain '..': " + dir);
+        const char* root = getenv("HETU_PS_CKPT_ROOT");
+        if (root != nullptr && root[0] && dir.compare(0, strlen(root), root) != 0)
+            throw std::runtime_error("checkpoint directory " + dir + " is outside HETU_PS_CKPT_ROOT");
+        return dir + "/" + std::to_string(req.key) + "_" + std::to_string(id_.load()) + ".dat";
     }
     void save(const Message& req) {
         auto p = get(req.key);

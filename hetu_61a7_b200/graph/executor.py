@@ -484,7 +484,13 @@ class Executor(object):
                 for k, t in node.state_tensors().items():
                     if t is not None:
                         state['%s/%s' % (node.name, k)] = t.detach().cpu().numpy()
-        if self.rank in (0, None) or cfg.comm_mode is None or getattr(cfg, 'pp_nrank', 1) > 1:
+        # Replicated layouts (single process, data parallel): rank 0's file is the checkpoint.  Pipeline stages and
+        # tensor-parallel shards hold DIFFERENT parameters (or different slices under the same name): every rank writes
+        # its own `<file_name>.rank<k>`, and load() reads the file of the same rank.
+        per_rank = self._per_rank_checkpoint()
+        if per_rank:
+            file_name = '%s.rank%d' % (file_name, self.rank or 0)
+        if per_rank or self.rank in (0, None) or cfg.comm_mode is None:
             with open(os.path.join(file_path, file_name), 'wb') as fw:
                 pickle.dump(state, fw)
             if save_optimizer:
@@ -508,7 +514,19 @@ class Executor(object):
         if cfg.ps_comm is not None:
             cfg.ps_comm.BarrierWorker()
 
+    def _per_rank_checkpoint(self) -> bool:
+        cfg = self.config
+        if (self.nrank or 1) <= 1:
+            return False
+        if getattr(cfg, 'pp_nrank', 1) > 1 or cfg.pipeline:
+            return True
+        return any(getattr(n, 'reshaped', False) for n in self._named_params().values())
+
     def load(self, file_path: str, file_name: str, consider_splits: bool = False):
+        mine = '%s.rank%d' % (file_name, self.rank or 0)
+        if self._per_rank_checkpoint() and os.path.exists(os.path.join(file_path, mine)):
+            file_name = mine                            # this rank's stage / shard (see save)
+            consider_splits = False
         with open(os.path.join(file_path, file_name), 'rb') as fr:
             state_dict = pickle.load(fr)
         self.load_dict(state_dict, file_path, consider_splits)

@@ -185,14 +185,22 @@ class PSWorker(object):
                                       out.ctypes.data_as(_F32P)), 'SparsePull')
         return out
 
+    def _check_rows(self, node_id, r, g, what):
+        # the native client reads rows x width floats from `grads`: a buffer of another size would be read out of bounds
+        width = self._meta[int(node_id)][2] if int(node_id) in self._meta else None
+        if width and g.size != r.size * width:
+            raise ValueError('%s: %d values for %d rows of width %d' % (what, g.size, r.size, width))
+
     def SparsePush(self, node_id, rows, grads):
         r, rp = _i64(np.asarray(rows).reshape(-1))
         g, gp = _f32(grads)
+        self._check_rows(node_id, r, g, 'SparsePush')
         _chk(self.lib.hps_sparse_push(ctypes.c_uint64(node_id), rp, ctypes.c_uint64(r.size), gp), 'SparsePush')
 
     def SDPushPull(self, node_id, rows, grads, out: Optional[np.ndarray] = None) -> np.ndarray:
         r, rp = _i64(np.asarray(rows).reshape(-1))
         g, gp = _f32(grads)
+        self._check_rows(node_id, r, g, 'SDPushPull')
         if out is None:
             out = np.empty(self._numel(node_id), dtype=np.float32)
         _chk(self.lib.hps_sd_pushpull(ctypes.c_uint64(node_id), rp, ctypes.c_uint64(r.size), gp,
@@ -202,6 +210,7 @@ class PSWorker(object):
     def SSPushPull(self, node_id, rows, grads, pull_rows, out: Optional[np.ndarray] = None) -> np.ndarray:
         r, rp = _i64(np.asarray(rows).reshape(-1))
         g, gp = _f32(grads)
+        self._check_rows(node_id, r, g, 'SSPushPull')
         pr, prp = _i64(np.asarray(pull_rows).reshape(-1))
         width = self._meta[int(node_id)][2]
         if out is None:

@@ -53,6 +53,21 @@ if rank == 0:
     w.LoadParam(2, out_dir)
 w.BarrierWorker()
 assert np.allclose(w.SparsePull(2, rows[:1])[0], after[0], atol=1e-5)
+# a push whose data does not hold rows x width floats is refused before it reaches the wire (the server checks the same
+# on its side), a checkpoint directory that climbs out with '..' is refused by the server, which keeps serving
+w.BarrierWorker()
+try:
+    w.SparsePush(2, rows[:2], np.ones((2, 5), np.float32))
+    raise AssertionError('a sparse push with the wrong width must be refused')
+except ValueError as exc:
+    assert 'rows of width' in str(exc), exc
+try:
+    w.SaveParam(2, out_dir + '/../escape')
+    raise AssertionError("a checkpoint path with '..' must be refused")
+except RuntimeError as exc:
+    assert '..' in str(exc), exc
+assert np.allclose(w.SparsePull(2, rows[:1])[0], after[0], atol=1e-5)
+w.BarrierWorker()
 # SSP: nobody may run more than 1 clock ahead of the slowest
 w.ssp_init(rank, nrank, 1)
 import time

@@ -44,8 +44,12 @@ def _launch_pp(mode, case, timeout=600):
     cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2',
            '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
            os.path.join(ROOT, 'tests', 'pp_worker.py'), mode, case]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=dict(os.environ, OMP_NUM_THREADS='2'))
-    assert r.returncode == 0 and r.stdout.count('OK') == 2, r.stdout[-2000:] + r.stderr[-4000:]
+    import tempfile
+    with tempfile.TemporaryDirectory() as ck:           # gpipe / left also do a per-rank checkpoint round trip
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout,
+                           env=dict(os.environ, OMP_NUM_THREADS='2', HETU_TEST_CKPT_DIR=ck))
+    want = 4 if case in ('gpipe', 'left') else 2
+    assert r.returncode == 0 and r.stdout.count('OK') == want, r.stdout[-2000:] + r.stderr[-4000:]
 
 
 @pytest.mark.parametrize('case', ['gpipe', 'pipedream', 'left', 'right', 'middle', 'sp'])
