@@ -98,27 +98,9 @@ HETU_API int hetu_symm_barrier(void* const* flag_ptrs, int rank, int world, void
     return 0;
 }
 
-// In multi-CTA collectives CTA 0 runs the cross-GPU barrier and releases the other CTAs through
-// a local gate: gate[0] = collectives completed, gate[1] = the same count as of the end of the
-// previous collective kernel (stable while this kernel runs), gate[2] = exit counter.  All CTAs
-// must be co-resident: grids are capped at 148 x 2.
-__device__ __forceinline__ void barrier_then_release(FlagPtrs flags, int rank, int world, unsigned* epoch,
-                                                     unsigned* gate) {
-    if (blockIdx.x == 0) {
-        cross_gpu_barrier(flags, rank, world, epoch);
-        if (threadIdx.x == 0) {
-            __threadfence();
-            atomicExch(gate, ((volatile unsigned*)gate)[1] + 1u);
-        }
-    } else {
-        if (threadIdx.x == 0) {
-            unsigned committed = ((volatile unsigned*)gate)[1];
-            while (((volatile unsigned*)gate)[0] == committed) __nanosleep(40);
-            __threadfence();
-        }
-        __syncthreads();
-    }
-}
+// Opening barrier of the multi-CTA collectives: "every rank's send data is in place".  It runs as the 1-CTA
+// symm_barrier_kernel queued right before the collective on the same stream (open_collective below), so no CTA of the
+// collective ever spins on another CTA of its own grid - the grid makes progress whatever else occupies the SMs.
 // Every CTA calls this last.  The final CTA to leave runs a second cross-GPU barrier - "every
 // rank has finished reading / its stores have landed" - so the buffers may be reused by the next
 // collective without double buffering (CUDA-graph replays bake buffer addresses in), then
@@ -202,7 +184,6 @@ __device__ __forceinline__ float opt_apply(int kind, float pv, float gv, float* 
 __global__ void __launch_bounds__(256) symm_allreduce_kernel(PeerPtrs arenas, FlagPtrs flags, int rank, int world,
                                                              unsigned* epoch, unsigned* gate, long long n,
                                                              float* __restrict__ out) {
-    barrier_then_release(flags, rank, world, epoch, gate);
     long long n4 = n >> 2;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -225,7 +206,6 @@ __global__ void __launch_bounds__(256) symm_allreduce_opt_kernel(PeerPtrs arenas
                                                                  const float* __restrict__ lr_p,
                                                                  const long long* __restrict__ step_p, float h0, float h1,
                                                                  float h2, float h3, float l2reg) {
-    barrier_then_release(flags, rank, world, epoch, gate);
     float lr = *lr_p;
     float b1t = 1.f, b2t = 1.f;
     if (kind >= OPT_ADAM) {
@@ -258,6 +238,7 @@ HETU_API int hetu_symm_allreduce(void* const* arena_ptrs, size_t byte_off, void*
     if (fill_flags(fp, flag_ptrs, world)) return -1;
     PeerPtrs pp;
     fill_peers(pp, arena_ptrs, world, byte_off);
+    symm_barrier_kernel<<<1, 32, 0, s>>>(fp, rank, world, (unsigned*)epoch);   // opening barrier (see above)
     symm_allreduce_kernel<<<coop_grid((n + 3) / 4), 256, 0, s>>>(pp, fp, rank, world, (unsigned*)epoch, (unsigned*)gate, n, out);
     HETU_CHECK_LAUNCH("hetu_symm_allreduce");
     return 0;
@@ -288,6 +269,7 @@ HETU_API int hetu_symm_allreduce_opt(void* const* arena_ptrs, size_t byte_off, v
     }
     long long total = 0;
     for (int i = 0; i < ntensors; ++i) total += sizes[i];
+    symm_barrier_kernel<<<1, 32, 0, s>>>(fp, rank, world, (unsigned*)epoch);   // opening barrier (see above)
     symm_allreduce_opt_kernel<<<coop_grid(total), 256, 0, s>>>(pp, fp, rank, world, (unsigned*)epoch, (unsigned*)gate, tl,
                                                                 kind, lr_p, (const long long*)step_p, h0, h1, h2, h3, l2reg);
     HETU_CHECK_LAUNCH("hetu_symm_allreduce_opt");
@@ -303,7 +285,6 @@ __global__ void __launch_bounds__(256) symm_exchange_kernel(const float* __restr
                                                             int rank, int world, unsigned* epoch, unsigned* gate,
                                                             long long chunk, int same_chunk) {
     // barrier 1: every peer has consumed the previous contents of its receive buffer
-    barrier_then_release(flags, rank, world, epoch, gate);
     long long chunk4 = chunk >> 2;
     long long total4 = chunk4 * world;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (long long)gridDim.x * blockDim.x) {
@@ -325,6 +306,7 @@ HETU_API int hetu_symm_exchange(const float* send, void* const* recv_ptrs, size_
     fill_peers(pp, recv_ptrs, world, byte_off);
     int grid = coop_grid(chunk / 4 * world);
     if (grid > kNumSMs) grid = kNumSMs * 2;
+    symm_barrier_kernel<<<1, 32, 0, s>>>(fp, rank, world, (unsigned*)epoch);   // opening barrier (see above)
     symm_exchange_kernel<<<grid, 256, 0, s>>>(send, pp, fp, rank, world, (unsigned*)epoch, (unsigned*)gate, chunk, same_chunk);
     HETU_CHECK_LAUNCH("hetu_symm_exchange");
     return 0;
@@ -336,7 +318,6 @@ HETU_API int hetu_symm_exchange(const float* send, void* const* recv_ptrs, size_
 __global__ void __launch_bounds__(256) symm_reduce_scatter_kernel(PeerPtrs arenas, FlagPtrs flags, int rank, int world,
                                                                   unsigned* epoch, unsigned* gate, long long chunk,
                                                                   float* __restrict__ out) {
-    barrier_then_release(flags, rank, world, epoch, gate);
     long long n4 = chunk >> 2;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -355,6 +336,7 @@ HETU_API int hetu_symm_reduce_scatter(void* const* arena_ptrs, size_t byte_off, 
     if (fill_flags(fp, flag_ptrs, world)) return -1;
     PeerPtrs pp;
     fill_peers(pp, arena_ptrs, world, byte_off);
+    symm_barrier_kernel<<<1, 32, 0, s>>>(fp, rank, world, (unsigned*)epoch);   // opening barrier (see above)
     symm_reduce_scatter_kernel<<<coop_grid(chunk / 4), 256, 0, s>>>(pp, fp, rank, world, (unsigned*)epoch, (unsigned*)gate, chunk, out);
     HETU_CHECK_LAUNCH("hetu_symm_reduce_scatter");
     return 0;

@@ -8,8 +8,10 @@ CuSparseCsrmm.cu).
 
 Here every dense product is ``hetu_gemm`` (csrc/gemm_sm100.cu): a
 warp-specialised tcgen05 kernel - TMA loads into 128B-swizzled shared memory,
-``tcgen05.mma kind::tf32`` (or ``kind::f16`` for bf16 storage) accumulating in
-TMEM, epilogue (alpha/beta/bias/activation) read back with ``tcgen05.ld``.  All
+``tcgen05.mma kind::tf32`` accumulating in TMEM, epilogue (alpha/beta/bias/activation) read back with
+``tcgen05.ld``.  ``set_matmul_precision('bf16' | 'fp16')`` routes large products through
+``hetu_gemm_f16`` (csrc/gemm_f16_sm100.cu): operands converted to 16 bit (and to K-major) in one pass,
+``tcgen05.mma kind::f16`` with fp32 accumulation, fp32 result - storage and master weights stay fp32.  All
 four transpose combinations are served by K-major / MN-major shared-memory
 descriptors, no operand is physically transposed.  Shapes TMA cannot describe
 (row pitch not a multiple of 16 B, e.g. the 13-feature WDL input) and the
@@ -28,12 +30,13 @@ from ..ndarray import ND_Sparse_Array
 
 ACT_NONE, ACT_RELU, ACT_GELU, ACT_SIGMOID = 0, 1, 2, 3
 _PRECISION = {'mode': os.environ.get('HETU_MATMUL_PRECISION', 'tf32')}
-_MODE_CODE = {'tf32': 0, 'fp32': 1, 'bf16': 3}
+_MODE_CODE = {'tf32': 0, 'fp32': 1, 'bf16': 3, 'fp16': 4}
 
 
 def set_matmul_precision(mode: str) -> None:
-    """'tf32' (default: tcgen05 kind::tf32, fp32 accumulate), 'fp32' (FFMA, exact)
-    or 'bf16' (operands rounded to bf16 on the fly, kind::f16)."""
+    """'tf32' (default: tcgen05 kind::tf32, fp32 accumulate), 'fp32' (FFMA, exact), 'bf16' / 'fp16' (operands
+    rounded to 16 bit on the fly, tcgen05 kind::f16, fp32 accumulate; products too small for the tensor-core
+    path run as tf32)."""
     assert mode in _MODE_CODE
     _PRECISION['mode'] = mode
 
@@ -76,6 +79,17 @@ def gemm(a: torch.Tensor, b: torch.Tensor, trans_a=False, trans_b=False, bias=No
     if bias is not None:
         bias = bias.reshape(-1).contiguous()
         assert bias.numel() == bn
+    mode = _PRECISION['mode']
+    if mode in ('bf16', 'fp16') and float(am) * bn * ak * batch >= float(1 << 25) and am >= 64 and bn >= 8 and ak >= 32 \
+            and (batch == 1 or (sa != 0 and sb != 0)):
+        kp = (ak + 7) // 8 * 8
+        h = torch.bfloat16 if mode == 'bf16' else torch.float16
+        a16 = torch.empty(batch * am * kp, dtype=h, device=a.device)
+        b16 = torch.empty(batch * bn * kp, dtype=h, device=a.device)
+        L.call('gemm_f16', L.p(a), L.p(b), L.p(c), L.p(bias), L.p(a16), L.p(b16), L.c_int(am), L.c_int(bn), L.c_int(ak),
+               L.c_int(int(trans_a)), L.c_int(int(trans_b)), L.c_int(batch), L.c_i64(sa), L.c_i64(sb), L.c_i64(am * bn),
+               L.c_f32(alpha), L.c_f32(beta), L.c_int(act), L.c_int(1 if mode == 'bf16' else 0), L.stream_ptr(a.device))
+        return c
     L.call('gemm', L.p(a), L.p(b), L.p(c), L.p(bias), L.c_int(am), L.c_int(bn), L.c_int(ak),
            L.c_int(int(trans_a)), L.c_int(int(trans_b)), L.c_int(batch), L.c_i64(sa), L.c_i64(sb),
            L.c_i64(am * bn), L.c_f32(alpha), L.c_f32(beta), L.c_int(act),

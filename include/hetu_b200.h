@@ -80,6 +80,14 @@ int hetu_cumsum_cols(const float* x, float* out, size_t T, size_t E, float bias,
 int hetu_gemm(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, int transA,
               int transB, int batch, long long sA, long long sB, long long sC, float alpha, float beta, int act,
               int mode, cudaStream_t s);
+/* 16-bit operand products (csrc/gemm_f16_sm100.cu): A / B fp32 in memory, converted (and made K-major) into the caller's
+ * scratch a16 / b16 (hetu_gemm_f16_scratch_elems(rows, K, batch) 2-byte elements each), multiplied with tcgen05.mma
+ * kind::f16 (half_kind 0 = fp16, 1 = bf16), fp32 accumulation and result.  No half GEMM exists in the reference
+ * (src/ops/MatrixMult.cu is cublasSgemm). */
+long long hetu_gemm_f16_scratch_elems(int rows, int K, int batch);
+int hetu_gemm_f16(const float* A, const float* B, float* C, const float* bias, void* a16, void* b16, int M, int N, int K,
+                  int transA, int transB, int batch, long long sA, long long sB, long long sC, float alpha, float beta,
+                  int act, int half_kind, cudaStream_t s);
 int hetu_csr_spmm(const float* val, const int* rowptr, const int* colidx, const float* dense, float* out,
                   int nrow, int n, int trans, cudaStream_t s);
 

@@ -397,3 +397,44 @@ def test_fused_attention_gpu(L):
     for got, ref in zip(res, [o.detach(), tq.grad, tk.grad, tv.grad]):
         ref = ref.numpy()
         assert np.abs(got - ref).max() / (np.abs(ref).max() + 1e-9) < 5e-3    # tf32 operands
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('mode,tol', [('bf16', 2e-2), ('fp16', 4e-3)])
+@pytest.mark.parametrize('m,n,k,tA,tB', [(256, 256, 512, False, False), (384, 200, 1000, True, False),
+                                          (512, 96, 136, False, True), (130, 520, 264, True, True)])
+def test_gemm_16bit_operands_match_fp32_reference(mode, tol, m, n, k, tA, tB):
+    """hetu_gemm_f16 (tcgen05 kind::f16, csrc/gemm_f16_sm100.cu) against the plain fp32 product; reference op:
+    src/ops/MatrixMult.cu:22-26."""
+    import torch
+    from hetu_61a7_b200.ops import linalg
+    dev = torch.device('cuda', 0)
+    g = torch.Generator().manual_seed(m + n + k)
+    a = torch.randn((k, m) if tA else (m, k), generator=g).to(dev)
+    b = torch.randn((n, k) if tB else (k, n), generator=g).to(dev)
+    bias = torch.randn(n, generator=g).to(dev)
+    ref = torch.relu((a.t() if tA else a).double() @ (b.t() if tB else b).double() + bias.double())
+    linalg.set_matmul_precision(mode)
+    try:
+        out = linalg.gemm(a, b, tA, tB, bias=bias, act=linalg.ACT_RELU)
+    finally:
+        linalg.set_matmul_precision('tf32')
+    scale = ref.abs().max().item()
+    assert (out.double() - ref).abs().max().item() <= tol * scale
+
+
+@pytest.mark.gpu
+def test_gemm_16bit_batched():
+    import torch
+    from hetu_61a7_b200.ops import linalg
+    dev = torch.device('cuda', 0)
+    g = torch.Generator().manual_seed(5)
+    a = torch.randn(4, 256, 320, generator=g).to(dev)
+    b = torch.randn(4, 320, 192, generator=g).to(dev)
+    linalg.set_matmul_precision('bf16')
+    try:
+        out = linalg.gemm(a, b)
+    finally:
+        linalg.set_matmul_precision('tf32')
+    ref = a.double() @ b.double()
+    assert (out.double() - ref).abs().max().item() <= 2e-2 * ref.abs().max().item()
