@@ -341,3 +341,64 @@ HETU_API int hetu_symm_reduce_scatter(void* const* arena_ptrs, size_t byte_off, 
     HETU_CHECK_LAUNCH("hetu_symm_reduce_scatter");
     return 0;
 }
+
+// ============================================================================================
+// NVLS collectives: the buffers are mapped through an NVSwitch multicast object (parallel/symm.py
+// MulticastBuffer), so ONE instruction addresses all ranks' copies - multimem.ld_reduce returns the sum over
+// the ranks computed in the switch, multimem.st writes every copy.  reference call sites:
+// python/hetu/gpu_ops/AllReduceCommunicate.py:15-44, BroadcastCommunicate.py:17-20, ReduceCommunicate.py:15-19
+// (ncclAllReduce / ncclBroadcast / ncclReduce on a side stream).
+//   all-reduce: rank r reduces slice r of the buffer in the switch and multicasts the result back into every rank's
+//               copy (two NVLink traversals per element, no intermediate buffer, every replica bit-identical);
+//   broadcast : the root multicasts its data into every copy;
+//   reduce    : the root reads the switch-reduced sum.
+// Each kernel is bracketed by the 1-CTA cross-GPU barrier kernel (launched by the host entry on the same stream).
+__device__ __forceinline__ float4 mm_ld_reduce4(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mm_st4(float* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+// mode 0: all-reduce in place (slice `rank` of [0, n4)); 1: broadcast src -> every copy; 2: reduce -> out (root only)
+__global__ void __launch_bounds__(256) nvls_collective_kernel(float* mc, const float* __restrict__ src, float* __restrict__ out,
+                                                              long long n4, int rank, int world, int mode, float scale) {
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+    if (mode == 0) {
+        const long long per = (n4 + world - 1) / world, lo = per * rank, hi = lo + per < n4 ? lo + per : n4;
+        for (long long i = lo + tid; i < hi; i += nth) {
+            float4 v = mm_ld_reduce4(mc + 4 * i);
+            v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+            mm_st4(mc + 4 * i, v);
+        }
+    } else if (mode == 1) {
+        for (long long i = tid; i < n4; i += nth) mm_st4(mc + 4 * i, __ldg(reinterpret_cast<const float4*>(src) + i));
+    } else {
+        for (long long i = tid; i < n4; i += nth) {
+            float4 v = mm_ld_reduce4(mc + 4 * i);
+            v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+            reinterpret_cast<float4*>(out)[i] = v;
+        }
+    }
+    __threadfence_system();
+}
+
+HETU_API int hetu_nvls_collective(void* mc_ptr, const float* src, float* out, long long n, int mode, int root, float scale,
+                                  void* const* flag_ptrs, int rank, int world, void* epoch, cudaStream_t s) {
+    if (n % 4 != 0 || mc_ptr == nullptr) { hetu_set_error("hetu_nvls_collective: needs a multicast mapping and n %% 4 == 0"); return -1; }
+    FlagPtrs fp;
+    if (fill_flags(fp, flag_ptrs, world)) return -1;
+    const long long n4 = n / 4;
+    symm_barrier_kernel<<<1, 32, 0, s>>>(fp, rank, world, (unsigned*)epoch);          // every rank's input is in its copy
+    const bool active = mode == 0 || rank == root;
+    if (active) {
+        const long long work = mode == 0 ? (n4 + world - 1) / world : n4;
+        nvls_collective_kernel<<<coop_grid(work), 256, 0, s>>>((float*)mc_ptr, src, out, n4, rank, world, mode, scale);
+    }
+    symm_barrier_kernel<<<1, 32, 0, s>>>(fp, rank, world, (unsigned*)epoch);          // results have landed everywhere
+    HETU_CHECK_LAUNCH("hetu_nvls_collective");
+    return 0;
+}

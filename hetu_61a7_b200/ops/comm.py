@@ -156,6 +156,11 @@ class BroadcastCommunicateOp(_CommOp):
         comm = _comm_of(self)
         if v.device.type == 'meta' or not comm.multi:
             return v
+        eng = _symm_engine(self)
+        if eng is not None and v.is_cuda:                # NVLS: the root's multimem.st writes every rank's copy
+            out = eng.broadcast(v, self.root, key=('bcast', self.id))
+            if out is not None:
+                return out
         out = v.clone()
         comm.broadcast(out, self.root)
         return out
@@ -174,6 +179,11 @@ class ReduceCommunicateOp(_CommOp):
         comm = _comm_of(self)
         if v.device.type == 'meta' or not comm.multi:
             return v
+        eng = _symm_engine(self)
+        if eng is not None and v.is_cuda:                # NVLS: the root reads the sum the switch computed
+            out = eng.reduce(v, self.root, key=('reduce', self.id))
+            if out is not None:
+                return out
         out = v.clone()
         comm.reduce(out, self.root)
         return out

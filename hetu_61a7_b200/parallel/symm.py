@@ -200,7 +200,39 @@ class SymmEngine(object):
         L.call('symm_barrier', self.flags.ptrs, L.c_int(self.rank), L.c_int(self.world), L.p(self.epoch),
                self._stream())
 
+    # -- NVLS (in-switch) collectives ------------------------------------------------------------
+    def _nvls(self, t: torch.Tensor, key, mode: int, root: int = 0, scale: float = 1.0) -> Optional[torch.Tensor]:
+        """mode 0 all-reduce, 1 broadcast from root, 2 reduce to root (csrc/collectives.cu hetu_nvls_collective).
+        None when the tensor does not qualify (no multicast mapping, numel % 4, not fp32)."""
+        n = t.numel()
+        if t.dtype != torch.float32 or n % 4 or n == 0:
+            return None
+        buf = self.mc_buffer((key, 'nvls'), n * 4)
+        if buf is None:
+            return None
+        t = t.contiguous()
+        local = buf.tensor(numel=n)
+        if mode != 1:
+            local.copy_(t.reshape(-1))                   # this rank's contribution, in its copy of the buffer
+        out = torch.empty_like(t) if mode == 2 else None
+        L.call('nvls_collective', ctypes.c_void_p(buf.mc_ptr), L.p(t if mode == 1 else None), L.p(out), L.c_i64(n),
+               L.c_int(mode), L.c_int(root), L.c_f32(scale), self.flags.ptrs, L.c_int(self.rank), L.c_int(self.world),
+               L.p(self.epoch), self._stream())
+        if mode == 2:
+            return out if self.rank == root else t.clone()
+        return local.view(t.shape).clone()
+
+    def broadcast(self, t: torch.Tensor, root: int = 0, key='bcast') -> Optional[torch.Tensor]:
+        return self._nvls(t, (key, tuple(t.shape)), 1, root)
+
+    def reduce(self, t: torch.Tensor, root: int = 0, key='reduce') -> Optional[torch.Tensor]:
+        return self._nvls(t, (key, tuple(t.shape)), 2, root)
+
     def allreduce(self, t: torch.Tensor, key='allreduce') -> torch.Tensor:
+        if os.environ.get('HETU_NVLS_ALLREDUCE', '1') == '1' and t.numel() * 4 >= (1 << 16):
+            out = self._nvls(t, (key, tuple(t.shape)), 0)
+            if out is not None:
+                return out
         t = t.contiguous()
         n = t.numel()
         nbytes = n * 4

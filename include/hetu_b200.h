@@ -240,6 +240,11 @@ int hetu_symm_alloc(size_t bytes, void** ptr, void* handle64);
 int hetu_symm_open(const void* handle64, void** ptr);
 int hetu_symm_close(void* ptr);
 int hetu_symm_free(void* ptr);
+/* NVLS collectives on a multicast-mapped symmetric buffer (parallel/symm.py MulticastBuffer): mode 0 all-reduce in place
+ * (multimem.ld_reduce of the rank's slice + multimem.st of the result), 1 broadcast of src from root, 2 reduce into out on
+ * root.  reference: gpu_ops/AllReduceCommunicate.py:15-44, BroadcastCommunicate.py:17-20, ReduceCommunicate.py:15-19. */
+int hetu_nvls_collective(void* mc_ptr, const float* src, float* out, long long n, int mode, int root, float scale,
+                         void* const* flag_ptrs /*host array*/, int rank, int world, void* epoch, cudaStream_t s);
 int hetu_symm_barrier(void* const* flag_ptrs, int rank, int world, void* epoch, cudaStream_t s);
 int hetu_pack_tensors(int ntensors, void* const* srcs, const long long* offsets, const long long* sizes, float* dst,
                       float scale, cudaStream_t s);

@@ -50,6 +50,22 @@ if gpu:
     check('symm alltoall big', eng.alltoall(big, key='t_a2ab').clone(), comm.alltoall(big))
     refb = big.clone(); comm.allreduce(refb)
     check('symm allreduce big', eng.allreduce(big, key='t_arb'), refb, rtol=1e-4, atol=1e-4)
+    # NVLS: in-switch reduction / multicast (falls back to None where the fabric has no multicast)
+    if eng.mc_buffer('probe', 4096) is not None:
+        for it in range(2):
+            check('nvls allreduce %d' % it, eng._nvls(big, 't_nvls_ar', 0), refb, rtol=1e-4, atol=1e-4)
+        bsrc = big * (rank + 1)
+        want = bsrc.clone(); comm.broadcast(want, 1 % nrank)
+        check('nvls broadcast', eng.broadcast(bsrc, 1 % nrank, key='t_nvls_b'), want)
+        red = eng.reduce(big, 0, key='t_nvls_r')
+        if rank == 0:
+            check('nvls reduce', red, refb, rtol=1e-4, atol=1e-4)
+        os.environ['HETU_NVLS_ALLREDUCE'] = '0'
+        check('peer-load allreduce (NVLS off)', eng.allreduce(big, key='t_arb2'), refb, rtol=1e-4, atol=1e-4)
+        os.environ['HETU_NVLS_ALLREDUCE'] = '1'
+        log('ok NVLS collectives')
+    else:
+        log('NVLS multicast not available on this fabric: skipped')
 
 
 # ---------------------------------------------- data-parallel equivalence (graph level)
