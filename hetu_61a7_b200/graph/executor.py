@@ -98,7 +98,7 @@ class HetuConfig(object):
         'param_allreduce_group', 'placeholder_to_arr_map', 'gpipe', 'pipedream', 'dynamic_memory',
         'dist_strategy', 'pipeline', 'use_preduce', 'overlap', 'use_nccl_collectives', 'symm',
         'fuse_dp_update', 'use_cuda_graph', 'dp_rank', 'dp_nrank', 'mp_index', 'shard_dataloaders',
-        'all_forward_nodes', 'lcm_dp_nrank', 'pp_rank', 'pp_nrank', 'stage_ranks', 'memory_pool',
+        'all_forward_nodes', 'lcm_dp_nrank', 'min_dp_nrank', 'pp_rank', 'pp_nrank', 'stage_ranks', 'memory_pool',
         'timing', 'dropped_eval_nodes', '_running_name',
     ]
 
@@ -175,6 +175,7 @@ class HetuConfig(object):
         self.mp_index = 0
         self.pp_rank, self.pp_nrank, self.stage_ranks = 0, 1, None
         self.all_forward_nodes, self.lcm_dp_nrank = None, 1
+        self.min_dp_nrank = None
 
         # ---- this process's device ----------------------------------------------------
         if context_launch:

@@ -152,25 +152,65 @@ class _PipeBase(SubExecutor):
         return out
 
 
+def schedule_for_different_dp(dp_rank: int, dp_nrank: int, min_dp_nrank: int):
+    """Which micro-batches a replica takes when its stage has MORE data-parallel replicas than the narrowest stage of
+    the pipeline (reference pipeline_subexecutor.py:83-106).  The narrow stages emit ``min_dp_nrank`` micro-batches
+    per tick, handed round-robin to the ``dp_nrank`` replicas of the wide stage; the pattern repeats after
+    ``dp_nrank / gcd(dp_nrank, min_dp_nrank)`` ticks.  [True] when the degrees are equal."""
+    if dp_nrank <= min_dp_nrank:
+        return [True]
+    a, b = dp_nrank, min_dp_nrank
+    while b:
+        a, b = b, a % b
+    cycle = dp_nrank // a
+    schedule, index = [], dp_rank
+    while len(schedule) < cycle:
+        if index < min_dp_nrank:
+            schedule.append(True)
+            index = index + dp_nrank - min_dp_nrank
+        else:
+            schedule.append(False)
+            index -= min_dp_nrank
+    return schedule
+
+
 class SubExecutor4Gpipe(_PipeBase):
-    """All micro-batch forwards, then all backwards, gradients accumulated, one optimizer step."""
+    """All micro-batch forwards, then all backwards, gradients accumulated, one optimizer step.  A replica of a stage
+    that is wider (more data-parallel replicas) than the narrowest stage runs only the micro-batches of its turn
+    (``schedule_for_different_dp``); the gradient all-reduce at the end of the batch puts the replicas' shares together."""
+
+    def _turns(self, M):
+        cfg = self.config
+        sched = schedule_for_different_dp(getattr(cfg, 'dp_rank', 0) or 0, getattr(cfg, 'dp_nrank', 1) or 1,
+                                          getattr(cfg, 'min_dp_nrank', None) or (getattr(cfg, 'dp_nrank', 1) or 1))
+        assert M % len(sched) == 0, ('the number of micro-batches (%d) must be a multiple of the schedule length (%d), '
+                                     'so that every replica reaches the gradient all-reduce' % (M, len(sched)))
+        start = getattr(self, '_turn_index', 0)
+        self._turn_index = (start + M) % len(sched)
+        return [sched[(start + m) % len(sched)] for m in range(M)]
 
     def run(self, eval_node_list=[], feed_dict={}, convert_to_numpy_ret_vals=False, batch_num=None, **kwargs):
         M = batch_num or 1
         eval_nodes = list(eval_node_list) if eval_node_list else getattr(self, 'result_nodes', self.eval_node_list)
         self._pre_step()
+        turns = self._turns(M)
         all_vals = []
         for m in range(M):
+            if not turns[m]:
+                all_vals.append(None)
+                continue
             vals = self._feeds(feed_dict, m)
             self._run_nodes(self.forward_nodes, vals)
             all_vals.append(vals)
         acc = None
         for m in range(M):
+            if all_vals[m] is None:
+                continue
             self._run_nodes(self.backward_nodes, all_vals[m])
             acc = self._accumulate(acc, self._grads_of(all_vals[m]))
         self.opt.compute(acc)
         self.step_count += 1
-        return self._results(eval_nodes, all_vals, convert_to_numpy_ret_vals)
+        return self._results(eval_nodes, [v for v in all_vals if v is not None], convert_to_numpy_ret_vals)
 
 
 class SubExecutor4Pipedream(_PipeBase):

@@ -86,6 +86,7 @@ def assign_placement(config, eval_nodes) -> None:
     mine = lambda n: isinstance(n, OptimizerOp) or n.raw_ctx is None or me in _ranks(n.raw_ctx)   # noqa: E731
     my_stage_ids = [i for i, s in enumerate(stages) if me in _ranks(s)]
     config.pp_nrank = len(stages)
+    config.min_dp_nrank = min(s.worker_num for s in stages)      # narrowest stage: sets the micro-batch turns of the wider ones
     config.pp_rank = my_stage_ids[0] if my_stage_ids else 0
     for s in stages:
         for j, k, r in _positions(s):
@@ -115,6 +116,26 @@ def assign_placement(config, eval_nodes) -> None:
         members = w if isinstance(w, tuple) else (w,)
         return members[k % len(members)].device_id
 
+    def source_ranks(u, recv_rank):
+        """All ranks of u's stage that feed ``recv_rank``.  Stages of equal width pair up position-wise; a WIDER
+        producer stage fans in (the replicas j with j % C == i take turns, micro-batch by micro-batch, in replica
+        order - parallel/pipeline.py schedule_for_different_dp); a narrower one is covered by source_rank."""
+        cons = [s for s in stages if recv_rank in _ranks(s) and s != u.raw_ctx]
+        if not cons:
+            return [source_rank(u, recv_rank)]
+        cons_stage = cons[0]
+        P, C = u.raw_ctx.worker_num, cons_stage.worker_num
+        if P <= C:
+            return [source_rank(u, recv_rank)]
+        j, k = next(((j, k) for j, k, r in _positions(cons_stage) if r == recv_rank), (0, 0))
+        out = []
+        for jj in range(P):
+            if jj % C == j:
+                w = u.raw_ctx.workers[jj]
+                members = w if isinstance(w, tuple) else (w,)
+                out.append(members[k % len(members)].device_id)
+        return out
+
     for i, n in enumerate(topo):
         n.global_order = float(i)
     # forward / backward side of every node, decided ONCE on the global graph so that all ranks agree
@@ -140,25 +161,34 @@ def assign_placement(config, eval_nodes) -> None:
             # consumer side
             if me in v_ranks and me not in u_ranks:
                 if u not in recv_cache:
-                    src = source_rank(u, me)
-                    rv = pipeline_receive_op(src, config.nccl_comm, use_indexed_slices=u.use_indexed_slices,
-                                             ctx=v.raw_ctx)
+                    srcs = source_ranks(u, me)
+                    src = srcs[0]
+                    rv = pipeline_receive_op(src if len(srcs) == 1 else tuple(srcs), config.nccl_comm,
+                                             use_indexed_slices=u.use_indexed_slices, ctx=v.raw_ctx)
                     rv.ctx = config.context
-                    rv.name = 'recv_%s_from%d' % (u.name, src)
+                    rv.name = 'recv_%s_from%s' % (u.name, '_'.join(str(x) for x in srcs))
                     rv.global_order = v.global_order - 0.5
                     rv.pp_forward = getattr(v, 'pp_forward', True)
                     recv_cache[u] = rv
                 v.inputs[idx] = recv_cache[u]
             # producer side
             if me in u_ranks:
-                for r in v_ranks:
-                    if r not in u_ranks and source_rank(u, r) == me and (u, r) not in sent:
-                        sent.add((u, r))
-                        sd = pipeline_send_op(u, r, config.nccl_comm, ctx=u.raw_ctx)
-                        sd.name = 'send_%s_to%d' % (u.name, r)
-                        sd.global_order = v.global_order - 0.25
-                        sd.pp_forward = getattr(v, 'pp_forward', True)
-                        sends.append((topo.index(v), sd))
+                targets = [r for r in v_ranks if r not in u_ranks and me in source_ranks(u, r)]
+                if len(targets) > 1 and v.raw_ctx.worker_num > u.raw_ctx.worker_num:
+                    # a wider consumer stage: ONE send node that hands the micro-batches out round-robin, in replica
+                    # order (the replicas take them in turns)
+                    groups = [tuple(targets)]
+                else:
+                    groups = [(r,) for r in targets]
+                for grp in groups:
+                    if (u, grp) in sent:
+                        continue
+                    sent.add((u, grp))
+                    sd = pipeline_send_op(u, grp[0] if len(grp) == 1 else grp, config.nccl_comm, ctx=u.raw_ctx)
+                    sd.name = 'send_%s_to%s' % (u.name, '_'.join(str(x) for x in grp))
+                    sd.global_order = v.global_order - 0.25
+                    sd.pp_forward = getattr(v, 'pp_forward', True)
+                    sends.append((topo.index(v), sd))
     # this rank evaluates: its own eval nodes + its sends, interleaved in topological position so
     # that both sides of every p2p pair issue them in the same relative order
     my_eval = [n for n in eval_nodes if mine(n)]

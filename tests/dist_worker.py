@@ -111,6 +111,29 @@ for opt_name, mk in (('sgd', lambda: ht.optim.SGDOptimizer(0.1 / nrank)), ('adam
         for a, b, n in zip(got, [tW1, tb1, tW2], ['W1', 'b1', 'W2']):
             check('dp %s %s %s' % (opt_name, engine, n), a, b.detach(), rtol=2e-3, atol=2e-5)
 
+# ---------------------------------------- 1.5-D distributed GCN layer: forward and backward against the dense product
+if True:
+    rs = np.random.RandomState(11)
+    Nn, Fi, Fo = 6 * nrank + 3, 7, 5                          # the last block-row is shorter than the others
+    Ad = rs.rand(Nn, Nn).astype(np.float32) * (rs.rand(Nn, Nn) < 0.4)
+    Ad = ((Ad + Ad.T) / 2).astype(np.float32)                 # symmetric, as a normalised adjacency is
+    Hd, Wd = rs.randn(Nn, Fi).astype(np.float32), rs.randn(Fi, Fo).astype(np.float32)
+    per = -(-Nn // nrank)
+    lo, hi = rank * per, min(Nn, (rank + 1) * per)
+    adj_n = ht.Variable('adj_blk', trainable=False)
+    h_n, w_n = ht.Variable('h_blk', value=Hd[lo:hi].copy(), ctx=ctx), ht.Variable('w_gcn', value=Wd.copy(), ctx=ctx)
+    z_n = ht.distgcn_15d_op(adj_n, h_n, w_n, hi - lo, Nn, nrank, 1, rank, comm, [None, None], True)
+    loss_n = ht.reduce_sum_op(ht.mul_op(z_n, z_n), [0, 1])
+    gh_n, gw_n = ht.gradients(loss_n, [h_n, w_n])
+    exg = ht.Executor([z_n, gh_n, gw_n], ctx=ctx)
+    zz, ghh, gww = [r.asnumpy() for r in exg.run(feed_dict={adj_n: torch.tensor(Ad[lo:hi]).to(dev)})]
+    tH, tW = torch.tensor(Hd, requires_grad=True), torch.tensor(Wd, requires_grad=True)
+    tz = torch.tensor(Ad) @ tH @ tW
+    (tz * tz).sum().backward()
+    check('distgcn forward', torch.tensor(zz), tz.detach()[lo:hi], rtol=1e-4, atol=1e-4)
+    check('distgcn grad H', torch.tensor(ghh), tH.grad[lo:hi], rtol=1e-3, atol=1e-3)
+    check('distgcn grad W (all-reduced)', torch.tensor(gww), tW.grad, rtol=1e-3, atol=1e-3)
+
 # -------------------------------------------------------- sharded embedding (hybrid)
 if gpu:
     V, D = 1000, 16

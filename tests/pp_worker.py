@@ -137,6 +137,41 @@ if case == 'sp':
     comm.barrier()
     print('PP %s rank %d OK' % (case, rank), flush=True)
     sys.exit(0)
+if case == 'unequal':
+    # stage 0 on one rank, stage 1 replicated on two: the replicas of the wide stage take the micro-batches in turns
+    # (schedule_for_different_dp), the narrow stage hands them out round-robin; result = plain GPipe
+    with ht.context(dev(0)):
+        x = ht.Variable('x')
+        w1 = ht.Variable('w1', value=W1.copy())
+        a = ht.relu_op(ht.matmul_op(x, w1))
+    with ht.context([dev(1), dev(2)]):
+        w2 = ht.Variable('w2', value=W2.copy())
+        a = ht.relu_op(ht.matmul_op(a, w2))
+        w3 = ht.Variable('w3', value=W3.copy())
+        y_ = ht.Variable('y_')
+        loss = ht.reduce_mean_op(ht.softmaxcrossentropy_op(ht.matmul_op(a, w3), y_), [0])
+        train = ht.optim.SGDOptimizer(0.1).minimize(loss)
+    ws = (w1, w2, w3)
+    ex = ht.Executor({'train': [loss, train]}, pipeline='gpipe', seed=0)
+    assert ex.config.min_dp_nrank == 1 and ex.config.dp_nrank == (1 if rank == 0 else 2), (ex.config.min_dp_nrank, ex.config.dp_nrank)
+    got = []
+    for step in range(3):
+        out = ex.run('train', feed_dict={x: [X[m] for m in range(4)], y_: [Y[m] for m in range(4)]}, batch_num=4)
+        if out[0] is not None:
+            got += [float(o.asnumpy()) for o in out[0]]
+    ref_l, ref_w = oracle(3, 4, per_micro_update=False)
+    assert (mine(ex, ws[0]) is not None) == (rank == 0)
+    assert (mine(ex, ws[2]) is not None) == (rank in (1, 2))
+    if rank in (1, 2):
+        mine_l = [l for s_ in range(3) for m, l in enumerate(ref_l[4 * s_:4 * s_ + 4]) if m % 2 == rank - 1]
+        assert len(got) == 6 and np.allclose(got, mine_l, rtol=2e-4, atol=1e-5), (got, mine_l)
+    for p_, r_ in zip(ws, ref_w):
+        m_ = mine(ex, p_)
+        if m_ is not None:
+            assert np.allclose(m_, r_, rtol=2e-3, atol=1e-5), (p_.name, np.abs(m_ - r_).max())
+    comm.barrier()
+    print('PP %s rank %d OK' % (case, rank), flush=True)
+    sys.exit(0)
 if case == 'gpipe':
     x, y_, loss, train, ws = build()
     ex = ht.Executor({'train': [loss, train]}, pipeline='gpipe', seed=0)

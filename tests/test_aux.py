@@ -167,3 +167,20 @@ def test_step_monitor_jsonl_and_prometheus(tmp_path):
     assert abs(rows[-1]['samples_per_second'] - 128 / 0.02) < 1e-6
     txt = urllib.request.urlopen('http://127.0.0.1:%d/metrics' % port).read().decode()
     assert 'hetu_loss{rank="0"} 0.333' in txt and 'hetu_step{rank="0"} 3.0' in txt
+
+
+def test_unequal_dp_schedule_matches_the_reference_rule():
+    """Micro-batch turns of the replicas of a stage that is wider than the narrowest stage
+    (reference pipeline_subexecutor.py:83-106)."""
+    from hetu_61a7_b200.parallel.pipeline import schedule_for_different_dp as sched
+    assert sched(0, 2, 2) == [True] and sched(1, 4, 4) == [True]
+    assert sched(0, 2, 1) == [True, False] and sched(1, 2, 1) == [False, True]
+    # 4 replicas fed by 2: two of them work per tick, every replica works every second tick
+    s4 = [sched(r, 4, 2) for r in range(4)]
+    assert s4 == [[True, False], [True, False], [False, True], [False, True]]
+    # 3 replicas fed by 2: cycle of 3 ticks, two active replicas per tick, every replica active twice per cycle
+    s3 = [sched(r, 3, 2) for r in range(3)]
+    assert all(len(s) == 3 for s in s3)
+    for t in range(3):
+        assert sum(s[t] for s in s3) == 2
+    assert all(sum(s) == 2 for s in s3)

@@ -40,21 +40,26 @@ def test_multi_gpu_symm_paths():
     _launch('gpu', min(n, 4), timeout=800)
 
 
-def _launch_pp(mode, case, timeout=600):
-    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2',
+def _launch_pp(mode, case, timeout=600, nproc=2):
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(nproc),
            '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
            os.path.join(ROOT, 'tests', 'pp_worker.py'), mode, case]
     import tempfile
     with tempfile.TemporaryDirectory() as ck:           # gpipe / left also do a per-rank checkpoint round trip
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout,
                            env=dict(os.environ, OMP_NUM_THREADS='2', HETU_TEST_CKPT_DIR=ck))
-    want = 4 if case in ('gpipe', 'left') else 2
+    want = 4 if case in ('gpipe', 'left') else nproc
     assert r.returncode == 0 and r.stdout.count('OK') == want, r.stdout[-2000:] + r.stderr[-4000:]
 
 
 @pytest.mark.parametrize('case', ['gpipe', 'pipedream', 'left', 'right', 'middle', 'sp'])
 def test_pipeline_and_model_parallel_equivalence_gloo(case):
     _launch_pp('cpu', case)
+
+
+def test_pipeline_with_unequal_data_parallel_degrees_gloo():
+    """Stage 0 on one rank, stage 1 on two replicas (reference pipeline_subexecutor.py:83-106)."""
+    _launch_pp('cpu', 'unequal', nproc=3)
 
 
 @pytest.mark.gpu
