@@ -9,4 +9,5 @@ python test_model_cnn_base.py
 run 2 test_model_cnn.py --stages 2
 run 4 test_model_cnn.py --stages 4
 run 2 test_model_cnn.py --stages 2 --pipeline gpipe
+for s in left right middle; do run 5 test_model_cnn_complex.py --split $s; done
 python validate_results.py --rtol "$RTOL" --prefix cnn_

@@ -56,6 +56,9 @@ def fuse_matmul_bias(topo: List) -> int:
             continue
         from ..ops.linalg import gemm
         mm.inputs = list(mm.inputs) + [bias]
+        if hasattr(mm, 'global_order') and getattr(bias, 'global_order', None) is not None \
+                and bias.global_order > mm.global_order:
+            bias.global_order = mm.global_order - 0.5   # placed graphs walk nodes in global order: the new input comes first
         mm.compute = (lambda input_vals, output_val=None, stream_handle=None, _m=mm:
                       gemm(input_vals[0], input_vals[1], _m.matmul_attr_trans_A, _m.matmul_attr_trans_B, bias=input_vals[2], act=_m.act))
         a.compute = (lambda input_vals, output_val=None, stream_handle=None: input_vals[0])

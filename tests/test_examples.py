@@ -81,3 +81,29 @@ def test_gnn_on_sampled_subgraphs(tmp_path):
                 '--steps', '15', '--port', str(_free_port_block())])
     accs = [float(l.rsplit(' ', 1)[1]) for l in out.splitlines() if 'held-out acc' in l]
     assert accs and max(accs) > 0.6, out[-1500:]
+
+
+def _torchrun(n, script, *args, port=0):
+    import socket
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        port = s.getsockname()[1]
+    return _run(['-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(n), '--master-addr', '127.0.0.1',
+                 '--master-port', str(port), script] + list(args), cwd=os.path.dirname(script),
+                env={'HETU_COMM_BACKEND': 'gloo', 'OMP_NUM_THREADS': '1'})
+
+
+def test_parallel_layout_examples_gloo():
+    """The DP x PP, DP + MP + PP and mixed CNN layouts of examples/runner/parallel (reference scripts of the same names)
+    run on a gloo CPU world; the CNN layout reproduces the single-device loss curve."""
+    import numpy as np
+    par = os.path.join(EX, 'runner', 'parallel')
+    out = _torchrun(4, os.path.join(par, 'gpipe_multi.py'), '--steps', '2', '--hidden', '64')
+    assert out.count('GPIPE_MULTI rank') == 4
+    out = _torchrun(5, os.path.join(par, 'data_model_pipeline_mlp.py'), '--steps', '2', '--hidden', '64')
+    assert out.count('DATA_MODEL_PIPELINE rank') == 5
+    _run([os.path.join(par, 'test_model_cnn_base.py')], cwd=par, env={'HETU_COMM_BACKEND': 'gloo'})
+    _torchrun(5, os.path.join(par, 'test_model_cnn_complex.py'), '--split', 'middle')
+    base = np.load(os.path.join(par, 'results', 'cnn_base.npy'))
+    got = np.load(os.path.join(par, 'results', 'cnn_complex_middle.npy'))
+    np.testing.assert_allclose(got, base[:len(got)], rtol=1e-5, atol=1e-6)
