@@ -255,3 +255,147 @@ HETU_API int hetu_scatter_add_rows(float* dense, const void* idx, int idx_code, 
     HETU_CHECK_LAUNCH("hetu_scatter_add_rows");
     return 0;
 }
+
+// ============================================================================================
+// Sharded table, optimizers with state (Momentum / Nesterov / AdaGrad / Adam / AdamW) applied AT THE OWNER.
+// reference: the PS server applies them per pushed row (ps-lite/include/ps/server/optimizer.h:36-357) after the
+// worker has de-duplicated its ids on the host (src/ops/OptimizersSparse.cu:54-67,287-330).
+//
+// Here: phase 1 (every rank, hetu_sparse_push_sharded): each gradient row is ADDED into the owner's accumulation
+// shard with remote vector atomics - duplicates, within a rank and across ranks, meet there, which is the
+// de-duplication - and the first toucher of a row (atomicExch on the owner's per-row flag) appends the row to the
+// owner's work list.  A cross-GPU barrier follows (host side).  Phase 2 (owner only, hetu_sparse_apply_owner):
+// one warp per listed row reads the summed gradient once, applies the optimizer to the row and its state rows,
+// clears the accumulator and the flag; the last CTA resets the list counter.
+struct OwnerPush {
+    float* acc[kMaxShards];          // [local_rows, width] accumulation shard of every rank
+    unsigned* flag[kMaxShards];      // [local_rows]
+    int* list[kMaxShards];           // work list of every rank
+    unsigned* count[kMaxShards];     // its length
+    int nshard, cap;
+};
+
+__global__ void __launch_bounds__(256) sparse_push_sharded_kernel(OwnerPush op, const void* __restrict__ idx, int idx_code,
+                                                                  const float* __restrict__ grad, size_t n, int width,
+                                                                  size_t vocab, float scale) {
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const size_t nwarp = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t i = warp; i < n; i += nwarp) {
+        const long long r = load_index(idx, idx_code, i);
+        if (r < 0 || (size_t)r >= vocab) continue;
+        const int owner = (int)(r % op.nshard);
+        const size_t local = (size_t)(r / op.nshard);
+        float* dst = op.acc[owner] + local * width;
+        const float* g = grad + i * width;
+        if ((width & 3) == 0) {
+            for (int j = lane; j < (width >> 2); j += 32) {
+                const float4 v = reinterpret_cast<const float4*>(g)[j];
+                atomicAdd(reinterpret_cast<float4*>(dst) + j, make_float4(scale * v.x, scale * v.y, scale * v.z, scale * v.w));
+            }
+        } else {
+            for (int j = lane; j < width; j += 32) atomicAdd(dst + j, scale * g[j]);
+        }
+        if (lane == 0 && atomicExch(op.flag[owner] + local, 1u) == 0u) {
+            const unsigned pos = atomicAdd(op.count[owner], 1u);
+            if ((int)pos < op.cap) op.list[owner][pos] = (int)local;
+        }
+    }
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(256) sparse_apply_owner_kernel(float* __restrict__ table, float* __restrict__ acc,
+                                                                 unsigned* __restrict__ flag, const int* __restrict__ list,
+                                                                 unsigned* __restrict__ count, unsigned* __restrict__ done,
+                                                                 float* __restrict__ s1, float* __restrict__ s2, int width, int cap,
+                                                                 const float* __restrict__ lr_p, const long long* __restrict__ step_p,
+                                                                 float h0, float h1, float h2, float h3, float l2reg) {
+    const unsigned n = min(*reinterpret_cast<volatile unsigned*>(count), (unsigned)cap);
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const size_t nwarp = ((size_t)gridDim.x * blockDim.x) >> 5;
+    const float lr = *lr_p;
+    float b1t = 1.f, b2t = 1.f;
+    if (KIND >= OPT_ADAM) {
+        const float t = (float)(*step_p);
+        b1t = 1.f - powf(h0, t);
+        b2t = 1.f - powf(h1, t);
+    }
+    for (size_t i = warp; i < n; i += nwarp) {
+        const size_t row = (size_t)list[i];
+        float* p = table + row * width;
+        float* a = acc + row * width;
+        for (int j = lane; j < width; j += 32) {
+            const float pv = p[j];
+            const float gv = a[j] + l2reg * pv;
+            a[j] = 0.f;
+            const size_t so = row * width + j;
+            if (KIND == OPT_MOMENTUM) {
+                const float v = h0 * s1[so] - lr * gv;
+                s1[so] = v;
+                p[j] = pv + v;
+            } else if (KIND == OPT_NESTEROV) {
+                const float tmp = lr * gv;
+                const float v = h0 * (s1[so] - tmp);
+                s1[so] = v;
+                p[j] = pv + v - tmp;
+            } else if (KIND == OPT_ADAGRAD) {
+                const float q = s1[so] + gv * gv;
+                s1[so] = q;
+                p[j] = pv - lr * gv / (sqrtf(q) + h0);
+            } else {
+                const float m = h0 * s1[so] + (1.f - h0) * gv;
+                const float v = h1 * s2[so] + (1.f - h1) * gv * gv;
+                s1[so] = m;
+                s2[so] = v;
+                const float upd = (m / b1t) / (sqrtf(v / b2t) + h2);
+                p[j] = (KIND == OPT_ADAM) ? pv - lr * upd : pv - lr * (upd + h3 * pv);
+            }
+        }
+        if (lane == 0) flag[row] = 0u;
+    }
+    // the last CTA to finish empties the work list for the next step
+    __shared__ bool last;
+    __syncthreads();
+    if (threadIdx.x == 0) { __threadfence(); last = atomicAdd(done, 1u) == gridDim.x - 1; }
+    __syncthreads();
+    if (last && threadIdx.x == 0) { *count = 0u; *done = 0u; }
+}
+
+HETU_API int hetu_sparse_push_sharded(void* const* acc, void* const* flag, void* const* list, void* const* count, int nshard,
+                                      int cap, const void* idx, int idx_code, const float* grad, size_t n, int width,
+                                      size_t vocab, float scale, cudaStream_t s) {
+    if (n == 0) return 0;
+    if (nshard < 1 || nshard > kMaxShards) { hetu_set_error("sparse_push_sharded: nshard %d outside [1, %d]", nshard, kMaxShards); return -1; }
+    OwnerPush op;
+    op.nshard = nshard; op.cap = cap;
+    for (int i = 0; i < kMaxShards; ++i) {
+        op.acc[i] = i < nshard ? (float*)acc[i] : nullptr;
+        op.flag[i] = i < nshard ? (unsigned*)flag[i] : nullptr;
+        op.list[i] = i < nshard ? (int*)list[i] : nullptr;
+        op.count[i] = i < nshard ? (unsigned*)count[i] : nullptr;
+    }
+    sparse_push_sharded_kernel<<<ew_grid(n * 32, 256, 16), 256, 0, s>>>(op, idx, idx_code, grad, n, width, vocab, scale);
+    HETU_CHECK_LAUNCH("hetu_sparse_push_sharded");
+    return 0;
+}
+
+HETU_API int hetu_sparse_apply_owner(int kind, float* table, float* acc, void* flag, const void* list, void* count, void* done,
+                                     float* s1, float* s2, int width, int cap, const float* lr_p, const void* step_p, float h0,
+                                     float h1, float h2, float h3, float l2reg, cudaStream_t s) {
+    const int grid = kNumSMs * 4;
+    const long long* st = (const long long*)step_p;
+#define AP(K) sparse_apply_owner_kernel<K><<<grid, 256, 0, s>>>(table, acc, (unsigned*)flag, (const int*)list, (unsigned*)count, \
+                                                                 (unsigned*)done, s1, s2, width, cap, lr_p, st, h0, h1, h2, h3, l2reg)
+    switch (kind) {
+        case OPT_MOMENTUM: AP(OPT_MOMENTUM); break;
+        case OPT_NESTEROV: AP(OPT_NESTEROV); break;
+        case OPT_ADAGRAD: AP(OPT_ADAGRAD); break;
+        case OPT_ADAM: AP(OPT_ADAM); break;
+        case OPT_ADAMW: case OPT_LAMB: AP(OPT_ADAMW); break;
+        default: hetu_set_error("hetu_sparse_apply_owner: kind %d has no state (SGD uses hetu_sparse_sgd_sharded)", kind); return -1;
+    }
+#undef AP
+    HETU_CHECK_LAUNCH("hetu_sparse_apply_owner");
+    return 0;
+}

@@ -14,6 +14,8 @@ rows with remote atomics (``hetu_sparse_sgd_sharded``) - the PS pull, push and s
 """
 from __future__ import annotations
 
+import ctypes
+
 import numpy as np
 import torch
 
@@ -68,11 +70,52 @@ class ShardedTable(object):
                L.p(out), L.c_sz(idx.numel()), L.c_int(self.width), L.c_sz(self.vocab), L.stream_ptr(self.device))
         return out
 
+    def _owner_state(self, optimizer, n_ids):
+        """Accumulation shard, per-row flags and work list (symmetric: peers write them with remote atomics) and the
+        optimizer's state shards (local) for the optimizers that are applied at the owner."""
+        st = getattr(self, '_owner', None)
+        cap = self.world * n_ids
+        if st is None or st['cap'] < cap:
+            eng, nrow, w = self.engine, self.local_rows, self.width
+            acc = eng.buffer(('embed_acc', self.name), nrow * w * 4)
+            flag = eng.buffer(('embed_flag', self.name), nrow * 4)
+            lst = eng.buffer(('embed_list', self.name, cap), cap * 4)
+            cnt = eng.buffer(('embed_cnt', self.name), 256)
+            acc.tensor(numel=nrow * w).zero_()
+            flag.tensor(dtype=torch.int32, numel=nrow).zero_()
+            cnt.tensor(dtype=torch.int32, numel=64).zero_()
+            old = st or {}
+            st = self._owner = dict(cap=cap, acc=acc, flag=flag, list=lst, cnt=cnt,
+                                    done=old.get('done', torch.zeros(1, dtype=torch.int32, device=self.device)),
+                                    s1=old.get('s1', torch.zeros((nrow, w), dtype=torch.float32, device=self.device)),
+                                    s2=old.get('s2'))
+            torch.cuda.synchronize(self.device)
+            eng.comm.barrier()
+        from ..optimizer import OPT_ADAM
+        if optimizer.kind >= OPT_ADAM and st['s2'] is None:
+            st['s2'] = torch.zeros((self.local_rows, self.width), dtype=torch.float32, device=self.device)
+        return st
+
     def apply_sparse_grad(self, ind: torch.Tensor, val: torch.Tensor, optimizer) -> None:
         from ..optimizer import OPT_SGD
         if optimizer.kind != OPT_SGD:
-            raise NotImplementedError('sharded embedding tables are updated with SGD (the reference PS '
-                                      'applies "+=" of -lr*grad as well); got %s' % optimizer.name)
+            # optimizers with state: gradients are summed at the owner (remote atomics = de-duplication across the
+            # whole job), then every owner applies the step to the rows on its work list (csrc/embedding.cu)
+            ind = ind.contiguous()
+            val = val.contiguous()
+            st = self._owner_state(optimizer, ind.numel())
+            h = optimizer.hyper()
+            L.call('sparse_push_sharded', st['acc'].ptrs, st['flag'].ptrs, st['list'].ptrs, st['cnt'].ptrs, L.c_int(self.world),
+                   L.c_int(st['cap']), L.p(ind), L.c_int(_IDX_CODE[ind.dtype]), L.p(val), L.c_sz(ind.numel()),
+                   L.c_int(self.width), L.c_sz(self.vocab), L.c_f32(1.0), L.stream_ptr(self.device))
+            self.engine.barrier()                          # every rank's pushes have landed
+            L.call('sparse_apply_owner', L.c_int(optimizer.kind), L.p(self.local), ctypes.c_void_p(st['acc'].local_ptr),
+                   ctypes.c_void_p(st['flag'].local_ptr), ctypes.c_void_p(st['list'].local_ptr),
+                   ctypes.c_void_p(st['cnt'].local_ptr), L.p(st['done']), L.p(st['s1']), L.p(st['s2']), L.c_int(self.width),
+                   L.c_int(st['cap']), L.p(optimizer.lr_t), L.p(optimizer.step_t), L.c_f32(h[0]), L.c_f32(h[1]),
+                   L.c_f32(h[2]), L.c_f32(h[3]), L.c_f32(float(optimizer.l2reg)), L.stream_ptr(self.device))
+            self.engine.barrier()                          # rows are updated and the work lists empty before the next step
+            return
         ind = ind.contiguous()
         if self.bsp == 0:
             self.engine.barrier()      # BSP: every rank has finished reading this step's rows

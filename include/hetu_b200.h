@@ -140,6 +140,16 @@ int hetu_sparse_opt(int kind, float* param, const void* idx, const float* grad, 
 int hetu_sparse_sgd_sharded(void* const* bases /*host array*/, int nshard, const void* idx, int idx_code,
                             const float* grad, size_t n, int width, size_t vocab, const float* lr_p, float scale,
                             cudaStream_t s);
+/* sharded table, optimizers with state applied at the owner: phase 1 adds every gradient row into the owner's accumulation
+ * shard (remote atomics; the first toucher lists the row), phase 2 (after a cross-GPU barrier) applies Momentum / Nesterov /
+ * AdaGrad / Adam / AdamW to the listed rows.  reference: ps-lite/include/ps/server/optimizer.h:36-357,
+ * src/ops/OptimizersSparse.cu:54-67,287-330 */
+int hetu_sparse_push_sharded(void* const* acc, void* const* flag, void* const* list, void* const* count /*host arrays*/,
+                             int nshard, int cap, const void* idx, int idx_code, const float* grad, size_t n, int width,
+                             size_t vocab, float scale, cudaStream_t s);
+int hetu_sparse_apply_owner(int kind, float* table, float* acc, void* flag, const void* list, void* count, void* done,
+                            float* s1, float* s2, int width, int cap, const float* lr_p, const void* step_p, float h0,
+                            float h1, float h2, float h3, float l2reg, cudaStream_t s);
 int hetu_scatter_add_rows(float* dense, const void* idx, int idx_code, const float* vals, size_t n, int width,
                           size_t vocab, cudaStream_t s);
 

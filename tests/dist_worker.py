@@ -163,6 +163,50 @@ if gpu:
             te -= 0.01 * te.grad
     check('sharded sgd (bsp)', tab.export_dense(), te.detach(), rtol=1e-3, atol=1e-4)
 
+# ------------------------------ sharded embedding, optimizers with state applied at the owner (Momentum, Adam)
+if gpu:
+    for opt_name in ('momentum', 'adam'):
+        V, D = 600, 16
+        table0 = np.random.RandomState(13).randn(V, D).astype(np.float32)
+        ids_all = np.random.RandomState(14).randint(0, V, (3, nrank, 8, 4))
+        ids_all[:, :, 0, 0] = 7                                   # a row every rank touches every step, twice on rank 0
+        ids_all[:, 0, 1, 1] = 7
+        emb = ht.Variable('emb_' + opt_name, value=table0.copy())
+        idn = ht.Variable('ids_' + opt_name)
+        w = ht.Variable('w_emb_' + opt_name, value=np.ones((4 * D, 1), np.float32))
+        e = ht.array_reshape_op(ht.embedding_lookup_op(emb, idn), (-1, 4 * D))
+        loss = ht.reduce_mean_op(ht.reduce_sum_op(ht.mul_op(ht.matmul_op(e, w), ht.matmul_op(e, w)), [1]), [0])
+        opt = ht.optim.MomentumOptimizer(0.01, 0.9) if opt_name == 'momentum' else ht.optim.AdamOptimizer(0.01)
+        train = opt.minimize(loss, var_list=[emb])
+        ex = ht.Executor({'train': [loss, train]}, ctx=ctx, comm_mode='Hybrid', seed=1, bsp=0)
+        tab = ex.config.placeholder_to_arr_map[emb]
+        assert getattr(tab, 'sharded', False)
+        for step in range(3):
+            ex.run('train', feed_dict={idn: ids_all[step, rank].astype(np.float32)})
+        # oracle: gradients of all ranks summed per row, the optimizer applied once to every touched row
+        P = torch.tensor(table0.copy(), dtype=torch.float64)
+        s1, s2 = torch.zeros_like(P), torch.zeros_like(P)
+        for step in range(3):
+            te = P.clone().float().requires_grad_(True)
+            tot = 0
+            for r in range(nrank):
+                ee = te[torch.tensor(ids_all[step, r])].reshape(-1, 4 * D)
+                tot = tot + (ee.sum(1) ** 2).mean()
+            tot.backward()
+            g = te.grad.double()
+            rows = torch.unique(torch.tensor(ids_all[step]).reshape(-1))
+            if opt_name == 'momentum':
+                v = 0.9 * s1[rows] - 0.01 * g[rows]
+                s1[rows] = v
+                P[rows] += v
+            else:
+                t_ = step + 1
+                m = 0.9 * s1[rows] + 0.1 * g[rows]
+                v = 0.999 * s2[rows] + 0.001 * g[rows] ** 2
+                s1[rows], s2[rows] = m, v
+                P[rows] -= 0.01 * (m / (1 - 0.9 ** t_)) / (torch.sqrt(v / (1 - 0.999 ** t_)) + opt.hyper()[2])
+        check('sharded %s at the owner' % opt_name, tab.export_dense().double(), P, rtol=2e-3, atol=2e-4)
+
 # ------------------------------------------------------------------ MoE fused vs NCCL
 if gpu:
     from hetu_61a7_b200.models.moe import moe_model
