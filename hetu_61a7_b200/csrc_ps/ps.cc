@@ -1026,6 +1026,35 @@ HPS_API int hps_query_dead_nodes(const char* sched_host, int sched_port, double 
 HPS_API int hps_is_recovery() { return g_worker && g_worker->is_recovery() ? 1 : 0; }
 HPS_API uint64_t hps_num_retransmits() { return g_worker ? g_worker->retransmits_.load() : 0; }
 
+// HET-cache RPCs for a cache that lives elsewhere (the GPU tier, parallel/gpu_cache.py): the staleness check / row fetch and
+// the push of kept gradients, exactly the two requests of the host cache (cache.cc).
+//   sync: rows[n] with the versions the caller holds (-1 = not cached); returns in out_* the k <= n rows that are missing or
+//         more than `bound` versions behind: out_idx[k] = position in rows, out_ver[k], out_rows[k, width].
+HPS_API int hps_sync_embedding(uint64_t key, const int64_t* rows, const int64_t* vers, uint64_t n, int64_t bound, int64_t* out_idx,
+                               int64_t* out_ver, float* out_rows, uint64_t* n_out) {
+    try {
+        if (!g_worker) throw std::runtime_error("PS worker not initialised");
+        std::vector<int64_t> idx, ver;
+        std::vector<float> data;
+        g_worker->sync_embedding(kSyncEmbedding, key, rows, vers, n, bound, nullptr, nullptr, nullptr, 0, &idx, &ver, &data);
+        *n_out = idx.size();
+        if (!idx.empty()) {
+            memcpy(out_idx, idx.data(), idx.size() * sizeof(int64_t));
+            memcpy(out_ver, ver.data(), ver.size() * sizeof(int64_t));
+            memcpy(out_rows, data.data(), data.size() * sizeof(float));
+        }
+        return 0;
+    } catch (const std::exception& e) { g_err = e.what(); return -1; }
+}
+HPS_API int hps_push_embedding(uint64_t key, const int64_t* rows, const float* grads, const int64_t* updates, uint64_t n) {
+    try {
+        if (!g_worker) throw std::runtime_error("PS worker not initialised");
+        if (n == 0) return 0;
+        g_worker->sync_embedding(kPushEmbedding, key, nullptr, nullptr, 0, 0, rows, grads, updates, n, nullptr, nullptr, nullptr);
+        return 0;
+    } catch (const std::exception& e) { g_err = e.what(); return -1; }
+}
+
 // HET-cache RPCs used by cache.cc ---------------------------------------------------------------
 namespace hps {
 void worker_sync_embedding(uint32_t type, uint64_t key, const int64_t* rows, const int64_t* vers, size_t n, int64_t bound,

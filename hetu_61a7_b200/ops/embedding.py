@@ -53,8 +53,10 @@ class EmbeddingLookUp(Op):
     def _ps_lookup(self, idx):
         import numpy as np
         emb = self.inputs[0]
-        ids = idx.detach().cpu().numpy().astype(np.int64).reshape(-1)
         cache = getattr(emb, 'cache', None)
+        if cache is not None and hasattr(cache, 'device_lookup'):       # GPU-resident HET cache: rows never visit the host
+            return cache.device_lookup(idx.detach())
+        ids = idx.detach().cpu().numpy().astype(np.int64).reshape(-1)
         width = int(emb.shape[-1])
         if cache is not None:
             rows = cache.embedding_lookup(ids, sync=True)

@@ -42,10 +42,18 @@ class ParameterServerCommunicateOp(Op):
         param = self.parameter
         width = param.shape[-1] if param.is_embed else 1
         if param.is_embed and config.cstable_policy is not None:
-            from ..parallel.cstable import CacheSparseTable
+            import os
             limit = max(param.shape[0] // 10, 1)
-            self.cache = CacheSparseTable(limit, param.shape[0], param.shape[1], param.id,
-                                          config.cstable_policy, config.cache_bound, comm=self.comm)
+            dev = config.context.torch_device
+            if dev.type == 'cuda' and torch.cuda.is_available() and os.environ.get('HETU_HET_GPU', '1') == '1':
+                # the cache lines live in HBM (csrc/het_cache.cu); only staleness checks, misses and pushes reach the host
+                from ..parallel.gpu_cache import GPUHetCache
+                self.cache = GPUHetCache(limit, param.shape[0], param.shape[1], param.id, config.cstable_policy,
+                                         config.cache_bound, comm=self.comm, device=dev)
+            else:
+                from ..parallel.cstable import CacheSparseTable
+                self.cache = CacheSparseTable(limit, param.shape[0], param.shape[1], param.id,
+                                              config.cstable_policy, config.cache_bound, comm=self.comm)
             param.cache = self.cache
         if self.bsp > 0 and not self._ssp_inited:
             self.comm.ssp_init(self.comm.rank() // 1, self.comm.nrank(), self.bsp)
@@ -64,6 +72,10 @@ class ParameterServerCommunicateOp(Op):
         dev = self.config.context.torch_device
         if isinstance(g, IndexedSlices):
             ind, val = g._iv()
+            if self.cache is not None and hasattr(self.cache, 'device_update'):
+                self.cache.device_update(ind.detach(), val.detach() * (-lr))
+                self._sync()
+                return None
             ind_h = ind.detach().cpu().numpy().astype(np.int64)
             val_h = (val.detach() * (-lr)).cpu().numpy().astype(np.float32)
             if self.cache is not None:

@@ -219,6 +219,31 @@ class PSWorker(object):
                                       ctypes.c_uint64(pr.size), out.ctypes.data_as(_F32P)), 'SSPushPull')
         return out
 
+    # ---- requests of a cache that lives outside this library (parallel/gpu_cache.py) -----------------------------------
+    def sync_embedding(self, node_id, rows, versions, bound, width):
+        """rows + the versions the caller holds (-1 = not cached) -> (positions, server versions, rows) of the entries
+        that are missing or more than ``bound`` versions behind."""
+        r, rp = _i64(np.asarray(rows).reshape(-1))
+        v, vp = _i64(np.asarray(versions).reshape(-1))
+        n = r.size
+        out_idx = np.empty(n, dtype=np.int64)
+        out_ver = np.empty(n, dtype=np.int64)
+        out_rows = np.empty((n, width), dtype=np.float32)
+        k = ctypes.c_uint64(0)
+        _chk(self.lib.hps_sync_embedding(ctypes.c_uint64(node_id), rp, vp, ctypes.c_uint64(n), ctypes.c_int64(int(bound)),
+                                         out_idx.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
+                                         out_ver.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
+                                         out_rows.ctypes.data_as(_F32P), ctypes.byref(k)), 'SyncEmbedding')
+        k = int(k.value)
+        return out_idx[:k], out_ver[:k], out_rows[:k]
+
+    def push_embedding(self, node_id, rows, grads, updates):
+        r, rp = _i64(np.asarray(rows).reshape(-1))
+        g, gp = _f32(grads)
+        u, up = _i64(np.asarray(updates).reshape(-1))
+        self._check_rows(node_id, r, g, 'PushEmbedding')
+        _chk(self.lib.hps_push_embedding(ctypes.c_uint64(node_id), rp, gp, up, ctypes.c_uint64(r.size)), 'PushEmbedding')
+
     # async variants keep their numpy buffers alive until Wait()
     def PushAsync(self, node_id, grad):
         g, gp = _f32(grad)

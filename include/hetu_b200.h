@@ -193,6 +193,25 @@ int hetu_wdl_sparse_sgd_rank1(void* const* bases /*host array*/, int nshard, con
                               int fields, size_t vocab, const void* dz_flag /*optional*/,
                               const void* dz_expect /*optional*/, cudaStream_t s);
 
+/* ---- HET embedding cache in HBM (csrc/het_cache.cu; reference src/hetu_cache/{include/embedding.h,src/cache.cc,
+ *      src/lfuopt_cache.cc}).  8-way set-associative table: tags [nsets*8] i64 (-1 empty), data / grad [nsets*8, width],
+ *      version i64, updates i32, score u32, queued i32, lock [nsets] i32; policy 0 LRU, 1 LFU, 2 LFUOpt.
+ *      probe: slot / cached version per id; install: rows from the server (miss) or refresh (stale), dirty victims to the
+ *      eviction list; gather: rows out; update: cached row and kept gradient += delta, lines over push_bound queued;
+ *      drain: queued (or all dirty) lines hand their gradients over.  Host side: parallel/gpu_cache.py. ---- */
+#define HETU_HET_ARGS void* tags, float* data, float* grad, void* version, void* updates, void* score, void* queued, \
+                      void* lock, int nsets, int width, int policy
+int hetu_het_probe(HETU_HET_ARGS, const void* ids, size_t n, int* slot, void* ver, unsigned tick, int touch, void* stats,
+                   cudaStream_t s);
+int hetu_het_install(HETU_HET_ARGS, const void* ids, const void* vers, const float* rows, size_t m, unsigned tick,
+                     void* ev_ids, float* ev_grads, void* ev_upd, void* ev_count, int ev_cap, void* stats, cudaStream_t s);
+int hetu_het_gather(HETU_HET_ARGS, const int* slot, size_t n, float* out, const float* fallback, const int* fb_index,
+                    cudaStream_t s);
+int hetu_het_update(HETU_HET_ARGS, const int* slot, const float* delta, size_t n, int push_bound, int* push_slots,
+                    void* push_count, int* direct, void* direct_count, cudaStream_t s);
+int hetu_het_drain(HETU_HET_ARGS, const int* push_slots, const void* push_count, int all_dirty, void* out_ids,
+                   float* out_grads, void* out_upd, void* out_count, int out_cap, cudaStream_t s);
+
 /* ---- dense optimizers, all tensors in one launch: Optimizers.cu ------------------------
  * kind: 0 SGD 1 Momentum 2 Nesterov 3 AdaGrad 4 Adam 5 AdamW 6 Lamb.  The pointer arrays are
  * HOST arrays of device pointers (<= 48 entries).  Lamb needs `scratch`: 2 floats per tensor of
