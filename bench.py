@@ -35,6 +35,9 @@ def parse():
     ap.add_argument('--vocab', type=int, default=33762577)
     ap.add_argument('--moe-steps', type=int, default=0, help='0 = same as --steps')
     ap.add_argument('--collectives', default=None, choices=[None, 'symm', 'nccl'])
+    ap.add_argument('--embedding', default='hbm', choices=['hbm', 'het'],
+                    help="W&D table: 'hbm' = HBM-resident (sharded over NVLink for N > 1); 'het' = BASELINE config 3 as written: "
+                         "host-DRAM parameter server + HET cache (GPU tier) + dense all-reduce")
     ap.add_argument('--profile', default=None, help='write a per-kernel time table of 50 W&D steps (torch.profiler) here')
     return ap.parse_args()
 
@@ -146,6 +149,20 @@ def timed(fn, steps, torch, device, comm, min_seconds=0.5, max_blocks=40, finish
     return srt[len(srt) // 2], {'blocks': len(srt), 'min_ms_per_step': srt[0], 'max_ms_per_step': srt[-1]}
 
 
+def start_parameter_server(world):
+    """--embedding het: a scheduler and one server process on this node (what `heturun -s 1` starts), workers = the ranks."""
+    port = int(os.environ.get('MASTER_PORT', '29500')) + 211
+    env = {'DMLC_PS_ROOT_URI': '127.0.0.1', 'DMLC_PS_ROOT_PORT': str(port), 'DMLC_NUM_WORKER': str(world), 'DMLC_NUM_SERVER': '1'}
+    os.environ.update(env)
+    procs = []
+    if int(os.environ.get('LOCAL_RANK', '0')) == 0:
+        e = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get('PYTHONPATH', ''))
+        for role in ('start_sched', 'start_server'):
+            procs.append(subprocess.Popen([sys.executable, '-c', 'import hetu_61a7_b200.launcher as l; l.%s()' % role], env=e))
+            time.sleep(0.5)
+    return procs
+
+
 def bench_wdl(args, ht, torch, np, comm, device):
     from hetu_61a7_b200 import _lib
     from hetu_61a7_b200.models import ctr
@@ -165,7 +182,11 @@ def bench_wdl(args, ht, torch, np, comm, device):
     sharded = world > 1
     loss, pred, _, train_op = ctr.wdl_criteo(dense, sparse, y_, feature_dimension=args.vocab, ctx=ctx)
     kw = dict(ctx=ctx, seed=123, shard_dataloaders=False)    # every rank generates its own shard
-    if world > 1:
+    if args.embedding == 'het':
+        from hetu_61a7_b200.graph import executor as _ex
+        _ex.worker_init()
+        kw.update(comm_mode='Hybrid', cstable_policy='LFUOpt', cache_bound=3, bsp=-1)      # examples/ctr/tests/hybrid_wdl_criteo.sh:7
+    elif world > 1:
         kw['comm_mode'] = 'Hybrid'
         if args.collectives:
             kw['use_nccl_collectives'] = args.collectives == 'nccl'
@@ -177,7 +198,11 @@ def bench_wdl(args, ht, torch, np, comm, device):
     s_buf = ht.NDArray(dev_pool[0][1].tensor.clone())
     l_buf = ht.NDArray(dev_pool[0][2].tensor.clone())
 
+    launches0 = _lib.launch_count
+    total_steps = [0]
+
     def step_dev(i):
+        total_steps[0] += 1
         d, s, l = dev_pool[i % len(dev_pool)]
         d_buf.tensor.copy_(d.tensor, non_blocking=True)
         s_buf.tensor.copy_(s.tensor, non_blocking=True)
@@ -233,12 +258,17 @@ def bench_wdl(args, ht, torch, np, comm, device):
     ms_e2e, spread_e2e = timed(step_e2e, args.steps, torch, device, comm, finish=finish_e2e)
     clocks = sampler.stop()
     launches = getattr(sub, 'graph_launches', 0) * args.steps if sub._graph is not None else 0
+    cache_perf = None
+    if args.embedding == 'het':
+        caches = [getattr(n, 'cache', None) for n in ex.param_nodes if getattr(n, 'cache', None) is not None]
+        cache_perf = caches[0].perf() if caches else None
+        launches = (_lib.launch_count - launches0) * args.steps // max(total_steps[0], 1)
     return {
         'ms_dev': ms_dev, 'ms_e2e': ms_e2e, 'clocks': clocks, 'h2d': h2d, 'd2h': 4,
         'global_batch': B * world, 'launches': launches, 'graph': sub._graph is not None,
         'loss': float(np.asarray(last['loss']).reshape(-1)[0]),
         'launches_per_step': getattr(sub, 'graph_launches', 0), 'spread': spread_dev, 'spread_e2e': spread_e2e,
-        'fused_wdl': getattr(ex, 'fused_wdl', 0),
+        'fused_wdl': getattr(ex, 'fused_wdl', 0), 'cache_perf': cache_perf,
     }
 
 
@@ -314,6 +344,7 @@ def main():
     if not os.path.exists(os.path.join(ge.LIB, 'libhetu_b200.so')):
         if int(os.environ.get('LOCAL_RANK', '0')) == 0:
             ge.build()
+    ps_procs = start_parameter_server(int(os.environ.get('WORLD_SIZE', '1'))) if args.embedding == 'het' else []
     import hetu_61a7_b200 as ht
     from hetu_61a7_b200.parallel.comm import world as get_world
     comm = ht.wrapped_mpi_nccl_init()
@@ -334,7 +365,10 @@ def main():
             'config': {'model': 'Wide&Deep (13 dense + 26 sparse, %d x 128 fp32 table, MLP 13-256-256-256)' % args.vocab,
                        'global_batch': w['global_batch'], 'seq_len': None,
                        'parallelism': 'dp%d' % world if world > 1 else 'single',
-                       'embedding': 'HBM-resident' + (' sharded over NVLink' if world > 1 else ''),
+                       'embedding': ('host-DRAM parameter server + HET cache in HBM (LFUOpt, bound 3), dense all-reduce'
+                                     if args.embedding == 'het' else
+                                     'HBM-resident' + (' sharded over NVLink' if world > 1 else '')),
+                       'het_cache': w.get('cache_perf'),
                        'optimizer': 'SGD lr 0.01', 'cuda_graph': w['graph'],
                        'kernel_launches_per_step': w['launches_per_step'],
                        'l2_policy': 'working set (17.3 GB embedding table, random rows) exceeds the 126 MB L2',
@@ -362,6 +396,12 @@ def main():
             out['moe'] = moe_out
     if comm.rank == 0:
         print(json.dumps(out))
+        sys.stdout.flush()
+    if args.embedding == 'het':
+        comm.barrier()
+        for p_ in ps_procs:
+            p_.terminate()
+        os._exit(0)
     return 0
 
 
