@@ -26,11 +26,23 @@ for _ in range(500):
     ex.run('train')
 torch.cuda.synchronize()
 print('no-readback %.1f us/step (host launch rate)' % ((time.perf_counter() - t0) / 500 * 1e6))
+pending = None
+t0 = time.perf_counter()
+for _ in range(500):
+    fut = ex.run('train')[0].asnumpy_async()
+    if pending is not None:
+        pending.get()
+    pending = fut
+torch.cuda.synchronize()
+print('async read-back %.1f us/step' % ((time.perf_counter() - t0) / 500 * 1e6))
 pr = cProfile.Profile()
 pr.enable()
-for _ in range(500):
-    ex.run('train')[0].asnumpy()
+for _ in range(2000):
+    fut = ex.run('train')[0].asnumpy_async()
+    if pending is not None:
+        pending.get()
+    pending = fut
 pr.disable()
 s = io.StringIO()
-pstats.Stats(pr, stream=s).sort_stats('tottime').print_stats(22)
-print(s.getvalue()[:5000])
+pstats.Stats(pr, stream=s).sort_stats('tottime').print_stats(32)
+print(s.getvalue()[:9000])

@@ -891,7 +891,7 @@ class SubExecutor(object):
 
     def _graph_signature(self, feeds):
         # where the feeds live is part of the plan: host feeds get a packed staging buffer, device feeds are read in place
-        return tuple((id(n), tuple(t.shape), str(t.dtype), t.device.type) for n, t in feeds.items())
+        return tuple((id(n), t.shape, t.dtype, t.device.type) for n, t in feeds.items())
 
     def _run_graph(self, feeds):
         key = self._graph_signature(feeds)
@@ -928,7 +928,7 @@ class SubExecutor(object):
             pk['dev'].copy_(host, non_blocking=True)
             if ev is None:
                 ev = pk['events'][slot] = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream(self.device))
+            ev.record()
         else:
             for node, t in feeds.items():
                 st = self._static_in[node]

@@ -141,7 +141,7 @@ def _pinned_copy(t):
     ring['turn'] += 1
     buf, ev = ring['bufs'][i], ring['events'][i]
     buf.copy_(t, non_blocking=True)
-    ev.record(torch.cuda.current_stream(t.device))
+    ev.record()                                          # on the current stream of the current device (the producer's)
     return buf, ev
 
 
