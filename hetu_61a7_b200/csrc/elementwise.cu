@@ -231,14 +231,15 @@ __global__ void __launch_bounds__(256) strided_copy_kernel(const float* __restri
     }
 }
 
-// fast path: innermost dim unit-stride on both sides and a multiple of 4 -> float4 rows
+// fast path: innermost dim a multiple of 4, unit-stride in dst and unit-stride (or broadcast, BCAST) in src -> float4 rows
+template <bool BCAST>
 __global__ void __launch_bounds__(256) strided_copy_vec4_kernel(const float* __restrict__ src, float* __restrict__ dst,
                                                                 StridedDesc d, size_t n4) {
     long long inner4 = d.shape[d.nd - 1] >> 2;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
         size_t rem = i / (size_t)inner4;
         long long col = (long long)(i % (size_t)inner4) << 2;
-        long long so = col, dof = col;
+        long long so = BCAST ? 0 : col, dof = col;
 #pragma unroll
         for (int k = 6; k >= 0; --k) {
             if (k < d.nd - 1) {
@@ -248,7 +249,12 @@ __global__ void __launch_bounds__(256) strided_copy_vec4_kernel(const float* __r
                 dof += idx * d.ds[k];
             }
         }
-        *reinterpret_cast<float4*>(dst + dof) = *reinterpret_cast<const float4*>(src + so);
+        if (BCAST) {
+            const float v = __ldg(src + so);
+            *reinterpret_cast<float4*>(dst + dof) = make_float4(v, v, v, v);
+        } else {
+            *reinterpret_cast<float4*>(dst + dof) = *reinterpret_cast<const float4*>(src + so);
+        }
     }
 }
 
@@ -257,17 +263,19 @@ HETU_API int hetu_strided_copy(const float* src, float* dst, int nd, const long 
     if (n == 0) return 0;
     StridedDesc d;
     d.nd = nd;
-    bool vec = nd >= 1 && ss[nd - 1] == 1 && ds[nd - 1] == 1 && (shape[nd - 1] & 3) == 0 &&
-               aligned16(src) && aligned16(dst);
+    const bool bcast = nd >= 1 && ss[nd - 1] == 0;           // e.g. the gradient of a row reduction, expanded
+    bool vec = nd >= 1 && (ss[nd - 1] == 1 || bcast) && ds[nd - 1] == 1 && (shape[nd - 1] & 3) == 0 &&
+               (bcast || aligned16(src)) && aligned16(dst);
     for (int i = 0; i < 8; ++i) {
         d.shape[i] = i < nd ? shape[i] : 1;
         d.ss[i] = i < nd ? ss[i] : 0;
         d.ds[i] = i < nd ? ds[i] : 0;
-        if (i < nd - 1 && ((ss[i] & 3) || (ds[i] & 3))) vec = false;
+        if (i < nd - 1 && ((!bcast && (ss[i] & 3)) || (ds[i] & 3))) vec = false;
     }
     if (vec) {
         size_t n4 = n >> 2;
-        strided_copy_vec4_kernel<<<ew_grid(n4, 256), 256, 0, s>>>(src, dst, d, n4);
+        if (bcast) strided_copy_vec4_kernel<true><<<ew_grid(n4, 256), 256, 0, s>>>(src, dst, d, n4);
+        else strided_copy_vec4_kernel<false><<<ew_grid(n4, 256), 256, 0, s>>>(src, dst, d, n4);
     } else {
         strided_copy_kernel<<<ew_grid(n, 256), 256, 0, s>>>(src, dst, d, n);
     }

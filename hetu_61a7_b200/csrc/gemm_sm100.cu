@@ -20,7 +20,9 @@
 #include <string>
 #include <cstring>
 
-enum { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2, ACT_SIGMOID = 3 };
+// ACT_RELU_MASK (tcgen05 kernels only): C holds the forward activations h on entry; C = (h > 0) ? alpha * A B : 0 -
+// the relu backward folded into the GEMM that produces dH, written over h.
+enum { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2, ACT_SIGMOID = 3, ACT_RELU_MASK = 4 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {
     if (act == ACT_RELU) return fmaxf(v, 0.f);
@@ -186,6 +188,16 @@ gemm_tf32_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             if (vec_ok && col + 3 < p.N) {
                 float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (p.bias != nullptr) bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+                // C is read for beta / the relu mask: all eight loads of this warp pass are issued before the first store
+                const bool need_c = p.beta != 0.f || p.act == ACT_RELU_MASK;
+                float4 cin[8];
+                if (need_c) {
+#pragma unroll
+                    for (int r = 0; r < 32; r += 4) {
+                        const int row = row_base + r + sub_row;
+                        cin[r >> 2] = row < p.M ? *reinterpret_cast<const float4*>(Cb + (size_t)row * p.N + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
 #pragma unroll
                 for (int r = 0; r < 32; r += 4) {
                     const int row = row_base + r + sub_row;
@@ -194,10 +206,13 @@ gemm_tf32_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                         float4 o = make_float4(p.alpha * a.x + bv.x, p.alpha * a.y + bv.y, p.alpha * a.z + bv.z, p.alpha * a.w + bv.w);
                         float4* dst = reinterpret_cast<float4*>(Cb + (size_t)row * p.N + col);
                         if (p.beta != 0.f) {
-                            float4 c = *dst;
+                            const float4 c = cin[r >> 2];
                             o.x += p.beta * c.x; o.y += p.beta * c.y; o.z += p.beta * c.z; o.w += p.beta * c.w;
                         }
-                        if (p.act != ACT_NONE) { o.x = apply_act(o.x, p.act); o.y = apply_act(o.y, p.act); o.z = apply_act(o.z, p.act); o.w = apply_act(o.w, p.act); }
+                        if (p.act == ACT_RELU_MASK) {
+                            const float4 h = cin[r >> 2];
+                            o.x = h.x > 0.f ? o.x : 0.f; o.y = h.y > 0.f ? o.y : 0.f; o.z = h.z > 0.f ? o.z : 0.f; o.w = h.w > 0.f ? o.w : 0.f;
+                        } else if (p.act != ACT_NONE) { o.x = apply_act(o.x, p.act); o.y = apply_act(o.y, p.act); o.z = apply_act(o.z, p.act); o.w = apply_act(o.w, p.act); }
                         *dst = o;
                     }
                 }
@@ -211,7 +226,7 @@ gemm_tf32_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                         float o = p.alpha * tile[(r + sub_row) * 36 + c4 + u] + (p.bias ? __ldg(p.bias + cc) : 0.f);
                         float* dst = Cb + (size_t)row * p.N + cc;
                         if (p.beta != 0.f) o += p.beta * (*dst);
-                        *dst = apply_act(o, p.act);
+                        *dst = p.act == ACT_RELU_MASK ? (*dst > 0.f ? o : 0.f) : apply_act(o, p.act);
                     }
                 }
             }
@@ -570,6 +585,16 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 } else if (vec_ok && col + 3 < p.N) {
                     float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (p.bias != nullptr) bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+                    // C is read for beta / the relu mask: all eight loads of this warp pass are issued before the first store
+                    const bool need_c = p.beta != 0.f || p.act == ACT_RELU_MASK;
+                    float4 cin[8];
+                    if (need_c) {
+#pragma unroll
+                        for (int r = 0; r < 32; r += 4) {
+                            const int row = row_base + r + sub_row;
+                            cin[r >> 2] = row < p.M ? *reinterpret_cast<const float4*>(Cb + (size_t)row * p.N + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                    }
 #pragma unroll
                     for (int r = 0; r < 32; r += 4) {
                         const int row = row_base + r + sub_row;
@@ -578,10 +603,13 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                             float4 o = make_float4(p.alpha * a.x + bv.x, p.alpha * a.y + bv.y, p.alpha * a.z + bv.z, p.alpha * a.w + bv.w);
                             float4* dst = reinterpret_cast<float4*>(Cb + (size_t)row * p.N + col);
                             if (p.beta != 0.f) {
-                                float4 c = *dst;
+                                const float4 c = cin[r >> 2];
                                 o.x += p.beta * c.x; o.y += p.beta * c.y; o.z += p.beta * c.z; o.w += p.beta * c.w;
                             }
-                            if (p.act != ACT_NONE) { o.x = apply_act(o.x, p.act); o.y = apply_act(o.y, p.act); o.z = apply_act(o.z, p.act); o.w = apply_act(o.w, p.act); }
+                            if (p.act == ACT_RELU_MASK) {
+                                const float4 h = cin[r >> 2];
+                                o.x = h.x > 0.f ? o.x : 0.f; o.y = h.y > 0.f ? o.y : 0.f; o.z = h.z > 0.f ? o.z : 0.f; o.w = h.w > 0.f ? o.w : 0.f;
+                            } else if (p.act != ACT_NONE) { o.x = apply_act(o.x, p.act); o.y = apply_act(o.y, p.act); o.z = apply_act(o.z, p.act); o.w = apply_act(o.w, p.act); }
                             *dst = o;
                         }
                     }
@@ -595,7 +623,7 @@ gemm_tf32_2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                             float o = p.alpha * tile_s[(r + sub_row) * 36 + c4 + u] + (p.bias ? __ldg(p.bias + cc) : 0.f);
                             float* dst = Cb + (size_t)row * p.N + cc;
                             if (p.beta != 0.f) o += p.beta * (*dst);
-                            *dst = apply_act(o, p.act);
+                            *dst = p.act == ACT_RELU_MASK ? (*dst > 0.f ? o : 0.f) : apply_act(o, p.act);
                         }
                     }
                 }
@@ -995,6 +1023,59 @@ __global__ void __launch_bounds__(256) gemm_skinny_cols_kernel(const float* __re
     }
 }
 
+// Same product when M % 4 == 0 and A is 16-byte aligned: every thread owns four consecutive m (one 128-bit load per
+// k), 32 lanes cover 128 m, 8 k-lanes per block with four loads in flight each - enough bytes in flight per SM to
+// stream A at HBM speed (the scalar kernel above stalls at ~1.3 TB/s on the MoE gate's weight gradient).
+template <int TB>
+__global__ void __launch_bounds__(256) gemm_skinny_cols_vec4_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                                    float* __restrict__ C, int M, int N, int K, int kchunk,
+                                                                    float alpha) {
+    __shared__ float red[8][32][4 * kSkinnyN + 1];
+    const int lane = threadIdx.x & 31, kl = threadIdx.x >> 5;
+    const int m = (blockIdx.x * 32 + lane) * 4;
+    const int k_beg = blockIdx.y * kchunk, k_end = min(K, k_beg + kchunk);
+    float acc[kSkinnyN][4];
+#pragma unroll
+    for (int n = 0; n < kSkinnyN; ++n) acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
+    if (m < M) {
+        for (int k0 = k_beg + kl; k0 < k_end; k0 += 32) {
+            float4 av[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int k = k0 + u * 8;
+                av[u] = k < k_end ? __ldcs(reinterpret_cast<const float4*>(A + (size_t)k * M + m)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int k = k0 + u * 8;
+                if (k >= k_end) break;
+#pragma unroll
+                for (int n = 0; n < kSkinnyN; ++n) {
+                    if (n < N) {
+                        const float b = __ldg(TB ? B + (size_t)n * K + k : B + (size_t)k * N + n);
+                        acc[n][0] += av[u].x * b; acc[n][1] += av[u].y * b; acc[n][2] += av[u].z * b; acc[n][3] += av[u].w * b;
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int n = 0; n < kSkinnyN; ++n)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) red[kl][lane][n * 4 + j] = acc[n][j];
+    __syncthreads();
+    // 128 m x N outputs per block: thread -> (m offset, n)
+    for (int o = threadIdx.x; o < 128 * N; o += 256) {
+        const int mo = o / N, n = o - mo * N;
+        const int mm = blockIdx.x * 128 + mo;
+        if (mm >= M) continue;
+        float v = 0.f;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v += red[q][mo >> 2][n * 4 + (mo & 3)];
+        atomicAdd(C + (size_t)mm * N + n, alpha * v);
+    }
+}
+
 // K <= 8: a sum of a few outer products (gradient of a [*, d] x [d, 1] projection); one thread per output.
 __global__ void __launch_bounds__(256) gemm_tinyk_kernel(const float* __restrict__ A, const float* __restrict__ B,
                                                          float* __restrict__ C, const float* __restrict__ bias, int M, int N,
@@ -1018,6 +1099,20 @@ static void launch_skinny(const float* A, const float* B, float* C, const float*
         const size_t sm = ((size_t)N * K * 4 <= 48 * 1024 && (K & 3) == 0) ? (size_t)N * K * 4 : 0;
         if (tB) gemm_skinny_rows_kernel<1><<<grid, 256, sm, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
         else gemm_skinny_rows_kernel<0><<<grid, 256, sm, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
+        return;
+    }
+    if ((M & 3) == 0 && (reinterpret_cast<uintptr_t>(A) & 15) == 0 && K >= 256) {
+        const int mb = (M + 127) / 128;
+        int sp = (4 * kNumSMs + mb - 1) / mb;
+        int kc = (K + sp - 1) / sp;
+        kc = (kc + 31) / 32 * 32;
+        sp = (K + kc - 1) / kc;
+        cudaMemsetAsync(C, 0, sizeof(float) * (size_t)M * N, s);
+        dim3 g(mb, sp);
+        if (tB) gemm_skinny_cols_vec4_kernel<1><<<g, 256, 0, s>>>(A, B, C, M, N, K, kc, alpha);
+        else gemm_skinny_cols_vec4_kernel<0><<<g, 256, 0, s>>>(A, B, C, M, N, K, kc, alpha);
+        if (bias || act != ACT_NONE)
+            gemm_finish_kernel<<<ew_grid((size_t)M * N, 256), 256, 0, s>>>(C, bias, (size_t)M * N, N, act);
         return;
     }
     const int mblocks = (M + 63) / 64;
@@ -1050,6 +1145,10 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
                   (sA % 4 == 0) && (sB % 4 == 0);
     const double macs = (double)M * N * K * batch;
     bool big = macs > (double)(1 << 25) && M >= 64 && N >= 8 && K >= 32;
+    if (act == ACT_RELU_MASK && !(mode != 1 && tma_ok && big && K > 8 && N > kSkinnyN && beta == 0.f)) {
+        hetu_set_error("hetu_gemm: the relu-mask epilogue exists in the tensor-core kernels only (M %d N %d K %d)", M, N, K);
+        return -1;
+    }
     if (K <= 8 && batch == 1) {
         gemm_tinyk_kernel<<<ew_grid((size_t)M * N, 256), 256, 0, s>>>(A, B, C, bias, M, N, K, transA, transB, alpha, beta, act);
         HETU_CHECK_LAUNCH("hetu_gemm(tiny-k)");
@@ -1062,7 +1161,7 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
     }
     static int force_simt = -1;
     if (force_simt < 0) { const char* e = getenv("HETU_GEMM_FORCE_SIMT"); force_simt = (e && e[0] == '1') ? 1 : 0; }
-    if (mode != 1 && tma_ok && big && !force_simt) {
+    if (mode != 1 && tma_ok && big && (!force_simt || act == ACT_RELU_MASK)) {
         GemmParams p;
         p.C = C; p.bias = bias; p.M = M; p.N = N; p.K = K; p.sC = sC;
         p.a_mn_major = transA ? 1 : 0;

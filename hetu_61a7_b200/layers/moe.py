@@ -88,14 +88,13 @@ def _slots(mask_topk, k):
 def topkgating(logits, k, capacity_factor, num_tokens, num_experts, embed_dim):
     capacity = k * math.ceil((num_tokens / num_experts) * capacity_factor)
     if os.environ.get('HETU_MOE_FUSED_GATE', '1') == '1' and k <= 4:
-        # one op for softmax + top-k + slots + balance loss (ops/moe_gate.py); the pieces are columns of its output
+        # one op for softmax + top-k + slots + balance loss (ops/moe_gate.py); the pieces are views of its output
         packed = ht.fused_topk_gate_op(logits, k)
         packed.expected_tokens = num_tokens
-        col = lambda c: ht.array_reshape_op(ht.slice_op(packed, (0, c), (num_tokens, 1)), [-1])     # noqa: E731
-        indices_s = [col(i) for i in range(k)]
-        location_s = [col(k + i) for i in range(k)]
-        gates_s = [col(2 * k + i) for i in range(k)]
-        l_aux = ht.array_reshape_op(ht.slice_op(packed, (num_tokens, 0), (1, 1)), [1])
+        indices_s = [ht.gate_piece_op(packed, ('idx', i), num_tokens) for i in range(k)]
+        location_s = [ht.gate_piece_op(packed, ('loc', i), num_tokens) for i in range(k)]
+        gates_s = [ht.gate_piece_op(packed, ('gate', i), num_tokens) for i in range(k)]
+        l_aux = ht.gate_piece_op(packed, 'aux', num_tokens)
         return l_aux, indices_s, location_s, gates_s, capacity
     gates = ht.softmax_op(logits)
     topk_indices = ht.topk_idx_op(gates, topk=k)
@@ -285,6 +284,13 @@ class MoELayer(BaseLayer):
             self.arange_array = Variable(value=np.arange(num_tokens).astype(np.float32),
                                          name='arange_array', trainable=False)
 
+    def _plain_ffn(self):
+        """Every local expert is the stock two-GEMM relu FFN without bias (what ops/moe_ffn.py computes itself)."""
+        return (os.environ.get('HETU_MOE_OVERLAP', '1') == '1'
+                and all(type(ex) is Expert and not ex.bias and ex.activation is ht.relu_op for ex in self.experts)
+                and len({(ex.embed_dim, ex.ffn_dim) for ex in self.experts}) == 1
+                and self.experts[0].embed_dim == self.embed_dim)
+
     def _a2a(self, x):
         if self.hierarchical is not None:
             return ht.halltoall_op(x, self.hierarchical[0], self.hierarchical[1])
@@ -314,6 +320,18 @@ class MoELayer(BaseLayer):
             l_aux, extra, indices_s, location_s, gates_s, capacity = self.gate(reshaped)
         else:
             l_aux, indices_s, location_s, gates_s, capacity = self.gate(reshaped)
+        if self.fused and self._plain_ffn():
+            # exchange chunks overlapped with the expert GEMMs, one op (ops/moe_ffn.py)
+            from ..ops.moe_ffn import fused_moe_ffn_op
+            for ex in self.experts:
+                ex.build()
+            out = fused_moe_ffn_op(reshaped, indices_s, location_s, gates_s, [ex.w1 for ex in self.experts],
+                                   [ex.w2 for ex in self.experts], capacity, self.all2all_size)
+            if gates_s is None:
+                return out
+            if extra is not None:
+                return out, l_aux, extra
+            return out, l_aux
         if self.fused:
             from ..ops.moe_fused import fused_moe_dispatch_op, fused_moe_combine_op
             E, W = self.num_local_experts, self.all2all_size

@@ -48,6 +48,6 @@ from .comm import (allreduceCommunicate_op, allreduceCommunicatep2p_op, groupall
 from .transfer import datah2d_op, datad2h_op, datah2d_sparse_op, datad2h_sparse_op
 from .ps_ops import parameterServerCommunicate_op, parameterServerSparsePull_op
 from .moe_fused import fused_moe_dispatch_op, fused_moe_combine_op
-from .moe_gate import fused_topk_gate_op
+from .moe_gate import fused_topk_gate_op, gate_piece_op
 from .attention import fused_attention_op
 from .gnn import distgcn_15d_op

@@ -29,6 +29,7 @@ from ..graph.node import Op, as_index
 from ..ndarray import ND_Sparse_Array
 
 ACT_NONE, ACT_RELU, ACT_GELU, ACT_SIGMOID = 0, 1, 2, 3
+ACT_RELU_MASK = 4      # tensor-core kernels only: out holds h on entry, out = (h > 0) ? A @ B : 0  (csrc/gemm_sm100.cu)
 _PRECISION = {'mode': os.environ.get('HETU_MATMUL_PRECISION', 'tf32')}
 _MODE_CODE = {'tf32': 0, 'fp32': 1, 'bf16': 3, 'fp16': 4}
 
@@ -46,7 +47,7 @@ def get_matmul_precision() -> str:
 
 
 def gemm(a: torch.Tensor, b: torch.Tensor, trans_a=False, trans_b=False, bias=None,
-         c_in=None, alpha=1.0, beta=0.0, act=ACT_NONE) -> torch.Tensor:
+         c_in=None, alpha=1.0, beta=0.0, act=ACT_NONE, out=None) -> torch.Tensor:
     """C = act(alpha * op(A) @ op(B) + beta * C_in + bias); 2-D or batched 3-D."""
     if not (L.kernels_on(a, b) and a.dtype == torch.float32 and b.dtype == torch.float32):
         return _gemm_torch(a, b, trans_a, trans_b, bias, c_in, alpha, beta, act)
@@ -72,7 +73,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, trans_a=False, trans_b=False, bias=No
         tuple(a.shape), tuple(b.shape), trans_a, trans_b)
     out_shape = (batch, am, bn) if batched else (am, bn)
     if c_in is not None and beta != 0.0:
-        c = c_in.expand(out_shape).contiguous() if tuple(c_in.shape) != out_shape else c_in.clone()
+        if out is not None and out.data_ptr() == c_in.data_ptr() and out.is_contiguous() and tuple(c_in.shape) == out_shape:
+            c = out                                          # accumulate in place
+        else:
+            c = c_in.expand(out_shape).contiguous() if tuple(c_in.shape) != out_shape else c_in.clone()
+    elif out is not None and out.is_contiguous() and out.numel() == int(np.prod(out_shape)) and out.dtype == torch.float32:
+        c = out.view(out_shape)                          # caller-provided destination (e.g. a symmetric-heap buffer)
+        beta = 0.0
     else:
         c = torch.empty(out_shape, dtype=torch.float32, device=a.device)
         beta = 0.0

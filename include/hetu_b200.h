@@ -247,6 +247,18 @@ int hetu_moe_combine_peer(void* const* idx, void* const* loc, void* const* gate,
                           void* const* peer_bases, int world, int rank, float* out, int T, int d, int capacity,
                           int e_local, cudaStream_t s);
 
+/* chunked exchanges: buffer layout [E_local, parts, world, capacity / parts, d]; one launch moves the routes of local
+ * expert e_filter whose slot falls into capacity part h_filter (h_filter < 0: every part); combine may accumulate into
+ * out.  ops/moe_ffn.py runs them on a side stream under the GEMMs of the other chunks. */
+int hetu_moe_dispatch_peer_x(const float* x, void* const* idx, void* const* loc, void* const* gate, int k, int has_gate,
+                             void* const* peer_bases, int world, int rank, int T, int d, int capacity, int e_local,
+                             int e_filter, int parts, int h_filter, cudaStream_t s);
+int hetu_moe_combine_peer_x(void* const* idx, void* const* loc, void* const* gate, int k, int has_gate,
+                            void* const* peer_bases, int world, int rank, float* out, int T, int d, int capacity,
+                            int e_local, int e_filter, int parts, int h_filter, int accumulate, cudaStream_t s);
+int hetu_moe_gate_grad_peer_x(const float* dout, const float* idx, const float* loc, void* const* peer_bases, int world,
+                              int rank, float* out, int T, int d, int capacity, int e_local, int parts, cudaStream_t s);
+
 int hetu_moe_gate_grad_peer(const float* dout, const float* idx, const float* loc, void* const* peer_bases,
                             int world, int rank, float* out, int T, int d, int capacity, int e_local,
                             cudaStream_t s);
@@ -318,11 +330,12 @@ int hetu_gbdt_route(const long long* indptr, const int* indices, const unsigned 
                     long long n, cudaStream_t s);
 
 /* ---- fused MoE gate: reference python/hetu/layers/TopGate.py:15-79 lowered through cudnnSoftmax, TopKIdx.cu,
- * OneHot.cu, CumSum.cu, ReduceSum/ReduceMean (about 30 launches).  P [T + 1, 3k]: expert index, capacity slot,
- * gate value per route; P[T][0] = balance loss.  Scratch: blk_cnt int[k * ceil(T / 256) * E], me float[E], cnt float[E]. */
+ * OneHot.cu, CumSum.cu, ReduceSum/ReduceMean (about 30 launches).  P planar [3k * T + 1 + E]: k planes of expert
+ * indices, k of capacity slots, k of gate values, then the balance loss and the per-expert route counts.
+ * Scratch: blk_cnt int[k * ceil(T / 256) * E], me float[E].  bwd: dgates = k pointers to [T] (null = no gradient). */
 int hetu_moe_gate_fwd(const float* logits, float* P, int* blk_cnt, float* me, int T, int E, int k, cudaStream_t s);
-int hetu_moe_gate_bwd(const float* logits, const float* P, const float* dP, float* cnt, float* dlogits, int T, int E, int k,
-                      cudaStream_t s);
+int hetu_moe_gate_bwd(const float* logits, const float* P, void* const* dgates, const float* daux, float* dlogits,
+                      int T, int E, int k, cudaStream_t s);
 
 #ifdef __cplusplus
 }

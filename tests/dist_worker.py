@@ -210,29 +210,34 @@ if gpu:
 # ------------------------------------------------------------------ MoE fused vs NCCL
 if gpu:
     from hetu_61a7_b200.models.moe import moe_model
-    losses = {}
-    for fused in ('1', '0'):
-        os.environ['HETU_MOE_FUSED'] = fused
-        xx, tt = ht.Variable('x'), ht.Variable('t')
-        ht_loss, _ = moe_model(xx, tt, batch_size=2, num_tokens=64, model_dim=64, hidden_size=64,
-                               num_local_experts=2, world=nrank, rank=rank, top=2)
-        tr = ht.optim.SGDOptimizer(0.05).minimize(ht_loss)
-        ex = ht.Executor({'train': [ht_loss, tr]}, ctx=ctx, comm_mode='AllReduce', seed=5,
-                         use_nccl_collectives=(fused == '0'))
-        # identical initial weights for both engines (node ids, hence init seeds, differ per build)
-        named = ex._named_params()
-        if fused == '1':
-            snapshot = {n: ex.config.placeholder_to_arr_map[p].detach().cpu().numpy().copy()
-                        for n, p in named.items()}
-        else:
-            ex.load_dict(snapshot)
-        xv = np.random.RandomState(10 + rank).randn(2, 64, 64).astype(np.float32)
-        ls = []
-        for _ in range(4):
-            ls.append(float(ex.run('train', feed_dict={xx: xv, tt: np.zeros(2, np.float32)})[0].asnumpy().reshape(-1)[0]))
-        losses[fused] = ls
-    log('moe losses fused', losses['1'], 'nccl', losses['0'])
-    assert np.allclose(losses['1'], losses['0'], rtol=2e-3, atol=1e-4), losses
+    for pre in (False, True):       # pre: a trainable projection in front, so the layer must also return d(input)
+        losses = {}
+        for fused in ('1', '0'):
+            os.environ['HETU_MOE_FUSED'] = fused
+            xx, tt = ht.Variable('x'), ht.Variable('t')
+            xin = xx
+            if pre:
+                wp = ht.init.random_normal((64, 64), stddev=0.2, name='pre_proj')
+                xin = ht.array_reshape_op(ht.matmul_op(ht.array_reshape_op(xx, [-1, 64]), wp), [2, 64, 64])
+            ht_loss, _ = moe_model(xin, tt, batch_size=2, num_tokens=64, model_dim=64, hidden_size=64,
+                                   num_local_experts=2, world=nrank, rank=rank, top=2)
+            tr = ht.optim.SGDOptimizer(0.05).minimize(ht_loss)
+            ex = ht.Executor({'train': [ht_loss, tr]}, ctx=ctx, comm_mode='AllReduce', seed=5,
+                             use_nccl_collectives=(fused == '0'))
+            # identical initial weights for both engines (node ids, hence init seeds, differ per build)
+            named = ex._named_params()
+            if fused == '1':
+                snapshot = {n: ex.config.placeholder_to_arr_map[p].detach().cpu().numpy().copy()
+                            for n, p in named.items()}
+            else:
+                ex.load_dict(snapshot)
+            xv = np.random.RandomState(10 + rank).randn(2, 64, 64).astype(np.float32)
+            ls = []
+            for _ in range(4):
+                ls.append(float(ex.run('train', feed_dict={xx: xv, tt: np.zeros(2, np.float32)})[0].asnumpy().reshape(-1)[0]))
+            losses[fused] = ls
+        log('moe losses (pre-projection %s) fused' % pre, losses['1'], 'nccl', losses['0'])
+        assert np.allclose(losses['1'], losses['0'], rtol=2e-3, atol=1e-4), losses
 
 # ------------------------------------- Wide&Deep: fused step (in-kernel push all-reduce + SGD) vs node-by-node
 if gpu:

@@ -59,6 +59,9 @@ def test_strided_copy_and_concat(L):
     torch.testing.assert_close(S.materialize(x.permute(0, 2, 1, 3)), x.permute(0, 2, 1, 3).contiguous())
     torch.testing.assert_close(S.materialize(x.permute(3, 1, 0, 2)), x.permute(3, 1, 0, 2).contiguous())
     torch.testing.assert_close(S.materialize(x[:, 1:4, ::2]), x[:, 1:4, ::2].contiguous())
+    g = rnd(16, 40)                                       # gradient of a row reduction: innermost dim broadcast
+    torch.testing.assert_close(S.materialize(g.unsqueeze(-1).expand(16, 40, 64)), g.unsqueeze(-1).expand(16, 40, 64).contiguous())
+    torch.testing.assert_close(S.materialize(g.unsqueeze(-1).expand(16, 40, 6)), g.unsqueeze(-1).expand(16, 40, 6).contiguous())
     a, b = rnd(128, 3328), rnd(128, 256, seed=1)
     torch.testing.assert_close(S._cat([a, b], 1), torch.cat([a, b], 1))
     torch.testing.assert_close(S._cat([a, a], 0), torch.cat([a, a], 0))
@@ -438,3 +441,31 @@ def test_gemm_16bit_batched():
         linalg.set_matmul_precision('tf32')
     ref = a.double() @ b.double()
     assert (out.double() - ref).abs().max().item() <= 2e-2 * ref.abs().max().item()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('m,n,k', [(1024, 512, 256), (2048, 2048, 2048), (700, 300, 260)])
+def test_gemm_relu_mask_epilogue(m, n, k):
+    """ACT_RELU_MASK: out holds the forward activations h on entry; out = (h > 0) ? A @ B^T : 0 (relu backward folded
+    into the GEMM that produces dH) - one-shot and persistent 2-SM tensor-core kernels."""
+    from hetu_61a7_b200.ops.linalg import gemm, ACT_RELU_MASK
+    dy, w2, h = rnd(m, k), rnd(n, k, seed=1), torch.relu(rnd(m, n, seed=2))
+    ref = (dy.double() @ w2.double().t()) * (h > 0).double()
+    out = h.clone()
+    res = gemm(dy, w2, False, True, act=ACT_RELU_MASK, out=out)
+    assert res.data_ptr() == out.data_ptr()
+    assert (out.double() - ref).abs().max().item() <= 2e-3 * ref.abs().max().item()
+    assert (out[h <= 0] == 0).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('m,n,k,tB', [(2048, 2, 16384, False), (512, 5, 4099, False), (260, 8, 1000, True), (130, 3, 700, False)])
+def test_gemm_skinny_weight_gradient(m, n, k, tB):
+    """A^T B with a handful of output columns (MoE gate / logistic-regression weight gradient): 128-bit-load kernel
+    (M % 4 == 0) and the scalar one, fp32 accumulation."""
+    from hetu_61a7_b200.ops.linalg import gemm
+    a = rnd(k, m)
+    b = rnd(n, k, seed=1) if tB else rnd(k, n, seed=1)
+    ref = a.double().t() @ (b.double().t() if tB else b.double())
+    out = gemm(a, b, True, tB)
+    assert (out.double() - ref).abs().max().item() <= 1e-4 * ref.abs().max().item() + 1e-4

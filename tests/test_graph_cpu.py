@@ -290,6 +290,39 @@ def test_moe_layer_cpu_forward_backward():
         assert np.isfinite(out[0].asnumpy()).all() and out[1].shape == (2, 32)
 
 
+def test_moe_ffn_op_matches_op_chain(monkeypatch):
+    """ops/moe_ffn.py (dispatch + expert FFN + combine and their gradients in one op) trains exactly like the
+    dispatch -> split -> matmul/relu/matmul -> concatenate -> combine chain it replaces."""
+    from hetu_61a7_b200.models.moe import moe_model
+    from hetu_61a7_b200.ops.moe_ffn import FusedMoEFFNOp
+    from hetu_61a7_b200.graph.autodiff import find_topo_sort
+    for gate, pre in (('top', False), ('top', True), ('hash', False), ('sam', True)):
+        losses, snapshot = {}, None
+        for overlap in ('1', '0'):
+            monkeypatch.setenv('HETU_MOE_OVERLAP', overlap)
+            x, t = ht.Variable('x'), ht.Variable('t')
+            hi = ht.Variable('hash_idx') if gate == 'hash' else None
+            xin = x
+            if pre:         # a trainable layer in front: the MoE layer has to return the gradient of its input too
+                wp = ht.init.random_normal((16, 16), stddev=0.3, name='pre_proj')
+                xin = ht.array_reshape_op(ht.matmul_op(ht.array_reshape_op(x, [-1, 16]), wp), [2, 32, 16])
+            loss, y = moe_model(xin, t, batch_size=2, num_tokens=32, model_dim=16, hidden_size=24, num_local_experts=4,
+                                world=1, top=2, gate=gate, num_local_gpus=2, hash_indices=hi)
+            assert any(isinstance(n, FusedMoEFFNOp) for n in find_topo_sort([loss])) == (overlap == '1')
+            train = ht.optim.SGDOptimizer(0.05).minimize(loss)
+            ex = ht.Executor([loss, train], ctx=ht.cpu(0), seed=0)
+            if snapshot is None:
+                snapshot = {n: ex.config.placeholder_to_arr_map[p_].detach().numpy().copy()
+                            for n, p_ in ex._named_params().items()}
+            else:
+                ex.load_dict(snapshot)
+            feed = {x: np.random.RandomState(3).randn(2, 32, 16).astype(np.float32), t: np.zeros(2, np.float32)}
+            if hi is not None:
+                feed[hi] = np.random.RandomState(4).randint(0, 4, 64).astype(np.float32)
+            losses[overlap] = [float(ex.run(feed_dict=feed)[0].asnumpy().reshape(-1)[0]) for _ in range(4)]
+        np.testing.assert_allclose(losses['1'], losses['0'], rtol=1e-5, atol=1e-6, err_msg=gate)
+
+
 def test_moe_dispatch_combine_identity():
     """combine(dispatch(x)) with gate 1 and enough capacity returns x for kept tokens."""
     T, d, E = 64, 8, 4
