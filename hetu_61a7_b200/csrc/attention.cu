@@ -51,6 +51,31 @@ __global__ void __launch_bounds__(256) attn_softmax_bwd_kernel(const float* __re
     for (int c = lane; c < cols; c += 32) dr[c] = pr[c] * (dr[c] - dot) * scale;
 }
 
+// backward after the flash forward (csrc/attention_sm100.cu keeps no probabilities): s holds raw scores q k^T on entry,
+// s <- exp(s * scale + mask[b, :] - lse[row]); one warp per row
+__global__ void __launch_bounds__(256) attn_probs_from_lse_kernel(float* __restrict__ s, const float* __restrict__ mask,
+                                                                  const float* __restrict__ lse, long long rows, int cols,
+                                                                  long long rows_per_batch, float scale) {
+    const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    float* r = s + row * cols;
+    const float* m = mask ? mask + (row / rows_per_batch) * cols : nullptr;
+    const float l = lse[row];
+    for (int c = lane; c < cols; c += 32) {
+        const float v = r[c] * scale + (m ? __ldg(m + c) : 0.f);
+        r[c] = (l == -INFINITY) ? 0.f : __expf(v - l);
+    }
+}
+
+HETU_API int hetu_attn_probs_from_lse(float* s, const float* mask, const float* lse, long long rows, int cols,
+                                      long long rows_per_batch, float scale, cudaStream_t st) {
+    if (rows <= 0 || cols <= 0) return 0;
+    attn_probs_from_lse_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(s, mask, lse, rows, cols, rows_per_batch, scale);
+    HETU_CHECK_LAUNCH("hetu_attn_probs_from_lse");
+    return 0;
+}
+
 HETU_API int hetu_attn_softmax(float* s, const float* mask, float* lse, long long rows, int cols, long long rows_per_batch,
                                float scale, cudaStream_t st) {
     if (rows <= 0 || cols <= 0) return 0;

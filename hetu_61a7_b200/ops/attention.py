@@ -10,6 +10,7 @@ backward pass is four batched GEMMs and one row kernel (ds = p * (dp - <dp, p>) 
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 
@@ -38,6 +39,18 @@ class FusedAttentionOp(Op):
         scale = self.scale if self.scale is not None else 1.0 / math.sqrt(q.shape[-1])
         B, H, S, D = q.shape
         Sk = k.shape[2]
+        if _k(q, k, v) and (mask is None or mask.numel() == B * Sk) and D in (32, 64) \
+                and os.environ.get('HETU_FLASH_ATTN', '1') == '1':
+            # one kernel, scores stay in TMEM / shared memory (csrc/attention_sm100.cu)
+            q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
+            out = torch.empty_like(q)
+            self.lse = torch.empty((B, H, S), dtype=torch.float32, device=q.device)
+            self.probs = None
+            m = mask.contiguous() if mask is not None else None
+            L.call('flash_attn_fwd', L.p(q), L.p(k), L.p(v), L.p(m), L.p(out), L.p(self.lse), L.c_int(B), L.c_int(H),
+                   L.c_int(S), L.c_int(Sk), L.c_int(D), L.c_f32(scale), L.stream_ptr(q.device))
+            self.flash_launches = getattr(self, 'flash_launches', 0) + 1
+            return out
         if _k(q, k, v) and (mask is None or mask.numel() == B * Sk):
             from .linalg import gemm
             q3, k3, v3 = (t.contiguous().view(B * H, t.shape[2], D) for t in (q, k, v))
@@ -78,11 +91,17 @@ class FusedAttentionGradOp(Op):
         scale = fwd.scale if fwd.scale is not None else 1.0 / math.sqrt(q.shape[-1])
         B, H, S, D = q.shape
         Sk = k.shape[2]
-        if _k(q, k, v, do, o) and getattr(fwd, 'probs', None) is not None \
-                and (mask is None or mask.numel() == B * Sk):
+        have_p = getattr(fwd, 'probs', None) is not None
+        if _k(q, k, v, do, o) and (have_p or fwd.lse is not None) and (mask is None or mask.numel() == B * Sk):
             from .linalg import gemm
             q3, k3, v3, do3 = (t.contiguous().view(B * H, t.shape[2], D) for t in (q, k, v, do))
-            p = fwd.probs
+            if have_p:
+                p = fwd.probs
+            else:           # flash forward kept only the log-sum-exp: p = exp(q k^T * scale + mask - lse)
+                p = gemm(q3, k3, False, True)
+                m = mask.contiguous() if mask is not None else None
+                L.call('attn_probs_from_lse', L.p(p), L.p(m), L.p(fwd.lse), L.c_i64(B * H * S), L.c_int(Sk),
+                       L.c_i64(H * S), L.c_f32(scale), L.stream_ptr(q.device))
             dv = gemm(p, do3, True, False).view(B, H, Sk, D)     # P^T dO
             ds = gemm(do3, v3, False, True)                      # dP = dO V^T, turned into dS in place
             L.call('attn_softmax_bwd', L.p(p), L.p(ds), L.c_i64(B * H * S), L.c_int(Sk), L.c_f32(scale),

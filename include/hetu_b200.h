@@ -268,6 +268,14 @@ int hetu_moe_gate_grad_peer(const float* dout, const float* idx, const float* lo
 int hetu_attn_softmax(float* s, const float* mask, float* lse, long long rows, int cols, long long rows_per_batch,
                       float scale, cudaStream_t st);
 int hetu_attn_softmax_bwd(const float* p, float* dp, long long rows, int cols, float scale, cudaStream_t st);
+/* s (raw scores q k^T) <- exp(s * scale + mask - lse[row]): probabilities recomputed for the backward pass */
+int hetu_attn_probs_from_lse(float* s, const float* mask, const float* lse, long long rows, int cols,
+                             long long rows_per_batch, float scale, cudaStream_t st);
+/* flash-style forward in one tcgen05 kernel (csrc/attention_sm100.cu): q [B,H,S,D], k/v [B,H,Sk,D] fp32 contiguous,
+ * additive key mask [B,Sk] or null, lse [B,H,S] or null; D = 32 or 64.  The reference builds attention from five ops
+ * (examples/nlp/bert/hetu_bert.py:249-264). */
+int hetu_flash_attn_fwd(const float* q, const float* k, const float* v, const float* mask, float* out, float* lse,
+                        int B, int H, int S, int Sk, int D, float scale, cudaStream_t st);
 
 /* ---- symmetric heap + in-kernel NVLink collectives (csrc/collectives.cu) ----------------------
  * reference: src/communication/mpi_nccl_communication.cu:31-483 (NCCL wrappers) and

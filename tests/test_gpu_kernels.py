@@ -469,3 +469,33 @@ def test_gemm_skinny_weight_gradient(m, n, k, tB):
     ref = a.double().t() @ (b.double().t() if tB else b.double())
     out = gemm(a, b, True, tB)
     assert (out.double() - ref).abs().max().item() <= 1e-4 * ref.abs().max().item() + 1e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('B,H,S,Sk,D,masked', [(2, 3, 128, 128, 64, False), (2, 2, 200, 333, 64, True), (3, 2, 77, 50, 32, True),
+                                               (1, 2, 512, 512, 64, False), (1, 1, 130, 1000, 64, True)])
+def test_flash_attention_forward_kernel(B, H, S, Sk, D, masked):
+    """csrc/attention_sm100.cu (one tcgen05 kernel: QK^T -> online softmax -> PV) against fp64 torch: output and
+    log-sum-exp, ragged tile edges, additive key mask, several key blocks."""
+    from hetu_61a7_b200 import _lib as L
+    q, k, v = rnd(B, H, S, D, scale=0.7), rnd(B, H, Sk, D, seed=1, scale=0.7), rnd(B, H, Sk, D, seed=2)
+    mask = None
+    if masked:
+        mask = ((torch.rand(B, Sk, generator=torch.Generator().manual_seed(3)) > 0.75).float() * -1e4).to(dev())
+    out = torch.empty_like(q)
+    lse = torch.empty(B, H, S, device=dev())
+    scale = 1.0 / np.sqrt(D)
+    L.call('flash_attn_fwd', L.p(q), L.p(k), L.p(v), L.p(mask), L.p(out), L.p(lse), L.c_int(B), L.c_int(H), L.c_int(S),
+           L.c_int(Sk), L.c_int(D), L.c_f32(scale), L.stream_ptr(dev()))
+    s = q.double() @ k.double().transpose(-1, -2) * scale
+    if mask is not None:
+        s = s + mask.double().view(B, 1, 1, Sk)
+    ref = torch.softmax(s, -1) @ v.double()
+    assert (out.double() - ref).abs().max().item() <= 4e-3 * ref.abs().max().item()
+    torch.testing.assert_close(lse.double(), torch.logsumexp(s, -1), rtol=2e-3, atol=2e-3)
+
+
+@pytest.mark.gpu
+def test_fused_attention_without_flash_kernel(L, monkeypatch):
+    monkeypatch.setenv('HETU_FLASH_ATTN', '0')
+    test_fused_attention_gpu(L)
