@@ -6,7 +6,7 @@
 //   one CTA per (128 query rows, batch*head); warp 4 lane 0 issues TMA and MMA, warps 0-3 own the TMEM lane quadrants
 //   (thread = query row) and do the online softmax.
 //
-//   per key block j (64 or 128 keys):  K_j, V_j by TMA (fp32, 128B swizzle; V as an MN-major operand, so no transpose anywhere)
+//   per block j of 64 keys:  K_j, V_j by TMA (fp32, 128B swizzle; V as an MN-major operand, so no transpose anywhere)
 //                         S    = Q K_j^T          tcgen05.mma kind::tf32 -> TMEM columns [0, BN)
 //                         p    = exp(S * scale + mask - m_new) in registers, row max / sum updated, O rescaled
 //                         P   -> shared memory, written by the row's thread in the K-major swizzle-128B layout
@@ -30,9 +30,28 @@ struct FaSmem {
     static constexpr int kVBytes = FA_BN * D * 4;                 // FA_BN/32 key blocks x D/32 groups of [32 keys][128 B]
     static constexpr int kPBytes = FA_BM * FA_BN * 4;             // FA_BN/32 tiles of [128 rows][128 B]
     static constexpr int kTmemCols = (FA_BN + D) <= 128 ? 128 : 256;
-    static constexpr int kTotal = kQBytes + kKBytes + kVBytes + kPBytes + 1024 /*alignment*/ + 128 /*barriers*/;
+    static constexpr int kTotal = kQBytes + kKBytes + kVBytes + kPBytes + 1024 /*alignment*/ + 1024 /*barriers, per-key bias*/;
 };
 
+__device__ __forceinline__ float fast_exp2(float x) {        // MUFU.EX2, flush-to-zero; exp2(-inf) = 0
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+// wait of the many softmax threads: back off between polls so the spin does not take issue slots from working warps
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+    uint32_t done, addr = smem_u32(bar);
+    for (;;) {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}" : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (done) break;
+        __nanosleep(40);
+    }
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -56,6 +75,7 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     uint64_t* barP = bars + 4;      // P_j in shared memory (128 arrivals)
     uint64_t* barO = bars + 5;      // PV_j in TMEM (tcgen05.commit)
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 6);
+    float* bias_s = reinterpret_cast<float*>(bars + 16);        // [2][FA_BN] per-key additive term of the current block
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q0 = blockIdx.x * FA_BM;
@@ -98,11 +118,7 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             // instruction descriptors: D = f32, A = B = tf32, N >> 3 @17, M >> 4 @24; bit 16 = B is MN-major
             const uint32_t idesc_s = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(FA_BN >> 3) << 17) | ((uint32_t)(FA_BM >> 4) << 24);
             const uint32_t idesc_o = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 16) | ((uint32_t)(D >> 3) << 17) | ((uint32_t)(FA_BM >> 4) << 24);
-            mbar_wait(barQ, 0);
-            for (int j = 0; j < nblk; ++j) {
-                const uint32_t ph = j & 1;
-                mbar_wait(barK, ph);
-                tc_fence_after();
+            auto mma_s = [&]() {                          // S = Q K_j^T
 #pragma unroll
                 for (int kb = 0; kb < D / 32; ++kb)
 #pragma unroll
@@ -112,9 +128,16 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                         umma_tf32(tmem_S, a, b, idesc_s, (kb > 0 || ki > 0) ? 1u : 0u);
                     }
                 umma_commit(barS);
+            };
+            mbar_wait(barQ, 0);
+            mbar_wait(barK, 0);
+            tc_fence_after();
+            mma_s();
+            for (int j = 0; j < nblk; ++j) {
+                const uint32_t ph = j & 1;
                 mbar_wait(barS, ph);                      // K_j consumed: fetch the next block under the softmax
                 if (j + 1 < nblk) load_k(j + 1);
-                mbar_wait(barP, ph);                      // P_j written by the softmax warps
+                mbar_wait(barP, ph);                      // P_j written, S_j read by every softmax thread
                 mbar_wait(barV, ph);
                 tc_fence_after();
 #pragma unroll
@@ -126,6 +149,11 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                         umma_tf32(tmem_PV, a, b, idesc_o, (kb > 0 || ki > 0) ? 1u : 0u);
                     }
                 umma_commit(barO);
+                if (j + 1 < nblk) {                       // S_{j+1} right behind PV_j: ready when the softmax warps return
+                    mbar_wait(barK, ph ^ 1);
+                    tc_fence_after();
+                    mma_s();
+                }
                 mbar_wait(barO, ph);                      // V_j and P_j consumed
                 if (j + 1 < nblk) load_v(j + 1);
             }
@@ -136,6 +164,9 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
         const int b = bh / heads;
         const float* mrow = mask ? mask + (size_t)b * Sk : nullptr;
+        // scores are kept in the log2 domain: t = s * scale * log2(e) (+ mask * log2(e)), p = 2^(t - m)
+        constexpr float kLog2e = 1.4426950408889634f;
+        const float sl2 = scale * kLog2e;
         float m = -INFINITY, l = 0.f;
         float o[D];
 #pragma unroll
@@ -143,55 +174,84 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         for (int j = 0; j < nblk; ++j) {
             const uint32_t ph = j & 1;
             const int kv0 = j * FA_BN;
-            mbar_wait(barS, ph);
+            // additive term per key (mask, -inf beyond the last key), staged once per block instead of two compares
+            // and a predicated load per element; blocks without one (the common case) skip it altogether
+            const bool biased = (mrow != nullptr) || (kv0 + FA_BN > Sk) || !(sl2 > 0.f);
+            const float* bj = bias_s + (j & 1) * FA_BN;
+            if (biased) {
+                if (r < FA_BN) {
+                    const int kv = kv0 + r;
+                    bias_s[(j & 1) * FA_BN + r] = kv < Sk ? (mrow != nullptr ? __ldg(mrow + kv) * kLog2e : 0.f) : -INFINITY;
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");      // the four softmax warps only
+            }
+            mbar_wait_backoff(barS, ph);
             tc_fence_after();
             // pass 1 over the TMEM row: running maximum (32 columns in registers at a time)
             float mx = m;
+            if (!biased) {
+                float raw = -INFINITY;
 #pragma unroll 1
-            for (int c0 = 0; c0 < FA_BN; c0 += 32) {
-                float s[32];
-                tmem_ld32(tmem_S + lane_off + (uint32_t)c0, s);
+                for (int c0 = 0; c0 < FA_BN; c0 += 32) {
+                    float s[32];
+                    tmem_ld32(tmem_S + lane_off + (uint32_t)c0, s);
 #pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    const int kv = kv0 + c0 + c;
-                    float v = s[c] * scale;
-                    if (mrow != nullptr && kv < Sk) v += __ldg(mrow + kv);
-                    if (kv >= Sk) v = -INFINITY;
-                    mx = fmaxf(mx, v);
+                    for (int c = 0; c < 32; ++c) raw = fmaxf(raw, s[c]);
+                }
+                mx = fmaxf(mx, raw * sl2);                        // sl2 > 0 here
+            } else {
+#pragma unroll 1
+                for (int c0 = 0; c0 < FA_BN; c0 += 32) {
+                    float s[32];
+                    tmem_ld32(tmem_S + lane_off + (uint32_t)c0, s);
+#pragma unroll
+                    for (int c = 0; c < 32; c += 4) {
+                        const float4 b4 = *reinterpret_cast<const float4*>(bj + c0 + c);
+                        mx = fmaxf(mx, fmaxf(fmaxf(fmaf(s[c], sl2, b4.x), fmaf(s[c + 1], sl2, b4.y)),
+                                             fmaxf(fmaf(s[c + 2], sl2, b4.z), fmaf(s[c + 3], sl2, b4.w))));
+                    }
                 }
             }
-            const float m_use = (mx == -INFINITY) ? 0.f : mx;     // fully masked so far: exp(-inf - 0) = 0
-            const float corr = __expf(m - m_use);                 // m = -inf -> 0
-            // pass 2: p = exp(s - m), row sum, P_j -> shared memory in the K-major swizzle-128B layout:
+            const float m_use = (mx == -INFINITY) ? 0.f : mx;     // fully masked so far: exp2(-inf - 0) = 0
+            const float corr = fast_exp2(m - m_use);              // m = -inf -> 0
+            const float neg_m = -m_use;
+            // pass 2: p = 2^(t - m), row sum, P_j -> shared memory in the K-major swizzle-128B layout:
             // tile kb = 32 keys, row r at r * 128 B, 16-byte chunk index ^ (r & 7)
             float sum = 0.f;
 #pragma unroll 1
             for (int c0 = 0; c0 < FA_BN; c0 += 32) {
                 float s[32];
                 tmem_ld32(tmem_S + lane_off + (uint32_t)c0, s);
+                if (!biased) {
 #pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    const int kv = kv0 + c0 + c;
-                    float v = s[c] * scale;
-                    if (mrow != nullptr && kv < Sk) v += __ldg(mrow + kv);
-                    if (kv >= Sk) v = -INFINITY;
-                    const float e = __expf(v - m_use);
-                    s[c] = e;
-                    sum += e;
+                    for (int c = 0; c < 32; ++c) s[c] = fast_exp2(fmaf(s[c], sl2, neg_m));
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 32; c += 4) {
+                        const float4 b4 = *reinterpret_cast<const float4*>(bj + c0 + c);
+                        s[c] = fast_exp2(fmaf(s[c], sl2, b4.x) + neg_m);
+                        s[c + 1] = fast_exp2(fmaf(s[c + 1], sl2, b4.y) + neg_m);
+                        s[c + 2] = fast_exp2(fmaf(s[c + 2], sl2, b4.z) + neg_m);
+                        s[c + 3] = fast_exp2(fmaf(s[c + 3], sl2, b4.w) + neg_m);
+                    }
                 }
                 uint8_t* trow = smP + (c0 >> 5) * (FA_BM * 128) + r * 128;
 #pragma unroll
-                for (int ch = 0; ch < 8; ++ch)
+                for (int ch = 0; ch < 8; ++ch) {
+                    sum += (s[4 * ch] + s[4 * ch + 1]) + (s[4 * ch + 2] + s[4 * ch + 3]);
                     *reinterpret_cast<float4*>(trow + ((ch ^ (r & 7)) << 4)) = make_float4(s[4 * ch], s[4 * ch + 1], s[4 * ch + 2], s[4 * ch + 3]);
+                }
             }
             l = l * corr + sum;
             m = mx;
             fence_proxy_async();                          // generic-proxy stores -> visible to the tensor core's reads
             tc_fence_before();                            // and our TMEM loads of S_j are done before S_{j+1} overwrites it
             mbar_arrive(barP);
+            if (__any_sync(0xffffffffu, corr != 1.f)) {       // the running maximum rarely moves after the first blocks
 #pragma unroll
-            for (int c = 0; c < D; ++c) o[c] *= corr;
-            mbar_wait(barO, ph);
+                for (int c = 0; c < D; ++c) o[c] *= corr;
+            }
+            mbar_wait_backoff(barO, ph);
             tc_fence_after();
 #pragma unroll
             for (int c0 = 0; c0 < D; c0 += 32) {
@@ -208,7 +268,7 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             float4* dst = reinterpret_cast<float4*>(O + ((size_t)bh * S + row) * D);
 #pragma unroll
             for (int c = 0; c < D; c += 4) dst[c >> 2] = make_float4(o[c] * inv, o[c + 1] * inv, o[c + 2] * inv, o[c + 3] * inv);
-            if (lse != nullptr) lse[(size_t)bh * S + row] = (l > 0.f) ? m + __logf(l) : -INFINITY;
+            if (lse != nullptr) lse[(size_t)bh * S + row] = (l > 0.f) ? (m + log2f(l)) * 0.6931471805599453f : -INFINITY;
         }
     }
     tc_fence_before();
@@ -247,11 +307,9 @@ HETU_API int hetu_flash_attn_fwd(const float* q, const float* k, const float* v,
         return -1;
     }
     int rc;
-    static int bn = -1;             // keys per block: 64 lets two CTAs share an SM (one's softmax under the other's MMAs)
-    if (bn < 0) { const char* e = getenv("HETU_FLASH_BN"); bn = (e && atoi(e) == 128) ? 128 : 64; }
-    if (D == 64 && bn == 128) rc = launch_flash_fwd<64, 128>(q, k, v, mask, out, lse, B, H, S, Sk, scale, st);
-    else if (D == 64) rc = launch_flash_fwd<64, 64>(q, k, v, mask, out, lse, B, H, S, Sk, scale, st);
-    else if (D == 32 && bn == 128) rc = launch_flash_fwd<32, 128>(q, k, v, mask, out, lse, B, H, S, Sk, scale, st);
+    // 64 keys per block: 96 KB of shared memory, so two CTAs share an SM and one's softmax runs under the other's MMAs
+    // (128 keys per block, one CTA per SM, measured 35% slower)
+    if (D == 64) rc = launch_flash_fwd<64, 64>(q, k, v, mask, out, lse, B, H, S, Sk, scale, st);
     else if (D == 32) rc = launch_flash_fwd<32, 64>(q, k, v, mask, out, lse, B, H, S, Sk, scale, st);
     else { hetu_set_error("flash_attn_fwd: head dimension %d not supported (32 or 64)", D); return -1; }
     if (rc) return rc;
