@@ -69,6 +69,12 @@ def main():
     shapes = [(32768, 2048, 2048, False, False), (32768, 2048, 2048, False, True), (2048, 2048, 32768, True, False),
               (16384, 2048, 2048, False, False), (4096, 4096, 1024, False, False), (4096, 1024, 4096, False, False),
               (8192, 8192, 8192, False, False), (4096, 4096, 4096, False, True)]
+    if os.environ.get('GEMM_BENCH_SHAPES') == 'bert':       # the products of one BERT-large / BERT-base layer at 4096 tokens
+        shapes = []
+        for h, f in ((1024, 4096), (768, 3072)):
+            shapes += [(4096, h, h, False, False), (4096, f, h, False, False), (4096, h, f, False, False),
+                       (4096, h, h, False, True), (4096, h, f, False, True), (4096, f, h, False, True),
+                       (h, h, 4096, True, False), (h, f, 4096, True, False), (f, h, 4096, True, False)]
     flush = torch.empty(256 * 1024 * 1024 // 4, device=dev)
     clk = Clocks()
     time.sleep(0.3)
@@ -83,6 +89,12 @@ def main():
         linalg.set_matmul_precision('tf32')
         ms_tf32 = timed(lambda: gemm(a, b, tA, tB), flush)
         ms_cublas_tf32 = timed(lambda: torch.matmul(aa, bb), flush)
+        if os.environ.get('GEMM_BENCH_SHAPES') == 'bert':
+            t1 = time.time()
+            emit('M%6d N%6d K%6d tA=%d tB=%d | tf32 %7.1f TFLOP/s %7.1f us (cuBLAS %7.1f, x%.2f) | %s' % (
+                m, n, k, tA, tB, flops / ms_tf32 / 1e9, ms_tf32 * 1e3, flops / ms_cublas_tf32 / 1e9, ms_cublas_tf32 / ms_tf32,
+                clk.window(t0, t1)))
+            continue
         linalg.set_matmul_precision('bf16')
         ms_bf16 = timed(lambda: gemm(a, b, tA, tB), flush)            # includes the fp32 -> bf16 operand conversion
         ms_cublas_bf16 = timed(lambda: torch.matmul(a16, b16), flush)  # operands already bf16

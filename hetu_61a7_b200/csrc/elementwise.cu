@@ -298,3 +298,24 @@ HETU_API int hetu_one_hot(const float* idx, float* out, size_t n, int classes, c
     HETU_CHECK_LAUNCH("hetu_one_hot");
     return 0;
 }
+
+// ---------------------------------------------------------------- 3xTF32 operand split
+// x = hi + lo with hi the nearest tf32 value (10 explicit mantissa bits) and lo = x - hi (exact in fp32).
+// ops/linalg.py runs A B as A_lo B_hi + A_hi B_lo + A_hi B_hi on the tensor cores: fp32-faithful products at a
+// third of the tf32 rate instead of the CUDA-core rate (reference precision: cublasSgemm, src/ops/MatrixMult.cu:22-26).
+__global__ void __launch_bounds__(256) split_tf32_kernel(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo,
+                                                         size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float v = x[i];
+        const uint32_t b = __float_as_uint(v);
+        const float h = ((b & 0x7f800000u) == 0x7f800000u) ? v : __uint_as_float((b + 0x1000u) & 0xffffe000u);
+        hi[i] = h;
+        lo[i] = v - h;
+    }
+}
+HETU_API int hetu_split_tf32(const float* x, float* hi, float* lo, size_t n, cudaStream_t s) {
+    if (n == 0) return 0;
+    split_tf32_kernel<<<ew_grid(n, 256), 256, 0, s>>>(x, hi, lo, n);
+    HETU_CHECK_LAUNCH("hetu_split_tf32");
+    return 0;
+}

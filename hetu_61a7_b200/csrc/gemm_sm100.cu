@@ -684,7 +684,12 @@ static int launch_tc_2sm(const float* A, const float* B, GemmParams& p, int batc
     if (use_streamk < 0) { const char* e = getenv("HETU_GEMM_STREAMK"); use_streamk = (e && e[0] == '1') ? 1 : 0; }   // opt-in: measured slower than whole tiles (atomics + lost L2 lockstep)
     // few output tiles but a very long K (weight gradients of convolutions / small layers): without
     // splitting K only num_tiles CTA pairs would work, so stream-K is always used there
-    const bool starved = num_tiles * 4 <= maxc && num_kb >= 256;
+    // (round 2: from 64 k-blocks on, and also when a single wave fills at most 60% of the CTA pairs - the weight
+    // gradients of transformer layers, e.g. 1024 x 1024 x 4096: 32 one-SM CTAs took 74 us, cuBLAS 25 us)
+    static int sk_policy = -1;
+    if (sk_policy < 0) { const char* e = getenv("HETU_GEMM_STREAMK_POLICY"); sk_policy = (e && e[0] == '0') ? 0 : 1; }
+    const int min_kb = sk_policy ? 64 : 256;
+    const bool starved = (num_tiles * 4 <= maxc || (sk_policy && waves == 1 && eff <= 0.6)) && num_kb >= min_kb;
     if ((starved || (use_streamk && eff < 0.9 && num_kb >= 128)) && p.beta == 0.f && p.act == ACT_NONE && p.rs_world <= 1 &&
         p.ag_world <= 1 && (long long)num_tiles * num_kb >= 8LL * maxc) {
         clusters = maxc;
@@ -1179,9 +1184,15 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
         // per-CTA set-up of the one-shot kernel costs more than the MMAs wasted on the empty part of the
         // 256-wide tile); and few-tile / long-K products, which it runs as stream-K
         const long long tiles_256 = (long long)((M + 255) / 256) * ((N + 255) / 256) * batch;
-        const bool big2 = M >= 512 && N >= 256 && (double)M * N * batch * K >= 74.0 * 256 * 256 * 1024;
+        static double min2 = -1.0;      // smallest product (MACs) sent to the 2-SM kernel; HETU_GEMM_2SM_MIN_MACS overrides
+        if (min2 < 0) { const char* e = getenv("HETU_GEMM_2SM_MIN_MACS"); min2 = e ? atof(e) : 74.0 * 256 * 256 * 1024; }
+        const bool big2 = M >= 512 && N >= 256 && (double)M * N * batch * K >= min2;
         const bool tall = M >= 8192 && N >= 64 && K >= 64;
-        const bool starved = tiles_256 * 4 <= 74 && K >= 8192 && M >= 32 && N >= 32 && beta == 0.f && act == ACT_NONE;
+        static int sk_policy = -1;
+        if (sk_policy < 0) { const char* e = getenv("HETU_GEMM_STREAMK_POLICY"); sk_policy = (e && e[0] == '0') ? 0 : 1; }
+        const bool starved = sk_policy ? ((tiles_256 * 4 <= 74 || (tiles_256 <= 44 && M >= 256 && N >= 256)) && K >= 2048 && M >= 32 &&
+                                          N >= 32 && beta == 0.f && act == ACT_NONE)
+                                       : (tiles_256 * 4 <= 74 && K >= 8192 && M >= 32 && N >= 32 && beta == 0.f && act == ACT_NONE);
         if (use_2sm && (big2 || tall || starved))
             rc = launch_tc_2sm(A, B, p, batch, sA, sB, s);
         else if (N > 128) rc = launch_tc<256>(A, B, p, batch, sA, sB, s);

@@ -31,13 +31,15 @@ from ..ndarray import ND_Sparse_Array
 ACT_NONE, ACT_RELU, ACT_GELU, ACT_SIGMOID = 0, 1, 2, 3
 ACT_RELU_MASK = 4      # tensor-core kernels only: out holds h on entry, out = (h > 0) ? A @ B : 0  (csrc/gemm_sm100.cu)
 _PRECISION = {'mode': os.environ.get('HETU_MATMUL_PRECISION', 'tf32')}
-_MODE_CODE = {'tf32': 0, 'fp32': 1, 'bf16': 3, 'fp16': 4}
+_MODE_CODE = {'tf32': 0, 'fp32': 1, 'bf16': 3, 'fp16': 4, '3xtf32': 1}     # 3xtf32: small products run as exact fp32
 
 
 def set_matmul_precision(mode: str) -> None:
     """'tf32' (default: tcgen05 kind::tf32, fp32 accumulate), 'fp32' (FFMA, exact), 'bf16' / 'fp16' (operands
     rounded to 16 bit on the fly, tcgen05 kind::f16, fp32 accumulate; products too small for the tensor-core
-    path run as tf32)."""
+    path run as tf32), '3xtf32' (fp32-faithful on the tensor cores: every operand is split into its nearest tf32
+    value and the remainder, A B = A_lo B_hi + A_hi B_lo + A_hi B_hi, three tcgen05 products with fp32 accumulation;
+    products too small for the tensor-core path run as exact fp32)."""
     assert mode in _MODE_CODE
     _PRECISION['mode'] = mode
 
@@ -53,7 +55,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, trans_a=False, trans_b=False, bias=No
         return _gemm_torch(a, b, trans_a, trans_b, bias, c_in, alpha, beta, act)
     a = a if a.is_contiguous() else a.contiguous()
     b = b if b.is_contiguous() else b.contiguous()
-    if a.dim() == 2 and b.dim() == 2 and _PRECISION['mode'] != 'fp32':
+    if _PRECISION['mode'] == '3xtf32' and act != ACT_RELU_MASK:
+        r = _gemm_3xtf32(a, b, trans_a, trans_b, bias, c_in, alpha, beta, act, out)
+        if r is not None:
+            return r
+    if a.dim() == 2 and b.dim() == 2 and _PRECISION['mode'] not in ('fp32', '3xtf32'):
         padded = _pad_for_tma(a, b, trans_a, trans_b, bias, c_in, alpha, beta, act)
         if padded is not None:
             return padded
@@ -101,6 +107,35 @@ def gemm(a: torch.Tensor, b: torch.Tensor, trans_a=False, trans_b=False, bias=No
            L.c_int(int(trans_a)), L.c_int(int(trans_b)), L.c_int(batch), L.c_i64(sa), L.c_i64(sb),
            L.c_i64(am * bn), L.c_f32(alpha), L.c_f32(beta), L.c_int(act),
            L.c_int(_MODE_CODE[_PRECISION['mode']]), L.stream_ptr(a.device))
+    return c
+
+
+def _split_tf32(t):
+    hi, lo = torch.empty_like(t), torch.empty_like(t)
+    L.call('split_tf32', L.p(t), L.p(hi), L.p(lo), L.c_sz(t.numel()), L.stream_ptr(t.device))
+    return hi, lo
+
+
+def _gemm_3xtf32(a, b, trans_a, trans_b, bias, c_in, alpha, beta, act, out):
+    """Three tf32 tensor-core products of the split operands; None when the product would not take the tensor-core
+    path anyway (too small, or a row pitch TMA cannot describe) - the caller then runs it as exact fp32."""
+    am, ak = ((a.shape[-1], a.shape[-2]) if trans_a else (a.shape[-2], a.shape[-1]))
+    bn = b.shape[-2] if trans_b else b.shape[-1]
+    batch = a.shape[0] if a.dim() == 3 else 1
+    a_inner, b_inner = (am if trans_a else ak), (ak if trans_b else bn)
+    if not (float(am) * bn * ak * batch > float(1 << 25) and am >= 64 and bn > 8 and ak >= 32
+            and a_inner % 4 == 0 and b_inner % 4 == 0):
+        return None
+    a_hi, a_lo = _split_tf32(a)
+    b_hi, b_lo = _split_tf32(b)
+    saved = _PRECISION['mode']
+    _PRECISION['mode'] = 'tf32'
+    try:
+        c = gemm(a_lo, b_hi, trans_a, trans_b, c_in=c_in, alpha=alpha, beta=beta, out=out if c_in is None else None)
+        c = gemm(a_hi, b_lo, trans_a, trans_b, c_in=c, alpha=alpha, beta=1.0, out=c)
+        c = gemm(a_hi, b_hi, trans_a, trans_b, bias=bias, c_in=c, alpha=alpha, beta=1.0, act=act, out=c)
+    finally:
+        _PRECISION['mode'] = saved
     return c
 
 

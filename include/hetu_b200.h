@@ -59,6 +59,8 @@ int hetu_unary(int op, const float* x, float* y, size_t n, float a, float b, cud
 int hetu_binary(int op, const float* x, const float* y, float* o, size_t n, float a, cudaStream_t s);
 /* mode 0: y[inner] broadcast over rows (bias); mode 1: y[outer] broadcast along each row. */
 int hetu_binary_bcast(int op, const float* x, const float* y, float* o, size_t n, size_t inner, int mode, cudaStream_t s);
+/* hi = nearest tf32 value of x, lo = x - hi (operands of the 3xTF32 matmul mode) */
+int hetu_split_tf32(const float* x, float* hi, float* lo, size_t n, cudaStream_t s);
 int hetu_where(const float* c, const float* a, const float* b, float* o, size_t n, cudaStream_t s);
 /* generic strided copy (transpose/slice/concat/pad/broadcast): reference
  * src/ops/{Transpose,Slice,Concat,Concatenate,Pad,Broadcast,BroadcastShape}.cu */

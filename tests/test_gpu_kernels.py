@@ -499,3 +499,45 @@ def test_flash_attention_forward_kernel(B, H, S, Sk, D, masked):
 def test_fused_attention_without_flash_kernel(L, monkeypatch):
     monkeypatch.setenv('HETU_FLASH_ATTN', '0')
     test_fused_attention_gpu(L)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('m,n,k,tA,tB', [(1024, 768, 2048, False, False), (900, 516, 1000, True, False), (512, 512, 4096, False, True)])
+def test_gemm_3xtf32_is_fp32_faithful(m, n, k, tA, tB):
+    """set_matmul_precision('3xtf32'): three tensor-core products of split operands reproduce the fp32 product to
+    ~1e-6 of its magnitude (plain tf32: ~1e-3), with the fused epilogue and the accumulate path."""
+    from hetu_61a7_b200.ops import linalg
+    a = rnd(k, m) if tA else rnd(m, k)
+    b = rnd(n, k, seed=1) if tB else rnd(k, n, seed=1)
+    bias, c0 = rnd(n, seed=2), rnd(m, n, seed=3)
+    A = a.double().t() if tA else a.double()
+    Bm = b.double().t() if tB else b.double()
+    ref = torch.relu(0.5 * (A @ Bm) + 2.0 * c0.double() + bias.double())
+    linalg.set_matmul_precision('3xtf32')
+    try:
+        out = linalg.gemm(a, b, tA, tB, bias=bias, c_in=c0, alpha=0.5, beta=2.0, act=linalg.ACT_RELU)
+        plain = linalg.gemm(a, b, tA, tB)
+    finally:
+        linalg.set_matmul_precision('tf32')
+    scale = (A.abs() @ Bm.abs()).max().item()
+    assert (out.double() - ref).abs().max().item() <= 3e-6 * scale
+    assert (plain.double() - A @ Bm).abs().max().item() <= 3e-6 * scale
+    tf = linalg.gemm(a, b, tA, tB)
+    assert (tf.double() - A @ Bm).abs().max().item() > 2e-5 * scale          # the plain tf32 product is visibly coarser
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('m,n,k,tA,tB', [(1024, 1024, 4096, True, False), (768, 3072, 4096, True, False), (768, 768, 2048, True, False),
+                                         (520, 1000, 2100, False, True), (3072, 768, 4096, True, False)])
+def test_gemm_stream_k_transformer_weight_gradients(m, n, k, tA, tB):
+    """Few output tiles, K of a few thousand (weight gradients of transformer layers): the persistent 2-SM kernel cuts
+    the k-blocks of all tiles into equal ranges per CTA pair and adds partial tiles with red.global."""
+    from hetu_61a7_b200.ops.linalg import gemm
+    a = rnd(k, m) if tA else rnd(m, k)
+    b = rnd(n, k, seed=1) if tB else rnd(k, n, seed=1)
+    bias = rnd(n, seed=2)
+    A = a.double().t() if tA else a.double()
+    Bm = b.double().t() if tB else b.double()
+    ref = A @ Bm + bias.double()
+    out = gemm(a, b, tA, tB, bias=bias)
+    assert (out.double() - ref).abs().max().item() <= 2e-3 * ref.abs().max().item()
