@@ -628,6 +628,49 @@ class Executor(object):
         pass
 
 
+def ctypes_void(h):
+    import ctypes
+    return ctypes.c_void_p(h)
+
+
+class _PlanFuture(object):
+    """Value of a result whose device->host copy was queued by the native step plan (csrc/step_plan.cu)."""
+
+    __slots__ = ('_fast', '_slot', '_step')
+
+    def __init__(self, fast, step):
+        self._fast, self._step, self._slot = fast, step, (step - 1) % 8
+
+    def ready(self):
+        return True
+
+    def get(self):
+        fast = self._fast
+        if fast['steps'] - self._step >= 8:
+            raise RuntimeError('result of step %d was overwritten: at most 8 read-backs may be outstanding' % self._step)
+        if not fast.get('dead'):                         # a dropped plan has drained its streams already
+            rc = fast['rb']['wait'](fast['handle'], self._slot)
+            if rc != 0:
+                L.check(rc, 'step_plan_wait')
+        return fast['rb']['ring'][self._slot].copy()
+
+
+class _PlanResult(NDArray):
+    """Result handle returned by the native steady-state path: ``asnumpy_async`` costs no extra copy."""
+
+    __slots__ = ('_fast',)
+
+    def __init__(self, tensor, ctx, fast):
+        super().__init__(tensor, ctx)
+        self._fast = fast
+
+    def asnumpy_async(self):
+        fast = self._fast
+        if fast.get('dead') or fast['steps'] == 0:
+            return super().asnumpy_async()
+        return _PlanFuture(fast, fast['steps'])
+
+
 class SubExecutor(object):
     def __init__(self, name: str, eval_node_list: List[Op], config: HetuConfig):
         self.name = name
@@ -674,6 +717,9 @@ class SubExecutor(object):
         self._graph = None
         self._graph_key = None
         self._packed = None
+        self._fast = None                                # native steady-state plan (see _build_fast_plan)
+        self._fast_ok = False
+        self._graph_replays = 0
         self._static_in: Dict[Op, torch.Tensor] = {}
         self._stage: Dict[Op, torch.Tensor] = {}
         self._static_out: Dict[Op, object] = {}
@@ -785,6 +831,11 @@ class SubExecutor(object):
 
     # --------------------------------------------------------------------------- run
     def run(self, eval_node_list=[], feed_dict={}, convert_to_numpy_ret_vals=False, **kwargs):
+        fast = self._fast
+        if fast is not None:
+            if not feed_dict and not eval_node_list and not convert_to_numpy_ret_vals:
+                return self._fast_step(fast)
+            self._drop_fast_plan()                       # a differently shaped call: back to the general path
         eval_nodes = list(eval_node_list) if eval_node_list else getattr(self, 'result_nodes', self.eval_node_list)
         feeds: Dict[Op, object] = {}
         for node, value in feed_dict.items():
@@ -804,6 +855,9 @@ class SubExecutor(object):
         self.step_count += 1
         from ..parallel.comm import drain_sends
         drain_sends()
+        if self._fast is None and self._fast_ok and self._graph is not None and not feed_dict and not eval_node_list \
+                and not convert_to_numpy_ret_vals and self._graph_replays >= 2:
+            self._build_fast_plan(feeds, eval_nodes, vals)
         results = []
         for n in eval_nodes:
             v = vals.get(n)
@@ -897,6 +951,7 @@ class SubExecutor(object):
         key = self._graph_signature(feeds)
         if self._graph is not None and key != self._graph_key:
             # shapes changed (e.g. last partial batch): drop the graph, run eagerly
+            self._drop_fast_plan()
             self._graph = None
             self._eager_steps = 0
         if self._graph is None:
@@ -925,7 +980,9 @@ class SubExecutor(object):
                     if t.is_contiguous() and len(views) < 64:
                         views[t.data_ptr()] = src
                 np.copyto(dst[off:off + nbytes], src)
-            pk['dev'].copy_(host, non_blocking=True)
+            d = pk['dturn']
+            pk['dturn'] = d + 1 if d + 1 < pk['dslots'] else 0
+            pk['stage_slots'][d].copy_(host, non_blocking=True)      # the slot the graph's feed_select node reads next
             if ev is None:
                 ev = pk['events'][slot] = torch.cuda.Event()
             ev.record()
@@ -936,7 +993,114 @@ class SubExecutor(object):
                     st.copy_(t, non_blocking=True)
         self._mark_feeds_consumed()
         self._graph.replay()
+        self._graph_replays += 1
         return self._static_out
+
+    # ---- steady state in one native call (csrc/step_plan.cu): every input comes from a dataloader whose batches are fixed
+    # views of a pinned dataset and the step is a captured graph with one packed input buffer.  The plan holds the
+    # cudaGraphExec_t, the staging slots and the byte layout; a step is then: advance the batch indices, hand the batch
+    # pointers to hetu_step_plan_run (host slices -> pinned slot -> one H2D -> cudaGraphLaunch), return the cached result
+    # handles.  Any other kind of call drops the plan and goes through the general path again.
+    def _build_fast_plan(self, feeds, eval_nodes, vals):
+        import ctypes
+        self._fast_ok = False                            # one attempt per captured graph
+        pk = self._packed
+        if (os.environ.get('HETU_FAST_REPLAY', '1') != '1' or pk is None or not hasattr(self._graph, 'raw_cuda_graph_exec')
+                or not getattr(self, '_pf_off', False) or getattr(self, '_pf_done', None) or len(feeds) > 16
+                or set(feeds) != set(self.dataloader_nodes) or set(feeds) != set(pk['layout'])):
+            return
+        from ..parallel import comm as _comm
+        if getattr(_comm, '_PENDING', None):
+            return                                       # pipeline / p2p traffic: keep the general path
+        loaders = []
+        for i, node in enumerate(pk['layout']):
+            dl = getattr(node, 'dataloaders', {}).get(self.name)
+            if dl is None or getattr(dl, '_views', None) is None:
+                return
+            off, nbytes = pk['layout'][node]
+            if any(v.numel() * v.element_size() != nbytes or not v.is_contiguous() for v in dl._views):
+                return
+            loaders.append((dl, [v.data_ptr() for v in dl._views], i))
+        lib = L.require_cuda_lib()
+        lib.hetu_step_plan_create.restype = ctypes.c_void_p
+        lib.hetu_step_plan_run.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        lib.hetu_step_plan_destroy.argtypes = [ctypes.c_void_p]
+        lib.hetu_step_plan_destroy.restype = None
+        n = len(loaders)
+        offs = (ctypes.c_longlong * n)(*[pk['layout'][node][0] for node in pk['layout']])
+        sizes = (ctypes.c_longlong * n)(*[pk['layout'][node][1] for node in pk['layout']])
+        hosts = (ctypes.c_void_p * len(pk['host']))(*[h.data_ptr() for h in pk['host']])
+        stream = torch.cuda.current_stream(self.device)
+        stream.synchronize()                             # staging slots of the Python path are idle from here on
+        handle = lib.hetu_step_plan_create(ctypes.c_void_p(self._graph.raw_cuda_graph_exec()), ctypes.c_void_p(stream.cuda_stream),
+                                           ctypes.c_int(n), offs, sizes, hosts, ctypes.c_int(len(pk['host'])),
+                                           ctypes.c_void_p(pk['stage'].data_ptr()), ctypes.c_int(pk['dslots']),
+                                           ctypes.c_longlong(pk['total']), ctypes.c_int(pk['dturn']))
+        if not handle:
+            return
+        results = []
+        for nd in eval_nodes:
+            v = vals.get(nd)
+            if v is None or isinstance(nd, OptimizerOp):
+                results.append(None)
+            elif isinstance(v, IndexedSlices):
+                lib.hetu_step_plan_destroy(handle)
+                return
+            else:
+                results.append(NDArray(v, nd.ctx if isinstance(nd.ctx, DLContext) else None))
+        fast = {'handle': handle, 'run': lib.hetu_step_plan_run, 'destroy': lib.hetu_step_plan_destroy,
+                'src': (ctypes.c_void_p * n)(), 'loaders': loaders, 'results': results, 'stream': stream.cuda_stream,
+                'keep': [offs, sizes, hosts], 'rb': None, 'steps': 0}
+        # the first small result (the loss) is copied to pinned memory behind every step, so asnumpy_async() on it is free
+        if pk['rb'] is not None:
+            rb_node, dev_ring, numel = pk['rb']
+            for k, nd in enumerate(eval_nodes):
+                if nd is rb_node and results[k] is not None:
+                    t = results[k].tensor
+                    ring = [torch.empty(tuple(t.shape), dtype=t.dtype).pin_memory() for _ in range(8)]
+                    slots = (ctypes.c_void_p * 8)(*[b.data_ptr() for b in ring])
+                    lib.hetu_step_plan_wait.argtypes = [ctypes.c_void_p, ctypes.c_int]
+                    if lib.hetu_step_plan_set_readback(ctypes.c_void_p(handle), ctypes.c_void_p(dev_ring.data_ptr()),
+                                                       ctypes.c_longlong(numel * 4), slots, ctypes.c_int(8)) == 0:
+                        fast['rb'] = {'ring': [b.numpy() for b in ring], 'keep': (ring, slots), 'wait': lib.hetu_step_plan_wait}
+                        results[k] = _PlanResult(t, results[k]._ctx, fast)
+                    break
+        self._fast = fast
+
+    def _fast_step(self, fast):
+        if torch.cuda.current_stream(self.device).cuda_stream != fast['stream']:
+            self._drop_fast_plan()
+            return self.run()
+        self.config._running_name = self.name
+        src = fast['src']
+        for dl, ptrs, i in fast['loaders']:
+            b = dl.batch_index
+            src[i] = ptrs[b]
+            b = b + 1 if b + 1 < dl.batch_num else 0
+            dl.batch_index = b
+            dl.index = b * dl.batch_size
+            dl.reads += 1
+        self._pre_step()
+        rc = fast['run'](fast['handle'], src)
+        if rc != 0:
+            L.check(rc, 'step_plan_run')
+        L.launch_count += 1
+        fast['steps'] += 1
+        self._graph_replays += 1
+        self.step_count += 1
+        return list(fast['results'])
+
+    def _drop_fast_plan(self):
+        fast, self._fast = self._fast, None
+        if fast is not None:
+            torch.cuda.current_stream(self.device).synchronize()
+            fast['dead'] = True                          # outstanding result handles fall back to a plain copy
+            if self._packed is not None:
+                self._packed['dturn'] = int(L.require_cuda_lib().hetu_step_plan_dturn(ctypes_void(fast['handle'])))
+            fast['destroy'](fast['handle'])
+            pk = self._packed
+            if pk is not None:                           # the Python path starts from idle slots again
+                pk['events'] = [None] * len(pk['events'])
 
     def _capture(self, feeds, key):
         dev = self.device
@@ -957,8 +1121,14 @@ class SubExecutor(object):
                 total += (nbytes + 255) // 256 * 256
             dev_buf = torch.empty(total, dtype=torch.uint8, device=dev)
             hosts = [torch.empty(total, dtype=torch.uint8).pin_memory() for _ in range(4)]
+            # the graph does not read the H2D target directly: its first node copies device staging slot s into dev_buf and
+            # advances s ON THE DEVICE, so the copy of the next step's inputs can run beside the current replay
+            # (csrc/step_plan.cu); dturn mirrors s on the host
+            stage = torch.zeros(4 * total, dtype=torch.uint8, device=dev)
             self._packed = {'layout': layout, 'dev': dev_buf, 'host': hosts, 'host_np': [h.numpy() for h in hosts],
-                            'events': [None] * 4, 'turn': 0, 'views': {}}
+                            'events': [None] * 4, 'turn': 0, 'views': {}, 'stage': stage, 'dslots': 4, 'dturn': 0, 'total': total,
+                            'stage_slots': [stage[i * total:(i + 1) * total] for i in range(4)],
+                            'state': torch.zeros(2, dtype=torch.int32, device=dev), 'rb': None}
             for n, t in host_feeds:
                 off, nbytes = layout[n]
                 self._static_in[n] = dev_buf[off:off + nbytes].view(t.dtype).view(tuple(t.shape))
@@ -975,12 +1145,30 @@ class SubExecutor(object):
         vals: Dict[Op, object] = {}
         launches_before = L.launch_count
         with torch.cuda.graph(graph):
+            pk = self._packed
+            if pk is not None:
+                L.call('feed_select', L.p(pk['stage']), L.p(pk['dev']), L.c_i64(pk['total']), L.c_int(pk['dslots']), L.p(pk['state']),
+                       L.stream_ptr(dev))
             for node, st in self._static_in.items():
                 vals[node] = st
             self._compute_all(vals, release=False)
+            if pk is not None:
+                # the first small fp32 result (the loss) also goes into a device ring indexed by the same slot, so its
+                # read-back never races with the next replay
+                for nd in getattr(self, 'result_nodes', self.eval_node_list):
+                    v = vals.get(nd)
+                    if isinstance(v, torch.Tensor) and not isinstance(nd, OptimizerOp) and v.dtype == torch.float32 \
+                            and v.is_contiguous() and 0 < v.numel() <= 1024:
+                        ring = torch.zeros(pk['dslots'] * v.numel(), dtype=torch.float32, device=dev)
+                        L.call('result_publish', L.p(v), L.p(ring), L.c_int(v.numel()), L.p(pk['state']), L.stream_ptr(dev))
+                        pk['rb'] = (nd, ring, v.numel())
+                        break
+        self._drop_fast_plan()
         self._graph = graph
         self._graph_key = key
         self._static_out = vals
+        self._graph_replays = 0
+        self._fast_ok = True
         self.graph_launches = L.launch_count - launches_before   # native kernels per replay
         torch.cuda.synchronize(dev)
 

@@ -347,6 +347,20 @@ int hetu_moe_gate_fwd(const float* logits, float* P, int* blk_cnt, float* me, in
 int hetu_moe_gate_bwd(const float* logits, const float* P, void* const* dgates, const float* daux, float* dlogits,
                       int T, int E, int k, cudaStream_t s);
 
+/* ---- steady-state replay of a captured step (csrc/step_plan.cu).  The captured graph starts with hetu_feed_select
+ * (device staging slot s -> static input buffer, s advances on the device) and ends with hetu_result_publish (small
+ * result -> device ring slot s); hetu_step_plan_run then overlaps the H2D of the next step and the D2H of the last
+ * result with the graph: host slices -> pinned slot -> H2D on a copy stream -> cudaGraphLaunch -> D2H on a third stream. */
+int hetu_feed_select(const void* stage, void* dst, long long total, int nslots, int* state, cudaStream_t s);
+int hetu_result_publish(const float* src, float* ring, int n, const int* state, cudaStream_t s);
+void* hetu_step_plan_create(void* graph_exec, cudaStream_t stream, int n, const long long* off, const long long* nbytes,
+                            void* const* host_slots, int nslots, void* stage, int dslots, long long total, int dturn0);
+int hetu_step_plan_set_readback(void* plan, const void* dev_ring, long long nbytes, void* const* host_slots, int nslots);
+int hetu_step_plan_run(void* plan, void* const* src);
+int hetu_step_plan_wait(void* plan, int slot);
+int hetu_step_plan_dturn(void* plan);
+void hetu_step_plan_destroy(void* plan);
+
 #ifdef __cplusplus
 }
 #endif
