@@ -154,9 +154,8 @@ def test_step_monitor_jsonl_and_prometheus(tmp_path):
     import socket
     import urllib.request
     from hetu_61a7_b200.utils.monitor import StepMonitor
-    with socket.socket() as s:
-        s.bind(('127.0.0.1', 0))
-        port = s.getsockname()[1]
+    from conftest import free_port_block
+    port = free_port_block(2)
     path = str(tmp_path / 'metrics.jsonl')
     mon = StepMonitor(samples_per_step=128, log_path=path, prometheus_port=port, rank=0)
     for i in range(3):

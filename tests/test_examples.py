@@ -66,13 +66,8 @@ def test_transformer_data_pipeline(tmp_path):
 
 
 def _free_port_block(span=4):
-    import socket
-    while True:
-        with socket.socket() as s:
-            s.bind(('127.0.0.1', 0))
-            p = s.getsockname()[1]
-        if p + span < 65000:
-            return p
+    from conftest import free_port_block
+    return free_port_block(span)
 
 
 def test_gnn_on_sampled_subgraphs(tmp_path):

@@ -14,12 +14,8 @@ from graphmix.dataset import synthetic_dataset
 
 
 def _free_port(span=8):
-    while True:
-        with socket.socket() as s:
-            s.bind(('127.0.0.1', 0))
-            p = s.getsockname()[1]
-        if p + span < 65000:
-            return p
+    from conftest import free_port_block
+    return free_port_block(span)
 
 
 def _check_graph(ds, edge_set, g):

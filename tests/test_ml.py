@@ -252,9 +252,8 @@ def test_parallel_models_over_parameter_server(tmp_path):
     import sys
     import time
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    with socket.socket() as s:
-        s.bind(('127.0.0.1', 0))
-        port = s.getsockname()[1]
+    from conftest import free_port_block
+    port = free_port_block(2)
     sched = '127.0.0.1:%d' % port
     env = dict(os.environ, PYTHONPATH=root + os.pathsep + os.environ.get('PYTHONPATH', ''), OMP_NUM_THREADS='2')
     role = ("import sys; sys.path.insert(0, %r); from hetuml.cluster import Cluster; c = Cluster(%r, 1, 2, %%r); "

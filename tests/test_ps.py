@@ -12,9 +12,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _free_port():
-    with socket.socket() as s:
-        s.bind(('127.0.0.1', 0))
-        return s.getsockname()[1]
+    from conftest import free_port_block
+    return free_port_block(8)            # scheduler / servers / ring ranks bind base, base + 1, ...
 
 
 def test_ps_scheduler_2servers_2workers():

@@ -14,9 +14,8 @@ pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
 
 
 def test_gpu_het_cache_against_the_parameter_server():
-    with socket.socket() as s:
-        s.bind(('127.0.0.1', 0))
-        port = s.getsockname()[1]
+    from conftest import free_port_block
+    port = free_port_block(2)
     env = dict(os.environ, DMLC_PS_ROOT_URI='127.0.0.1', DMLC_PS_ROOT_PORT=str(port), DMLC_NUM_WORKER='1',
                DMLC_NUM_SERVER='1', PYTHONPATH=ROOT + os.pathsep + os.environ.get('PYTHONPATH', ''))
     procs = []
