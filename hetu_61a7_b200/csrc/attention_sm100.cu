@@ -52,20 +52,6 @@ __device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity
         __nanosleep(40);
     }
 }
-// 2^x for x <= 0 on the FMA / ALU pipes (no MUFU): round to the nearest integer n with the 1.5 * 2^23 trick, degree-4
-// polynomial for 2^f on f in [-0.5, 0.5] (relative error 4e-5, well below the tf32 rounding P goes through), n added to
-// the exponent field.  The kernel is bound by the 16 / clk / SM exp unit (ncu: XU pipe 88 % busy), so every other
-// element takes this path.  Inputs below -125 (masked keys: -inf) give 2^-125, i.e. nothing.
-__device__ __forceinline__ float poly_exp2(float x) {
-    x = fmaxf(x, -125.f);
-    const float r = x + 12582912.f;
-    const float f = x - (r - 12582912.f);
-    float p = fmaf(f, 0.009618129f, 0.05550411f);
-    p = fmaf(p, f, 0.2402265f);
-    p = fmaf(p, f, 0.6931472f);
-    p = fmaf(p, f, 1.0f);
-    return __int_as_float(__float_as_int(p) + (__float_as_int(r) << 23));
-}
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -238,18 +224,15 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
                 tmem_ld32(tmem_S + lane_off + (uint32_t)c0, s);
                 if (!biased) {
 #pragma unroll
-                    for (int c = 0; c < 32; c += 2) {                 // exp unit and FMA pipe share the work
-                        s[c] = fast_exp2(fmaf(s[c], sl2, neg_m));
-                        s[c + 1] = poly_exp2(fmaf(s[c + 1], sl2, neg_m));
-                    }
+                    for (int c = 0; c < 32; ++c) s[c] = fast_exp2(fmaf(s[c], sl2, neg_m));
                 } else {
 #pragma unroll
                     for (int c = 0; c < 32; c += 4) {
                         const float4 b4 = *reinterpret_cast<const float4*>(bj + c0 + c);
                         s[c] = fast_exp2(fmaf(s[c], sl2, b4.x) + neg_m);
-                        s[c + 1] = poly_exp2(fmaf(s[c + 1], sl2, b4.y) + neg_m);
+                        s[c + 1] = fast_exp2(fmaf(s[c + 1], sl2, b4.y) + neg_m);
                         s[c + 2] = fast_exp2(fmaf(s[c + 2], sl2, b4.z) + neg_m);
-                        s[c + 3] = poly_exp2(fmaf(s[c + 3], sl2, b4.w) + neg_m);
+                        s[c + 3] = fast_exp2(fmaf(s[c + 3], sl2, b4.w) + neg_m);
                     }
                 }
                 uint8_t* trow = smP + (c0 >> 5) * (FA_BM * 128) + r * 128;
