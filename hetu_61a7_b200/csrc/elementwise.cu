@@ -319,3 +319,33 @@ HETU_API int hetu_split_tf32(const float* x, float* hi, float* lo, size_t n, cud
     HETU_CHECK_LAUNCH("hetu_split_tf32");
     return 0;
 }
+
+// ---------------------------------------------------------------- batched 2-D transpose
+// src [B, R, C] -> dst [B, C, R] through 32 x 32 shared-memory tiles (both sides coalesced).  NCHW <-> NHWC changes
+// around the convolution GEMMs are this pattern; the generic strided copy does a 64-bit div / mod chain per element and
+// reads with a stride.
+__global__ void __launch_bounds__(256) transpose_batched_kernel(const float* __restrict__ src, float* __restrict__ dst, int R, int C) {
+    __shared__ float tile[32][33];
+    const size_t boff = (size_t)blockIdx.z * R * C;
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;          // 32 x 8
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+        const int r = r0 + ty + j, c = c0 + tx;
+        if (r < R && c < C) tile[ty + j][tx] = src[boff + (size_t)r * C + c];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+        const int c = c0 + ty + j, r = r0 + tx;
+        if (r < R && c < C) dst[boff + (size_t)c * R + r] = tile[tx][ty + j];
+    }
+}
+HETU_API int hetu_transpose_batched(const float* src, float* dst, int B, int R, int C, cudaStream_t s) {
+    if (B <= 0 || R <= 0 || C <= 0) return 0;
+    if (B > 65535) { hetu_set_error("transpose_batched: batch %d > 65535", B); return -1; }
+    dim3 grid((C + 31) / 32, (R + 31) / 32, B);
+    transpose_batched_kernel<<<grid, 256, 0, s>>>(src, dst, R, C);
+    HETU_CHECK_LAUNCH("hetu_transpose_batched");
+    return 0;
+}

@@ -1191,7 +1191,7 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
         static int sk_policy = -1;
         if (sk_policy < 0) { const char* e = getenv("HETU_GEMM_STREAMK_POLICY"); sk_policy = (e && e[0] == '0') ? 0 : 1; }
         const bool starved = sk_policy ? ((tiles_256 * 4 <= 74 || (tiles_256 <= 44 && M >= 256 && N >= 256)) && K >= 2048 && M >= 32 &&
-                                          N >= 32 && beta == 0.f && act == ACT_NONE)
+                                          N > kSkinnyN && beta == 0.f && act == ACT_NONE)   // e.g. conv1's weight gradient: 64 x 28 x 131072
                                        : (tiles_256 * 4 <= 74 && K >= 8192 && M >= 32 && N >= 32 && beta == 0.f && act == ACT_NONE);
         if (use_2sm && (big2 || tall || starved))
             rc = launch_tc_2sm(A, B, p, batch, sA, sB, s);

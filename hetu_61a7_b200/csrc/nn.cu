@@ -504,6 +504,55 @@ HETU_API int hetu_col2im(const float* col, float* x, int N, int C, int H, int W,
     return 0;
 }
 
+// same gather from the transposed layout colT [N, C*kh*kw, OH*OW] (what the batched GEMM W^T dY_n writes when dY stays
+// NCHW): neighbouring threads (w, w+1) read neighbouring ow of the same row, so the reads coalesce - the [N*OH*OW, C*kh*kw]
+// layout above makes every thread of a warp touch its own 32-byte sector
+// grid: x = pixel blocks of one (image, channel) plane, y = plane.  All index arithmetic is 32-bit and the stride is a
+// template parameter: the generic kernel above spends ~400 instructions per element on 64-bit div / mod and `% stride`,
+// which - not memory - was its limit (235 us for a 302 MB buffer).
+template <int S>
+__global__ void __launch_bounds__(256) col2im_t_kernel(const float* __restrict__ colT, float* __restrict__ x, int H, int W, int kh,
+                                                       int kw, int ph, int pw, int OH, int OW) {
+    const int P = OH * OW, HW = H * W;
+    const size_t nc = blockIdx.y;
+    const float* base = colT + nc * (size_t)(kh * kw) * P;            // rows (c, ky, kx) of image n
+    float* out = x + nc * HW;
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < HW; p += gridDim.x * blockDim.x) {
+        const int h = p / W, w = p - h * W;
+        float acc = 0.f;
+        for (int ky = 0; ky < kh; ++ky) {
+            const int t = h + ph - ky;
+            if (t < 0 || (S > 1 && (t % S))) continue;
+            const int oh = t / S;
+            if (oh >= OH) continue;
+            const float* row = base + (size_t)(ky * kw) * P + oh * OW;
+            for (int kx = 0; kx < kw; ++kx) {
+                const int u = w + pw - kx;
+                if (u < 0 || (S > 1 && (u % S))) continue;
+                const int ow = u / S;
+                if (ow >= OW) continue;
+                acc += row[(size_t)kx * P + ow];
+            }
+        }
+        out[p] = acc;
+    }
+}
+HETU_API int hetu_col2im_t(const float* colT, float* x, int N, int C, int H, int W, int kh, int kw, int ph, int pw,
+                           int sh, int sw, int OH, int OW, cudaStream_t s) {
+    if ((size_t)N * C * H * W == 0) return 0;
+    if (sh != sw || sh < 1 || sh > 2 || (long long)N * C > 2147483647LL / 4) {
+        hetu_set_error("col2im_t: stride (%d, %d) not supported", sh, sw);
+        return -1;
+    }
+    const int HW = H * W;
+    dim3 grid((HW + 255) / 256 > 64 ? 64 : (HW + 255) / 256, N * C);
+    if (grid.y > 65535) { hetu_set_error("col2im_t: %d planes > 65535", N * C); return -1; }
+    if (sh == 1) col2im_t_kernel<1><<<grid, 256, 0, s>>>(colT, x, H, W, kh, kw, ph, pw, OH, OW);
+    else col2im_t_kernel<2><<<grid, 256, 0, s>>>(colT, x, H, W, kh, kw, ph, pw, OH, OW);
+    HETU_CHECK_LAUNCH("hetu_col2im_t");
+    return 0;
+}
+
 // ------------------------------------------------------------------- pooling
 __global__ void __launch_bounds__(256) pool2d_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int NC, int H,
                                                          int W, int kh, int kw, int pad, int stride, int OH, int OW, int is_max) {

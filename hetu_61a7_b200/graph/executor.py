@@ -787,6 +787,8 @@ class SubExecutor(object):
         if self._uses_step_counter and self.device.type == 'cuda' and L.cuda_lib() is not None:
             from ..ops.nn import step_counter
             L.call('increment_i64', L.p(step_counter(self.device)), L.stream_ptr(self.device))
+        from ..ops.nn import reset_conv_cache
+        reset_conv_cache()                               # per-pass caches of the convolution ops (im2col buffers, NHWC copies)
         plan = getattr(self, '_node_plan', None)
         if plan is None or len(plan) != len(self.topo_order) or self._node_plan_of is not self.topo_order:
             self._node_plan_of = self.topo_order
@@ -821,6 +823,7 @@ class SubExecutor(object):
                     if (inp is not None and self._last_use.get(inp) == idx and inp not in self._eval_set
                             and not isinstance(inp, PlaceholderOp) and inp not in self._side_refs):
                         vals[inp] = None
+        reset_conv_cache()
 
     def _pre_step(self):
         opts = getattr(self, '_opt_nodes', None)

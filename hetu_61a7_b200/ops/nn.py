@@ -14,6 +14,8 @@ the mask is recomputed - never stored - in backward and is CUDA-graph safe.
 """
 from __future__ import annotations
 
+import os
+
 import math
 
 import numpy as np
@@ -67,6 +69,44 @@ def col2im(col: torch.Tensor, n, c, h, w, kh, kw, ph, pw, sh, sw) -> torch.Tenso
     return F.fold(col, (h, w), (kh, kw), padding=(ph, pw), stride=(sh, sw))
 
 
+# ---- per-step caches: the backward pass of a convolution needs im2col(x) and the NHWC copy of dY again (weight and data
+# gradient); recomputing them was a quarter of the ResNet-18 step.  Entries are valid for the tensor object they were
+# built from; the executor clears them at the start and end of every pass over the graph (reset_conv_cache).
+_CONV_CACHE = {'col': {}, 'dy': None, 'bytes': 0}
+
+
+def reset_conv_cache():
+    _CONV_CACHE['col'].clear()
+    _CONV_CACHE['dy'] = None
+    _CONV_CACHE['bytes'] = 0
+
+
+def _cached_im2col(x, kh, kw, ph, pw, sh, sw, store):
+    key = (id(x), kh, kw, ph, pw, sh, sw)
+    hit = _CONV_CACHE['col'].get(key)
+    if hit is not None and hit[0] is x and hit[1] == x._version:
+        if not store:                                    # the weight gradient is the last user: let the buffer go
+            del _CONV_CACHE['col'][key]
+            _CONV_CACHE['bytes'] -= hit[2].numel() * hit[2].element_size()
+        return hit[2]
+    col = im2col(x, kh, kw, ph, pw, sh, sw)
+    limit = float(os.environ.get('HETU_CONV_COL_CACHE_MB', '8192')) * (1 << 20)
+    nbytes = col.numel() * col.element_size()
+    if store and _CONV_CACHE['bytes'] + nbytes <= limit:
+        _CONV_CACHE['col'][key] = (x, x._version, col)
+        _CONV_CACHE['bytes'] += nbytes
+    return col
+
+
+def _nhwc_rows(dy, oc):
+    hit = _CONV_CACHE['dy']
+    if hit is not None and hit[0] is dy and hit[1] == dy._version:
+        return hit[2]
+    dy2 = materialize(dy.permute(0, 2, 3, 1)).reshape(-1, oc)       # [N*OH*OW, OC]
+    _CONV_CACHE['dy'] = (dy, dy._version, dy2)
+    return dy2
+
+
 def conv2d_forward(x, w, bias, padding, stride, act=0):
     ph, pw = _pair(padding)
     sh, sw = _pair(stride)
@@ -75,7 +115,7 @@ def conv2d_forward(x, w, bias, padding, stride, act=0):
     n, c, h, wd = x.shape
     oc, _, kh, kw = w.shape
     oh, ow = _conv_out(h, kh, ph, sh), _conv_out(wd, kw, pw, sw)
-    col = im2col(x, kh, kw, ph, pw, sh, sw)                       # [N*OH*OW, C*kh*kw]
+    col = _cached_im2col(x, kh, kw, ph, pw, sh, sw, store=kh * kw > 1)   # [N*OH*OW, C*kh*kw]; kept for the weight gradient
     y = gemm(col, w.reshape(oc, -1), False, True, bias=bias, act=act)   # [N*OH*OW, OC]
     return materialize(y.reshape(n, oh, ow, oc).permute(0, 3, 1, 2))
 
@@ -87,7 +127,18 @@ def conv2d_grad_data(dy, w, x_shape, padding, stride):
         return torch.nn.grad.conv2d_input(x_shape, w, dy, stride=(sh, sw), padding=(ph, pw))
     n, c, h, wd = x_shape
     oc, _, kh, kw = w.shape
-    dy2 = materialize(dy.permute(0, 2, 3, 1)).reshape(-1, oc)       # [N*OH*OW, OC]
+    oh, ow = dy.shape[2], dy.shape[3]
+    if _k(dy, w) and oh * ow >= 256 and (oh * ow) % 4 == 0 and oc % 4 == 0 and kh * kw > 1 and sh == sw and sh <= 2 \
+            and n * c <= 65535 and os.environ.get('HETU_CONV_DGRAD_BATCHED', '1') == '1':
+        # dY stays NCHW: per image colT_n [C*kh*kw, OH*OW] = W^T [C*kh*kw, OC] @ dY_n [OC, OH*OW] (one batched GEMM), and the
+        # gather that folds it back reads rows along ow - no NHWC copy of dY, coalesced col2im
+        w3 = w.reshape(1, oc, c * kh * kw).expand(n, oc, c * kh * kw).contiguous()
+        colT = gemm(w3, dy.contiguous().view(n, oc, oh * ow), True, False)          # [N, C*kh*kw, OH*OW]
+        x = torch.empty((n, c, h, wd), dtype=dy.dtype, device=dy.device)
+        L.call('col2im_t', L.p(colT), L.p(x), L.c_int(n), L.c_int(c), L.c_int(h), L.c_int(wd), L.c_int(kh), L.c_int(kw),
+               L.c_int(ph), L.c_int(pw), L.c_int(sh), L.c_int(sw), L.c_int(oh), L.c_int(ow), L.stream_ptr(dy.device))
+        return x
+    dy2 = _nhwc_rows(dy, oc)                                        # [N*OH*OW, OC]
     col = gemm(dy2, w.reshape(oc, -1), False, False)               # [N*OH*OW, C*kh*kw]
     return col2im(col, n, c, h, wd, kh, kw, ph, pw, sh, sw)
 
@@ -98,8 +149,8 @@ def conv2d_grad_filter(x, dy, w_shape, padding, stride):
     if x.device.type != 'cuda':
         return torch.nn.grad.conv2d_weight(x, w_shape, dy, stride=(sh, sw), padding=(ph, pw))
     oc, c, kh, kw = w_shape
-    col = im2col(x, kh, kw, ph, pw, sh, sw)                         # [N*OH*OW, C*kh*kw]
-    dy2 = materialize(dy.permute(0, 2, 3, 1)).reshape(-1, oc)       # [N*OH*OW, OC]
+    col = _cached_im2col(x, kh, kw, ph, pw, sh, sw, store=False)    # [N*OH*OW, C*kh*kw]: the forward pass's, when it is still there
+    dy2 = _nhwc_rows(dy, oc)                                        # [N*OH*OW, OC]
     return gemm(dy2, col, True, False).reshape(w_shape)             # [OC, C*kh*kw]
 
 

@@ -46,6 +46,14 @@ def strided_copy(src: torch.Tensor, dst: torch.Tensor) -> None:
     if not merged:
         merged = [(1, 1, 1)]
     nd = len(merged)
+    # batched 2-D transpose (NCHW <-> NHWC around the convolution GEMMs): dst [B, X, Y] contiguous, src laid out [B, Y, X]
+    m3 = merged if nd == 3 else ([(1, 0, 0)] + merged if nd == 2 else None)
+    if m3 is not None:
+        (bn, ba, bb), (x, xa, xb), (y, ya, yb) = m3
+        if xb == y and yb == 1 and xa == 1 and ya == x and (bn == 1 or (ba == x * y and bb == x * y)) and bn <= 65535 \
+                and x >= 8 and y >= 8:
+            L.call('transpose_batched', L.p(src), L.p(dst), L.c_int(bn), L.c_int(y), L.c_int(x), L.stream_ptr(src.device))
+            return
     shp = _I64x8(*([m[0] for m in merged] + [1] * (8 - nd)))
     ss = _I64x8(*([m[1] for m in merged] + [0] * (8 - nd)))
     ds = _I64x8(*([m[2] for m in merged] + [0] * (8 - nd)))

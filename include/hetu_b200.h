@@ -61,6 +61,8 @@ int hetu_binary(int op, const float* x, const float* y, float* o, size_t n, floa
 int hetu_binary_bcast(int op, const float* x, const float* y, float* o, size_t n, size_t inner, int mode, cudaStream_t s);
 /* hi = nearest tf32 value of x, lo = x - hi (operands of the 3xTF32 matmul mode) */
 int hetu_split_tf32(const float* x, float* hi, float* lo, size_t n, cudaStream_t s);
+/* src [B, R, C] -> dst [B, C, R] (shared-memory tiles); the NCHW <-> NHWC changes around the convolution GEMMs */
+int hetu_transpose_batched(const float* src, float* dst, int B, int R, int C, cudaStream_t s);
 int hetu_where(const float* c, const float* a, const float* b, float* o, size_t n, cudaStream_t s);
 /* generic strided copy (transpose/slice/concat/pad/broadcast): reference
  * src/ops/{Transpose,Slice,Concat,Concatenate,Pad,Broadcast,BroadcastShape}.cu */
@@ -112,6 +114,9 @@ int hetu_im2col(const float* x, float* col, int N, int C, int H, int W, int kh, 
                 int sw, int OH, int OW, cudaStream_t s);
 int hetu_col2im(const float* col, float* x, int N, int C, int H, int W, int kh, int kw, int ph, int pw, int sh,
                 int sw, int OH, int OW, cudaStream_t s);
+/* same from colT [N, C*kh*kw, OH*OW] (batched GEMM W^T dY_n on NCHW dY): coalesced reads */
+int hetu_col2im_t(const float* colT, float* x, int N, int C, int H, int W, int kh, int kw, int ph, int pw,
+                  int sh, int sw, int OH, int OW, cudaStream_t s);
 int hetu_pool2d_fwd(const float* x, float* y, int NC, int H, int W, int kh, int kw, int pad, int stride, int OH,
                     int OW, int is_max, cudaStream_t s);
 int hetu_pool2d_bwd(const float* x, const float* y, const float* dy, float* dx, int NC, int H, int W, int kh, int kw,

@@ -59,6 +59,12 @@ def test_strided_copy_and_concat(L):
     torch.testing.assert_close(S.materialize(x.permute(0, 2, 1, 3)), x.permute(0, 2, 1, 3).contiguous())
     torch.testing.assert_close(S.materialize(x.permute(3, 1, 0, 2)), x.permute(3, 1, 0, 2).contiguous())
     torch.testing.assert_close(S.materialize(x[:, 1:4, ::2]), x[:, 1:4, ::2].contiguous())
+    for shp in ((5, 37, 9, 11), (3, 64, 32, 32), (1, 130, 7, 5)):      # NCHW <-> NHWC: batched tile transpose kernel
+        t = rnd(*shp, seed=7)
+        torch.testing.assert_close(S.materialize(t.permute(0, 2, 3, 1)), t.permute(0, 2, 3, 1).contiguous())
+        torch.testing.assert_close(S.materialize(t.permute(0, 3, 1, 2)), t.permute(0, 3, 1, 2).contiguous())
+    m2 = rnd(300, 70, seed=8)
+    torch.testing.assert_close(S.materialize(m2.t()), m2.t().contiguous())
     g = rnd(16, 40)                                       # gradient of a row reduction: innermost dim broadcast
     torch.testing.assert_close(S.materialize(g.unsqueeze(-1).expand(16, 40, 64)), g.unsqueeze(-1).expand(16, 40, 64).contiguous())
     torch.testing.assert_close(S.materialize(g.unsqueeze(-1).expand(16, 40, 6)), g.unsqueeze(-1).expand(16, 40, 6).contiguous())
