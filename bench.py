@@ -242,16 +242,19 @@ def bench_wdl(args, ht, torch, np, comm, device):
     h2d = sum(a.nbytes for a in pool[0])
     last = {}
 
+    from collections import deque
+    inflight = deque()
+    depth = max(1, int(os.environ.get('HETU_BENCH_READBACK_LAG', '1')))
+
     def step_e2e(i):
-        out = ex.run('train')                   # batch i: H2D from the pinned dataset, prefetched one step ahead
-        fut = out[0].asnumpy_async()            # loss i: D2H queued behind step i, read while step i+1 is queued
-        if last.get('pending') is not None:
-            last['loss'] = last['pending'].get()
-        last['pending'] = fut
+        out = ex.run('train')                   # batch i: its H2D copy runs beside the replay of step i-1
+        inflight.append(out[0].asnumpy_async())  # loss i: D2H queued behind step i ...
+        if len(inflight) > depth:               # ... and read one step later (a lag of 2 measured the same), so the host never waits on the newest step
+            last['loss'] = inflight.popleft().get()
 
     def finish_e2e():
-        if last.get('pending') is not None:
-            last['loss'] = last.pop('pending').get()
+        while inflight:
+            last['loss'] = inflight.popleft().get()
 
     for i in range(max(args.warmup, 3)):
         step_e2e(i)
