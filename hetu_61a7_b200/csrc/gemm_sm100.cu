@@ -907,6 +907,7 @@ static void launch_small(const float* A, const float* B, float* C, const float* 
 // MoE gate / logistic-regression shapes: [tokens, d] @ [d, n_experts] and its weight gradient.  These are
 // bandwidth-bound reads of the big operand; a tile kernel wastes 8-32x of its columns on them.
 constexpr int kSkinnyN = 8;
+constexpr size_t kSkinnySmemMax = 96 * 1024;     // B table of the row kernel in shared memory (dynamic, opt-in above 48 KB)
 
 // A row-major [M, K] (not transposed): one warp per output row, lanes stride K with 128-bit loads.
 template <int TB>
@@ -916,7 +917,7 @@ __global__ void __launch_bounds__(256) gemm_skinny_rows_kernel(const float* __re
     extern __shared__ float4 skinny_smem[];
     float* Bs = reinterpret_cast<float*>(skinny_smem);      // [N][K] when it fits (bs_ok), else unused
     const int lane = threadIdx.x & 31;
-    const bool bs_ok = (size_t)N * K * 4 <= 48 * 1024 && (K & 3) == 0;
+    const bool bs_ok = (size_t)N * K * 4 <= kSkinnySmemMax && (K & 3) == 0;     // must match launch_skinny
     if (bs_ok) {
         for (int i = threadIdx.x; i < N * K; i += 256) {
             const int n = i / K, k = i - n * K;
@@ -1097,11 +1098,60 @@ __global__ void __launch_bounds__(256) gemm_tinyk_kernel(const float* __restrict
     }
 }
 
+// K <= 8 (measured: from K = 9 on the tiled kernels win), A not transposed, N % 4 == 0: every thread owns four consecutive columns and keeps their K x 4 block of B in
+// registers while it walks the 64 rows of its row block (32-bit index arithmetic, one 128-bit store per row).  The
+// per-element kernel above spends a 64-bit div / mod per output and ran at 0.4 TB/s on the MoE gate's input gradient
+// [tokens, E] x [E, d].
+constexpr int kTinyKRows = 64;
+template <int TB>
+__global__ void __launch_bounds__(256) gemm_tinyk_rows_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                              float* __restrict__ C, const float* __restrict__ bias, int M, int N,
+                                                              int K, float alpha, float beta, int act) {
+    const int n = (blockIdx.x * 256 + threadIdx.x) * 4;
+    if (n >= N) return;
+    float4 b[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        b[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k < K) {
+            if (TB) b[k] = make_float4(__ldg(B + (size_t)n * K + k), __ldg(B + (size_t)(n + 1) * K + k), __ldg(B + (size_t)(n + 2) * K + k),
+                                       __ldg(B + (size_t)(n + 3) * K + k));
+            else b[k] = __ldg(reinterpret_cast<const float4*>(B + (size_t)k * N + n));
+        }
+    }
+    float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (bias != nullptr) bv = __ldg(reinterpret_cast<const float4*>(bias + n));
+    const int m_end = min(M, (int)(blockIdx.y + 1) * kTinyKRows);
+    for (int m = blockIdx.y * kTinyKRows; m < m_end; ++m) {
+        const float* a = A + (size_t)m * K;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            if (k < K) {
+                const float av = __ldg(a + k);                        // same address for the whole block: broadcast
+                acc.x += av * b[k].x; acc.y += av * b[k].y; acc.z += av * b[k].z; acc.w += av * b[k].w;
+            }
+        }
+        float4 o = make_float4(alpha * acc.x + bv.x, alpha * acc.y + bv.y, alpha * acc.z + bv.z, alpha * acc.w + bv.w);
+        float4* dst = reinterpret_cast<float4*>(C + (size_t)m * N + n);
+        if (beta != 0.f) { const float4 c = *dst; o.x += beta * c.x; o.y += beta * c.y; o.z += beta * c.z; o.w += beta * c.w; }
+        *dst = make_float4(apply_act(o.x, act), apply_act(o.y, act), apply_act(o.z, act), apply_act(o.w, act));
+    }
+}
+
 static void launch_skinny(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, int tA, int tB,
                           float alpha, float beta, int act, cudaStream_t s) {
     if (!tA) {
         dim3 grid(std::min((M + 7) / 8, kNumSMs * 6));
-        const size_t sm = ((size_t)N * K * 4 <= 48 * 1024 && (K & 3) == 0) ? (size_t)N * K * 4 : 0;
+        // B in shared memory up to 96 KB (opt-in above 48 KB): with 8 experts and d = 2048 the table is 64 KB, and without it
+        // every lane fetched B from global memory per k (1 ms for the MoE gate at 4 GPUs - the N = 4 anomaly of round 1)
+        const size_t sm = ((size_t)N * K * 4 <= kSkinnySmemMax && (K & 3) == 0) ? (size_t)N * K * 4 : 0;
+        static bool attr_done = false;
+        if (!attr_done) {
+            cudaFuncSetAttribute(gemm_skinny_rows_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSkinnySmemMax);
+            cudaFuncSetAttribute(gemm_skinny_rows_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSkinnySmemMax);
+            attr_done = true;
+        }
         if (tB) gemm_skinny_rows_kernel<1><<<grid, 256, sm, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
         else gemm_skinny_rows_kernel<0><<<grid, 256, sm, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
         return;
@@ -1153,6 +1203,14 @@ HETU_API int hetu_gemm(const float* A, const float* B, float* C, const float* bi
     if (act == ACT_RELU_MASK && !(mode != 1 && tma_ok && big && K > 8 && N > kSkinnyN && beta == 0.f)) {
         hetu_set_error("hetu_gemm: the relu-mask epilogue exists in the tensor-core kernels only (M %d N %d K %d)", M, N, K);
         return -1;
+    }
+    if (K <= 8 && batch == 1 && !transA && (N & 3) == 0 && N >= 256 && M <= 65535 * kTinyKRows && act != ACT_RELU_MASK &&
+        ((reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(C) | reinterpret_cast<uintptr_t>(bias)) & 15) == 0) {
+        dim3 grid((N / 4 + 255) / 256, (M + kTinyKRows - 1) / kTinyKRows);
+        if (transB) gemm_tinyk_rows_kernel<1><<<grid, 256, 0, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
+        else gemm_tinyk_rows_kernel<0><<<grid, 256, 0, s>>>(A, B, C, bias, M, N, K, alpha, beta, act);
+        HETU_CHECK_LAUNCH("hetu_gemm(tiny-k rows)");
+        return 0;
     }
     if (K <= 8 && batch == 1) {
         gemm_tinyk_kernel<<<ew_grid((size_t)M * N, 256), 256, 0, s>>>(A, B, C, bias, M, N, K, transA, transB, alpha, beta, act);

@@ -566,3 +566,20 @@ def test_gemm_stream_k_transformer_weight_gradients(m, n, k, tA, tB):
     ref = A @ Bm + bias.double()
     out = gemm(a, b, tA, tB, bias=bias)
     assert (out.double() - ref).abs().max().item() <= 2e-3 * ref.abs().max().item()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('m,n,k,tB', [(5000, 2048, 5, True), (70000, 256, 8, False), (3000, 1024, 16, True), (16384, 2048, 8, True)])
+def test_gemm_tiny_k_rows_and_wide_skinny(m, n, k, tB):
+    """[tokens, E] x [E, d] (input gradient of the MoE gate: K = E <= 16) and [tokens, d] x [d, E] with an E x d table
+    above 48 KB of shared memory (8 experts, d = 2048)."""
+    from hetu_61a7_b200.ops.linalg import gemm
+    a, bias = rnd(m, k), rnd(n, seed=2)
+    b = rnd(n, k, seed=1) if tB else rnd(k, n, seed=1)
+    ref = a.double() @ (b.double().t() if tB else b.double()) + bias.double()
+    out = gemm(a, b, False, tB, bias=bias)
+    assert (out.double() - ref).abs().max().item() <= 1e-5 * ref.abs().max().item() + 1e-5
+    x, w = rnd(4096, 2048, seed=3), rnd(2048, 8, seed=4, scale=0.05)       # skinny rows kernel, 64 KB table
+    ref2 = x.double() @ w.double()
+    out2 = gemm(x, w)
+    assert (out2.double() - ref2).abs().max().item() <= 1e-4 * ref2.abs().max().item() + 1e-5
