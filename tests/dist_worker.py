@@ -208,7 +208,8 @@ if gpu:
         check('sharded %s at the owner' % opt_name, tab.export_dense().double(), P, rtol=2e-3, atol=2e-4)
 
 # ------------------------------------------------------------------ MoE fused vs NCCL
-if gpu:
+# (on the gloo world the one-op MoE layer runs its stage-by-stage path with all-to-alls, against the reference op chain)
+if True:
     from hetu_61a7_b200.models.moe import moe_model
     for pre in (False, True):       # pre: a trainable projection in front, so the layer must also return d(input)
         losses = {}
