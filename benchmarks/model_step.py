@@ -35,3 +35,4 @@ for i in range(steps):
     l = float(ex.run(feed_dict=fd)[0].asnumpy())
     torch.cuda.synchronize()
     print('step %d loss %.4f %.2f ms  (%.0f units/s)' % (i, l, (time.time() - t0) * 1e3, units / (time.time() - t0)), flush=True)
+print('peak device memory %.2f GB (allocated), %.2f GB (reserved)' % (torch.cuda.max_memory_allocated() / 2**30, torch.cuda.max_memory_reserved() / 2**30))

@@ -1154,7 +1154,12 @@ class SubExecutor(object):
                        L.stream_ptr(dev))
             for node, st in self._static_in.items():
                 vals[node] = st
-            self._compute_all(vals, release=False)
+            # memory plan of the captured step (reference memory_pool.py:80-126 reuses a buffer once its last consumer has
+            # run): with dynamic_memory=True (or HETU_GRAPH_RELEASE=1) a value is dropped at its last use DURING capture, so
+            # the graph's private pool hands its block to later nodes - peak memory of a replay is the liveness peak instead
+            # of the sum of all intermediates.  Eval results, placeholders and values other ops keep a handle on stay.
+            release = bool(getattr(self.config, 'dynamic_memory', False)) or os.environ.get('HETU_GRAPH_RELEASE', '0') == '1'
+            self._compute_all(vals, release=release)
             if pk is not None:
                 # the first small fp32 result (the loss) also goes into a device ring indexed by the same slot, so its
                 # read-back never races with the next replay

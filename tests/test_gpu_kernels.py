@@ -583,3 +583,28 @@ def test_gemm_tiny_k_rows_and_wide_skinny(m, n, k, tB):
     ref2 = x.double() @ w.double()
     out2 = gemm(x, w)
     assert (out2.double() - ref2).abs().max().item() <= 1e-4 * ref2.abs().max().item() + 1e-5
+
+
+@pytest.mark.gpu
+def test_graph_capture_with_release_matches(L):
+    """Executor(dynamic_memory=True): values dropped at their last use during capture (the graph pool reuses their blocks)
+    - same losses as the default plan, lower peak memory."""
+    import hetu as ht
+    from hetu_61a7_b200.models import cnn
+    rs = np.random.RandomState(3)
+    xs = rs.randn(64, 3072).astype(np.float32)
+    ys = np.eye(10, dtype=np.float32)[rs.randint(0, 10, 64)]
+    out = {}
+    for dyn in (False, True):
+        np.random.seed(0)
+        x, y_ = ht.Variable('x'), ht.Variable('y_')
+        loss, _ = cnn.resnet18(x, y_)
+        train = ht.optim.SGDOptimizer(0.01).minimize(loss)
+        ex = ht.Executor([loss, train], ctx=ht.gpu(0), seed=4, dynamic_memory=dyn)
+        torch.cuda.synchronize()
+        torch.cuda.reset_peak_memory_stats()
+        out[dyn] = ([float(ex.run(feed_dict={x: xs, y_: ys})[0].asnumpy()) for _ in range(6)], torch.cuda.max_memory_allocated())
+        assert ex.subexecutor['default']._graph is not None
+        del ex
+    np.testing.assert_allclose(out[True][0], out[False][0], rtol=2e-3, atol=1e-4)
+    assert out[True][1] < out[False][1]
