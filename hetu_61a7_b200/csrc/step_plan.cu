@@ -151,6 +151,13 @@ HETU_API int hetu_step_plan_wait(void* plan, int slot) {
     return 0;
 }
 
+// 1: the read-back in host slot `slot` has landed, 0: still in flight
+HETU_API int hetu_step_plan_ready(void* plan, int slot) {
+    StepPlan* p = (StepPlan*)plan;
+    if (slot < 0 || slot >= p->rb_slots) return 0;
+    return cudaEventQuery(p->rb_ev[slot]) == cudaSuccess ? 1 : 0;
+}
+
 // device slot the next replay reads (the general path continues from here after the plan is dropped)
 HETU_API int hetu_step_plan_dturn(void* plan) { return (int)(((StepPlan*)plan)->dturn % (unsigned)((StepPlan*)plan)->dslots); }
 

@@ -642,7 +642,11 @@ class _PlanFuture(object):
         self._fast, self._step, self._slot = fast, step, (step - 1) % 8
 
     def ready(self):
-        return True
+        fast = self._fast
+        if fast.get('dead'):
+            return True
+        lib = L.require_cuda_lib()
+        return bool(lib.hetu_step_plan_ready(ctypes_void(fast['handle']), self._slot))
 
     def get(self):
         fast = self._fast

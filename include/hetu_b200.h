@@ -363,6 +363,7 @@ void* hetu_step_plan_create(void* graph_exec, cudaStream_t stream, int n, const 
 int hetu_step_plan_set_readback(void* plan, const void* dev_ring, long long nbytes, void* const* host_slots, int nslots);
 int hetu_step_plan_run(void* plan, void* const* src);
 int hetu_step_plan_wait(void* plan, int slot);
+int hetu_step_plan_ready(void* plan, int slot);
 int hetu_step_plan_dturn(void* plan);
 void hetu_step_plan_destroy(void* plan);
 

@@ -392,6 +392,7 @@ def test_dataloader_prefetch_matches_feed_dict(L):
         fut = ex1.run('train')[0].asnumpy_async()
         if pending is not None:
             c.append(float(pending.get()))
+            assert pending.ready()
         pending = fut
         k = i % 6
         b.append(float(ex2.run('train', feed_dict={x: data[k * 32:(k + 1) * 32], y_: labels[k * 32:(k + 1) * 32]})[0].asnumpy()))
