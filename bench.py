@@ -192,21 +192,35 @@ def bench_wdl(args, ht, torch, np, comm, device):
             kw['use_nccl_collectives'] = args.collectives == 'nccl'
     ex = ht.Executor({'train': [loss, pred, train_op]}, **kw)
     # --- device-timed: inputs resident in HBM, graph replays back to back ---------------
-    dev_pool = [(ht.array(d, ctx), ht.NDArray(torch.from_numpy(s).to(device)), ht.array(l, ctx))
-                for d, s, l in pool[:8]]
-    d_buf = ht.NDArray(dev_pool[0][0].tensor.clone())
-    s_buf = ht.NDArray(dev_pool[0][1].tensor.clone())
-    l_buf = ht.NDArray(dev_pool[0][2].tensor.clone())
+    # eight batches packed [dense | ids | labels] in HBM; the fed arrays are views of ONE buffer, so a step's inputs change
+    # with one device-to-device copy of 33 KB (three separate copies cost ~4 us of a 43 us step)
+    def _pack(d, s_, l):
+        parts = [np.ascontiguousarray(d, dtype=np.float32).view(np.uint8).reshape(-1),
+                 np.ascontiguousarray(s_, dtype=np.int64).view(np.uint8).reshape(-1),
+                 np.ascontiguousarray(l, dtype=np.float32).view(np.uint8).reshape(-1)]
+        offs, total = [], 0
+        for p_ in parts:
+            offs.append(total)
+            total += (p_.size + 255) // 256 * 256
+        flat = np.zeros(total, dtype=np.uint8)
+        for o, p_ in zip(offs, parts):
+            flat[o:o + p_.size] = p_
+        return flat, offs, [p_.size for p_ in parts]
+
+    packed = [_pack(*pool[i]) for i in range(8)]
+    dev_pool = [torch.from_numpy(f).to(device) for f, _, _ in packed]
+    offs, sizes = packed[0][1], packed[0][2]
+    in_buf = dev_pool[0].clone()
+    d_buf = ht.NDArray(in_buf[offs[0]:offs[0] + sizes[0]].view(torch.float32).view(tuple(pool[0][0].shape)))
+    s_buf = ht.NDArray(in_buf[offs[1]:offs[1] + sizes[1]].view(torch.int64).view(tuple(pool[0][1].shape)))
+    l_buf = ht.NDArray(in_buf[offs[2]:offs[2] + sizes[2]].view(torch.float32).view(tuple(pool[0][2].shape)))
 
     launches0 = _lib.launch_count
     total_steps = [0]
 
     def step_dev(i):
         total_steps[0] += 1
-        d, s, l = dev_pool[i % len(dev_pool)]
-        d_buf.tensor.copy_(d.tensor, non_blocking=True)
-        s_buf.tensor.copy_(s.tensor, non_blocking=True)
-        l_buf.tensor.copy_(l.tensor, non_blocking=True)
+        in_buf.copy_(dev_pool[i % len(dev_pool)], non_blocking=True)
         ex.run('train', feed_dict={dense: d_buf, sparse: s_buf, y_: l_buf})
 
     for i in range(max(args.warmup, 3)):
