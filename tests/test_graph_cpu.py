@@ -523,3 +523,29 @@ def test_checkpoint_resume_is_exact_with_run_state(tmp_path):
     ex2.load(str(tmp_path), 'ckpt.pkl')
     rest = [float(ex2.run('train')[0].asnumpy()) for _ in range(6)]
     np.testing.assert_allclose(first + rest, ref, rtol=1e-6)
+
+
+def test_fused_gate_partial_uses_match_composed_gate(monkeypatch):
+    """The fused gate's backward takes the gradients of its pieces directly: a loss that leaves the balance loss out,
+    uses one gate value twice, or uses the balance loss alone must still give the composed gate's gradient."""
+    from hetu_61a7_b200.layers import moe as M
+    T, E, k = 96, 8, 2
+    lv = np.random.RandomState(0).randn(T, E).astype(np.float32)
+
+    def grad(case, flag):
+        monkeypatch.setenv('HETU_MOE_FUSED_GATE', flag)
+        logits = ht.Variable('lg_%s_%s' % (case, flag), value=lv.copy())
+        l_aux, idx, loc, gates, cap = M.topkgating(logits, k, 1.0, T, E, 16)
+        if case == 'no_aux':
+            obj = ht.reduce_sum_op(gates[0], axes=0) + ht.reduce_sum_op(ht.mul_byconst_op(gates[1], 2.0), axes=0)
+        elif case == 'gate_twice':
+            obj = ht.reduce_sum_op(ht.mul_op(gates[0], gates[0]), axes=0) + l_aux
+        else:
+            obj = l_aux
+        g = ht.gradients(obj, [logits])[0]
+        return ht.Executor([obj, g], ctx=ht.cpu(0)).run(convert_to_numpy_ret_vals=True)
+
+    for case in ('no_aux', 'gate_twice', 'aux_only'):
+        a, b = grad(case, '1'), grad(case, '0')
+        np.testing.assert_allclose(np.ravel(a[0]), np.ravel(b[0]), rtol=1e-5, atol=1e-6, err_msg=case)
+        np.testing.assert_allclose(a[1], b[1], rtol=1e-4, atol=1e-6, err_msg=case)
