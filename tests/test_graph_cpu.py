@@ -296,7 +296,7 @@ def test_moe_ffn_op_matches_op_chain(monkeypatch):
     from hetu_61a7_b200.models.moe import moe_model
     from hetu_61a7_b200.ops.moe_ffn import FusedMoEFFNOp
     from hetu_61a7_b200.graph.autodiff import find_topo_sort
-    for gate, pre in (('top', False), ('top', True), ('hash', False), ('sam', True)):
+    for gate, pre in (('top', False), ('top', True), ('hash', False), ('hash', True), ('ktop1', True), ('sam', True)):
         losses, snapshot = {}, None
         for overlap in ('1', '0'):
             monkeypatch.setenv('HETU_MOE_OVERLAP', overlap)
